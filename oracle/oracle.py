@@ -1,0 +1,117 @@
+"""ctypes loader for the CPU oracle (oracle/liboracle.so).  TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this.
+"""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+c_dp = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+c_ip = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+
+NORM_ABS_L2, NORM_ABS_LINF, NORM_REL_L2 = 0, 1, 2
+OK, MAX_ITERATION_EXCEEDED = 0, 3
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "liboracle.so")
+    srcs = [os.path.join(_HERE, f) for f in ("cg_ref.c", "mg_ref.c") if os.path.exists(os.path.join(_HERE, f))]
+    if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        subprocess.check_call(["make", "-s", "-C", _HERE, "-B", "liboracle.so"])
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        L = C.CDLL(build())
+        L.ref_spmv.argtypes = [C.c_int, c_dp, c_ip, c_ip, c_dp, c_dp]
+        L.ref_dot.argtypes = [C.c_int, c_dp, c_dp]; L.ref_dot.restype = C.c_double
+        L.ref_max_absolute.argtypes = [C.c_int, c_dp]; L.ref_max_absolute.restype = C.c_double
+        L.ref_set_added.argtypes = [C.c_int, c_dp, c_dp, c_dp, C.c_double]
+        L.ref_cg_solve.argtypes = [C.c_int, c_dp, c_ip, c_ip, c_dp, c_dp, c_dp, c_dp, c_dp,
+                                   C.c_double, C.c_int, C.c_int, C.c_int, C.c_int,
+                                   C.POINTER(C.c_int), C.POINTER(C.c_double)]
+        L.ref_cg_solve.restype = C.c_int
+        L.ref_partition_offsets.argtypes = [C.c_int, C.c_int, c_ip]
+        L.ref_initialize_block.argtypes = [c_ip, c_ip, C.c_int, C.c_int, c_ip] + [C.POINTER(C.c_int)] * 4
+        L.ref_halo_counts.argtypes = [C.c_int] * 6 + [C.POINTER(C.c_int)] * 2
+        L.ref_cg_solve_parallel.argtypes = [C.c_int, C.c_int, c_dp, c_ip, c_ip, c_dp, c_dp,
+                                            C.c_double, C.c_int, C.c_int,
+                                            C.POINTER(C.c_int), C.POINTER(C.c_double)]
+        L.ref_cg_solve_parallel.restype = C.c_int
+        L.ref_gen_tridiag121.argtypes = [C.c_int, c_dp, c_ip, c_ip, c_dp]; L.ref_gen_tridiag121.restype = C.c_int
+        L.ref_gen_banded_sin.argtypes = [C.c_int, C.c_int, c_dp, c_ip, c_ip, c_dp, c_dp]
+        L.ref_gen_banded_sin.restype = C.c_int
+        _LIB = L
+    return _LIB
+
+
+def spmv(val, rowptr, col, x):
+    n = len(rowptr) - 1
+    y = np.empty(n)
+    lib().ref_spmv(n, val, rowptr, col, x, y)
+    return y
+
+
+def dot(a, b):
+    return lib().ref_dot(len(a), a, b)
+
+
+def cg_solve(val, rowptr, col, b, x0=None, tol=1e-8, min_iteration=0, max_iteration=None,
+             norm=NORM_ABS_L2, min_strict=False):
+    """ConjugateGradientCpu.Solve restatement. Returns (x, iteration_index, residual, status)."""
+    n = len(rowptr) - 1
+    x = np.zeros(n) if x0 is None else np.array(x0, dtype=np.float64, copy=True)
+    r, p, Ap = np.empty(n), np.empty(n), np.empty(n)
+    it, res = C.c_int(0), C.c_double(0)
+    st = lib().ref_cg_solve(n, val, rowptr, col, x, np.ascontiguousarray(b, dtype=np.float64), r, p, Ap, tol,
+                            min_iteration, n if max_iteration is None else max_iteration,
+                            norm, int(min_strict), C.byref(it), C.byref(res))
+    return x, it.value, res.value, st
+
+
+def cg_solve_parallel(val, rowptr, col, b, devices, x0=None, tol=1e-8, min_iteration=0, max_iteration=None):
+    n = len(rowptr) - 1
+    x = np.zeros(n) if x0 is None else np.array(x0, dtype=np.float64, copy=True)
+    it, res = C.c_int(0), C.c_double(0)
+    st = lib().ref_cg_solve_parallel(n, devices, val, rowptr, col, x, np.ascontiguousarray(b, dtype=np.float64), tol,
+                                     min_iteration, n if max_iteration is None else max_iteration,
+                                     C.byref(it), C.byref(res))
+    return x, it.value, res.value, st
+
+
+def partition_offsets(count, devices):
+    off = np.zeros(devices + 1, dtype=np.int32)
+    lib().ref_partition_offsets(count, devices, off)
+    return off
+
+
+def initialize_block(rowptr, col, offset, count):
+    lro = np.zeros(count + 1, dtype=np.int32)
+    eo, ec, mn, mx = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    lib().ref_initialize_block(rowptr, col, offset, count, lro, C.byref(eo), C.byref(ec), C.byref(mn), C.byref(mx))
+    return lro, eo.value, ec.value, mn.value, mx.value
+
+
+def halo_counts(dev, devices, offset, count, min_j, max_j):
+    lc, nc = C.c_int(), C.c_int()
+    lib().ref_halo_counts(dev, devices, offset, count, min_j, max_j, C.byref(lc), C.byref(nc))
+    return lc.value, nc.value
+
+
+def gen_tridiag121(n):
+    val, col, rp, b = np.zeros(3 * n), np.zeros(3 * n, dtype=np.int32), np.zeros(n + 1, dtype=np.int32), np.zeros(n)
+    nnz = lib().ref_gen_tridiag121(n, val, col, rp, b)
+    return val[:nnz].copy(), rp, col[:nnz].copy(), b
+
+
+def gen_banded_sin(n, max_nonzero=160):
+    val, col = np.zeros(n * max_nonzero), np.zeros(n * max_nonzero, dtype=np.int32)
+    rp, b, x0 = np.zeros(n + 1, dtype=np.int32), np.zeros(n), np.zeros(n)
+    nnz = lib().ref_gen_banded_sin(n, max_nonzero, val, col, rp, b, x0)
+    return val[:nnz].copy(), rp, col[:nnz].copy(), b, x0
