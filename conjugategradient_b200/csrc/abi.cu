@@ -1,0 +1,327 @@
+// abi.cu — the mgcg_* C ABI (include/mgcg.h): context lifetime, setup/solve on device and host pointers,
+// individually exported kernels, the reference partition rule.
+#include "mg.cuh"
+#include <math.h>
+#include <stdarg.h>
+#include <string.h>
+
+namespace mgcg {
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+const char *get_error() { return g_err; }
+
+int ctx_ensure_work(mgcg_ctx *c, int n)
+{
+    if (c->work_n >= n && c->r) return MGCG_OK;
+    if (c->r) cudaFree(c->r);
+    if (c->p) cudaFree(c->p);
+    if (c->Ap) cudaFree(c->Ap);
+    c->r = c->p = c->Ap = nullptr;
+    size_t bytes = sizeof(double) * (size_t)(n > 0 ? n : 1);
+    MGCG_CUDA(cudaMalloc((void **)&c->r, bytes));
+    MGCG_CUDA(cudaMalloc((void **)&c->p, bytes));
+    MGCG_CUDA(cudaMalloc((void **)&c->Ap, bytes));
+    c->work_n = n;
+    if (c->graph_exec) { cudaGraphExecDestroy(c->graph_exec); c->graph_exec = nullptr; }
+    if (c->graph) { cudaGraphDestroy(c->graph); c->graph = nullptr; }
+    return MGCG_OK;
+}
+
+struct HostPath {   // device copies owned by mgcg_solve_host
+    double *val = nullptr; int *rowptr = nullptr; int *col = nullptr; double *b = nullptr; double *x = nullptr;
+    size_t cap_n = 0, cap_nnz = 0;
+    void release()
+    {
+        if (val) cudaFree(val); if (rowptr) cudaFree(rowptr); if (col) cudaFree(col); if (b) cudaFree(b); if (x) cudaFree(x);
+        val = nullptr; rowptr = nullptr; col = nullptr; b = nullptr; x = nullptr; cap_n = cap_nnz = 0;
+    }
+};
+
+}  // namespace mgcg
+
+using namespace mgcg;
+
+extern "C" {
+
+int mgcg_version(void) { return MGCG_VERSION; }
+const char *mgcg_last_error(void) { return get_error(); }
+
+void mgcg_options_default(mgcg_options *o)
+{
+    memset(o, 0, sizeof(*o));
+    o->tolerance = 1e-8;
+    o->min_iteration = 0;
+    o->max_iteration = 1 << 30;
+    o->norm = MGCG_NORM_ABS_L2;
+    o->min_strict = 0;
+    o->precond = MGCG_PRECOND_NONE;
+    o->mg_max_levels = 12;
+    o->mg_coarse_size = 512;
+    o->mg_pre_sweeps = 1;
+    o->mg_post_sweeps = 1;
+    o->mg_omega = 0.8;
+    o->mg_smoother = MGCG_SMOOTHER_JACOBI;
+    o->mg_smoothed = 1;
+    o->mg_prolong_omega = 2.0 / 3.0;
+    o->spmv_kernel = MGCG_SPMV_AUTO;
+    o->check_interval = 8;
+    o->use_graph = 1;
+    o->profile = 0;
+}
+
+mgcg_ctx *mgcg_create(int device)
+{
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count <= 0) {
+        set_error("mgcg_create: no CUDA device (%s) - this library has no CPU fallback", cudaGetErrorString(e));
+        return nullptr;
+    }
+    if (device < 0 || device >= count) { set_error("mgcg_create: device %d out of range [0,%d)", device, count); return nullptr; }
+    if (cudaSetDevice(device) != cudaSuccess) { set_error("mgcg_create: cudaSetDevice(%d) failed", device); return nullptr; }
+    mgcg_ctx *c = new mgcg_ctx();
+    c->device = device;
+    cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
+    if (c->sm_count <= 0) c->sm_count = 148;
+    bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
+    c->own_stream = true;
+    ok = ok && cudaMalloc((void **)&c->d_scalars, sizeof(Scalars)) == cudaSuccess;
+    ok = ok && cudaMallocHost((void **)&c->h_scalars, 2 * sizeof(Scalars)) == cudaSuccess;
+    ok = ok && cudaMalloc((void **)&c->ws.partial, sizeof(double) * 2 * kMaxPartials) == cudaSuccess;
+    ok = ok && cudaMalloc((void **)&c->ws.ticket, sizeof(unsigned int)) == cudaSuccess;
+    ok = ok && cudaMalloc((void **)&c->d_tmp_scalar, sizeof(double) * 4) == cudaSuccess;
+    ok = ok && cudaMallocHost((void **)&c->h_tmp_scalar, sizeof(double) * 4) == cudaSuccess;
+    ok = ok && cudaMemset(c->ws.ticket, 0, sizeof(unsigned int)) == cudaSuccess;
+    ok = ok && cudaMemset(c->d_scalars, 0, sizeof(Scalars)) == cudaSuccess;
+    if (!ok) { set_error("mgcg_create: allocation failed: %s", cudaGetErrorString(cudaGetLastError())); mgcg_destroy(c); return nullptr; }
+    mgcg_options_default(&c->opt);
+    return c;
+}
+
+void mgcg_destroy(mgcg_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    mg_free(c);
+    if (c->graph_exec) cudaGraphExecDestroy(c->graph_exec);
+    if (c->graph) cudaGraphDestroy(c->graph);
+    if (c->host_path) { ((HostPath *)c->host_path)->release(); delete (HostPath *)c->host_path; }
+    if (c->r) cudaFree(c->r);
+    if (c->p) cudaFree(c->p);
+    if (c->Ap) cudaFree(c->Ap);
+    if (c->d_scalars) cudaFree(c->d_scalars);
+    if (c->h_scalars) cudaFreeHost(c->h_scalars);
+    if (c->ws.partial) cudaFree(c->ws.partial);
+    if (c->ws.ticket) cudaFree(c->ws.ticket);
+    if (c->d_tmp_scalar) cudaFree(c->d_tmp_scalar);
+    if (c->h_tmp_scalar) cudaFreeHost(c->h_tmp_scalar);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int mgcg_set_stream(mgcg_ctx *c, void *cuda_stream)
+{
+    if (!c) { set_error("mgcg_set_stream: null context"); return MGCG_ERR_INVALID; }
+    MGCG_CUDA(cudaSetDevice(c->device));
+    if (c->stream) MGCG_CUDA(cudaStreamSynchronize(c->stream));
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    c->stream = (cudaStream_t)cuda_stream;
+    c->own_stream = false;
+    if (c->graph_exec) { cudaGraphExecDestroy(c->graph_exec); c->graph_exec = nullptr; }
+    if (c->graph) { cudaGraphDestroy(c->graph); c->graph = nullptr; }
+    return MGCG_OK;
+}
+
+int mgcg_setup(mgcg_ctx *c, int count, int elements_count,
+               const double *d_elements, const int *d_row_offsets, const int *d_column_indeces, const mgcg_options *opt)
+{
+    if (!c) { set_error("mgcg_setup: null context"); return MGCG_ERR_INVALID; }
+    if (count <= 0 || elements_count < 0 || !d_elements || !d_row_offsets || !d_column_indeces) {
+        set_error("mgcg_setup: empty or null matrix (count=%d, elements=%d)", count, elements_count);
+        return MGCG_ERR_INVALID;
+    }
+    MGCG_CUDA(cudaSetDevice(c->device));
+    if (opt) c->opt = *opt;
+    c->A.rows = count; c->A.cols = count; c->A.nnz = elements_count;
+    c->A.val = d_elements; c->A.rowptr = d_row_offsets; c->A.col = d_column_indeces;
+    c->planA = spmv_make_plan(c, count, elements_count, c->opt.spmv_kernel);
+    if (c->graph_exec) { cudaGraphExecDestroy(c->graph_exec); c->graph_exec = nullptr; }
+    if (c->graph) { cudaGraphDestroy(c->graph); c->graph = nullptr; }
+    c->is_setup = false;
+    c->setup_ms = 0.f;
+    MGCG_CHECK(ctx_ensure_work(c, count));
+    if (c->opt.precond == MGCG_PRECOND_MG) {
+        cudaEvent_t e0, e1;
+        MGCG_CUDA(cudaEventCreate(&e0)); MGCG_CUDA(cudaEventCreate(&e1));
+        MGCG_CUDA(cudaEventRecord(e0, c->stream));
+        int s = mg_build(c);
+        if (s != MGCG_OK) { mg_free(c); cudaEventDestroy(e0); cudaEventDestroy(e1); return s; }
+        MGCG_CUDA(cudaEventRecord(e1, c->stream));
+        MGCG_CUDA(cudaEventSynchronize(e1));
+        MGCG_CUDA(cudaEventElapsedTime(&c->setup_ms, e0, e1));
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+    } else {
+        mg_free(c);
+    }
+    c->is_setup = true;
+    return MGCG_OK;
+}
+
+int mgcg_solve(mgcg_ctx *c, const double *d_b, double *d_x, mgcg_result *res)
+{
+    if (!c || !d_b || !d_x) { set_error("mgcg_solve: null argument"); return MGCG_ERR_INVALID; }
+    MGCG_CUDA(cudaSetDevice(c->device));
+    if (res) memset(res, 0, sizeof(*res));
+    int s = cg_solve(c, d_b, d_x, res);
+    if (res) {
+        res->status = s;
+        res->operator_complexity = 1.0;
+        if (c->mg) res->operator_complexity = c->mg->op_complexity;
+    }
+    return s;
+}
+
+int mgcg_solve_host(mgcg_ctx *c, int count, int elements_count,
+                    const double *elements, const int *row_offsets, const int *column_indeces,
+                    const double *b, double *x, const mgcg_options *opt, mgcg_result *res)
+{
+    if (!c || !elements || !row_offsets || !column_indeces || !b || !x || count <= 0) {
+        set_error("mgcg_solve_host: null or empty argument");
+        return MGCG_ERR_INVALID;
+    }
+    MGCG_CUDA(cudaSetDevice(c->device));
+    if (!c->host_path) c->host_path = new HostPath();
+    HostPath *h = (HostPath *)c->host_path;
+    if (h->cap_n < (size_t)count || h->cap_nnz < (size_t)elements_count) {
+        h->release();
+        MGCG_CUDA(cudaMalloc((void **)&h->val, sizeof(double) * (size_t)(elements_count > 0 ? elements_count : 1)));
+        MGCG_CUDA(cudaMalloc((void **)&h->col, sizeof(int) * (size_t)(elements_count > 0 ? elements_count : 1)));
+        MGCG_CUDA(cudaMalloc((void **)&h->rowptr, sizeof(int) * ((size_t)count + 1)));
+        MGCG_CUDA(cudaMalloc((void **)&h->b, sizeof(double) * (size_t)count));
+        MGCG_CUDA(cudaMalloc((void **)&h->x, sizeof(double) * (size_t)count));
+        h->cap_n = count; h->cap_nnz = elements_count;
+    }
+    cudaStream_t st = c->stream;
+    MGCG_CUDA(cudaMemcpyAsync(h->val, elements, sizeof(double) * (size_t)elements_count, cudaMemcpyHostToDevice, st));
+    MGCG_CUDA(cudaMemcpyAsync(h->col, column_indeces, sizeof(int) * (size_t)elements_count, cudaMemcpyHostToDevice, st));
+    MGCG_CUDA(cudaMemcpyAsync(h->rowptr, row_offsets, sizeof(int) * ((size_t)count + 1), cudaMemcpyHostToDevice, st));
+    MGCG_CUDA(cudaMemcpyAsync(h->b, b, sizeof(double) * (size_t)count, cudaMemcpyHostToDevice, st));
+    MGCG_CUDA(cudaMemcpyAsync(h->x, x, sizeof(double) * (size_t)count, cudaMemcpyHostToDevice, st));
+    MGCG_CHECK(mgcg_setup(c, count, elements_count, h->val, h->rowptr, h->col, opt));
+    int s = mgcg_solve(c, h->b, h->x, res);
+    MGCG_CUDA(cudaMemcpyAsync(x, h->x, sizeof(double) * (size_t)count, cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    return s;
+}
+
+// ---- individually exported kernels ----------------------------------------------------------------------
+static int fetch_scalar(mgcg_ctx *c, const double *d, double *host_out)
+{
+    if (!host_out) return MGCG_OK;
+    MGCG_CUDA(cudaMemcpyAsync(c->h_tmp_scalar, d, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    MGCG_CUDA(cudaStreamSynchronize(c->stream));
+    *host_out = c->h_tmp_scalar[0];
+    return MGCG_OK;
+}
+
+int mgcg_spmv(mgcg_ctx *c, int rows, int cols, int elements_count,
+              const double *d_elements, const int *d_row_offsets, const int *d_column_indeces,
+              const double *d_x, double *d_y, double alpha, double beta, int kernel)
+{
+    if (!c) { set_error("mgcg_spmv: null context"); return MGCG_ERR_INVALID; }
+    MGCG_CUDA(cudaSetDevice(c->device));
+    SpmvArgs a;
+    a.A.rows = rows; a.A.cols = cols; a.A.nnz = elements_count; a.A.val = d_elements; a.A.rowptr = d_row_offsets; a.A.col = d_column_indeces;
+    a.x = d_x; a.y = d_y; a.alpha = alpha; a.beta = beta;
+    SpmvPlan p = spmv_make_plan(c, rows, elements_count, kernel);
+    const bool plain = (alpha == 1.0 && beta == 0.0);
+    return spmv_launch(c, p, plain ? EPI_PLAIN : EPI_AXPBY, a);
+}
+
+int mgcg_spmv_dot(mgcg_ctx *c, int rows, int cols, int elements_count,
+                  const double *d_elements, const int *d_row_offsets, const int *d_column_indeces,
+                  const double *d_x, double *d_y, const double *d_w, double *d_dot, int kernel)
+{
+    if (!c) { set_error("mgcg_spmv_dot: null context"); return MGCG_ERR_INVALID; }
+    MGCG_CUDA(cudaSetDevice(c->device));
+    SpmvArgs a;
+    a.A.rows = rows; a.A.cols = cols; a.A.nnz = elements_count; a.A.val = d_elements; a.A.rowptr = d_row_offsets; a.A.col = d_column_indeces;
+    a.x = d_x; a.y = d_y; a.w = d_w; a.fin = FIN_STORE; a.out = d_dot;
+    SpmvPlan p = spmv_make_plan(c, rows, elements_count, kernel);
+    return spmv_launch(c, p, EPI_DOT, a);
+}
+
+int mgcg_dot(mgcg_ctx *c, int n, const double *d_a, const double *d_b, double *d_out, double *host_out)
+{
+    if (!c) { set_error("mgcg_dot: null context"); return MGCG_ERR_INVALID; }
+    MGCG_CUDA(cudaSetDevice(c->device));
+    double *out = d_out ? d_out : c->d_tmp_scalar;
+    MGCG_CHECK(vec_dot(c, n, d_a, d_b, FIN_STORE, out));
+    return fetch_scalar(c, out, host_out);
+}
+
+int mgcg_max_abs(mgcg_ctx *c, int n, const double *d_a, double *d_out, double *host_out)
+{
+    if (!c) { set_error("mgcg_max_abs: null context"); return MGCG_ERR_INVALID; }
+    MGCG_CUDA(cudaSetDevice(c->device));
+    double *out = d_out ? d_out : c->d_tmp_scalar;
+    MGCG_CHECK(vec_max_abs(c, n, d_a, out));
+    return fetch_scalar(c, out, host_out);
+}
+
+int mgcg_axpy(mgcg_ctx *c, int n, double alpha, const double *d_x, double *d_y)
+{
+    if (!c) return MGCG_ERR_INVALID;
+    MGCG_CUDA(cudaSetDevice(c->device));
+    return vec_axpy(c, n, alpha, d_x, d_y);
+}
+int mgcg_scal(mgcg_ctx *c, int n, double alpha, double *d_x)
+{
+    if (!c) return MGCG_ERR_INVALID;
+    MGCG_CUDA(cudaSetDevice(c->device));
+    return vec_scal(c, n, alpha, d_x);
+}
+int mgcg_copy(mgcg_ctx *c, int n, const double *d_x, double *d_y)
+{
+    if (!c) return MGCG_ERR_INVALID;
+    MGCG_CUDA(cudaSetDevice(c->device));
+    return vec_copy(c, n, d_x, d_y);
+}
+
+int mgcg_update_xr(mgcg_ctx *c, int n, double alpha, const double *d_p, const double *d_Ap,
+                   double *d_x, double *d_r, double *d_rr, double *host_rr)
+{
+    if (!c) return MGCG_ERR_INVALID;
+    MGCG_CUDA(cudaSetDevice(c->device));
+    double *out = d_rr ? d_rr : c->d_tmp_scalar;
+    MGCG_CHECK(cg_update_xr(c, n, d_p, d_Ap, d_x, d_r, FIN_STORE, true, alpha, out));
+    return fetch_scalar(c, out, host_rr);
+}
+
+int mgcg_update_p(mgcg_ctx *c, int n, double beta, const double *d_r, double *d_p)
+{
+    if (!c) return MGCG_ERR_INVALID;
+    MGCG_CUDA(cudaSetDevice(c->device));
+    return cg_update_p(c, n, d_r, d_p, true, beta);
+}
+
+// ConjugateGradientParallelGpu.cs:271-277 — bit-exact integer rule
+int mgcg_partition_offsets(int count, int device_count, int *offsets)
+{
+    if (device_count <= 0 || !offsets || count < 0) { set_error("mgcg_partition_offsets: bad argument"); return MGCG_ERR_INVALID; }
+    offsets[0] = 0;
+    for (int i = 1; i < device_count; i++) offsets[i] = offsets[i - 1] + (int)floor((double)count / device_count);
+    offsets[device_count] = count;
+    return MGCG_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,175 @@
+// cg.cu — the (preconditioned) conjugate-gradient loop, device-resident scalars, speculative launch.
+// Algorithm and ordering: ConjugateGradientCpu.cs:45-98 == Mgcg.cu:217-269 == SimpleConjugateGradient.cu:75-125.
+// The reference reads two dots back to the host every iteration; here alpha/beta/stop-rule live in a device struct
+// written by the last block of each reducing kernel, the host enqueues iterations ahead and polls a `done` flag
+// with a lag (kernels enqueued past convergence see `done` and return immediately, so the result is exact).
+#include "common.cuh"
+
+namespace mgcg {
+
+static int enqueue_iteration(mgcg_ctx *c, const double *b, double *x, std::vector<cudaEvent_t> *pev = nullptr)
+{
+    (void)b;
+    const int n = c->A.rows;
+    const bool pre = (c->opt.precond == MGCG_PRECOND_MG) && c->mg;
+    // Ap = A p ; pAp ; alpha = rz / pAp                                  (ConjugateGradientCpu.cs:70-71)
+    SpmvArgs a;
+    a.A = c->A; a.x = c->p; a.y = c->Ap; a.w = c->p; a.fin = FIN_PAP; a.gated = true;
+    if (pev) {   // profile=1: bracket the fine-level SpMV+dot launch with events on the solve stream
+        cudaEvent_t a0, a1;
+        MGCG_CUDA(cudaEventCreate(&a0)); MGCG_CUDA(cudaEventCreate(&a1));
+        MGCG_CUDA(cudaEventRecord(a0, c->stream));
+        MGCG_CHECK(spmv_launch(c, c->planA, EPI_DOT, a));
+        MGCG_CUDA(cudaEventRecord(a1, c->stream));
+        pev->push_back(a0); pev->push_back(a1);
+    } else {
+        MGCG_CHECK(spmv_launch(c, c->planA, EPI_DOT, a));
+    }
+    if (!pre) {
+        // x += alpha p ; r -= alpha Ap ; rr' ; stop rule ; beta           (cs:72-80,93)
+        MGCG_CHECK(cg_update_xr(c, n, c->p, c->Ap, x, c->r, FIN_RR, false, 0.0, nullptr));
+        // p = r + beta p                                                  (cs:94)
+        MGCG_CHECK(cg_update_p(c, n, c->r, c->p, false, 0.0));
+    } else {
+        // same update, fused with the V-cycle's first pre-smoothing sweep from a zero guess: z0 = omega D^-1 r
+        MGCG_CHECK(cg_update_xr(c, n, c->p, c->Ap, x, c->r, FIN_RR_PRECOND, false, 0.0, nullptr,
+                                mg_level0_first_x(c), mg_level0_dinv(c), c->opt.mg_omega));
+        double *z = nullptr;
+        MGCG_CHECK(mg_vcycle(c, c->r, &z, true, FIN_RZ));   // z = M r ; r.z ; beta = rz'/rz (fused into the last sweep)
+        MGCG_CHECK(cg_update_p(c, n, z, c->p, false, 0.0)); // p = z + beta p
+    }
+    return MGCG_OK;
+}
+
+int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
+{
+    if (!c->is_setup) { set_error("mgcg_solve: mgcg_setup has not been called"); return MGCG_ERR_INVALID; }
+    const int n = c->A.rows;
+    const bool pre = (c->opt.precond == MGCG_PRECOND_MG) && c->mg;
+    MGCG_CHECK(ctx_ensure_work(c, n));
+    cudaStream_t st = c->stream;
+    cudaEvent_t ev0, ev1, evp[2];
+    MGCG_CUDA(cudaEventCreate(&ev0));
+    MGCG_CUDA(cudaEventCreate(&ev1));
+    MGCG_CUDA(cudaEventCreateWithFlags(&evp[0], cudaEventDisableTiming));
+    MGCG_CUDA(cudaEventCreateWithFlags(&evp[1], cudaEventDisableTiming));
+    c->launches = 0;
+
+    // scalars
+    Scalars h{};
+    h.tolerance = c->opt.tolerance;
+    h.min_iteration = c->opt.min_iteration;
+    h.max_iteration = c->opt.max_iteration;
+    h.norm = c->opt.norm;
+    h.min_strict = c->opt.min_strict;
+    c->h_scalars[0] = h;
+    MGCG_CUDA(cudaMemcpyAsync(c->d_scalars, &c->h_scalars[0], sizeof(Scalars), cudaMemcpyHostToDevice, st));
+    MGCG_CUDA(cudaEventRecord(ev0, st));
+
+    // init: Ap = A x ; r = b - Ap ; p = r (or z) ; rr                      (ConjugateGradientCpu.cs:54-57)
+    {
+        SpmvArgs a;
+        a.A = c->A; a.x = x; a.y = c->Ap;
+        MGCG_CHECK(spmv_launch(c, c->planA, EPI_PLAIN, a));
+        if (!pre) {
+            MGCG_CHECK(cg_init_residual(c, n, b, c->Ap, c->r, c->p, FIN_INIT));
+        } else {
+            MGCG_CHECK(cg_init_residual(c, n, b, c->Ap, c->r, nullptr, FIN_INIT_RR));
+            double *z = nullptr;
+            MGCG_CHECK(mg_vcycle(c, c->r, &z, false, FIN_INIT_RZ));
+            MGCG_CHECK(vec_copy(c, n, z, c->p));
+        }
+    }
+
+    // loop
+    const int interval = c->opt.check_interval > 0 ? c->opt.check_interval : 8;
+    const bool profile = c->opt.profile != 0;
+    const bool use_graph = c->opt.use_graph && !profile;
+    std::vector<cudaEvent_t> pev;
+    float spmv_ms = 0.f;
+    int spmv_n = 0;
+
+    if (use_graph && (!c->graph_exec || c->graph_b != b || c->graph_x != x)) {
+        if (c->graph_exec) { cudaGraphExecDestroy(c->graph_exec); c->graph_exec = nullptr; }
+        if (c->graph) { cudaGraphDestroy(c->graph); c->graph = nullptr; }
+        int saved = c->launches;
+        MGCG_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        int s = enqueue_iteration(c, b, x);
+        cudaError_t e = cudaStreamEndCapture(st, &c->graph);
+        if (s != MGCG_OK) return s;
+        MGCG_CUDA(e);
+        MGCG_CUDA(cudaGraphInstantiate(&c->graph_exec, c->graph, 0));
+        c->graph_b = b; c->graph_x = x;
+        c->launches = saved;
+    }
+    long long enq = 0;
+    int slot = 0;
+    bool finished = false;
+    bool have_prev = false;
+    Scalars fin{};
+    const long long hard_cap = (long long)c->opt.max_iteration + 2;
+    while (!finished) {
+        for (int k = 0; k < interval; ++k) {
+            if (use_graph) {
+                MGCG_CUDA(cudaGraphLaunch(c->graph_exec, st));
+            } else {
+                MGCG_CHECK(enqueue_iteration(c, b, x, profile ? &pev : nullptr));
+            }
+            ++enq;
+        }
+        MGCG_CUDA(cudaMemcpyAsync(&c->h_scalars[slot], c->d_scalars, sizeof(Scalars), cudaMemcpyDeviceToHost, st));
+        MGCG_CUDA(cudaEventRecord(evp[slot], st));
+        if (have_prev) {   // inspect the PREVIOUS batch while this one runs
+            MGCG_CUDA(cudaEventSynchronize(evp[slot ^ 1]));
+            if (c->h_scalars[slot ^ 1].done) { finished = true; }
+        }
+        have_prev = true;
+        slot ^= 1;
+        if (!finished && enq > hard_cap + 2LL * interval) {   // the device-side max-iteration test must have fired
+            finished = true;
+        }
+    }
+    MGCG_CUDA(cudaMemcpyAsync(&c->h_scalars[0], c->d_scalars, sizeof(Scalars), cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaEventRecord(ev1, st));
+    MGCG_CUDA(cudaEventSynchronize(ev1));
+    fin = c->h_scalars[0];
+    if (use_graph) {
+        size_t nodes = 0;
+        cudaGraphGetNodes(c->graph, nullptr, &nodes);
+        c->launches += (int)(nodes * enq);
+    }
+
+    float ms = 0.f;
+    MGCG_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
+    for (size_t i = 0; i + 1 < pev.size(); i += 2) {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, pev[i], pev[i + 1]);
+        // launches enqueued after convergence return immediately: count only real iterations
+        if ((int)(i / 2) <= fin.iteration) { spmv_ms += t; spmv_n++; }
+        cudaEventDestroy(pev[i]); cudaEventDestroy(pev[i + 1]);
+    }
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(evp[0]); cudaEventDestroy(evp[1]);
+
+    if (res) {
+        res->status = fin.done ? fin.status : MGCG_ERR_NOT_CONVERGED;
+        res->iteration = fin.iteration;
+        res->iterations_done = fin.iteration + 1;
+        res->residual = fin.residual;
+        res->rr = fin.rr;
+        res->rr0 = fin.rr0;
+        res->solve_ms = ms;
+        res->setup_ms = c->setup_ms;
+        res->levels = mgcg_mg_levels(c);
+        res->kernel_launches = c->launches;
+        res->spmv_ms_total = spmv_ms;
+        res->spmv_launches = spmv_n;
+    }
+    if (!fin.done) { set_error("cg_solve: iteration cap reached without the device flag"); return MGCG_ERR_NOT_CONVERGED; }
+    if (fin.status != MGCG_OK) {
+        set_error(fin.status == MGCG_ERR_NOT_CONVERGED ? "cg_solve: Iteration > MaxIteration (reference throws here, ConjugateGradient.cs:70-74)"
+                                                       : "cg_solve: breakdown (p.Ap <= 0 or NaN)");
+    }
+    return fin.status;
+}
+
+}  // namespace mgcg

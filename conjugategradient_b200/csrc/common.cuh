@@ -1,0 +1,199 @@
+// common.cuh — shared declarations of libMgcgGpu.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+#include "../../include/mgcg.h"
+
+namespace mgcg {
+
+// ---------------------------------------------------------------------------------------------------------
+// error plumbing
+void set_error(const char *fmt, ...);
+const char *get_error();
+
+#define MGCG_CUDA(call)                                                                                  \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) {                                                                         \
+            mgcg::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));       \
+            return MGCG_ERR_CUDA;                                                                        \
+        }                                                                                                \
+    } while (0)
+
+#define MGCG_CHECK(call)                                                                                 \
+    do {                                                                                                 \
+        int s_ = (call);                                                                                 \
+        if (s_ != MGCG_OK) return s_;                                                                    \
+    } while (0)
+
+#define MGCG_LAUNCH_CHECK() MGCG_CUDA(cudaGetLastError())
+
+// ---------------------------------------------------------------------------------------------------------
+// device-resident CG scalars: alpha/beta never visit the host inside the loop (the reference syncs twice per
+// iteration to read its dots, SimpleConjugateGradient.cu:98,103).
+struct Scalars {
+    double rr;        // current r.r
+    double rr0;       // initial r.r
+    double rz;        // current r.z (== rr without preconditioner)
+    double pAp;
+    double alpha;
+    double beta;
+    double residual;  // measure of the stop rule
+    double rmax;      // max|r_i| (LINF mode)
+    double tolerance;
+    int iteration;    // 0-based index of the iteration in flight
+    int min_iteration;
+    int max_iteration;
+    int norm;
+    int min_strict;
+    int done;         // set by the device when converged / failed: every later kernel of the loop is a no-op
+    int status;       // MGCG_OK / MGCG_ERR_*
+    int pad;
+};
+
+// what the LAST block of a reducing kernel does with the finished sum (runs in one thread)
+enum FinOp {
+    FIN_STORE = 0,  // out[0] = sum
+    FIN_INIT,       // rr = rr0 = rz = sum  (unpreconditioned init)
+    FIN_INIT_RR,    // rr = rr0 = sum       (preconditioned init: rz comes from FIN_INIT_RZ)
+    FIN_INIT_RZ,    // rz = sum
+    FIN_PAP,        // pAp = sum; alpha = rz / pAp; breakdown test
+    FIN_RR,         // rr_new = sum; stop rule; (no precond) beta = rr_new/rr, rz = rr = rr_new
+    FIN_RR_PRECOND, // rr = sum; stop rule only
+    FIN_RZ,         // beta = sum / rz; rz = sum
+    FIN_STORE_MAX   // out[0] = max
+};
+
+constexpr int kMaxPartials = 4096;   // upper bound on the grid of any reducing kernel
+
+// A reduction workspace: partial sums (two lanes: sum and max), ticket counter.
+struct ReduceWs {
+    double *partial;     // [2 * kMaxPartials]
+    unsigned int *ticket;
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// CSR view (device pointers, not owned)
+struct Csr {
+    int rows = 0, cols = 0, nnz = 0;
+    const double *val = nullptr;
+    const int *rowptr = nullptr;
+    const int *col = nullptr;
+};
+
+// SpMV plan: kernel choice and launch geometry for one matrix
+struct SpmvPlan {
+    int kernel = MGCG_SPMV_STREAM;  // STREAM or VECTOR
+    int rows_per_tile = 256;        // STREAM: rows handled per tile (<= 256)
+    int lanes = 8;                  // VECTOR: lanes per row
+    int grid = 0;
+};
+
+// epilogues of the SpMV kernels (s = sum_k a_ik x_k)
+enum SpmvEpi {
+    EPI_PLAIN = 0,   // y = s
+    EPI_AXPBY,       // y = alpha*s + beta*y                     (CsrMV compat, prolongation with beta=1)
+    EPI_DOT,         // y = s; partial += w_i * s                (p.Ap fused)
+    EPI_RESID,       // y = b_i - s
+    EPI_JACOBI,      // y = x_i + omega*dinv_i*(b_i - s)         (x is the SpMV input vector)
+    EPI_JACOBI_DOT   // as EPI_JACOBI; partial += b_i * y_i      (r.z fused into the last post-smoothing sweep)
+};
+
+struct SpmvArgs {
+    Csr A;
+    const double *x = nullptr;
+    double *y = nullptr;
+    const double *b = nullptr;     // RESID / JACOBI
+    const double *dinv = nullptr;  // JACOBI
+    const double *w = nullptr;     // DOT
+    double alpha = 1.0, beta = 0.0, omega = 1.0;
+    int fin = FIN_STORE;
+    double *out = nullptr;         // FIN_STORE target
+    bool gated = false;            // true: no-op once Scalars.done is set (kernels inside the CG loop)
+};
+
+// ---------------------------------------------------------------------------------------------------------
+struct MgLevel;
+struct Hierarchy;
+struct DistState;
+
+}  // namespace mgcg
+
+// The opaque context of the C ABI.
+struct mgcg_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int sm_count = 148;
+    mgcg::Scalars *d_scalars = nullptr;
+    mgcg::Scalars *h_scalars = nullptr;  // pinned, 2 slots
+    mgcg::ReduceWs ws{};
+    double *d_tmp_scalar = nullptr;      // scratch device scalar for the standalone dot / maxabs calls
+    double *h_tmp_scalar = nullptr;      // pinned
+    // problem
+    mgcg_options opt{};
+    mgcg::Csr A;
+    mgcg::SpmvPlan planA;
+    bool is_setup = false;
+    // work vectors (owned)
+    double *r = nullptr, *p = nullptr, *Ap = nullptr;
+    int work_n = 0;
+    mgcg::Hierarchy *mg = nullptr;
+    mgcg::DistState *dist = nullptr;
+    float setup_ms = 0.f;
+    // solve-time accounting
+    int launches = 0;
+    // CUDA graph of one iteration
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t graph_exec = nullptr;
+    const double *graph_b = nullptr;
+    double *graph_x = nullptr;
+    // host-pointer path buffers (mgcg_solve_host)
+    void *host_path = nullptr;
+};
+
+namespace mgcg {
+
+// ---- kernels_vec.cu
+int vec_dot(mgcg_ctx *c, int n, const double *a, const double *b, int fin, double *out);
+int vec_max_abs(mgcg_ctx *c, int n, const double *a, double *out);
+int vec_axpy(mgcg_ctx *c, int n, double alpha, const double *x, double *y);
+int vec_scal(mgcg_ctx *c, int n, double alpha, double *x);
+int vec_copy(mgcg_ctx *c, int n, const double *x, double *y);
+int vec_fill(mgcg_ctx *c, int n, double v, double *x);
+// r = b - Ap ; p = r ; partial r.r  -> fin
+int cg_init_residual(mgcg_ctx *c, int n, const double *b, const double *Ap, double *r, double *p, int fin);
+// x += alpha p ; r -= alpha Ap ; r.r (and max|r|) -> fin.  alpha from Scalars unless use_host_alpha.
+// z0/dinv != nullptr: also z0 = omega*dinv*r (first pre-smoothing sweep of the V-cycle from a zero guess, fused)
+int cg_update_xr(mgcg_ctx *c, int n, const double *p, const double *Ap, double *x, double *r, int fin,
+                 bool use_host_alpha, double host_alpha, double *out,
+                 double *z0 = nullptr, const double *dinv = nullptr, double omega = 0.0);
+// p = z + beta p   (z == r without preconditioner)
+int cg_update_p(mgcg_ctx *c, int n, const double *z, double *p, bool use_host_beta, double host_beta);
+// x = omega * dinv .* b
+int mg_jacobi_first(mgcg_ctx *c, int n, double omega, const double *dinv, const double *b, double *x);
+// y = Minv * b for the dense coarsest level (n x n row-major)
+int mg_dense_apply(mgcg_ctx *c, int n, const double *Minv, const double *b, double *y);
+
+// ---- kernels_spmv.cu
+SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel);
+int spmv_launch(mgcg_ctx *c, const SpmvPlan &plan, int epi, const SpmvArgs &a);
+
+// ---- mg_setup.cu / mg_cycle.cu
+int mg_build(mgcg_ctx *c);
+void mg_free(mgcg_ctx *c);
+int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done, int rz_fin);
+double *mg_level0_first_x(mgcg_ctx *c);   // buffer that receives the fused first pre-smoothing sweep
+const double *mg_level0_dinv(mgcg_ctx *c);
+
+// ---- cg.cu
+int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res);
+
+// ---- helpers
+int ctx_ensure_work(mgcg_ctx *c, int n);
+inline int div_up(int a, int b) { return (a + b - 1) / b; }
+
+}  // namespace mgcg

@@ -1,0 +1,40 @@
+// mg.cuh — multigrid hierarchy data structures (device-resident).
+#pragma once
+#include "common.cuh"
+
+namespace mgcg {
+
+// an owned device CSR
+struct DevCsr {
+    int rows = 0, cols = 0, nnz = 0;
+    double *val = nullptr;
+    int *rowptr = nullptr;
+    int *col = nullptr;
+    Csr view() const { Csr c; c.rows = rows; c.cols = cols; c.nnz = nnz; c.val = val; c.rowptr = rowptr; c.col = col; return c; }
+    void free_all();
+};
+
+struct MgLevel {
+    Csr A;                 // operator of this level (level 0: the caller's arrays)
+    DevCsr Aown;           // owned storage for levels >= 1
+    DevCsr P, R;           // prolongation (rows x rows_coarse) and its transpose; empty on the coarsest level
+    int *agg = nullptr;    // fine -> coarse aggregate id (rows entries); nullptr on the coarsest level
+    double *dinv = nullptr;
+    double *xa = nullptr, *xb = nullptr, *b = nullptr, *r = nullptr;   // level vectors (level 0: b is the CG residual)
+    double *xcur = nullptr;
+    SpmvPlan planA, planP, planR;
+    int dims[3] = {0, 0, 0};
+};
+
+struct Hierarchy {
+    std::vector<MgLevel> L;
+    double *coarse_inv = nullptr;   // dense inverse of the coarsest operator (n x n row-major)
+    int coarse_n = 0;
+    double op_complexity = 1.0;
+};
+
+// ---- mg_setup.cu building blocks (also used by tests through the introspection API)
+int spgemm_esc(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C);
+int csr_transpose(mgcg_ctx *c, const Csr &A, DevCsr *T);
+
+}  // namespace mgcg

@@ -1,0 +1,89 @@
+// mg_cycle.cu — one multigrid V(nu1,nu2)-cycle z = M r used as the CG preconditioner.
+// (No counterpart in the reference; CPU twin: oracle/mg_ref.c mg_ref_vcycle.)
+// M is a fixed symmetric positive-definite linear operator: weighted-Jacobi pre/post smoothing with the same
+// sweep count, R = P^T, exact (dense-inverse) coarsest solve, zero initial guess on every level.
+// Per level: [x = w D^-1 b]  (nu1-1 more sweeps)  r = b - A x   b_c = R r   ...   x += P x_c   nu2 sweeps.
+// The buffers used by each step are fixed, so the whole cycle can be captured into a CUDA graph.
+#include "mg.cuh"
+
+namespace mgcg {
+
+static int jacobi_sweep(mgcg_ctx *c, MgLevel &L, double omega, bool with_dot, int fin)
+{
+    double *other = (L.xcur == L.xa) ? L.xb : L.xa;
+    SpmvArgs a;
+    a.A = L.A; a.x = L.xcur; a.y = other; a.b = L.b; a.dinv = L.dinv; a.omega = omega; a.gated = true; a.fin = fin;
+    MGCG_CHECK(spmv_launch(c, L.planA, with_dot ? EPI_JACOBI_DOT : EPI_JACOBI, a));
+    L.xcur = other;
+    return MGCG_OK;
+}
+
+// z_out receives the level-0 buffer holding z.  fuse_first_done: level 0's first sweep (xa = w D^-1 r) was already
+// produced by cg_update_xr.  rz_fin: FinOp applied to sum_i r_i z_i (fused into the last post-smoothing sweep).
+int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done, int rz_fin)
+{
+    Hierarchy *H = c->mg;
+    if (!H) { set_error("mg_vcycle: no hierarchy"); return MGCG_ERR_INVALID; }
+    const int nl = (int)H->L.size();
+    const double omega = c->opt.mg_omega;
+    const int pre = c->opt.mg_pre_sweeps, post = c->opt.mg_post_sweeps;
+    H->L[0].b = const_cast<double *>(r);
+
+    if (nl == 1) {   // the whole problem is the dense coarsest level
+        MgLevel &L = H->L[0];
+        MGCG_CHECK(mg_dense_apply(c, L.A.rows, H->coarse_inv, L.b, L.xb));
+        if (rz_fin >= 0) MGCG_CHECK(vec_dot(c, L.A.rows, r, L.xb, rz_fin, nullptr));
+        *z_out = L.xb;
+        return MGCG_OK;
+    }
+    // ---- down
+    for (int l = 0; l < nl - 1; ++l) {
+        MgLevel &L = H->L[l];
+        L.xcur = L.xa;
+        if (!(l == 0 && fuse_first_done)) MGCG_CHECK(mg_jacobi_first(c, L.A.rows, omega, L.dinv, L.b, L.xa));
+        for (int s = 1; s < pre; ++s) MGCG_CHECK(jacobi_sweep(c, L, omega, false, FIN_STORE));
+        SpmvArgs a;
+        a.A = L.A; a.x = L.xcur; a.y = L.r; a.b = L.b; a.gated = true;
+        MGCG_CHECK(spmv_launch(c, L.planA, EPI_RESID, a));
+        SpmvArgs q;
+        q.A = L.R.view(); q.x = L.r; q.y = H->L[l + 1].b; q.gated = true;
+        MGCG_CHECK(spmv_launch(c, L.planR, EPI_PLAIN, q));
+    }
+    // ---- coarsest
+    {
+        MgLevel &L = H->L[nl - 1];
+        MGCG_CHECK(mg_dense_apply(c, L.A.rows, H->coarse_inv, L.b, L.xa));
+        L.xcur = L.xa;
+    }
+    // ---- up
+    for (int l = nl - 2; l >= 0; --l) {
+        MgLevel &L = H->L[l];
+        SpmvArgs a;
+        a.A = L.P.view(); a.x = H->L[l + 1].xcur; a.y = L.xcur; a.alpha = 1.0; a.beta = 1.0; a.gated = true;
+        MGCG_CHECK(spmv_launch(c, L.planP, EPI_AXPBY, a));
+        for (int s = 0; s < post; ++s) {
+            const bool last = (l == 0 && s == post - 1 && rz_fin >= 0);
+            MGCG_CHECK(jacobi_sweep(c, L, omega, last, last ? rz_fin : FIN_STORE));
+        }
+    }
+    if (post == 0 && rz_fin >= 0) MGCG_CHECK(vec_dot(c, H->L[0].A.rows, r, H->L[0].xcur, rz_fin, nullptr));
+    *z_out = H->L[0].xcur;
+    return MGCG_OK;
+}
+
+}  // namespace mgcg
+
+using namespace mgcg;
+
+extern "C" int mgcg_mg_apply(mgcg_ctx *c, const double *d_r, double *d_z)
+{
+    if (!c || !c->mg) { set_error("mgcg_mg_apply: no hierarchy (setup with precond = MGCG_PRECOND_MG)"); return MGCG_ERR_INVALID; }
+    MGCG_CUDA(cudaSetDevice(c->device));
+    // make sure the loop gate is open
+    MGCG_CUDA(cudaMemsetAsync(c->d_scalars, 0, sizeof(Scalars), c->stream));
+    double *z = nullptr;
+    MGCG_CHECK(mg_vcycle(c, d_r, &z, false, -1));
+    MGCG_CUDA(cudaMemcpyAsync(d_z, z, sizeof(double) * (size_t)c->A.rows, cudaMemcpyDeviceToDevice, c->stream));
+    MGCG_CUDA(cudaStreamSynchronize(c->stream));
+    return MGCG_OK;
+}

@@ -1,0 +1,510 @@
+// mg_setup.cu — multigrid hierarchy built ON THE DEVICE from the caller's CSR matrix.
+// The reference has no multigrid at all ("Mgcg" is a name only, MgcgMain.cs:8); this is new work
+// specified by BASELINE.json north_star item (3).  Parity is against the CPU twin oracle/mg_ref.c, which runs the
+// same steps in the same order: every floating-point operation that defines the hierarchy (prolongator smoothing,
+// Galerkin products, dense coarse inverse) is an explicit rounded multiply / add in a fixed order (no FMA
+// contraction), so level operators can be compared bit-for-bit.
+//
+//   aggregates : geometric 2x2x2 blocks when a grid hint is given, else blocks of 8 consecutive rows
+//                (== octants for Morton-sorted particles)
+//   P          : plain aggregation T, or smoothed aggregation (I - w D^-1 A) T
+//   A_coarse   : R (A P), R = P^T, both products by expand / stable radix sort / ordered segment sum (ESC)
+//   coarsest   : dense inverse by in-place Gauss-Jordan (SPD, no pivoting)
+// cub::DeviceRadixSort / DeviceScan are used for the sort and the scans of the SETUP only (not the solve path).
+#include "mg.cuh"
+#include <cub/cub.cuh>
+
+namespace mgcg {
+
+typedef unsigned long long u64;
+
+template <class T>
+static int dalloc(T **p, size_t n)
+{
+    *p = nullptr;
+    if (n == 0) n = 1;
+    MGCG_CUDA(cudaMalloc((void **)p, n * sizeof(T)));
+    return MGCG_OK;
+}
+
+void DevCsr::free_all()
+{
+    if (val) cudaFree(val);
+    if (rowptr) cudaFree(rowptr);
+    if (col) cudaFree(col);
+    val = nullptr; rowptr = nullptr; col = nullptr; rows = cols = nnz = 0;
+}
+
+static inline int grid_for(long long n, int threads = 256)
+{
+    long long g = (n + threads - 1) / threads;
+    if (g < 1) g = 1;
+    if (g > 1048576) g = 1048576;
+    return (int)g;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+__global__ void k_extract_dinv(Csr A, double *dinv)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x) {
+        double d = 1.0;
+        for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k)
+            if (A.col[k] == i) { d = A.val[k]; break; }
+        dinv[i] = 1.0 / d;
+    }
+}
+
+__global__ void k_agg_geometric(int nx, int ny, int nz, int cx, int cy, int *agg)
+{
+    const long long n = (long long)nx * ny * nz;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        int x = (int)(i % nx), y = (int)((i / nx) % ny), z = (int)(i / ((long long)nx * ny));
+        agg[i] = (x >> 1) + cx * ((y >> 1) + cy * (z >> 1));
+    }
+}
+
+__global__ void k_agg_blocks(int n, int block, int *agg)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) agg[i] = i / block;
+}
+
+// plain aggregation: P = T (one unit entry per row)
+__global__ void k_build_T(int n, const int *agg, double *val, int *rowptr, int *col)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i <= n; i += gridDim.x * blockDim.x) {
+        rowptr[i] = i;
+        if (i < n) { val[i] = 1.0; col[i] = agg[i]; }
+    }
+}
+
+// smoothed aggregation, expansion of P = T - w D^-1 A T : per row i the entry (agg[i], 1) FIRST, then for every
+// stored a_ik in storage order (agg[col_k], -(w*dinv_i)*a_ik).  Duplicates are summed later in this order.
+__global__ void k_expand_sa(Csr A, const int *agg, const double *dinv, double w, u64 *keys, double *vals)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x) {
+        size_t o = (size_t)A.rowptr[i] + i;
+        keys[o] = ((u64)i << 32) | (unsigned)agg[i];
+        vals[o] = 1.0;
+        ++o;
+        const double f = -__dmul_rn(w, dinv[i]);
+        for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k, ++o) {
+            keys[o] = ((u64)i << 32) | (unsigned)agg[A.col[k]];
+            vals[o] = __dmul_rn(f, A.val[k]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// COO (key = row<<32 | col) -> CSR with ordered duplicate summation
+__global__ void k_mark_heads(size_t count, const u64 *keys, int *head)
+{
+    for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < count; k += (size_t)gridDim.x * blockDim.x)
+        head[k] = (k == 0 || keys[k] != keys[k - 1]) ? 1 : 0;
+}
+__global__ void k_write_heads(size_t count, const int *head, const int *idx, unsigned *pos, int uniq)
+{
+    for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < count; k += (size_t)gridDim.x * blockDim.x)
+        if (head[k]) pos[idx[k]] = (unsigned)k;
+    if (blockIdx.x == 0 && threadIdx.x == 0) pos[uniq] = (unsigned)count;
+}
+__global__ void k_compress(int uniq, const unsigned *pos, const u64 *keys, const double *vals,
+                           double *oval, int *ocol, int *rowcnt)
+{
+    for (int o = blockIdx.x * blockDim.x + threadIdx.x; o < uniq; o += gridDim.x * blockDim.x) {
+        unsigned k0 = pos[o], k1 = pos[o + 1];
+        double s = vals[k0];
+        for (unsigned k = k0 + 1; k < k1; ++k) s = __dadd_rn(s, vals[k]);
+        oval[o] = s;
+        u64 key = keys[k0];
+        ocol[o] = (int)(key & 0xffffffffu);
+        atomicAdd(&rowcnt[(int)(key >> 32)], 1);
+    }
+}
+
+static int bits_for(unsigned v) { int b = 1; while ((v >> b) != 0 && b < 32) ++b; return b; }
+
+// Sort `count` (key,val) pairs stably and compress to CSR rows [0,rows). keys/vals are consumed (scratch).
+static int coo_to_csr_sum(mgcg_ctx *c, int rows, int cols, size_t count, u64 *keys, double *vals, DevCsr *out)
+{
+    cudaStream_t st = c->stream;
+    out->rows = rows; out->cols = cols;
+    MGCG_CHECK(dalloc(&out->rowptr, (size_t)rows + 1));
+    if (count == 0) {
+        MGCG_CUDA(cudaMemsetAsync(out->rowptr, 0, sizeof(int) * ((size_t)rows + 1), st));
+        out->nnz = 0;
+        MGCG_CHECK(dalloc(&out->val, 1)); MGCG_CHECK(dalloc(&out->col, 1));
+        return MGCG_OK;
+    }
+    if (count >= 0xfffffff0ull) { set_error("coo_to_csr_sum: chunk too large"); return MGCG_ERR_UNSUPPORTED; }
+    u64 *keys2 = nullptr; double *vals2 = nullptr;
+    MGCG_CHECK(dalloc(&keys2, count)); MGCG_CHECK(dalloc(&vals2, count));
+    cub::DoubleBuffer<u64> dk(keys, keys2);
+    cub::DoubleBuffer<double> dv(vals, vals2);
+    const int end_bit = 32 + bits_for((unsigned)(rows > 0 ? rows - 1 : 0));
+    size_t tmp_bytes = 0;
+    MGCG_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, (long long)count, 0, end_bit, st));
+    void *tmp = nullptr;
+    MGCG_CUDA(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1));
+    MGCG_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, dk, dv, (long long)count, 0, end_bit, st));
+    cudaFree(tmp);
+    const u64 *sk = dk.Current(); const double *sv = dv.Current();
+
+    int *head = nullptr, *idx = nullptr;
+    MGCG_CHECK(dalloc(&head, count)); MGCG_CHECK(dalloc(&idx, count));
+    k_mark_heads<<<grid_for((long long)count), 256, 0, st>>>(count, sk, head);
+    MGCG_LAUNCH_CHECK();
+    size_t sbytes = 0;
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, sbytes, head, idx, (long long)count, st));
+    MGCG_CUDA(cudaMalloc(&tmp, sbytes ? sbytes : 1));
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, sbytes, head, idx, (long long)count, st));
+    cudaFree(tmp);
+    int last_idx = 0, last_head = 0;
+    MGCG_CUDA(cudaMemcpyAsync(&last_idx, idx + count - 1, sizeof(int), cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaMemcpyAsync(&last_head, head + count - 1, sizeof(int), cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    const int uniq = last_idx + last_head;
+    unsigned *pos = nullptr;
+    MGCG_CHECK(dalloc(&pos, (size_t)uniq + 1));
+    k_write_heads<<<grid_for((long long)count), 256, 0, st>>>(count, head, idx, pos, uniq);
+    MGCG_LAUNCH_CHECK();
+    out->nnz = uniq;
+    MGCG_CHECK(dalloc(&out->val, (size_t)uniq)); MGCG_CHECK(dalloc(&out->col, (size_t)uniq));
+    int *rowcnt = nullptr;
+    MGCG_CHECK(dalloc(&rowcnt, (size_t)rows + 1));
+    MGCG_CUDA(cudaMemsetAsync(rowcnt, 0, sizeof(int) * ((size_t)rows + 1), st));
+    k_compress<<<grid_for(uniq), 256, 0, st>>>(uniq, pos, sk, sv, out->val, out->col, rowcnt);
+    MGCG_LAUNCH_CHECK();
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, sbytes, rowcnt, out->rowptr, rows + 1, st));
+    MGCG_CUDA(cudaMalloc(&tmp, sbytes ? sbytes : 1));
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, sbytes, rowcnt, out->rowptr, rows + 1, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    cudaFree(tmp);
+    cudaFree(rowcnt); cudaFree(pos); cudaFree(head); cudaFree(idx); cudaFree(keys2); cudaFree(vals2);
+    return MGCG_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// C = A * B by expand / sort / compress, in row chunks bounded by a product budget.
+__global__ void k_spgemm_count(Csr A, Csr B, long long *cnt)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x) {
+        long long s = 0;
+        for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k) { int j = A.col[k]; s += B.rowptr[j + 1] - B.rowptr[j]; }
+        cnt[i] = s;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) cnt[A.rows] = 0;
+}
+// largest `end` in (start, rows] with off[end]-off[start] <= budget (at least start+1)
+__global__ void k_find_chunk_end(const long long *off, int rows, int start, long long budget, int *out_end, long long *out_cnt)
+{
+    int lo = start + 1, hi = rows;
+    const long long base = off[start];
+    while (lo < hi) { int mid = lo + (hi - lo + 1) / 2; if (off[mid] - base <= budget) lo = mid; else hi = mid - 1; }
+    *out_end = lo; *out_cnt = off[lo] - base;
+}
+__global__ void k_spgemm_expand(Csr A, Csr B, const long long *off, int row0, int row1, u64 *keys, double *vals)
+{
+    for (int i = row0 + blockIdx.x * blockDim.x + threadIdx.x; i < row1; i += gridDim.x * blockDim.x) {
+        size_t o = (size_t)(off[i] - off[row0]);
+        for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k) {
+            const int j = A.col[k];
+            const double a = A.val[k];
+            for (int q = B.rowptr[j]; q < B.rowptr[j + 1]; ++q, ++o) {
+                keys[o] = ((u64)(unsigned)(i - row0) << 32) | (unsigned)B.col[q];
+                vals[o] = __dmul_rn(a, B.val[q]);
+            }
+        }
+    }
+}
+__global__ void k_add_offset(int n, int *a, int off)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) a[i] += off;
+}
+
+int spgemm_esc(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C)
+{
+    cudaStream_t st = c->stream;
+    const long long budget = 1ll << 27;   // products per chunk (x 32 B of sort buffers)
+    long long *cnt = nullptr, *off = nullptr;
+    MGCG_CHECK(dalloc(&cnt, (size_t)A.rows + 1)); MGCG_CHECK(dalloc(&off, (size_t)A.rows + 1));
+    k_spgemm_count<<<grid_for(A.rows), 256, 0, st>>>(A, B, cnt);
+    MGCG_LAUNCH_CHECK();
+    size_t sbytes = 0; void *tmp = nullptr;
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, sbytes, cnt, off, A.rows + 1, st));
+    MGCG_CUDA(cudaMalloc(&tmp, sbytes ? sbytes : 1));
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, sbytes, cnt, off, A.rows + 1, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    cudaFree(tmp); cudaFree(cnt);
+    int *d_end = nullptr; long long *d_cnt = nullptr;
+    MGCG_CHECK(dalloc(&d_end, 1)); MGCG_CHECK(dalloc(&d_cnt, 1));
+
+    std::vector<DevCsr> parts;
+    std::vector<int> part_row0;
+    int row0 = 0;
+    while (row0 < A.rows) {
+        int row1 = 0; long long count = 0;
+        k_find_chunk_end<<<1, 1, 0, st>>>(off, A.rows, row0, budget, d_end, d_cnt);
+        MGCG_LAUNCH_CHECK();
+        MGCG_CUDA(cudaMemcpyAsync(&row1, d_end, sizeof(int), cudaMemcpyDeviceToHost, st));
+        MGCG_CUDA(cudaMemcpyAsync(&count, d_cnt, sizeof(long long), cudaMemcpyDeviceToHost, st));
+        MGCG_CUDA(cudaStreamSynchronize(st));
+        u64 *keys = nullptr; double *vals = nullptr;
+        MGCG_CHECK(dalloc(&keys, (size_t)count)); MGCG_CHECK(dalloc(&vals, (size_t)count));
+        if (count > 0) {
+            k_spgemm_expand<<<grid_for(row1 - row0, 128), 128, 0, st>>>(A, B, off, row0, row1, keys, vals);
+            MGCG_LAUNCH_CHECK();
+        }
+        DevCsr part;
+        MGCG_CHECK(coo_to_csr_sum(c, row1 - row0, B.cols, (size_t)count, keys, vals, &part));
+        cudaFree(keys); cudaFree(vals);
+        parts.push_back(part); part_row0.push_back(row0);
+        row0 = row1;
+    }
+    cudaFree(off); cudaFree(d_end); cudaFree(d_cnt);
+    // concatenate
+    if (parts.size() == 1) { *C = parts[0]; C->rows = A.rows; C->cols = B.cols; return MGCG_OK; }
+    long long total = 0;
+    for (auto &p : parts) total += p.nnz;
+    if (total >= (1ll << 31)) { set_error("spgemm_esc: coarse operator exceeds int32 non-zeros"); return MGCG_ERR_UNSUPPORTED; }
+    C->rows = A.rows; C->cols = B.cols; C->nnz = (int)total;
+    MGCG_CHECK(dalloc(&C->val, (size_t)total)); MGCG_CHECK(dalloc(&C->col, (size_t)total));
+    MGCG_CHECK(dalloc(&C->rowptr, (size_t)A.rows + 1));
+    int nz0 = 0;
+    for (size_t i = 0; i < parts.size(); ++i) {
+        DevCsr &p = parts[i];
+        MGCG_CUDA(cudaMemcpyAsync(C->val + nz0, p.val, sizeof(double) * (size_t)p.nnz, cudaMemcpyDeviceToDevice, st));
+        MGCG_CUDA(cudaMemcpyAsync(C->col + nz0, p.col, sizeof(int) * (size_t)p.nnz, cudaMemcpyDeviceToDevice, st));
+        k_add_offset<<<grid_for(p.rows + 1), 256, 0, st>>>(p.rows + 1, p.rowptr, nz0);
+        MGCG_LAUNCH_CHECK();
+        MGCG_CUDA(cudaMemcpyAsync(C->rowptr + part_row0[i], p.rowptr, sizeof(int) * ((size_t)p.rows + 1), cudaMemcpyDeviceToDevice, st));
+        nz0 += p.nnz;
+    }
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    for (auto &p : parts) p.free_all();
+    return MGCG_OK;
+}
+
+__global__ void k_transpose_expand(Csr A, u64 *keys, double *vals)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x)
+        for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k) {
+            keys[k] = ((u64)(unsigned)A.col[k] << 32) | (unsigned)i;
+            vals[k] = A.val[k];
+        }
+}
+
+int csr_transpose(mgcg_ctx *c, const Csr &A, DevCsr *T)
+{
+    u64 *keys = nullptr; double *vals = nullptr;
+    MGCG_CHECK(dalloc(&keys, (size_t)A.nnz)); MGCG_CHECK(dalloc(&vals, (size_t)A.nnz));
+    k_transpose_expand<<<grid_for(A.rows), 256, 0, c->stream>>>(A, keys, vals);
+    MGCG_LAUNCH_CHECK();
+    int s = coo_to_csr_sum(c, A.cols, A.rows, (size_t)A.nnz, keys, vals, T);
+    cudaFree(keys); cudaFree(vals);
+    return s;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// dense coarsest level: M = A^-1 by in-place Gauss-Jordan, two launches per pivot
+__global__ void k_csr_to_dense(Csr A, double *M)
+{
+    const int n = A.rows;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k) M[(size_t)i * n + A.col[k]] = A.val[k];
+}
+__global__ void k_gj_pivot(int n, int k, const double *M, double *colk, double *rowk)
+{
+    const double p = M[(size_t)k * n + k];
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+        colk[j] = M[(size_t)j * n + k];
+        rowk[j] = (j == k) ? 1.0 / p : M[(size_t)k * n + j] / p;
+    }
+}
+__global__ void k_gj_update(int n, int k, double *M, const double *colk, const double *rowk)
+{
+    const long long nn = (long long)n * n;
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < nn; e += (long long)gridDim.x * blockDim.x) {
+        const int i = (int)(e / n), j = (int)(e % n);
+        double v;
+        if (i == k) v = rowk[j];
+        else if (j == k) v = -__dmul_rn(colk[i], rowk[k]);
+        else v = __dadd_rn(M[e], -__dmul_rn(colk[i], rowk[j]));
+        M[e] = v;
+    }
+}
+
+static int dense_inverse(mgcg_ctx *c, const Csr &A, double **Minv)
+{
+    const int n = A.rows;
+    cudaStream_t st = c->stream;
+    double *M = nullptr, *colk = nullptr, *rowk = nullptr;
+    MGCG_CHECK(dalloc(&M, (size_t)n * n)); MGCG_CHECK(dalloc(&colk, (size_t)n)); MGCG_CHECK(dalloc(&rowk, (size_t)n));
+    MGCG_CUDA(cudaMemsetAsync(M, 0, sizeof(double) * (size_t)n * n, st));
+    k_csr_to_dense<<<grid_for(n), 256, 0, st>>>(A, M);
+    MGCG_LAUNCH_CHECK();
+    for (int k = 0; k < n; ++k) {
+        k_gj_pivot<<<grid_for(n), 256, 0, st>>>(n, k, M, colk, rowk);
+        k_gj_update<<<grid_for((long long)n * n), 256, 0, st>>>(n, k, M, colk, rowk);
+    }
+    MGCG_LAUNCH_CHECK();
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    cudaFree(colk); cudaFree(rowk);
+    *Minv = M;
+    return MGCG_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+static int alloc_level_vectors(MgLevel &L, bool level0)
+{
+    const size_t n = (size_t)L.A.rows;
+    MGCG_CHECK(dalloc(&L.xa, n)); MGCG_CHECK(dalloc(&L.xb, n)); MGCG_CHECK(dalloc(&L.r, n));
+    if (!level0) MGCG_CHECK(dalloc(&L.b, n));
+    return MGCG_OK;
+}
+
+void mg_free(mgcg_ctx *c)
+{
+    if (!c->mg) return;
+    Hierarchy *H = c->mg;
+    for (size_t l = 0; l < H->L.size(); ++l) {
+        MgLevel &L = H->L[l];
+        L.Aown.free_all(); L.P.free_all(); L.R.free_all();
+        if (L.agg) cudaFree(L.agg);
+        if (L.dinv) cudaFree(L.dinv);
+        if (L.xa) cudaFree(L.xa);
+        if (L.xb) cudaFree(L.xb);
+        if (L.r) cudaFree(L.r);
+        if (l > 0 && L.b) cudaFree(L.b);
+    }
+    if (H->coarse_inv) cudaFree(H->coarse_inv);
+    delete H;
+    c->mg = nullptr;
+}
+
+int mg_build(mgcg_ctx *c)
+{
+    mg_free(c);
+    const mgcg_options &o = c->opt;
+    if (o.mg_pre_sweeps < 1 || o.mg_post_sweeps < 0) { set_error("mg_build: mg_pre_sweeps must be >= 1, mg_post_sweeps >= 0"); return MGCG_ERR_INVALID; }
+    if (o.mg_smoother != MGCG_SMOOTHER_JACOBI) { set_error("mg_build: only the weighted-Jacobi smoother is implemented"); return MGCG_ERR_UNSUPPORTED; }
+    cudaStream_t st = c->stream;
+    Hierarchy *H = new Hierarchy();
+    c->mg = H;
+    const int max_levels = o.mg_max_levels > 0 ? o.mg_max_levels : 12;
+    const int coarse_size = o.mg_coarse_size > 0 ? o.mg_coarse_size : 512;
+    const bool hint = (o.nx > 0 && o.ny > 0 && o.nz > 0 && (long long)o.nx * o.ny * o.nz == c->A.rows);
+
+    MgLevel L0;
+    L0.A = c->A;
+    L0.planA = c->planA;
+    L0.dims[0] = hint ? o.nx : 0; L0.dims[1] = hint ? o.ny : 0; L0.dims[2] = hint ? o.nz : 0;
+    H->L.push_back(L0);
+    double nnz_sum = (double)c->A.nnz;
+
+    for (int l = 0;; ++l) {
+        MgLevel &L = H->L[l];
+        const int n = L.A.rows;
+        MGCG_CHECK(dalloc(&L.dinv, (size_t)n));
+        k_extract_dinv<<<grid_for(n), 256, 0, st>>>(L.A, L.dinv);
+        MGCG_LAUNCH_CHECK();
+        MGCG_CHECK(alloc_level_vectors(L, l == 0));
+        if (n <= coarse_size || l + 1 >= max_levels) break;
+
+        // ---- aggregates
+        int nc;
+        int cd[3] = {0, 0, 0};
+        MGCG_CHECK(dalloc(&L.agg, (size_t)n));
+        if (L.dims[0] > 0) {
+            cd[0] = (L.dims[0] + 1) / 2; cd[1] = (L.dims[1] + 1) / 2; cd[2] = (L.dims[2] + 1) / 2;
+            nc = cd[0] * cd[1] * cd[2];
+            k_agg_geometric<<<grid_for(n), 256, 0, st>>>(L.dims[0], L.dims[1], L.dims[2], cd[0], cd[1], L.agg);
+        } else {
+            nc = (n + 7) / 8;
+            k_agg_blocks<<<grid_for(n), 256, 0, st>>>(n, 8, L.agg);
+        }
+        MGCG_LAUNCH_CHECK();
+        if (nc >= n) break;   // cannot coarsen further
+
+        // ---- prolongator
+        if (!o.mg_smoothed) {
+            L.P.rows = n; L.P.cols = nc; L.P.nnz = n;
+            MGCG_CHECK(dalloc(&L.P.val, (size_t)n)); MGCG_CHECK(dalloc(&L.P.col, (size_t)n)); MGCG_CHECK(dalloc(&L.P.rowptr, (size_t)n + 1));
+            k_build_T<<<grid_for(n + 1), 256, 0, st>>>(n, L.agg, L.P.val, L.P.rowptr, L.P.col);
+            MGCG_LAUNCH_CHECK();
+        } else {
+            const size_t count = (size_t)L.A.nnz + n;
+            u64 *keys = nullptr; double *vals = nullptr;
+            MGCG_CHECK(dalloc(&keys, count)); MGCG_CHECK(dalloc(&vals, count));
+            k_expand_sa<<<grid_for(n), 256, 0, st>>>(L.A, L.agg, L.dinv, o.mg_prolong_omega, keys, vals);
+            MGCG_LAUNCH_CHECK();
+            int s = coo_to_csr_sum(c, n, nc, count, keys, vals, &L.P);
+            cudaFree(keys); cudaFree(vals);
+            MGCG_CHECK(s);
+        }
+        MGCG_CHECK(csr_transpose(c, L.P.view(), &L.R));
+
+        // ---- Galerkin coarse operator  A_c = R (A P)
+        DevCsr AP, Ac;
+        MGCG_CHECK(spgemm_esc(c, L.A, L.P.view(), &AP));
+        int s = spgemm_esc(c, L.R.view(), AP.view(), &Ac);
+        AP.free_all();
+        MGCG_CHECK(s);
+
+        L.planP = spmv_make_plan(c, L.P.rows, L.P.nnz, MGCG_SPMV_AUTO);
+        L.planR = spmv_make_plan(c, L.R.rows, L.R.nnz, MGCG_SPMV_AUTO);
+
+        MgLevel N;
+        N.Aown = Ac;
+        N.A = Ac.view();
+        N.planA = spmv_make_plan(c, Ac.rows, Ac.nnz, MGCG_SPMV_AUTO);
+        N.dims[0] = cd[0]; N.dims[1] = cd[1]; N.dims[2] = cd[2];
+        nnz_sum += (double)Ac.nnz;
+        H->L.push_back(N);   // invalidates L
+    }
+    // ---- coarsest level: dense inverse
+    MgLevel &Lc = H->L.back();
+    if (Lc.A.rows > 4096) { set_error("mg_build: coarsest level has %d rows (> 4096): raise mg_max_levels", Lc.A.rows); return MGCG_ERR_UNSUPPORTED; }
+    H->coarse_n = Lc.A.rows;
+    MGCG_CHECK(dense_inverse(c, Lc.A, &H->coarse_inv));
+    H->op_complexity = nnz_sum / (double)(c->A.nnz > 0 ? c->A.nnz : 1);
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    return MGCG_OK;
+}
+
+double *mg_level0_first_x(mgcg_ctx *c) { return c->mg ? c->mg->L[0].xa : nullptr; }
+const double *mg_level0_dinv(mgcg_ctx *c) { return c->mg ? c->mg->L[0].dinv : nullptr; }
+
+}  // namespace mgcg
+
+// ---------------------------------------------------------------------------------------------------------
+// introspection exports (tests: hierarchy parity against the CPU twin)
+using namespace mgcg;
+
+extern "C" int mgcg_mg_levels(mgcg_ctx *c) { return (c && c->mg) ? (int)c->mg->L.size() : 1; }
+
+extern "C" int mgcg_mg_level_size(mgcg_ctx *c, int level, int *rows, int *nnz)
+{
+    if (!c || !c->mg || level < 0 || level >= (int)c->mg->L.size()) { set_error("mgcg_mg_level_size: no such level"); return MGCG_ERR_INVALID; }
+    *rows = c->mg->L[level].A.rows; *nnz = c->mg->L[level].A.nnz;
+    return MGCG_OK;
+}
+
+extern "C" int mgcg_mg_level_get(mgcg_ctx *c, int level, double *elements, int *row_offsets, int *column_indeces)
+{
+    if (!c || !c->mg || level < 0 || level >= (int)c->mg->L.size()) { set_error("mgcg_mg_level_get: no such level"); return MGCG_ERR_INVALID; }
+    const Csr &A = c->mg->L[level].A;
+    MGCG_CUDA(cudaSetDevice(c->device));
+    MGCG_CUDA(cudaMemcpy(elements, A.val, sizeof(double) * (size_t)A.nnz, cudaMemcpyDeviceToHost));
+    MGCG_CUDA(cudaMemcpy(column_indeces, A.col, sizeof(int) * (size_t)A.nnz, cudaMemcpyDeviceToHost));
+    MGCG_CUDA(cudaMemcpy(row_offsets, A.rowptr, sizeof(int) * ((size_t)A.rows + 1), cudaMemcpyDeviceToHost));
+    return MGCG_OK;
+}
+
+extern "C" int mgcg_mg_level_aggregates(mgcg_ctx *c, int level, int *agg)
+{
+    if (!c || !c->mg || level < 0 || level + 1 >= (int)c->mg->L.size()) { set_error("mgcg_mg_level_aggregates: no such level"); return MGCG_ERR_INVALID; }
+    const MgLevel &L = c->mg->L[level];
+    MGCG_CUDA(cudaSetDevice(c->device));
+    MGCG_CUDA(cudaMemcpy(agg, L.agg, sizeof(int) * (size_t)L.A.rows, cudaMemcpyDeviceToHost));
+    return MGCG_OK;
+}

@@ -1,0 +1,157 @@
+/*
+ * mgcg.h — C ABI of the B200-native multigrid-preconditioned conjugate-gradient library (libMgcgGpu.so).
+ *
+ * Two groups of entry points:
+ *   (A) mgcg_*  : the native API (status codes, options struct, device- and host-pointer solves,
+ *                 one-process-per-GPU sharded solve).
+ *   (B) the 32 export names of the reference's MgcgGpu.dll with the reference's argument lists, so the C#
+ *       P/Invoke bindings (or any other FFI) of aokomoriuta/ConjugateGradient bind unchanged.
+ *       See mgcg_compat.h.
+ * Plain pointers and sizes only; no C++/torch/thrust types cross this boundary.
+ * Citations are file:line under the reference tree (/root/reference).
+ */
+#ifndef MGCG_H
+#define MGCG_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MGCG_VERSION 100
+
+/* ---- status codes (the reference reports no errors at all: every CUDA/cuBLAS/cuSPARSE status is dropped,
+ *      Runtime.cu:23,37, Mgcg.cu:17; only the C# side throws on Iteration > MaxIteration, ConjugateGradient.cs:70-74) */
+enum {
+    MGCG_OK = 0,
+    MGCG_ERR_INVALID = 1,        /* bad argument / not set up */
+    MGCG_ERR_CUDA = 2,           /* CUDA runtime failure (see mgcg_last_error) */
+    MGCG_ERR_NOT_CONVERGED = 3,  /* iteration index exceeded max_iteration (== the C# ApplicationException) */
+    MGCG_ERR_BREAKDOWN = 4,      /* p.Ap <= 0 or NaN: matrix not SPD / preconditioner not SPD */
+    MGCG_ERR_COMM = 5,           /* NCCL failure */
+    MGCG_ERR_UNSUPPORTED = 6
+};
+
+/* ---- stop rule */
+enum {
+    MGCG_NORM_ABS_L2 = 0,    /* sqrt(r.r) < tol      — ConjugateGradientCpu.cs:77, Mgcg.cu:251-252, SimpleConjugateGradient.cu:106-107 */
+    MGCG_NORM_ABS_LINF = 1,  /* max|r_i| < tol       — Mgcg/HandmadeCL/MgcgCL/ConjugateGradientSingleGpu.cs:268 */
+    MGCG_NORM_REL_L2 = 2     /* r.r / r0.r0 < tol^2  — Mgcg/ViennaCL/Mgcg/ComputerCpu.cpp:82 */
+};
+
+enum { MGCG_PRECOND_NONE = 0, MGCG_PRECOND_MG = 1 };
+enum { MGCG_SMOOTHER_JACOBI = 0, MGCG_SMOOTHER_RBGS = 1 };
+enum { MGCG_SPMV_AUTO = 0, MGCG_SPMV_STREAM = 1, MGCG_SPMV_VECTOR = 2 };
+
+typedef struct mgcg_options {
+    /* CG control — same meaning as the reference's ctor arguments (ConjugateGradient.cs:41-50) */
+    double tolerance;        /* AllowableResidual */
+    int    min_iteration;    /* MinIteration */
+    int    max_iteration;    /* MaxIteration (honoured natively; the reference's native loops ignore it, Mgcg.cu:234) */
+    int    norm;             /* MGCG_NORM_* */
+    int    min_strict;       /* 1: `min < iteration` (SimpleConjugateGradient.cu:107); 0: `min <= iteration` (Mgcg.cu:252) */
+    /* preconditioner */
+    int    precond;          /* MGCG_PRECOND_* */
+    int    nx, ny, nz;       /* optional structured-grid hint (0 = none): rows are idx = x + nx*(y + ny*z) */
+    int    mg_max_levels;    /* default 12 */
+    int    mg_coarse_size;   /* stop coarsening at <= this many rows; dense inverse there (default 512) */
+    int    mg_pre_sweeps;    /* default 1 */
+    int    mg_post_sweeps;   /* default 1 (keep == pre for an SPD preconditioner) */
+    double mg_omega;         /* Jacobi damping, default 0.8 */
+    int    mg_smoother;      /* MGCG_SMOOTHER_* */
+    int    mg_smoothed;      /* 1: smoothed-aggregation prolongator P=(I-w D^-1 A)T; 0: plain aggregation */
+    double mg_prolong_omega; /* default 2/3 */
+    /* execution */
+    int    spmv_kernel;      /* MGCG_SPMV_* */
+    int    check_interval;   /* host polls the device-side convergence flag every this many iterations (default 8) */
+    int    use_graph;        /* 1: capture one iteration into a CUDA graph and replay it */
+    int    profile;          /* 1: time the fine-level SpMV launches with CUDA events (disables the graph) */
+    int    reserved[8];
+} mgcg_options;
+
+typedef struct mgcg_result {
+    int    status;           /* MGCG_OK / MGCG_ERR_* */
+    int    iteration;        /* 0-based index of the converging iteration == C# `Iteration` (ConjugateGradientCpu.cs:60) */
+    int    iterations_done;  /* iteration + 1 == what the reference's native Solve reports (Mgcg.cu:234) */
+    double residual;         /* the stop rule's measure at exit: sqrt(r.r), max|r|, or sqrt(r.r/r0.r0) */
+    double rr;               /* final r.r */
+    double rr0;              /* initial r.r */
+    float  setup_ms;         /* hierarchy / plan construction (device time) */
+    float  solve_ms;         /* CG loop (device time, CUDA events on the solve stream) */
+    int    levels;           /* multigrid levels (1 = none) */
+    int    kernel_launches;  /* kernels of this library launched inside the solve */
+    float  spmv_ms_total;    /* profile=1: summed device time of the fine-level SpMV(+dot) launches */
+    int    spmv_launches;    /* profile=1: how many of them */
+    double operator_complexity; /* sum_l nnz_l / nnz_0 */
+    int    reserved[6];
+} mgcg_result;
+
+typedef struct mgcg_ctx mgcg_ctx;
+
+/* ---- lifetime */
+int         mgcg_version(void);
+const char *mgcg_last_error(void);                 /* thread-local message of the last failing call */
+void        mgcg_options_default(mgcg_options *o); /* reference-parity defaults: ABS_L2, non-strict, no preconditioner */
+mgcg_ctx   *mgcg_create(int device);               /* replaces CreateBlas/CreateSparse/CreateMatDescr (Runtime.cu:20-62) */
+void        mgcg_destroy(mgcg_ctx *c);
+int         mgcg_set_stream(mgcg_ctx *c, void *cuda_stream); /* run on the caller's stream (cudaStream_t) */
+
+/* ---- solver on DEVICE pointers: replaces Solve (Mgcg.cu:201-270) and SolveGpu (SimpleConjugateGradient.cu:12-126).
+ * setup analyses the matrix (SpMV plan, multigrid hierarchy built on the device); the CSR arrays are NOT copied and
+ * must stay valid until the next setup / destroy.  solve: x holds the initial guess on entry (Mgcg.cu:225). */
+int mgcg_setup(mgcg_ctx *c, int count, int elements_count,
+               const double *d_elements, const int *d_row_offsets, const int *d_column_indeces,
+               const mgcg_options *opt);
+int mgcg_solve(mgcg_ctx *c, const double *d_b, double *d_x, mgcg_result *res);
+
+/* ---- solver on HOST pointers: upload + setup + solve + download in one call (the end-to-end path) */
+int mgcg_solve_host(mgcg_ctx *c, int count, int elements_count,
+                    const double *elements, const int *row_offsets, const int *column_indeces,
+                    const double *b, double *x, const mgcg_options *opt, mgcg_result *res);
+
+/* ---- individual kernels on device pointers (tests, benches, and building blocks of the compat exports) */
+/* y = alpha*A*x + beta*y, rectangular rows x cols — replaces CsrMV (Mgcg.cu:10-19) */
+int mgcg_spmv(mgcg_ctx *c, int rows, int cols, int elements_count,
+              const double *d_elements, const int *d_row_offsets, const int *d_column_indeces,
+              const double *d_x, double *d_y, double alpha, double beta, int kernel);
+/* y = A*x and *d_dot = sum_i w_i*y_i in one launch (fused p.Ap epilogue); deterministic */
+int mgcg_spmv_dot(mgcg_ctx *c, int rows, int cols, int elements_count,
+                  const double *d_elements, const int *d_row_offsets, const int *d_column_indeces,
+                  const double *d_x, double *d_y, const double *d_w, double *d_dot, int kernel);
+/* deterministic fixed-order dot / max|.| ; result to a device scalar and (if host_out != NULL) to the host */
+int mgcg_dot(mgcg_ctx *c, int n, const double *d_a, const double *d_b, double *d_out, double *host_out);
+int mgcg_max_abs(mgcg_ctx *c, int n, const double *d_a, double *d_out, double *host_out);
+int mgcg_axpy(mgcg_ctx *c, int n, double alpha, const double *d_x, double *d_y);  /* y += alpha x */
+int mgcg_scal(mgcg_ctx *c, int n, double alpha, double *d_x);
+int mgcg_copy(mgcg_ctx *c, int n, const double *d_x, double *d_y);
+/* fused CG updates (replace Solve2 / Solve3 bodies, Mgcg.cu:181-183,197) */
+int mgcg_update_xr(mgcg_ctx *c, int n, double alpha, const double *d_p, const double *d_Ap,
+                   double *d_x, double *d_r, double *d_rr, double *host_rr);
+int mgcg_update_p(mgcg_ctx *c, int n, double beta, const double *d_r, double *d_p);
+
+/* ---- multigrid introspection (tests: hierarchy parity against the CPU twin) */
+int mgcg_mg_levels(mgcg_ctx *c);
+int mgcg_mg_level_size(mgcg_ctx *c, int level, int *rows, int *nnz);
+/* copy level `level`'s operator (CSR) to host arrays sized by mgcg_mg_level_size */
+int mgcg_mg_level_get(mgcg_ctx *c, int level, double *elements, int *row_offsets, int *column_indeces);
+/* copy the fine->coarse aggregate map of `level` (rows entries) */
+int mgcg_mg_level_aggregates(mgcg_ctx *c, int level, int *agg);
+/* z = M r : one V-cycle applied to a device vector */
+int mgcg_mg_apply(mgcg_ctx *c, const double *d_r, double *d_z);
+
+/* ---- row-block partition rule of the reference (bit-exact): ConjugateGradientParallelGpu.cs:271-277 */
+int mgcg_partition_offsets(int count, int device_count, int *offsets /* [device_count+1] */);
+
+/* ---- one-process-per-GPU sharded solve (replaces the host-threaded ConjugateGradientParallelGpu.Solve,
+ *      cs:424-565): each rank owns rows [row_offset, row_offset+local_count); column indices are GLOBAL;
+ *      local row offsets are rebased to 0 (Mgcg.cu:73).  Halo exchange of p and the scalar reductions go over NCCL. */
+int mgcg_comm_unique_id(void *out128);             /* rank 0: 128-byte NCCL id to broadcast out of band */
+int mgcg_comm_init(mgcg_ctx *c, const void *id128, int rank, int world);
+int mgcg_setup_dist(mgcg_ctx *c, int global_count, int row_offset, int local_count, int local_elements_count,
+                    const double *d_elements, const int *d_row_offsets, const int *d_column_indeces,
+                    const mgcg_options *opt);
+int mgcg_solve_dist(mgcg_ctx *c, const double *d_b_local, double *d_x_local, mgcg_result *res);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MGCG_H */

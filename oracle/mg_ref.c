@@ -1,0 +1,318 @@
+/*
+ * oracle/mg_ref.c — TEST INFRASTRUCTURE ONLY: CPU twin of the multigrid-preconditioned CG.
+ *
+ * PARITY UNPINNED: the reference contains NO multigrid and no preconditioner (SURVEY.md F1 — "Mgcg" appears only
+ * in two doc-comments, Mgcg/cuBlas/Mgcg/MgcgMain.cs:8; the planned `p_0 = (LDLr)_0` of
+ * Mgcg/HandmadeCL/MgcgCL/ConjugateGradientCpu.cs:51 was never written).  There is no reference output to pin this
+ * file against.  It is a sequential restatement of the SAME algorithm the CUDA path runs (aggregation, prolongator
+ * smoothing, Galerkin products with ordered summation, Gauss-Jordan coarse inverse, V-cycle, PCG in the operation
+ * order of ConjugateGradientCpu.cs:45-98 with z = M r inserted), cross-checked in tests against the unpreconditioned
+ * oracle (cg_ref.c) and scipy direct solves.  Compile with -ffp-contract=off.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+void ref_spmv(int rows, const double *elements, const int *row_offsets, const int *column_indeces, const double *vector, double *answer);
+double ref_dot(int n, const double *left, const double *right);
+double ref_max_absolute(int n, const double *v);
+
+typedef struct { int rows, cols, nnz; double *val; int *rowptr; int *col; } csr_t;
+typedef struct {
+    csr_t A, P, R;
+    int *agg;
+    double *dinv, *x, *x2, *b, *r;
+    int dims[3];
+    int ownA;
+} level_t;
+typedef struct { int nl; level_t *L; double *coarse_inv; int coarse_n; } mg_ref_t;
+
+static void csr_free(csr_t *m) { free(m->val); free(m->rowptr); free(m->col); memset(m, 0, sizeof(*m)); }
+
+typedef struct { int col; int ord; double v; } ent_t;
+static int ent_cmp(const void *a, const void *b)
+{
+    const ent_t *x = (const ent_t *)a, *y = (const ent_t *)b;
+    if (x->col != y->col) return x->col < y->col ? -1 : 1;
+    return x->ord < y->ord ? -1 : (x->ord > y->ord);
+}
+
+/* growable CSR builder: append one row given its entries in EXPANSION order; duplicates (same col) are summed
+ * sequentially in that order after a stable sort by col == the device's stable radix sort + ordered segment sum */
+typedef struct { csr_t m; size_t cap; } builder_t;
+static void b_init(builder_t *b, int rows, int cols)
+{
+    memset(b, 0, sizeof(*b));
+    b->m.rows = rows; b->m.cols = cols;
+    b->m.rowptr = (int *)calloc((size_t)rows + 1, sizeof(int));
+    b->cap = 1024;
+    b->m.val = (double *)malloc(b->cap * sizeof(double));
+    b->m.col = (int *)malloc(b->cap * sizeof(int));
+}
+static void b_row(builder_t *b, int row, ent_t *e, int cnt)
+{
+    for (int i = 0; i < cnt; i++) e[i].ord = i;
+    qsort(e, (size_t)cnt, sizeof(ent_t), ent_cmp);
+    int i = 0;
+    while (i < cnt) {
+        double s = e[i].v;
+        int j = i + 1;
+        while (j < cnt && e[j].col == e[i].col) { s = s + e[j].v; j++; }
+        if ((size_t)b->m.nnz + 1 > b->cap) {
+            b->cap *= 2;
+            b->m.val = (double *)realloc(b->m.val, b->cap * sizeof(double));
+            b->m.col = (int *)realloc(b->m.col, b->cap * sizeof(int));
+        }
+        b->m.val[b->m.nnz] = s; b->m.col[b->m.nnz] = e[i].col; b->m.nnz++;
+        i = j;
+    }
+    b->m.rowptr[row + 1] = b->m.nnz;
+}
+
+/* C = A*B, expansion order: A's entries of the row in storage order, each times B's row in storage order */
+static csr_t spgemm(const csr_t *A, const csr_t *B)
+{
+    builder_t bd; b_init(&bd, A->rows, B->cols);
+    size_t cap = 256; ent_t *e = (ent_t *)malloc(cap * sizeof(ent_t));
+    for (int i = 0; i < A->rows; i++) {
+        int cnt = 0;
+        for (int k = A->rowptr[i]; k < A->rowptr[i + 1]; k++) {
+            int j = A->col[k]; double a = A->val[k];
+            for (int q = B->rowptr[j]; q < B->rowptr[j + 1]; q++) {
+                if ((size_t)cnt + 1 > cap) { cap *= 2; e = (ent_t *)realloc(e, cap * sizeof(ent_t)); }
+                e[cnt].col = B->col[q]; e[cnt].v = a * B->val[q]; cnt++;
+            }
+        }
+        b_row(&bd, i, e, cnt);
+    }
+    free(e);
+    return bd.m;
+}
+
+/* T = A^T; within a row of T entries are in ascending original-row order (== sort by (col,row)) */
+static csr_t transpose(const csr_t *A)
+{
+    csr_t T; T.rows = A->cols; T.cols = A->rows; T.nnz = A->nnz;
+    T.rowptr = (int *)calloc((size_t)T.rows + 1, sizeof(int));
+    T.val = (double *)malloc(sizeof(double) * (size_t)(A->nnz > 0 ? A->nnz : 1));
+    T.col = (int *)malloc(sizeof(int) * (size_t)(A->nnz > 0 ? A->nnz : 1));
+    for (int k = 0; k < A->nnz; k++) T.rowptr[A->col[k] + 1]++;
+    for (int i = 0; i < T.rows; i++) T.rowptr[i + 1] += T.rowptr[i];
+    int *fill = (int *)malloc(sizeof(int) * (size_t)(T.rows > 0 ? T.rows : 1));
+    memcpy(fill, T.rowptr, sizeof(int) * (size_t)T.rows);
+    for (int i = 0; i < A->rows; i++)
+        for (int k = A->rowptr[i]; k < A->rowptr[i + 1]; k++) { int p = fill[A->col[k]]++; T.col[p] = i; T.val[p] = A->val[k]; }
+    free(fill);
+    return T;
+}
+
+/* in-place Gauss-Jordan inverse, same update formulas and order as k_gj_pivot / k_gj_update */
+static double *dense_inverse(const csr_t *A)
+{
+    int n = A->rows;
+    double *M = (double *)calloc((size_t)n * n, sizeof(double));
+    double *colk = (double *)malloc(sizeof(double) * (size_t)n), *rowk = (double *)malloc(sizeof(double) * (size_t)n);
+    for (int i = 0; i < n; i++) for (int k = A->rowptr[i]; k < A->rowptr[i + 1]; k++) M[(size_t)i * n + A->col[k]] = A->val[k];
+    for (int k = 0; k < n; k++) {
+        double p = M[(size_t)k * n + k];
+        for (int j = 0; j < n; j++) { colk[j] = M[(size_t)j * n + k]; rowk[j] = (j == k) ? 1.0 / p : M[(size_t)k * n + j] / p; }
+        for (int i = 0; i < n; i++)
+            for (int j = 0; j < n; j++) {
+                double v;
+                if (i == k) v = rowk[j];
+                else if (j == k) v = -(colk[i] * rowk[k]);
+                else v = M[(size_t)i * n + j] + (-(colk[i] * rowk[j]));
+                M[(size_t)i * n + j] = v;
+            }
+    }
+    free(colk); free(rowk);
+    return M;
+}
+
+static void level_vectors(level_t *L)
+{
+    size_t n = (size_t)L->A.rows;
+    L->x = (double *)calloc(n, sizeof(double)); L->x2 = (double *)calloc(n, sizeof(double));
+    L->b = (double *)calloc(n, sizeof(double)); L->r = (double *)calloc(n, sizeof(double));
+    L->dinv = (double *)malloc(n * sizeof(double));
+    for (int i = 0; i < L->A.rows; i++) {
+        double d = 1.0;
+        for (int k = L->A.rowptr[i]; k < L->A.rowptr[i + 1]; k++) if (L->A.col[k] == i) { d = L->A.val[k]; break; }
+        L->dinv[i] = 1.0 / d;
+    }
+}
+
+mg_ref_t *mg_ref_build(int n, int nnz, const double *val, const int *rowptr, const int *col,
+                       int nx, int ny, int nz, int max_levels, int coarse_size, int smoothed, double prolong_omega)
+{
+    mg_ref_t *H = (mg_ref_t *)calloc(1, sizeof(mg_ref_t));
+    if (max_levels <= 0) max_levels = 12;
+    if (coarse_size <= 0) coarse_size = 512;
+    H->L = (level_t *)calloc((size_t)max_levels + 1, sizeof(level_t));
+    level_t *L0 = &H->L[0];
+    L0->A.rows = n; L0->A.cols = n; L0->A.nnz = nnz;
+    L0->A.val = (double *)val; L0->A.rowptr = (int *)rowptr; L0->A.col = (int *)col; L0->ownA = 0;
+    int hint = (nx > 0 && ny > 0 && nz > 0 && (long long)nx * ny * nz == n);
+    L0->dims[0] = hint ? nx : 0; L0->dims[1] = hint ? ny : 0; L0->dims[2] = hint ? nz : 0;
+    H->nl = 1;
+    for (int l = 0;; l++) {
+        level_t *L = &H->L[l];
+        int m = L->A.rows;
+        level_vectors(L);
+        if (m <= coarse_size || l + 1 >= max_levels) break;
+        int nc, cd[3] = {0, 0, 0};
+        L->agg = (int *)malloc(sizeof(int) * (size_t)m);
+        if (L->dims[0] > 0) {
+            cd[0] = (L->dims[0] + 1) / 2; cd[1] = (L->dims[1] + 1) / 2; cd[2] = (L->dims[2] + 1) / 2;
+            nc = cd[0] * cd[1] * cd[2];
+            for (int i = 0; i < m; i++) {
+                int x = i % L->dims[0], y = (i / L->dims[0]) % L->dims[1], z = i / (L->dims[0] * L->dims[1]);
+                L->agg[i] = (x >> 1) + cd[0] * ((y >> 1) + cd[1] * (z >> 1));
+            }
+        } else {
+            nc = (m + 7) / 8;
+            for (int i = 0; i < m; i++) L->agg[i] = i / 8;
+        }
+        if (nc >= m) break;
+        /* prolongator */
+        builder_t bp; b_init(&bp, m, nc);
+        size_t cap = 256; ent_t *e = (ent_t *)malloc(cap * sizeof(ent_t));
+        for (int i = 0; i < m; i++) {
+            int cnt = 0;
+            e[cnt].col = L->agg[i]; e[cnt].v = 1.0; cnt++;
+            if (smoothed) {
+                double f = -(prolong_omega * L->dinv[i]);
+                for (int k = L->A.rowptr[i]; k < L->A.rowptr[i + 1]; k++) {
+                    if ((size_t)cnt + 1 > cap) { cap *= 2; e = (ent_t *)realloc(e, cap * sizeof(ent_t)); }
+                    e[cnt].col = L->agg[L->A.col[k]]; e[cnt].v = f * L->A.val[k]; cnt++;
+                }
+            }
+            b_row(&bp, i, e, cnt);
+        }
+        free(e);
+        L->P = bp.m;
+        L->R = transpose(&L->P);
+        csr_t AP = spgemm(&L->A, &L->P);
+        csr_t Ac = spgemm(&L->R, &AP);
+        csr_free(&AP);
+        level_t *N = &H->L[l + 1];
+        N->A = Ac; N->ownA = 1;
+        N->dims[0] = cd[0]; N->dims[1] = cd[1]; N->dims[2] = cd[2];
+        H->nl = l + 2;
+    }
+    level_t *Lc = &H->L[H->nl - 1];
+    H->coarse_n = Lc->A.rows;
+    H->coarse_inv = dense_inverse(&Lc->A);
+    return H;
+}
+
+void mg_ref_free(mg_ref_t *H)
+{
+    if (!H) return;
+    for (int l = 0; l < H->nl; l++) {
+        level_t *L = &H->L[l];
+        if (L->ownA) csr_free(&L->A);
+        csr_free(&L->P); csr_free(&L->R);
+        free(L->agg); free(L->dinv); free(L->x); free(L->x2); free(L->b); free(L->r);
+    }
+    free(H->L); free(H->coarse_inv); free(H);
+}
+
+int mg_ref_levels(const mg_ref_t *H) { return H->nl; }
+void mg_ref_level_size(const mg_ref_t *H, int l, int *rows, int *nnz) { *rows = H->L[l].A.rows; *nnz = H->L[l].A.nnz; }
+void mg_ref_level_get(const mg_ref_t *H, int l, double *val, int *rowptr, int *col)
+{
+    const csr_t *A = &H->L[l].A;
+    memcpy(val, A->val, sizeof(double) * (size_t)A->nnz);
+    memcpy(col, A->col, sizeof(int) * (size_t)A->nnz);
+    memcpy(rowptr, A->rowptr, sizeof(int) * ((size_t)A->rows + 1));
+}
+void mg_ref_level_agg(const mg_ref_t *H, int l, int *agg) { memcpy(agg, H->L[l].agg, sizeof(int) * (size_t)H->L[l].A.rows); }
+
+static void jacobi_sweep(level_t *L, double omega)
+{
+    const csr_t *A = &L->A;
+    ref_spmv(A->rows, A->val, A->rowptr, A->col, L->x, L->x2);
+    for (int i = 0; i < A->rows; i++) L->x2[i] = L->x[i] + omega * L->dinv[i] * (L->b[i] - L->x2[i]);
+    double *t = L->x; L->x = L->x2; L->x2 = t;
+}
+
+/* z = M r : V(pre,post) with weighted Jacobi, zero initial guess, dense-inverse coarsest solve */
+void mg_ref_apply(mg_ref_t *H, int pre, int post, double omega, const double *r, double *z)
+{
+    int nl = H->nl;
+    memcpy(H->L[0].b, r, sizeof(double) * (size_t)H->L[0].A.rows);
+    for (int l = 0; l < nl - 1; l++) {
+        level_t *L = &H->L[l];
+        int m = L->A.rows;
+        for (int i = 0; i < m; i++) L->x[i] = omega * L->dinv[i] * L->b[i];
+        for (int s = 1; s < pre; s++) jacobi_sweep(L, omega);
+        ref_spmv(m, L->A.val, L->A.rowptr, L->A.col, L->x, L->r);
+        for (int i = 0; i < m; i++) L->r[i] = L->b[i] - L->r[i];
+        ref_spmv(L->R.rows, L->R.val, L->R.rowptr, L->R.col, L->r, H->L[l + 1].b);
+    }
+    {
+        level_t *L = &H->L[nl - 1];
+        int m = L->A.rows;
+        for (int i = 0; i < m; i++) {
+            double s = 0;
+            for (int j = 0; j < m; j++) s += H->coarse_inv[(size_t)i * m + j] * L->b[j];
+            L->x[i] = s;
+        }
+    }
+    for (int l = nl - 2; l >= 0; l--) {
+        level_t *L = &H->L[l];
+        int m = L->A.rows;
+        ref_spmv(m, L->P.val, L->P.rowptr, L->P.col, H->L[l + 1].x, L->x2);
+        for (int i = 0; i < m; i++) L->x[i] = 1.0 * L->x2[i] + 1.0 * L->x[i];
+        for (int s = 0; s < post; s++) jacobi_sweep(L, omega);
+    }
+    memcpy(z, H->L[0].x, sizeof(double) * (size_t)H->L[0].A.rows);
+}
+
+/* Preconditioned CG in the reference's operation order (ConjugateGradientCpu.cs:45-98) with z = M r:
+ *   alpha = rz/pAp ; x += alpha p ; r -= alpha Ap ; stop rule on r ; z = M r ; beta = rz'/rz ; p = z + beta p.
+ * norm: 0 abs-L2, 1 abs-Linf, 2 rel-L2 (see cg_ref.c).  Returns 0 ok / 3 max-iteration exceeded.          */
+int mg_ref_pcg(mg_ref_t *H, int pre, int post, double omega, const double *b, double *x,
+               double tol, int min_iteration, int max_iteration, int norm, int min_strict,
+               int *iteration, double *residual)
+{
+    const csr_t *A = &H->L[0].A;
+    int n = A->rows, status = 0, it;
+    double *r = (double *)malloc(sizeof(double) * (size_t)n), *z = (double *)malloc(sizeof(double) * (size_t)n);
+    double *p = (double *)malloc(sizeof(double) * (size_t)n), *Ap = (double *)malloc(sizeof(double) * (size_t)n);
+    ref_spmv(n, A->val, A->rowptr, A->col, x, Ap);
+    for (int i = 0; i < n; i++) r[i] = b[i] - Ap[i];
+    double rr0 = ref_dot(n, r, r);
+    mg_ref_apply(H, pre, post, omega, r, z);
+    memcpy(p, z, sizeof(double) * (size_t)n);
+    double rz = ref_dot(n, r, z);
+    for (it = 0;; it++) {
+        ref_spmv(n, A->val, A->rowptr, A->col, p, Ap);
+        double pAp = ref_dot(n, p, Ap);
+        double alpha = (rz == 0.0) ? 0.0 : rz / pAp;
+        for (int i = 0; i < n; i++) x[i] = x[i] + alpha * p[i];
+        for (int i = 0; i < n; i++) r[i] = r[i] + (-alpha) * Ap[i];
+        double rr = ref_dot(n, r, r), res;
+        int below;
+        if (norm == 0) { res = sqrt(rr); below = res < tol; }
+        else if (norm == 1) { res = ref_max_absolute(n, r); below = res < tol; }
+        else if (rr0 == 0.0) { res = 0; below = 1; }
+        else { res = sqrt(rr / rr0); below = (rr / rr0) < tol * tol; }
+        *residual = res;
+        int c;
+        if (min_strict) { if (it > max_iteration) c = -1; else c = (min_iteration < it) && below; }
+        else { if (it < min_iteration) c = 0; else if (it > max_iteration) c = -1; else c = below; }
+        if (c < 0) { status = 3; break; }
+        if (c) break;
+        mg_ref_apply(H, pre, post, omega, r, z);
+        double rzn = ref_dot(n, r, z);
+        double beta = (rz == 0.0) ? 0.0 : rzn / rz;
+        for (int i = 0; i < n; i++) p[i] = z[i] + beta * p[i];
+        rz = rzn;
+    }
+    *iteration = it;
+    free(r); free(z); free(p); free(Ap);
+    return status;
+}

@@ -115,3 +115,63 @@ def gen_banded_sin(n, max_nonzero=160):
     rp, b, x0 = np.zeros(n + 1, dtype=np.int32), np.zeros(n), np.zeros(n)
     nnz = lib().ref_gen_banded_sin(n, max_nonzero, val, col, rp, b, x0)
     return val[:nnz].copy(), rp, col[:nnz].copy(), b, x0
+
+
+# ---- multigrid CPU twin (oracle/mg_ref.c; parity unpinned: the reference has no multigrid) ------------------
+class MgRef:
+    def __init__(self, val, rowptr, col, nx=0, ny=0, nz=0, max_levels=12, coarse_size=512, smoothed=1, prolong_omega=2.0 / 3.0):
+        L = lib()
+        L.mg_ref_build.restype = C.c_void_p
+        L.mg_ref_build.argtypes = [C.c_int, C.c_int, c_dp, c_ip, c_ip, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double]
+        L.mg_ref_free.argtypes = [C.c_void_p]
+        L.mg_ref_levels.argtypes = [C.c_void_p]
+        L.mg_ref_level_size.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.mg_ref_level_get.argtypes = [C.c_void_p, C.c_int, c_dp, c_ip, c_ip]
+        L.mg_ref_level_agg.argtypes = [C.c_void_p, C.c_int, c_ip]
+        L.mg_ref_apply.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, c_dp, c_dp]
+        L.mg_ref_pcg.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, c_dp, c_dp, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int,
+                                 C.POINTER(C.c_int), C.POINTER(C.c_double)]
+        self._keep = (np.ascontiguousarray(val, dtype=np.float64), np.ascontiguousarray(rowptr, dtype=np.int32),
+                      np.ascontiguousarray(col, dtype=np.int32))
+        self.n = len(rowptr) - 1
+        self.h = L.mg_ref_build(self.n, len(val), *self._keep, nx, ny, nz, max_levels, coarse_size, smoothed, prolong_omega)
+
+    def levels(self):
+        return lib().mg_ref_levels(self.h)
+
+    def level(self, l):
+        rows, nnz = C.c_int(), C.c_int()
+        lib().mg_ref_level_size(self.h, l, C.byref(rows), C.byref(nnz))
+        val, rp, col = np.empty(nnz.value), np.empty(rows.value + 1, dtype=np.int32), np.empty(nnz.value, dtype=np.int32)
+        lib().mg_ref_level_get(self.h, l, val, rp, col)
+        return val, rp, col
+
+    def aggregates(self, l):
+        rows, nnz = C.c_int(), C.c_int()
+        lib().mg_ref_level_size(self.h, l, C.byref(rows), C.byref(nnz))
+        agg = np.empty(rows.value, dtype=np.int32)
+        lib().mg_ref_level_agg(self.h, l, agg)
+        return agg
+
+    def apply(self, r, pre=1, post=1, omega=0.8):
+        z = np.empty(self.n)
+        lib().mg_ref_apply(self.h, pre, post, omega, np.ascontiguousarray(r, dtype=np.float64), z)
+        return z
+
+    def pcg(self, b, x0=None, tol=1e-8, min_iteration=0, max_iteration=None, norm=NORM_ABS_L2, min_strict=False, pre=1, post=1, omega=0.8):
+        x = np.zeros(self.n) if x0 is None else np.array(x0, dtype=np.float64, copy=True)
+        it, res = C.c_int(0), C.c_double(0)
+        st = lib().mg_ref_pcg(self.h, pre, post, omega, np.ascontiguousarray(b, dtype=np.float64), x, tol, min_iteration,
+                              self.n if max_iteration is None else max_iteration, norm, int(min_strict), C.byref(it), C.byref(res))
+        return x, it.value, res.value, st
+
+    def close(self):
+        if self.h:
+            lib().mg_ref_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

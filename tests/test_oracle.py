@@ -1,0 +1,113 @@
+"""CPU oracle (oracle/cg_ref.c) against the known answers derivable from the reference's own inputs.
+The reference ships no golden vectors; these are its generators + a direct solve (the R/CG.R:34 idea)."""
+import json
+import os
+
+import numpy as np
+import scipy.sparse as sp
+import scipy.sparse.linalg as spl
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def test_tridiag10_known_answer(oracle):
+    # SimpleConjugateGradientCpu.cpp's N=10 input, solved to 1e-8 with the strict min-iteration rule of the .cu
+    v, rp, c, b = oracle.gen_tridiag121(10)
+    x, it, res, st = oracle.cg_solve(v, rp, c, b, tol=1e-8, min_strict=True)
+    assert st == oracle.OK and it == 9
+    A = sp.csr_matrix((v, c, rp)).toarray()
+    np.testing.assert_allclose(x, np.linalg.solve(A, b), rtol=1e-12)
+    gold = json.load(open(os.path.join(GOLD, "tridiag10.json")))
+    np.testing.assert_allclose(x, gold["x"], rtol=1e-6)       # the 7-digit values recorded in SURVEY.md §8c
+    assert it == gold["iteration_index"]
+
+
+def test_tridiag_int_wrap(oracle, gen):
+    # b[i] = (int32)(i*i) * 0.5 wraps negative from i = 46341 (SimpleConjugateGradient.cu:196)
+    v, rp, c, b = oracle.gen_tridiag121(46400)
+    assert b[46340] == 46340 * 46340 * 0.5 and b[46341] < 0
+    v2, rp2, c2, b2 = gen.tridiag121(46400)
+    assert np.array_equal(v, v2) and np.array_equal(rp, rp2) and np.array_equal(c, c2) and np.array_equal(b, b2)
+
+
+def test_banded_sin_known_answer(oracle, gen):
+    v, rp, c, b, x0 = oracle.gen_banded_sin(2000, 160)
+    g = gen.banded_sin(2000, 160)
+    for a, bb in zip((v, rp, c, b, x0), g):
+        assert np.array_equal(a, bb)
+    assert np.all(c[rp[:-1]] == np.arange(2000))               # diagonal stored first (MgcgMain.cs:59-60)
+    x, it, res, st = oracle.cg_solve(v, rp, c, b, x0, tol=1e-8)
+    assert st == oracle.OK and it == 26                        # SURVEY.md §8c case (2)
+    A = sp.csr_matrix((v, c, rp)).tocsc()
+    np.testing.assert_allclose(x, spl.spsolve(A, b), rtol=1e-7, atol=1e-10)   # |r| < 1e-8, lambda_min ~ 46
+    # MIN_ITERATION = 200 pads the loop (MgcgMain.cs:25): the index is exactly 200
+    x2, it2, res2, st2 = oracle.cg_solve(v, rp, c, b, x0, tol=1e-8, min_iteration=200)
+    assert it2 == 200 and np.isfinite(res2)
+
+
+def test_poisson2d_c1_iterations(oracle, gen):
+    v, rp, c = gen.poisson2d5(128, 128)
+    n = 128 * 128
+    x, it, res, st = oracle.cg_solve(v, rp, c, np.ones(n), tol=1e-8)
+    assert it == 266                                           # SURVEY.md §8c case (3)
+    x, it, res, st = oracle.cg_solve(v, rp, c, gen.rhs_uniform(n, 0), tol=1e-8)
+    assert it == 442
+    x, it, res, st = oracle.cg_solve(v, rp, c, gen.rhs_uniform(n, 0), tol=1e-8, norm=oracle.NORM_REL_L2)
+    assert it == 382
+
+
+def test_stop_rules(oracle):
+    v, rp, c, b = oracle.gen_tridiag121(50)
+    _, it_ns, _, _ = oracle.cg_solve(v, rp, c, b, tol=1e-8, min_iteration=60, max_iteration=1000)
+    _, it_s, _, _ = oracle.cg_solve(v, rp, c, b, tol=1e-8, min_iteration=60, max_iteration=1000, min_strict=True)
+    assert it_ns == 60 and it_s == 61                          # `min <= it` vs `min < it`
+    _, it, _, st = oracle.cg_solve(v, rp, c, b, tol=1e-300, max_iteration=5)
+    assert st == oracle.MAX_ITERATION_EXCEEDED and it == 6     # C# throws when Iteration > Max
+    xi, iti, resi, _ = oracle.cg_solve(v, rp, c, b, tol=1e-6, norm=oracle.NORM_ABS_LINF)
+    A = sp.csr_matrix((v, c, rp))
+    assert abs(np.abs(b - A @ xi).max() - resi) < 1e-9 and resi < 1e-6
+
+
+def test_partition_and_halo_maps(oracle):
+    # ConjugateGradientParallelGpu.cs:271-277,397-398 and Mgcg.cu:68-84
+    off = oracle.partition_offsets(207402, 4)
+    assert off.tolist() == [0, 51850, 103700, 155550, 207402]
+    assert oracle.partition_offsets(10, 3).tolist() == [0, 3, 6, 10]
+    assert oracle.partition_offsets(5, 8).tolist() == [0, 0, 0, 0, 0, 0, 0, 0, 5]
+    v, rp, c, b, x0 = oracle.gen_banded_sin(1000, 160)
+    off = oracle.partition_offsets(1000, 4)
+    for d in range(4):
+        cnt = int(off[d + 1] - off[d])
+        lro, eo, ec, mn, mx = oracle.initialize_block(rp, c, int(off[d]), cnt)
+        assert lro[0] == 0 and lro[-1] == ec and eo == rp[off[d]]
+        assert mn == max(0, off[d] - 79) and mx == min(999, off[d + 1] - 1 + 79)
+        lc, nc = oracle.halo_counts(d, 4, int(off[d]), cnt, mn, mx)
+        assert lc == (79 if d > 0 else 0) and nc == (79 if d < 3 else 0)
+
+
+def test_parallel_restatement_matches_sequential(oracle):
+    v, rp, c, b, x0 = oracle.gen_banded_sin(3000, 160)
+    x1, it1, r1, _ = oracle.cg_solve(v, rp, c, b, x0, tol=1e-8)
+    for D in (1, 2, 3, 8):
+        xd, itd, rd, st = oracle.cg_solve_parallel(v, rp, c, b, D, x0, tol=1e-8)
+        assert st == oracle.OK and itd == it1
+        np.testing.assert_allclose(xd, x1, rtol=1e-11, atol=1e-13)
+
+
+def test_mg_twin_against_direct_and_plain_cg(oracle, gen):
+    # multigrid has no reference (parity unpinned): the twin must at least solve the same system as the plain oracle
+    n = 16
+    v, rp, c = gen.poisson3d7(n)
+    b = gen.rhs_uniform(n ** 3, 0)
+    xd = spl.spsolve(sp.csr_matrix((v, c, rp)).tocsc(), b)
+    xc, itc, _, _ = oracle.cg_solve(v, rp, c, b, tol=1e-10)
+    for sm in (0, 1):
+        H = oracle.MgRef(v, rp, c, n, n, n, smoothed=sm)
+        assert H.levels() == 2
+        x, it, res, st = H.pcg(b, tol=1e-10)
+        assert st == 0 and it < itc / 2
+        np.testing.assert_allclose(x, xd, rtol=1e-8, atol=1e-10)
+        # M is symmetric: <M u, w> == <u, M w>
+        u, w = gen.rhs_uniform(n ** 3, 5), gen.rhs_uniform(n ** 3, 6)
+        assert abs(H.apply(u) @ w - u @ H.apply(w)) < 1e-10 * abs(H.apply(u) @ w)
+        H.close()
