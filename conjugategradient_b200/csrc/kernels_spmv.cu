@@ -51,7 +51,8 @@ __global__ void __launch_bounds__(kSpmvThreads) k_spmv_stream(SpmvArgs a, int ro
         const int r0 = tile * rows_per_tile;
         const int nr = min(rows_per_tile, a.A.rows - r0);
         __syncthreads();                       // previous tile's readers of rp/prod are done
-        if (t <= nr) rp[t] = a.A.rowptr[r0 + t];
+        if (t < nr) rp[t] = a.A.rowptr[r0 + t];
+        if (t == 0) rp[nr] = a.A.rowptr[r0 + nr];   // nr can equal blockDim.x: the end pointer needs its own load
         __syncthreads();
         const int k0 = rp[0], k1 = rp[nr];
         const int ms = (t < nr) ? rp[t] : 0, me = (t < nr) ? rp[t + 1] : 0;
