@@ -19,7 +19,7 @@ OK, MAX_ITERATION_EXCEEDED = 0, 3
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("cg_ref.c", "mg_ref.c") if os.path.exists(os.path.join(_HERE, f))]
+    srcs = [os.path.join(_HERE, f) for f in ("cg_ref.c", "mg_ref.c", "cg_ref_mt.c") if os.path.exists(os.path.join(_HERE, f))]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-s", "-C", _HERE, "-B", "liboracle.so"])
     return so
@@ -47,6 +47,10 @@ def lib():
         L.ref_gen_tridiag121.argtypes = [C.c_int, c_dp, c_ip, c_ip, c_dp]; L.ref_gen_tridiag121.restype = C.c_int
         L.ref_gen_banded_sin.argtypes = [C.c_int, C.c_int, c_dp, c_ip, c_ip, c_dp, c_dp]
         L.ref_gen_banded_sin.restype = C.c_int
+        L.ref_cg_solve_mt.argtypes = [C.c_int, C.c_int, c_dp, c_ip, c_ip, c_dp, c_dp, c_dp, c_dp, c_dp,
+                                      C.c_double, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double)]
+        L.ref_cg_solve_mt.restype = C.c_int
+        L.ref_mt_max_threads.restype = C.c_int
         _LIB = L
     return _LIB
 
@@ -73,6 +77,21 @@ def cg_solve(val, rowptr, col, b, x0=None, tol=1e-8, min_iteration=0, max_iterat
                             min_iteration, n if max_iteration is None else max_iteration,
                             norm, int(min_strict), C.byref(it), C.byref(res))
     return x, it.value, res.value, st
+
+
+def cg_solve_mt(val, rowptr, col, b, x0=None, tol=1e-8, min_iteration=0, max_iteration=None, norm=NORM_ABS_L2, threads=0):
+    """cg_ref_mt.c: the same CG with the reference's commented-out Parallel.For loops run over OpenMP threads."""
+    n = len(rowptr) - 1
+    x = np.zeros(n) if x0 is None else np.array(x0, dtype=np.float64, copy=True)
+    r, p, Ap = np.empty(n), np.empty(n), np.empty(n)
+    it, res = C.c_int(0), C.c_double(0)
+    st = lib().ref_cg_solve_mt(threads, n, val, rowptr, col, x, np.ascontiguousarray(b, dtype=np.float64), r, p, Ap, tol,
+                               min_iteration, n if max_iteration is None else max_iteration, norm, C.byref(it), C.byref(res))
+    return x, it.value, res.value, st
+
+
+def max_threads():
+    return lib().ref_mt_max_threads()
 
 
 def cg_solve_parallel(val, rowptr, col, b, devices, x0=None, tol=1e-8, min_iteration=0, max_iteration=None):

@@ -111,3 +111,19 @@ def test_mg_twin_against_direct_and_plain_cg(oracle, gen):
         u, w = gen.rhs_uniform(n ** 3, 5), gen.rhs_uniform(n ** 3, 6)
         assert abs(H.apply(u) @ w - u @ H.apply(w)) < 1e-10 * abs(H.apply(u) @ w)
         H.close()
+
+
+def test_threaded_port_matches_sequential(oracle, gen):
+    """cg_ref_mt.c (bench CPU baseline: the reference's commented-out Parallel.For loops over OpenMP) vs cg_ref.c."""
+    v, rp, c = gen.poisson3d7(20)
+    b = gen.rhs_uniform(20 ** 3, 0)
+    x1, i1, r1, s1 = oracle.cg_solve(v, rp, c, b, tol=1e-8, norm=oracle.NORM_REL_L2)
+    xs, is_, rs, ss = oracle.cg_solve_mt(v, rp, c, b, tol=1e-8, norm=oracle.NORM_REL_L2, threads=1)
+    assert (is_, ss) == (i1, s1) and np.array_equal(xs, x1)          # one thread: bit-identical
+    for t in (3, 0):
+        x2, i2, r2, s2 = oracle.cg_solve_mt(v, rp, c, b, tol=1e-8, norm=oracle.NORM_REL_L2, threads=t)
+        assert s2 == s1 and abs(i2 - i1) <= 1
+        assert np.abs(x2 - x1).max() / np.abs(x1).max() <= 1e-10
+    # bounded sample: max_iteration stops the loop like the C# throw
+    _, it, _, st = oracle.cg_solve_mt(v, rp, c, b, tol=0.0, max_iteration=8, threads=2)
+    assert st == oracle.MAX_ITERATION_EXCEEDED and it == 9
