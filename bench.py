@@ -193,3 +193,140 @@ def run_reference(args):
            "gpu_launches": 0}
     print(json.dumps(out), flush=True)
     return 0
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def run_ours_single(args):
+    """N = 1: the whole system on cuda:0 through the C ABI (mgcg_setup / mgcg_solve / mgcg_solve_host)."""
+    import torch
+    from conjugategradient_b200 import solver as S
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    dev = torch.device("cuda:0")
+    torch.cuda.set_device(dev)
+    torch.cuda.set_stream(torch.cuda.Stream(dev))   # a real (capturable) stream shared by torch's events and the library
+    n_side = args.size
+    n = n_side ** 3
+    problem = make_problem(n_side)
+    val, rp, col, b = problem
+    nnz = int(rp[-1])
+    # pinned host copies (the e2e leg uploads from these)
+    hv, hr, hc, hb = (torch.from_numpy(a).pin_memory() for a in (val, rp, col, b))
+    hx = torch.zeros(n, dtype=torch.float64).pin_memory()
+    tv, tr, tc, tb = (t.to(dev, non_blocking=True) for t in (hv, hr, hc, hb))
+    tx = torch.zeros(n, dtype=torch.float64, device=dev)
+    torch.cuda.synchronize()
+
+    m = S.Mgcg(0, use_torch_stream=True)     # run on torch's current stream so torch.cuda.Event brackets the library's work
+    opts = S.default_options(precond=1, nx=n_side, ny=n_side, nz=n_side, norm=2, tolerance=TOL, max_iteration=1000, use_graph=1)
+    m.setup(tv, tr, tc, opts)
+
+    def step():
+        tx.zero_()
+        return m.solve(tb, tx)
+
+    for _ in range(args.warmup):
+        res = step()
+    torch.cuda.synchronize()
+    clocks = ClockSampler(0)
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches = 0
+    e0.record()
+    for _ in range(args.steps):
+        res = step()
+        launches += res.kernel_launches + 1
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    clk = clocks.stop()
+    iters = res.iterations_done
+    setup_ms = res.setup_ms
+    # true residual check of the last solve (not timed): ||b - A x|| / ||b||
+    ty = torch.empty_like(tx)
+    S.check(m.L.mgcg_spmv(m.ctx, n, n, nnz, S._p(tv), S._p(tr), S._p(tc), S._p(tx), S._p(ty), 1.0, 0.0, 0), "mgcg_spmv")
+    torch.cuda.synchronize()
+    true_rel = float(torch.linalg.vector_norm(tb - ty) / torch.linalg.vector_norm(tb))
+
+    # roofline leg: the fine-level SpMV(+p.Ap) launches timed with CUDA events inside one more solve (profile=1)
+    popts = S.default_options(precond=1, nx=n_side, ny=n_side, nz=n_side, norm=2, tolerance=TOL, max_iteration=1000, profile=1)
+    m.setup(tv, tr, tc, popts)
+    tx.zero_()
+    pres = m.solve(tb, tx)
+    spmv_ms = pres.spmv_ms_total / max(pres.spmv_launches, 1)
+    # ... and back-to-back in isolation (inputs 1.6 GB >> 126 MB L2, so no flush is needed)
+    td = torch.zeros(1, dtype=torch.float64, device=dev)
+    for _ in range(3):
+        m.L.mgcg_spmv_dot(m.ctx, n, n, nnz, S._p(tv), S._p(tr), S._p(tc), S._p(tb), S._p(ty), S._p(tb), S._p(td), 0)
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 20
+    s0.record()
+    for _ in range(reps):
+        m.L.mgcg_spmv_dot(m.ctx, n, n, nnz, S._p(tv), S._p(tr), S._p(tc), S._p(tb), S._p(ty), S._p(tb), S._p(td), 0)
+    s1.record()
+    torch.cuda.synchronize()
+    spmv_iso_ms = s0.elapsed_time(s1) / reps
+    spmv_bytes = 12.0 * nnz + 20.0 * n
+    peak, peak_how = measured_peak()
+    achieved = spmv_bytes / (spmv_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_spmv_stream<EPI_DOT> (fine-level A*p with fused p.Ap)", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "frac_of_8TBs_nominal": achieved / 8000.0, "traffic": None,
+                "peak_source": peak_how, "bytes_per_launch": spmv_bytes, "ms_per_launch": spmv_ms,
+                "launches_timed": pres.spmv_launches, "isolated_ms_per_launch": spmv_iso_ms,
+                "isolated_gbs": spmv_bytes / (spmv_iso_ms * 1e-3) / 1e9}
+
+    # e2e leg: host CSR + b in, x out, everything (upload, hierarchy, solve, download) inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        m2 = S.Mgcg(0, use_torch_stream=True)
+        hx.zero_()
+        m2.solve_host(hv.numpy(), hr.numpy(), hc.numpy(), hb.numpy(), hx.numpy(), opts)     # warm-up (allocations)
+        k = max(1, min(args.steps, 3))
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        g0.record()
+        for _ in range(k):
+            hx.zero_()
+            r2 = m2.solve_host(hv.numpy(), hr.numpy(), hc.numpy(), hb.numpy(), hx.numpy(), opts)
+        g1.record()
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3 / k
+        e2e = {"value": max(g0.elapsed_time(g1) / k, wall), "unit": "ms",
+               "h2d_bytes_per_step": int(12 * nnz + 4 * (n + 1) + 16 * n), "d2h_bytes_per_step": int(8 * n),
+               "setup_ms": r2.setup_ms, "solve_ms": r2.solve_ms, "iterations": r2.iterations_done,
+               "api": "mgcg_solve_host (include/mgcg.h): pinned host CSR + b + x0 -> x"}
+        assert abs(r2.iterations_done - iters) <= 1
+        m2.close()
+
+    cpu = None if args.no_cpu else cpu_baseline_leg(problem, n_side, args.cpu_seconds)
+    out = {"metric": METRIC, "value": ms, "unit": "ms", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": ms, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+           "data": "synthetic",
+           "config": {"workload": f"3-D 7-point Poisson {n_side}^3 MGCG, fp64, b~U(-1,1) seed 0, x0=0, relative residual 1e-8",
+                      "rows": n, "nnz": nnz, "preconditioner": "smoothed-aggregation V(1,1), weighted Jacobi 0.8, built on device",
+                      "l2": "inputs (1.6 GB matrix + 128 MiB vectors) larger than the 126 MB L2; no flush",
+                      "parallelism": "1 GPU"},
+           "iterations": iters, "iterations_per_s": iters / (ms * 1e-3), "final_relative_residual": res.residual,
+           "true_relative_residual": true_rel, "setup_ms": setup_ms, "levels": res.levels,
+           "operator_complexity": res.operator_complexity, "spmv_gbs": achieved,
+           "gpu_launches": launches, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e}
+    print(json.dumps(out), flush=True)
+    m.close()
+    return 0
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1 or args.gpus > 1:
+        return run_ours_dist(args)
+    return run_ours_single(args)
+
+
+def run_ours_dist(args):
+    raise SystemExit("bench.py: the sharded (N > 1) arm is not wired yet")
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -35,6 +35,7 @@ struct Hierarchy {
 
 // ---- mg_setup.cu building blocks (also used by tests through the introspection API)
 int spgemm_esc(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C);
+int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C);   // mg_spgemm.cu
 int csr_transpose(mgcg_ctx *c, const Csr &A, DevCsr *T);
 
 }  // namespace mgcg

@@ -445,8 +445,8 @@ int mg_build(mgcg_ctx *c)
 
         // ---- Galerkin coarse operator  A_c = R (A P)
         DevCsr AP, Ac;
-        MGCG_CHECK(spgemm_esc(c, L.A, L.P.view(), &AP));
-        int s = spgemm_esc(c, L.R.view(), AP.view(), &Ac);
+        MGCG_CHECK(spgemm(c, L.A, L.P.view(), &AP));
+        int s = spgemm(c, L.R.view(), AP.view(), &Ac);
         AP.free_all();
         MGCG_CHECK(s);
 

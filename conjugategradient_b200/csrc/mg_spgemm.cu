@@ -1,0 +1,224 @@
+// mg_spgemm.cu — row-wise sparse matrix product C = A * B for the hierarchy build (Galerkin products A*P and R*(A*P)).
+// (No counterpart in the reference; CPU twin: oracle/mg_ref.c spgemm.)
+//
+// A group of G lanes owns one row of C.  It walks the row of A entry by entry IN STORAGE ORDER; for each a_ik the lanes take
+// the entries of row k of B (distinct columns) and add a_ik*b_kj into a per-group hash table in shared memory.  Because
+// the walk over k is sequential and the lanes of one step hit distinct columns, every c_ij is the sum of its products in
+// storage order of the A row, each product rounded before the add (__dmul_rn/__dadd_rn, no FMA) — the same order and the
+// same roundings as the CPU twin, so the coarse operators are bit-identical and run-to-run deterministic without a global
+// sort.  Two phases: symbolic (unique columns per row) -> scan -> numeric (fill, bitonic-sort the row by column, write).
+// Rows whose product count exceeds the largest table fall back to the expand/sort/compress path (spgemm_esc).
+#include "mg.cuh"
+#include <cub/cub.cuh>
+
+namespace mgcg {
+
+constexpr int kEmpty = -1;
+
+__device__ __forceinline__ unsigned hash_col(int col, int cap_mask) { return ((unsigned)col * 0x9E3779B1u >> 7) & (unsigned)cap_mask; }
+
+template <int G>
+__device__ __forceinline__ unsigned group_mask()
+{
+    if (G == 32) return 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    return ((1u << G) - 1u) << (lane & ~(G - 1));
+}
+
+// ---- symbolic: cnt[row] = number of distinct columns of row `row` of A*B
+template <int G>
+__global__ void __launch_bounds__(256) k_spgemm_symbolic(Csr A, Csr B, int cap, int *__restrict__ cnt)
+{
+    extern __shared__ int sm_keys[];
+    const int gpb = blockDim.x / G;
+    const int lane = threadIdx.x & (G - 1);
+    int *keys = sm_keys + (size_t)(threadIdx.x / G) * cap;
+    const unsigned mask = group_mask<G>();
+    const int cap_mask = cap - 1;
+    for (int row = blockIdx.x * gpb + threadIdx.x / G; row < A.rows; row += gridDim.x * gpb) {
+        for (int s = lane; s < cap; s += G) keys[s] = kEmpty;
+        __syncwarp(mask);
+        int mine = 0;
+        const int ks = A.rowptr[row], ke = A.rowptr[row + 1];
+        for (int k = ks; k < ke; ++k) {
+            const int j = A.col[k];
+            const int qe = B.rowptr[j + 1];
+            for (int q = B.rowptr[j] + lane; q < qe; q += G) {
+                const int col = B.col[q];
+                unsigned s = hash_col(col, cap_mask);
+                while (true) {
+                    const int old = atomicCAS(&keys[s], kEmpty, col);
+                    if (old == kEmpty) { ++mine; break; }
+                    if (old == col) break;
+                    s = (s + 1) & cap_mask;
+                }
+            }
+        }
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) mine += __shfl_down_sync(mask, mine, o, G);
+        if (lane == 0) cnt[row] = mine;
+        __syncwarp(mask);
+    }
+}
+
+// ---- numeric: fill row `row` of C (columns ascending)
+template <int G>
+__global__ void __launch_bounds__(256) k_spgemm_numeric(Csr A, Csr B, int cap, const int *__restrict__ c_rowptr,
+                                                        int *__restrict__ c_col, double *__restrict__ c_val)
+{
+    extern __shared__ double sm_raw[];
+    const int gpb = blockDim.x / G;
+    const int lane = threadIdx.x & (G - 1);
+    double *vals = sm_raw + (size_t)(threadIdx.x / G) * cap;
+    int *keys = reinterpret_cast<int *>(sm_raw + (size_t)gpb * cap) + (size_t)(threadIdx.x / G) * cap;
+    const unsigned mask = group_mask<G>();
+    const int cap_mask = cap - 1;
+    for (int row = blockIdx.x * gpb + threadIdx.x / G; row < A.rows; row += gridDim.x * gpb) {
+        for (int s = lane; s < cap; s += G) { keys[s] = kEmpty; vals[s] = 0.0; }
+        __syncwarp(mask);
+        const int ks = A.rowptr[row], ke = A.rowptr[row + 1];
+        for (int k = ks; k < ke; ++k) {
+            const int j = A.col[k];
+            const double a = A.val[k];
+            const int qe = B.rowptr[j + 1];
+            for (int q = B.rowptr[j] + lane; q < qe; q += G) {
+                const int col = B.col[q];
+                const double prod = __dmul_rn(a, B.val[q]);
+                unsigned s = hash_col(col, cap_mask);
+                while (true) {
+                    const int old = atomicCAS(&keys[s], kEmpty, col);
+                    if (old == kEmpty || old == col) break;
+                    s = (s + 1) & cap_mask;
+                }
+                vals[s] = __dadd_rn(vals[s], prod);   // first product: 0 + prod == prod exactly
+            }
+            __syncwarp(mask);                          // orders step k's table writes before step k+1's reads
+        }
+        // empty slots sort to the end
+        for (int s = lane; s < cap; s += G) if (keys[s] == kEmpty) keys[s] = 0x7fffffff;
+        __syncwarp(mask);
+        for (int kk = 2; kk <= cap; kk <<= 1) {
+            for (int jj = kk >> 1; jj > 0; jj >>= 1) {
+                for (int idx = lane; idx < cap; idx += G) {
+                    const int partner = idx ^ jj;
+                    if (partner > idx) {
+                        const int ka = keys[idx], kb = keys[partner];
+                        const bool up = (idx & kk) == 0;
+                        if ((ka > kb) == up) {
+                            keys[idx] = kb; keys[partner] = ka;
+                            const double va = vals[idx]; vals[idx] = vals[partner]; vals[partner] = va;
+                        }
+                    }
+                }
+                __syncwarp(mask);
+            }
+        }
+        const int o0 = c_rowptr[row], n_out = c_rowptr[row + 1] - o0;
+        for (int s = lane; s < n_out; s += G) { c_col[o0 + s] = keys[s]; c_val[o0 + s] = vals[s]; }
+        __syncwarp(mask);
+    }
+}
+
+// max over rows of the product count (upper bound of the distinct columns of a row of C), clipped to int
+__global__ void k_spgemm_maxprod(Csr A, Csr B, int *out_max)
+{
+    int m = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x) {
+        long long s = 0;
+        for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k) { const int j = A.col[k]; s += B.rowptr[j + 1] - B.rowptr[j]; }
+        m = max(m, (int)min(s, (long long)0x7fffffff));
+    }
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_down_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(out_max, m);
+}
+
+static int pow2_at_least(long long v) { int p = 32; while (p < v) p <<= 1; return p; }
+
+template <int G>
+static int run_hash(mgcg_ctx *c, const Csr &A, const Csr &B, int maxprod, DevCsr *C, bool *done)
+{
+    cudaStream_t st = c->stream;
+    *done = false;
+    // symbolic table: 1.5x the distinct-column bound (keys only)
+    long long bound = maxprod < B.cols ? maxprod : B.cols;
+    const int cap_s = pow2_at_least(bound + bound / 2 + 1);
+    int threads = 256;
+    while (threads > G && (size_t)(threads / G) * cap_s * sizeof(int) > 160 * 1024) threads >>= 1;
+    if (threads < 32) threads = 32;
+    if ((size_t)(threads / G) * cap_s * sizeof(int) > 200 * 1024) return MGCG_OK;   // too wide: caller falls back
+    const size_t sm_s = (size_t)(threads / G) * cap_s * sizeof(int);
+    MGCG_CUDA(cudaFuncSetAttribute(k_spgemm_symbolic<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_s));
+    int *cnt = nullptr;
+    MGCG_CUDA(cudaMalloc((void **)&cnt, sizeof(int) * ((size_t)A.rows + 2)));
+    MGCG_CUDA(cudaMemsetAsync(cnt + A.rows, 0, 2 * sizeof(int), st));
+    const int gpb = threads / G;
+    int grid = (A.rows + gpb - 1) / gpb;
+    const int cap_grid = c->sm_count * 16;
+    if (grid > cap_grid) grid = cap_grid;
+    k_spgemm_symbolic<G><<<grid, threads, sm_s, st>>>(A, B, cap_s, cnt);
+    MGCG_LAUNCH_CHECK();
+    // scan + max
+    C->rows = A.rows; C->cols = B.cols;
+    MGCG_CUDA(cudaMalloc((void **)&C->rowptr, sizeof(int) * ((size_t)A.rows + 1)));
+    size_t tb = 0, tb2 = 0;
+    int *d_max = cnt + A.rows + 1;
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, C->rowptr, A.rows + 1, st));
+    MGCG_CUDA(cub::DeviceReduce::Max(nullptr, tb2, cnt, d_max, A.rows, st));
+    if (tb2 > tb) tb = tb2;
+    void *tmp = nullptr;
+    MGCG_CUDA(cudaMalloc(&tmp, tb ? tb : 1));
+    MGCG_CUDA(cub::DeviceReduce::Max(tmp, tb, cnt, d_max, A.rows, st));
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, C->rowptr, A.rows + 1, st));
+    int h[2] = {0, 0};   // total nnz, max row length
+    MGCG_CUDA(cudaMemcpyAsync(&h[0], C->rowptr + A.rows, sizeof(int), cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaMemcpyAsync(&h[1], d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    cudaFree(tmp); cudaFree(cnt);
+    C->nnz = h[0];
+    MGCG_CUDA(cudaMalloc((void **)&C->val, sizeof(double) * (size_t)(h[0] > 0 ? h[0] : 1)));
+    MGCG_CUDA(cudaMalloc((void **)&C->col, sizeof(int) * (size_t)(h[0] > 0 ? h[0] : 1)));
+    // numeric table: 1.5x the longest row
+    const int cap_n = pow2_at_least((long long)h[1] + h[1] / 2 + 1);
+    threads = 256;
+    while (threads > G && (size_t)(threads / G) * cap_n * 12 > 160 * 1024) threads >>= 1;
+    if (threads < 32) threads = 32;
+    const size_t sm_n = (size_t)(threads / G) * cap_n * 12;
+    if (sm_n > 200 * 1024) { C->free_all(); return MGCG_OK; }
+    MGCG_CUDA(cudaFuncSetAttribute(k_spgemm_numeric<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_n));
+    const int gpb_n = threads / G;
+    grid = (A.rows + gpb_n - 1) / gpb_n;
+    if (grid > cap_grid) grid = cap_grid;
+    k_spgemm_numeric<G><<<grid, threads, sm_n, st>>>(A, B, cap_n, C->rowptr, C->col, C->val);
+    MGCG_LAUNCH_CHECK();
+    *done = true;
+    return MGCG_OK;
+}
+
+// C = A * B.  Uses the shared-memory hash kernels; falls back to spgemm_esc for rows too wide for the tables.
+int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C)
+{
+    cudaStream_t st = c->stream;
+    if (A.rows <= 0 || A.nnz <= 0 || B.nnz <= 0) return spgemm_esc(c, A, B, C);
+    int *d_max = nullptr, maxprod = 0;
+    MGCG_CUDA(cudaMalloc((void **)&d_max, sizeof(int)));
+    MGCG_CUDA(cudaMemsetAsync(d_max, 0, sizeof(int), st));
+    int g = (A.rows + 255) / 256;
+    if (g > c->sm_count * 16) g = c->sm_count * 16;
+    k_spgemm_maxprod<<<g, 256, 0, st>>>(A, B, d_max);
+    MGCG_LAUNCH_CHECK();
+    MGCG_CUDA(cudaMemcpyAsync(&maxprod, d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    cudaFree(d_max);
+    const double avg_b = (double)B.nnz / (B.rows > 0 ? B.rows : 1);
+    bool done = false;
+    int s;
+    if (avg_b <= 4.5) s = run_hash<4>(c, A, B, maxprod, C, &done);
+    else if (avg_b <= 10.0) s = run_hash<8>(c, A, B, maxprod, C, &done);
+    else if (avg_b <= 20.0) s = run_hash<16>(c, A, B, maxprod, C, &done);
+    else s = run_hash<32>(c, A, B, maxprod, C, &done);
+    MGCG_CHECK(s);
+    if (done) return MGCG_OK;
+    return spgemm_esc(c, A, B, C);
+}
+
+}  // namespace mgcg
