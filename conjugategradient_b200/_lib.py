@@ -23,7 +23,8 @@ class Options(C.Structure):
         ("mg_max_levels", C.c_int), ("mg_coarse_size", C.c_int), ("mg_pre_sweeps", C.c_int), ("mg_post_sweeps", C.c_int),
         ("mg_omega", C.c_double), ("mg_smoother", C.c_int), ("mg_smoothed", C.c_int), ("mg_prolong_omega", C.c_double),
         ("spmv_kernel", C.c_int), ("check_interval", C.c_int), ("use_graph", C.c_int), ("profile", C.c_int),
-        ("reserved", C.c_int * 8),
+        ("mg_smoothed_levels", C.c_int), ("mg_aggregate_size", C.c_int), ("mg_aggregate_size_coarse", C.c_int),
+        ("reserved", C.c_int * 5),
     ]
 
 

@@ -70,6 +70,8 @@ void mgcg_options_default(mgcg_options *o)
     o->mg_omega = 0.8;
     o->mg_smoother = MGCG_SMOOTHER_JACOBI;
     o->mg_smoothed = 1;
+    o->mg_aggregate_size = 3;          /* 3x3x3 on the finest level, 2x2x2 below: fewest total bytes per digit of residual */
+    o->mg_aggregate_size_coarse = 2;
     o->mg_prolong_omega = 2.0 / 3.0;
     o->spmv_kernel = MGCG_SPMV_AUTO;
     o->check_interval = 8;

@@ -13,6 +13,8 @@
 // cub::DeviceRadixSort / DeviceScan are used for the sort and the scans of the SETUP only (not the solve path).
 #include "mg.cuh"
 #include <cub/cub.cuh>
+#include <chrono>
+#include <stdlib.h>
 
 namespace mgcg {
 
@@ -54,12 +56,12 @@ __global__ void k_extract_dinv(Csr A, double *dinv)
     }
 }
 
-__global__ void k_agg_geometric(int nx, int ny, int nz, int cx, int cy, int *agg)
+__global__ void k_agg_geometric(int nx, int ny, int nz, int cx, int cy, int a, int *agg)
 {
     const long long n = (long long)nx * ny * nz;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         int x = (int)(i % nx), y = (int)((i / nx) % ny), z = (int)(i / ((long long)nx * ny));
-        agg[i] = (x >> 1) + cx * ((y >> 1) + cy * (z >> 1));
+        agg[i] = (x / a) + cx * ((y / a) + cy * (z / a));
     }
 }
 
@@ -381,9 +383,25 @@ void mg_free(mgcg_ctx *c)
     c->mg = nullptr;
 }
 
+// MGCG_TRACE=1: wall-clock of every phase of the hierarchy build on stderr (synchronises the stream at each mark)
+struct PhaseTrace {
+    bool on; cudaStream_t st; std::chrono::steady_clock::time_point t0;
+    PhaseTrace(cudaStream_t s) : on(getenv("MGCG_TRACE") != nullptr), st(s) { if (on) { cudaStreamSynchronize(st); t0 = std::chrono::steady_clock::now(); } }
+    void mark(int level, const char *what)
+    {
+        if (!on) return;
+        cudaStreamSynchronize(st);
+        auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[mgcg setup] level %d %-12s %8.3f ms\n", level, what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
+
 int mg_build(mgcg_ctx *c)
 {
+    PhaseTrace tr(c->stream);
     mg_free(c);
+    tr.mark(-1, "free-old");
     const mgcg_options &o = c->opt;
     if (o.mg_pre_sweeps < 1 || o.mg_post_sweeps < 0) { set_error("mg_build: mg_pre_sweeps must be >= 1, mg_post_sweeps >= 0"); return MGCG_ERR_INVALID; }
     if (o.mg_smoother != MGCG_SMOOTHER_JACOBI) { set_error("mg_build: only the weighted-Jacobi smoother is implemented"); return MGCG_ERR_UNSUPPORTED; }
@@ -415,18 +433,22 @@ int mg_build(mgcg_ctx *c)
         int cd[3] = {0, 0, 0};
         MGCG_CHECK(dalloc(&L.agg, (size_t)n));
         if (L.dims[0] > 0) {
-            cd[0] = (L.dims[0] + 1) / 2; cd[1] = (L.dims[1] + 1) / 2; cd[2] = (L.dims[2] + 1) / 2;
+            int a = (l == 0 || o.mg_aggregate_size_coarse <= 0) ? o.mg_aggregate_size : o.mg_aggregate_size_coarse;
+            if (a < 2) a = 2;
+            cd[0] = (L.dims[0] + a - 1) / a; cd[1] = (L.dims[1] + a - 1) / a; cd[2] = (L.dims[2] + a - 1) / a;
             nc = cd[0] * cd[1] * cd[2];
-            k_agg_geometric<<<grid_for(n), 256, 0, st>>>(L.dims[0], L.dims[1], L.dims[2], cd[0], cd[1], L.agg);
+            k_agg_geometric<<<grid_for(n), 256, 0, st>>>(L.dims[0], L.dims[1], L.dims[2], cd[0], cd[1], a, L.agg);
         } else {
             nc = (n + 7) / 8;
             k_agg_blocks<<<grid_for(n), 256, 0, st>>>(n, 8, L.agg);
         }
         MGCG_LAUNCH_CHECK();
         if (nc >= n) break;   // cannot coarsen further
+        tr.mark(l, "aggregate");
 
         // ---- prolongator
-        if (!o.mg_smoothed) {
+        const bool smooth_here = o.mg_smoothed && (o.mg_smoothed_levels <= 0 || l < o.mg_smoothed_levels);
+        if (!smooth_here) {
             L.P.rows = n; L.P.cols = nc; L.P.nnz = n;
             MGCG_CHECK(dalloc(&L.P.val, (size_t)n)); MGCG_CHECK(dalloc(&L.P.col, (size_t)n)); MGCG_CHECK(dalloc(&L.P.rowptr, (size_t)n + 1));
             k_build_T<<<grid_for(n + 1), 256, 0, st>>>(n, L.agg, L.P.val, L.P.rowptr, L.P.col);
@@ -441,12 +463,16 @@ int mg_build(mgcg_ctx *c)
             cudaFree(keys); cudaFree(vals);
             MGCG_CHECK(s);
         }
+        tr.mark(l, "P");
         MGCG_CHECK(csr_transpose(c, L.P.view(), &L.R));
+        tr.mark(l, "R=P^T");
 
         // ---- Galerkin coarse operator  A_c = R (A P)
         DevCsr AP, Ac;
         MGCG_CHECK(spgemm(c, L.A, L.P.view(), &AP));
+        tr.mark(l, "A*P");
         int s = spgemm(c, L.R.view(), AP.view(), &Ac);
+        tr.mark(l, "R*(AP)");
         AP.free_all();
         MGCG_CHECK(s);
 
@@ -465,7 +491,9 @@ int mg_build(mgcg_ctx *c)
     MgLevel &Lc = H->L.back();
     if (Lc.A.rows > 4096) { set_error("mg_build: coarsest level has %d rows (> 4096): raise mg_max_levels", Lc.A.rows); return MGCG_ERR_UNSUPPORTED; }
     H->coarse_n = Lc.A.rows;
+    tr.mark((int)H->L.size() - 1, "pre-dense");
     MGCG_CHECK(dense_inverse(c, Lc.A, &H->coarse_inv));
+    tr.mark((int)H->L.size() - 1, "dense-inverse");
     H->op_complexity = nnz_sum / (double)(c->A.nnz > 0 ? c->A.nnz : 1);
     MGCG_CUDA(cudaStreamSynchronize(st));
     return MGCG_OK;

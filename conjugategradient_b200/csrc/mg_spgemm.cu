@@ -25,35 +25,70 @@ __device__ __forceinline__ unsigned group_mask()
     return ((1u << G) - 1u) << (lane & ~(G - 1));
 }
 
+// One pass over row `row` of A*B for a group of G lanes.  The lanes first load up to G entries of the A row together with
+// the extents of the B rows they select (one memory latency for G entries instead of a dependent chain per entry), then
+// walk them in storage order by shuffle broadcast; the first G entries of the NEXT B row are prefetched while the current
+// ones are inserted.  NUMERIC = false: count distinct columns (returns this lane's share);  true: accumulate values.
+template <int G, bool NUMERIC>
+__device__ __forceinline__ int spgemm_row(const Csr &A, const Csr &B, int row, int lane, unsigned mask, int cap_mask,
+                                          int *keys, double *vals, int *overflow)
+{
+    int mine = 0;
+    const int ks = A.rowptr[row], ke = A.rowptr[row + 1];
+    for (int kb = ks; kb < ke; kb += G) {
+        const int kk = kb + lane;
+        int q0_l = 0, q1_l = 0;
+        double a_l = 0.0;
+        if (kk < ke) {
+            const int j = A.col[kk];
+            if (NUMERIC) a_l = A.val[kk];
+            q0_l = B.rowptr[j]; q1_l = B.rowptr[j + 1];
+        }
+        const int nk = min(G, ke - kb);
+        int q0 = __shfl_sync(mask, q0_l, 0, G), q1 = __shfl_sync(mask, q1_l, 0, G);
+        int c_cur = 0; double v_cur = 0.0;
+        if (q0 + lane < q1) { c_cur = B.col[q0 + lane]; if (NUMERIC) v_cur = B.val[q0 + lane]; }
+        for (int t = 0; t < nk; ++t) {
+            const double a = NUMERIC ? __shfl_sync(mask, a_l, t, G) : 0.0;
+            int q0n = 0, q1n = 0, c_nxt = 0; double v_nxt = 0.0;
+            if (t + 1 < nk) {
+                q0n = __shfl_sync(mask, q0_l, t + 1, G); q1n = __shfl_sync(mask, q1_l, t + 1, G);
+                if (q0n + lane < q1n) { c_nxt = B.col[q0n + lane]; if (NUMERIC) v_nxt = B.val[q0n + lane]; }
+            }
+            for (int q = q0 + lane; q < q1; q += G) {
+                int col = c_cur; double bv = v_cur;
+                if (q != q0 + lane) { col = B.col[q]; if (NUMERIC) bv = B.val[q]; }   // B rows longer than G (rare)
+                unsigned s = hash_col(col, cap_mask);
+                int probes = 0;
+                while (true) {
+                    const int old = atomicCAS(&keys[s], kEmpty, col);
+                    if (old == kEmpty) { ++mine; break; }
+                    if (old == col) break;
+                    s = (s + 1) & cap_mask;
+                    if (!NUMERIC && ++probes > 48) { *overflow = 1; break; }   // table (nearly) full: the host retries larger
+                }
+                if (NUMERIC) vals[s] = __dadd_rn(vals[s], __dmul_rn(a, bv));   // first product: 0 + prod == prod exactly
+            }
+            __syncwarp(mask);   // orders this step's table writes before the next step's reads
+            q0 = q0n; q1 = q1n; c_cur = c_nxt; v_cur = v_nxt;
+        }
+    }
+    return mine;
+}
+
 // ---- symbolic: cnt[row] = number of distinct columns of row `row` of A*B
 template <int G>
-__global__ void __launch_bounds__(256) k_spgemm_symbolic(Csr A, Csr B, int cap, int *__restrict__ cnt)
+__global__ void __launch_bounds__(256) k_spgemm_symbolic(Csr A, Csr B, int cap, int *__restrict__ cnt, int *__restrict__ overflow)
 {
     extern __shared__ int sm_keys[];
     const int gpb = blockDim.x / G;
     const int lane = threadIdx.x & (G - 1);
     int *keys = sm_keys + (size_t)(threadIdx.x / G) * cap;
     const unsigned mask = group_mask<G>();
-    const int cap_mask = cap - 1;
     for (int row = blockIdx.x * gpb + threadIdx.x / G; row < A.rows; row += gridDim.x * gpb) {
         for (int s = lane; s < cap; s += G) keys[s] = kEmpty;
         __syncwarp(mask);
-        int mine = 0;
-        const int ks = A.rowptr[row], ke = A.rowptr[row + 1];
-        for (int k = ks; k < ke; ++k) {
-            const int j = A.col[k];
-            const int qe = B.rowptr[j + 1];
-            for (int q = B.rowptr[j] + lane; q < qe; q += G) {
-                const int col = B.col[q];
-                unsigned s = hash_col(col, cap_mask);
-                while (true) {
-                    const int old = atomicCAS(&keys[s], kEmpty, col);
-                    if (old == kEmpty) { ++mine; break; }
-                    if (old == col) break;
-                    s = (s + 1) & cap_mask;
-                }
-            }
-        }
+        int mine = spgemm_row<G, false>(A, B, row, lane, mask, cap - 1, keys, nullptr, overflow);
 #pragma unroll
         for (int o = G / 2; o > 0; o >>= 1) mine += __shfl_down_sync(mask, mine, o, G);
         if (lane == 0) cnt[row] = mine;
@@ -72,42 +107,22 @@ __global__ void __launch_bounds__(256) k_spgemm_numeric(Csr A, Csr B, int cap, c
     double *vals = sm_raw + (size_t)(threadIdx.x / G) * cap;
     int *keys = reinterpret_cast<int *>(sm_raw + (size_t)gpb * cap) + (size_t)(threadIdx.x / G) * cap;
     const unsigned mask = group_mask<G>();
-    const int cap_mask = cap - 1;
     for (int row = blockIdx.x * gpb + threadIdx.x / G; row < A.rows; row += gridDim.x * gpb) {
         for (int s = lane; s < cap; s += G) { keys[s] = kEmpty; vals[s] = 0.0; }
         __syncwarp(mask);
-        const int ks = A.rowptr[row], ke = A.rowptr[row + 1];
-        for (int k = ks; k < ke; ++k) {
-            const int j = A.col[k];
-            const double a = A.val[k];
-            const int qe = B.rowptr[j + 1];
-            for (int q = B.rowptr[j] + lane; q < qe; q += G) {
-                const int col = B.col[q];
-                const double prod = __dmul_rn(a, B.val[q]);
-                unsigned s = hash_col(col, cap_mask);
-                while (true) {
-                    const int old = atomicCAS(&keys[s], kEmpty, col);
-                    if (old == kEmpty || old == col) break;
-                    s = (s + 1) & cap_mask;
-                }
-                vals[s] = __dadd_rn(vals[s], prod);   // first product: 0 + prod == prod exactly
-            }
-            __syncwarp(mask);                          // orders step k's table writes before step k+1's reads
-        }
+        spgemm_row<G, true>(A, B, row, lane, mask, cap - 1, keys, vals, nullptr);
         // empty slots sort to the end
         for (int s = lane; s < cap; s += G) if (keys[s] == kEmpty) keys[s] = 0x7fffffff;
         __syncwarp(mask);
         for (int kk = 2; kk <= cap; kk <<= 1) {
             for (int jj = kk >> 1; jj > 0; jj >>= 1) {
-                for (int idx = lane; idx < cap; idx += G) {
-                    const int partner = idx ^ jj;
-                    if (partner > idx) {
-                        const int ka = keys[idx], kb = keys[partner];
-                        const bool up = (idx & kk) == 0;
-                        if ((ka > kb) == up) {
-                            keys[idx] = kb; keys[partner] = ka;
-                            const double va = vals[idx]; vals[idx] = vals[partner]; vals[partner] = va;
-                        }
+                for (int pr = lane; pr < (cap >> 1); pr += G) {     // one compare-exchange per pair
+                    const int idx = ((pr & ~(jj - 1)) << 1) | (pr & (jj - 1)), partner = idx | jj;
+                    const int ka = keys[idx], kb = keys[partner];
+                    const bool up = (idx & kk) == 0;
+                    if ((ka > kb) == up) {
+                        keys[idx] = kb; keys[partner] = ka;
+                        const double va = vals[idx]; vals[idx] = vals[partner]; vals[partner] = va;
                     }
                 }
                 __syncwarp(mask);
@@ -139,24 +154,32 @@ static int run_hash(mgcg_ctx *c, const Csr &A, const Csr &B, int maxprod, DevCsr
 {
     cudaStream_t st = c->stream;
     *done = false;
-    // symbolic table: 1.5x the distinct-column bound (keys only)
+    // symbolic table (keys only): sized from the product-count bound when that is small, else grown x4 on overflow —
+    // rows of R*(A*P) have thousands of products but only a few hundred distinct columns
     long long bound = maxprod < B.cols ? maxprod : B.cols;
-    const int cap_s = pow2_at_least(bound + bound / 2 + 1);
-    int threads = 256;
-    while (threads > G && (size_t)(threads / G) * cap_s * sizeof(int) > 160 * 1024) threads >>= 1;
-    if (threads < 32) threads = 32;
-    if ((size_t)(threads / G) * cap_s * sizeof(int) > 200 * 1024) return MGCG_OK;   // too wide: caller falls back
-    const size_t sm_s = (size_t)(threads / G) * cap_s * sizeof(int);
-    MGCG_CUDA(cudaFuncSetAttribute(k_spgemm_symbolic<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_s));
+    int cap_s = pow2_at_least(bound + bound / 2 + 1);
+    if (cap_s > 512) cap_s = 512;
     int *cnt = nullptr;
-    MGCG_CUDA(cudaMalloc((void **)&cnt, sizeof(int) * ((size_t)A.rows + 2)));
-    MGCG_CUDA(cudaMemsetAsync(cnt + A.rows, 0, 2 * sizeof(int), st));
-    const int gpb = threads / G;
-    int grid = (A.rows + gpb - 1) / gpb;
+    MGCG_CUDA(cudaMalloc((void **)&cnt, sizeof(int) * ((size_t)A.rows + 3)));
     const int cap_grid = c->sm_count * 16;
-    if (grid > cap_grid) grid = cap_grid;
-    k_spgemm_symbolic<G><<<grid, threads, sm_s, st>>>(A, B, cap_s, cnt);
-    MGCG_LAUNCH_CHECK();
+    int threads, grid;
+    for (;; cap_s *= 4) {
+        threads = 256;
+        while (threads > G && threads > 32 && (size_t)(threads / G) * cap_s * sizeof(int) > 96 * 1024) threads >>= 1;
+        const size_t sm_s = (size_t)(threads / G) * cap_s * sizeof(int);
+        if (sm_s > 200 * 1024) { cudaFree(cnt); return MGCG_OK; }   // too wide: caller falls back to spgemm_esc
+        MGCG_CUDA(cudaFuncSetAttribute(k_spgemm_symbolic<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_s));
+        MGCG_CUDA(cudaMemsetAsync(cnt + A.rows, 0, 3 * sizeof(int), st));
+        const int gpb = threads / G;
+        grid = (A.rows + gpb - 1) / gpb;
+        if (grid > cap_grid) grid = cap_grid;
+        k_spgemm_symbolic<G><<<grid, threads, sm_s, st>>>(A, B, cap_s, cnt, cnt + A.rows + 2);
+        MGCG_LAUNCH_CHECK();
+        int ov = 0;
+        MGCG_CUDA(cudaMemcpyAsync(&ov, cnt + A.rows + 2, sizeof(int), cudaMemcpyDeviceToHost, st));
+        MGCG_CUDA(cudaStreamSynchronize(st));
+        if (!ov) break;
+    }
     // scan + max
     C->rows = A.rows; C->cols = B.cols;
     MGCG_CUDA(cudaMalloc((void **)&C->rowptr, sizeof(int) * ((size_t)A.rows + 1)));

@@ -65,7 +65,11 @@ typedef struct mgcg_options {
     int    check_interval;   /* host polls the device-side convergence flag every this many iterations (default 8) */
     int    use_graph;        /* 1: capture one iteration into a CUDA graph and replay it */
     int    profile;          /* 1: time the fine-level SpMV launches with CUDA events (disables the graph) */
-    int    reserved[8];
+    int    mg_smoothed_levels; /* with mg_smoothed: smooth the prolongator on the finest this-many levels only, plain
+                                  aggregation below (0 = every level).  Smoothing widens the coarse stencils level by level. */
+    int    mg_aggregate_size;        /* geometric aggregates are s x s x s grid blocks on level 0 (default 3; needs nx,ny,nz) */
+    int    mg_aggregate_size_coarse; /* the same for levels >= 1 (default 2; 0 = as level 0) */
+    int    reserved[5];
 } mgcg_options;
 
 typedef struct mgcg_result {

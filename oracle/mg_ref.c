@@ -144,7 +144,8 @@ static void level_vectors(level_t *L)
 }
 
 mg_ref_t *mg_ref_build(int n, int nnz, const double *val, const int *rowptr, const int *col,
-                       int nx, int ny, int nz, int max_levels, int coarse_size, int smoothed, double prolong_omega)
+                       int nx, int ny, int nz, int max_levels, int coarse_size, int smoothed, double prolong_omega,
+                       int smoothed_levels, int agg_size, int agg_size_coarse)
 {
     mg_ref_t *H = (mg_ref_t *)calloc(1, sizeof(mg_ref_t));
     if (max_levels <= 0) max_levels = 12;
@@ -164,11 +165,13 @@ mg_ref_t *mg_ref_build(int n, int nnz, const double *val, const int *rowptr, con
         int nc, cd[3] = {0, 0, 0};
         L->agg = (int *)malloc(sizeof(int) * (size_t)m);
         if (L->dims[0] > 0) {
-            cd[0] = (L->dims[0] + 1) / 2; cd[1] = (L->dims[1] + 1) / 2; cd[2] = (L->dims[2] + 1) / 2;
+            int a = (l == 0 || agg_size_coarse <= 0) ? agg_size : agg_size_coarse;
+            if (a < 2) a = 2;
+            cd[0] = (L->dims[0] + a - 1) / a; cd[1] = (L->dims[1] + a - 1) / a; cd[2] = (L->dims[2] + a - 1) / a;
             nc = cd[0] * cd[1] * cd[2];
             for (int i = 0; i < m; i++) {
                 int x = i % L->dims[0], y = (i / L->dims[0]) % L->dims[1], z = i / (L->dims[0] * L->dims[1]);
-                L->agg[i] = (x >> 1) + cd[0] * ((y >> 1) + cd[1] * (z >> 1));
+                L->agg[i] = (x / a) + cd[0] * ((y / a) + cd[1] * (z / a));
             }
         } else {
             nc = (m + 7) / 8;
@@ -181,7 +184,7 @@ mg_ref_t *mg_ref_build(int n, int nnz, const double *val, const int *rowptr, con
         for (int i = 0; i < m; i++) {
             int cnt = 0;
             e[cnt].col = L->agg[i]; e[cnt].v = 1.0; cnt++;
-            if (smoothed) {
+            if (smoothed && (smoothed_levels <= 0 || l < smoothed_levels)) {
                 double f = -(prolong_omega * L->dinv[i]);
                 for (int k = L->A.rowptr[i]; k < L->A.rowptr[i + 1]; k++) {
                     if ((size_t)cnt + 1 > cap) { cap *= 2; e = (ent_t *)realloc(e, cap * sizeof(ent_t)); }
