@@ -24,7 +24,7 @@ class Options(C.Structure):
         ("mg_omega", C.c_double), ("mg_smoother", C.c_int), ("mg_smoothed", C.c_int), ("mg_prolong_omega", C.c_double),
         ("spmv_kernel", C.c_int), ("check_interval", C.c_int), ("use_graph", C.c_int), ("profile", C.c_int),
         ("mg_smoothed_levels", C.c_int), ("mg_aggregate_size", C.c_int), ("mg_aggregate_size_coarse", C.c_int),
-        ("reserved", C.c_int * 5),
+        ("dist_replicate_below", C.c_int), ("reserved", C.c_int * 4),
     ]
 
 
@@ -101,7 +101,7 @@ def lib():
     L.mgcg_mg_apply.argtypes = [vp, vp, vp]
     L.mgcg_partition_offsets.argtypes = [ci, ci, vp]
     L.mgcg_comm_unique_id.argtypes = [vp]
-    L.mgcg_comm_init.argtypes = [vp, vp, ci, ci]
+    L.mgcg_comm_init.argtypes = [vp, C.c_char_p, ci, ci]
     L.mgcg_setup_dist.argtypes = [vp, ci, ci, ci, ci, vp, vp, vp, C.POINTER(Options)]
     L.mgcg_solve_dist.argtypes = [vp, vp, vp, C.POINTER(Result)]
     # compat exports

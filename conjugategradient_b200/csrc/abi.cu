@@ -72,6 +72,7 @@ void mgcg_options_default(mgcg_options *o)
     o->mg_smoothed = 1;
     o->mg_aggregate_size = 3;          /* 3x3x3 on the finest level, 2x2x2 below: fewest total bytes per digit of residual */
     o->mg_aggregate_size_coarse = 2;
+    o->dist_replicate_below = 1 << 20;
     o->mg_prolong_omega = 2.0 / 3.0;
     o->spmv_kernel = MGCG_SPMV_AUTO;
     o->check_interval = 8;
@@ -113,6 +114,7 @@ void mgcg_destroy(mgcg_ctx *c)
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    dist_free(c);
     mg_free(c);
     if (c->graph_exec) cudaGraphExecDestroy(c->graph_exec);
     if (c->graph) cudaGraphDestroy(c->graph);

@@ -105,6 +105,7 @@ enum SpmvEpi {
 struct SpmvArgs {
     Csr A;
     const double *x = nullptr;
+    const double *xrow = nullptr;  // JACOBI: x indexed by ROW (nullptr: same as x; differs when x is a shifted global-index view)
     double *y = nullptr;
     const double *b = nullptr;     // RESID / JACOBI
     const double *dinv = nullptr;  // JACOBI
@@ -165,7 +166,7 @@ int vec_scal(mgcg_ctx *c, int n, double alpha, double *x);
 int vec_copy(mgcg_ctx *c, int n, const double *x, double *y);
 int vec_fill(mgcg_ctx *c, int n, double v, double *x);
 // r = b - Ap ; p = r ; partial r.r  -> fin
-int cg_init_residual(mgcg_ctx *c, int n, const double *b, const double *Ap, double *r, double *p, int fin);
+int cg_init_residual(mgcg_ctx *c, int n, const double *b, const double *Ap, double *r, double *p, int fin, double *out = nullptr);
 // x += alpha p ; r -= alpha Ap ; r.r (and max|r|) -> fin.  alpha from Scalars unless use_host_alpha.
 // z0/dinv != nullptr: also z0 = omega*dinv*r (first pre-smoothing sweep of the V-cycle from a zero guess, fused)
 int cg_update_xr(mgcg_ctx *c, int n, const double *p, const double *Ap, double *x, double *r, int fin,
@@ -188,6 +189,9 @@ void mg_free(mgcg_ctx *c);
 int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done, int rz_fin);
 double *mg_level0_first_x(mgcg_ctx *c);   // buffer that receives the fused first pre-smoothing sweep
 const double *mg_level0_dinv(mgcg_ctx *c);
+
+// ---- dist.cu
+void dist_free(mgcg_ctx *c);
 
 // ---- cg.cu
 int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res);

@@ -25,7 +25,7 @@ __device__ __forceinline__ void epilogue(int row, double s, const SpmvArgs &a, d
     else if (EPI == EPI_RESID) a.y[row] = a.b[row] - s;
     else if (EPI == EPI_JACOBI || EPI == EPI_JACOBI_DOT) {
         const double bi = a.b[row];
-        const double yi = a.x[row] + a.omega * a.dinv[row] * (bi - s);
+        const double yi = (a.xrow ? a.xrow : a.x)[row] + a.omega * a.dinv[row] * (bi - s);
         a.y[row] = yi;
         if (EPI == EPI_JACOBI_DOT) dsum += bi * yi;
     }

@@ -143,9 +143,9 @@ __global__ void __launch_bounds__(kVecThreads) k_init_residual(int n, const doub
     grid_reduce_finish<false>(s, m, ws, fin, sc, out);
 }
 
-int cg_init_residual(mgcg_ctx *c, int n, const double *b, const double *Ap, double *r, double *p, int fin)
+int cg_init_residual(mgcg_ctx *c, int n, const double *b, const double *Ap, double *r, double *p, int fin, double *out)
 {
-    k_init_residual<<<vec_grid(c, n, 2), kVecThreads, 0, c->stream>>>(n, b, Ap, r, p, c->ws, fin, c->d_scalars, c->d_tmp_scalar);
+    k_init_residual<<<vec_grid(c, n, 2), kVecThreads, 0, c->stream>>>(n, b, Ap, r, p, c->ws, fin, c->d_scalars, out ? out : c->d_tmp_scalar);
     c->launches++;
     MGCG_LAUNCH_CHECK();
     return MGCG_OK;

@@ -35,7 +35,12 @@ struct Hierarchy {
 
 // ---- mg_setup.cu building blocks (also used by tests through the introspection API)
 int spgemm_esc(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C);
-int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C);   // mg_spgemm.cu
+// C = A * B where row j of B is selected by (A.col[k] - col_shift)                                   (mg_spgemm.cu)
+int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C, int col_shift = 0);
+int coo_to_csr_sum(mgcg_ctx *c, int rows, int cols, size_t count, unsigned long long *keys, double *vals, DevCsr *out);
+int build_prolongator(mgcg_ctx *c, const Csr &A, int row_base, const int *agg, const double *dinv, bool smooth, double omega,
+                      int ncoarse, DevCsr *P);
+int extract_dinv(mgcg_ctx *c, const Csr &A, int row_base, double *dinv);
 int csr_transpose(mgcg_ctx *c, const Csr &A, DevCsr *T);
 
 }  // namespace mgcg

@@ -46,12 +46,12 @@ static inline int grid_for(long long n, int threads = 256)
 }
 
 // ---------------------------------------------------------------------------------------------------------
-__global__ void k_extract_dinv(Csr A, double *dinv)
+__global__ void k_extract_dinv(Csr A, int row_base, double *dinv)
 {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x) {
         double d = 1.0;
         for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k)
-            if (A.col[k] == i) { d = A.val[k]; break; }
+            if (A.col[k] == i + row_base) { d = A.val[k]; break; }
         dinv[i] = 1.0 / d;
     }
 }
@@ -71,21 +71,22 @@ __global__ void k_agg_blocks(int n, int block, int *agg)
 }
 
 // plain aggregation: P = T (one unit entry per row)
-__global__ void k_build_T(int n, const int *agg, double *val, int *rowptr, int *col)
+__global__ void k_build_T(int n, int row_base, const int *agg, double *val, int *rowptr, int *col)
 {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i <= n; i += gridDim.x * blockDim.x) {
         rowptr[i] = i;
-        if (i < n) { val[i] = 1.0; col[i] = agg[i]; }
+        if (i < n) { val[i] = 1.0; col[i] = agg[i + row_base]; }
     }
 }
 
 // smoothed aggregation, expansion of P = T - w D^-1 A T : per row i the entry (agg[i], 1) FIRST, then for every
 // stored a_ik in storage order (agg[col_k], -(w*dinv_i)*a_ik).  Duplicates are summed later in this order.
-__global__ void k_expand_sa(Csr A, const int *agg, const double *dinv, double w, u64 *keys, double *vals)
+__global__ void k_expand_sa(Csr A, int row_base, const int *agg, const double *dinv, double w, u64 *keys, double *vals)
 {
+    const int nz0 = A.rowptr[0];   // A may be a row sub-block of a larger CSR
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x) {
-        size_t o = (size_t)A.rowptr[i] + i;
-        keys[o] = ((u64)i << 32) | (unsigned)agg[i];
+        size_t o = (size_t)(A.rowptr[i] - nz0) + i;
+        keys[o] = ((u64)i << 32) | (unsigned)agg[i + row_base];
         vals[o] = 1.0;
         ++o;
         const double f = -__dmul_rn(w, dinv[i]);
@@ -126,7 +127,7 @@ __global__ void k_compress(int uniq, const unsigned *pos, const u64 *keys, const
 static int bits_for(unsigned v) { int b = 1; while ((v >> b) != 0 && b < 32) ++b; return b; }
 
 // Sort `count` (key,val) pairs stably and compress to CSR rows [0,rows). keys/vals are consumed (scratch).
-static int coo_to_csr_sum(mgcg_ctx *c, int rows, int cols, size_t count, u64 *keys, double *vals, DevCsr *out)
+int coo_to_csr_sum(mgcg_ctx *c, int rows, int cols, size_t count, u64 *keys, double *vals, DevCsr *out)
 {
     cudaStream_t st = c->stream;
     out->rows = rows; out->cols = cols;
@@ -355,6 +356,37 @@ static int dense_inverse(mgcg_ctx *c, const Csr &A, double **Minv)
     return MGCG_OK;
 }
 
+// P = T (plain aggregation) or (I - w D^-1 A) T (smoothed) for the rows of A.  `agg` is indexed by GLOBAL row / column id
+// (row i of A is global row i + row_base); columns of P are aggregate ids.
+int build_prolongator(mgcg_ctx *c, const Csr &A, int row_base, const int *agg, const double *dinv, bool smooth, double omega,
+                      int ncoarse, DevCsr *P)
+{
+    cudaStream_t st = c->stream;
+    const int n = A.rows;
+    if (!smooth) {
+        P->rows = n; P->cols = ncoarse; P->nnz = n;
+        MGCG_CHECK(dalloc(&P->val, (size_t)n)); MGCG_CHECK(dalloc(&P->col, (size_t)n)); MGCG_CHECK(dalloc(&P->rowptr, (size_t)n + 1));
+        k_build_T<<<grid_for(n + 1), 256, 0, st>>>(n, row_base, agg, P->val, P->rowptr, P->col);
+        MGCG_LAUNCH_CHECK();
+        return MGCG_OK;
+    }
+    const size_t count = (size_t)A.nnz + n;
+    u64 *keys = nullptr; double *vals = nullptr;
+    MGCG_CHECK(dalloc(&keys, count)); MGCG_CHECK(dalloc(&vals, count));
+    k_expand_sa<<<grid_for(n), 256, 0, st>>>(A, row_base, agg, dinv, omega, keys, vals);
+    MGCG_LAUNCH_CHECK();
+    int s = coo_to_csr_sum(c, n, ncoarse, count, keys, vals, P);
+    cudaFree(keys); cudaFree(vals);
+    return s;
+}
+
+int extract_dinv(mgcg_ctx *c, const Csr &A, int row_base, double *dinv)
+{
+    k_extract_dinv<<<grid_for(A.rows), 256, 0, c->stream>>>(A, row_base, dinv);
+    MGCG_LAUNCH_CHECK();
+    return MGCG_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 static int alloc_level_vectors(MgLevel &L, bool level0)
 {
@@ -423,7 +455,7 @@ int mg_build(mgcg_ctx *c)
         MgLevel &L = H->L[l];
         const int n = L.A.rows;
         MGCG_CHECK(dalloc(&L.dinv, (size_t)n));
-        k_extract_dinv<<<grid_for(n), 256, 0, st>>>(L.A, L.dinv);
+        k_extract_dinv<<<grid_for(n), 256, 0, st>>>(L.A, 0, L.dinv);
         MGCG_LAUNCH_CHECK();
         MGCG_CHECK(alloc_level_vectors(L, l == 0));
         if (n <= coarse_size || l + 1 >= max_levels) break;
@@ -448,21 +480,7 @@ int mg_build(mgcg_ctx *c)
 
         // ---- prolongator
         const bool smooth_here = o.mg_smoothed && (o.mg_smoothed_levels <= 0 || l < o.mg_smoothed_levels);
-        if (!smooth_here) {
-            L.P.rows = n; L.P.cols = nc; L.P.nnz = n;
-            MGCG_CHECK(dalloc(&L.P.val, (size_t)n)); MGCG_CHECK(dalloc(&L.P.col, (size_t)n)); MGCG_CHECK(dalloc(&L.P.rowptr, (size_t)n + 1));
-            k_build_T<<<grid_for(n + 1), 256, 0, st>>>(n, L.agg, L.P.val, L.P.rowptr, L.P.col);
-            MGCG_LAUNCH_CHECK();
-        } else {
-            const size_t count = (size_t)L.A.nnz + n;
-            u64 *keys = nullptr; double *vals = nullptr;
-            MGCG_CHECK(dalloc(&keys, count)); MGCG_CHECK(dalloc(&vals, count));
-            k_expand_sa<<<grid_for(n), 256, 0, st>>>(L.A, L.agg, L.dinv, o.mg_prolong_omega, keys, vals);
-            MGCG_LAUNCH_CHECK();
-            int s = coo_to_csr_sum(c, n, nc, count, keys, vals, &L.P);
-            cudaFree(keys); cudaFree(vals);
-            MGCG_CHECK(s);
-        }
+        MGCG_CHECK(build_prolongator(c, L.A, 0, L.agg, L.dinv, smooth_here, o.mg_prolong_omega, nc, &L.P));
         tr.mark(l, "P");
         MGCG_CHECK(csr_transpose(c, L.P.view(), &L.R));
         tr.mark(l, "R=P^T");

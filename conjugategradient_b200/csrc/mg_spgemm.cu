@@ -30,7 +30,7 @@ __device__ __forceinline__ unsigned group_mask()
 // walk them in storage order by shuffle broadcast; the first G entries of the NEXT B row are prefetched while the current
 // ones are inserted.  NUMERIC = false: count distinct columns (returns this lane's share);  true: accumulate values.
 template <int G, bool NUMERIC>
-__device__ __forceinline__ int spgemm_row(const Csr &A, const Csr &B, int row, int lane, unsigned mask, int cap_mask,
+__device__ __forceinline__ int spgemm_row(const Csr &A, const Csr &B, int shift, int row, int lane, unsigned mask, int cap_mask,
                                           int *keys, double *vals, int *overflow)
 {
     int mine = 0;
@@ -40,7 +40,7 @@ __device__ __forceinline__ int spgemm_row(const Csr &A, const Csr &B, int row, i
         int q0_l = 0, q1_l = 0;
         double a_l = 0.0;
         if (kk < ke) {
-            const int j = A.col[kk];
+            const int j = A.col[kk] - shift;
             if (NUMERIC) a_l = A.val[kk];
             q0_l = B.rowptr[j]; q1_l = B.rowptr[j + 1];
         }
@@ -78,7 +78,7 @@ __device__ __forceinline__ int spgemm_row(const Csr &A, const Csr &B, int row, i
 
 // ---- symbolic: cnt[row] = number of distinct columns of row `row` of A*B
 template <int G>
-__global__ void __launch_bounds__(256) k_spgemm_symbolic(Csr A, Csr B, int cap, int *__restrict__ cnt, int *__restrict__ overflow)
+__global__ void __launch_bounds__(256) k_spgemm_symbolic(Csr A, Csr B, int shift, int cap, int *__restrict__ cnt, int *__restrict__ overflow)
 {
     extern __shared__ int sm_keys[];
     const int gpb = blockDim.x / G;
@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(256) k_spgemm_symbolic(Csr A, Csr B, int cap, 
     for (int row = blockIdx.x * gpb + threadIdx.x / G; row < A.rows; row += gridDim.x * gpb) {
         for (int s = lane; s < cap; s += G) keys[s] = kEmpty;
         __syncwarp(mask);
-        int mine = spgemm_row<G, false>(A, B, row, lane, mask, cap - 1, keys, nullptr, overflow);
+        int mine = spgemm_row<G, false>(A, B, shift, row, lane, mask, cap - 1, keys, nullptr, overflow);
 #pragma unroll
         for (int o = G / 2; o > 0; o >>= 1) mine += __shfl_down_sync(mask, mine, o, G);
         if (lane == 0) cnt[row] = mine;
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(256) k_spgemm_symbolic(Csr A, Csr B, int cap, 
 
 // ---- numeric: fill row `row` of C (columns ascending)
 template <int G>
-__global__ void __launch_bounds__(256) k_spgemm_numeric(Csr A, Csr B, int cap, const int *__restrict__ c_rowptr,
+__global__ void __launch_bounds__(256) k_spgemm_numeric(Csr A, Csr B, int shift, int cap, const int *__restrict__ c_rowptr,
                                                         int *__restrict__ c_col, double *__restrict__ c_val)
 {
     extern __shared__ double sm_raw[];
@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(256) k_spgemm_numeric(Csr A, Csr B, int cap, c
     for (int row = blockIdx.x * gpb + threadIdx.x / G; row < A.rows; row += gridDim.x * gpb) {
         for (int s = lane; s < cap; s += G) { keys[s] = kEmpty; vals[s] = 0.0; }
         __syncwarp(mask);
-        spgemm_row<G, true>(A, B, row, lane, mask, cap - 1, keys, vals, nullptr);
+        spgemm_row<G, true>(A, B, shift, row, lane, mask, cap - 1, keys, vals, nullptr);
         // empty slots sort to the end
         for (int s = lane; s < cap; s += G) if (keys[s] == kEmpty) keys[s] = 0x7fffffff;
         __syncwarp(mask);
@@ -135,12 +135,12 @@ __global__ void __launch_bounds__(256) k_spgemm_numeric(Csr A, Csr B, int cap, c
 }
 
 // max over rows of the product count (upper bound of the distinct columns of a row of C), clipped to int
-__global__ void k_spgemm_maxprod(Csr A, Csr B, int *out_max)
+__global__ void k_spgemm_maxprod(Csr A, Csr B, int shift, int *out_max)
 {
     int m = 0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x) {
         long long s = 0;
-        for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k) { const int j = A.col[k]; s += B.rowptr[j + 1] - B.rowptr[j]; }
+        for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k) { const int j = A.col[k] - shift; s += B.rowptr[j + 1] - B.rowptr[j]; }
         m = max(m, (int)min(s, (long long)0x7fffffff));
     }
     for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_down_sync(0xffffffffu, m, o));
@@ -150,7 +150,7 @@ __global__ void k_spgemm_maxprod(Csr A, Csr B, int *out_max)
 static int pow2_at_least(long long v) { int p = 32; while (p < v) p <<= 1; return p; }
 
 template <int G>
-static int run_hash(mgcg_ctx *c, const Csr &A, const Csr &B, int maxprod, DevCsr *C, bool *done)
+static int run_hash(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, int maxprod, DevCsr *C, bool *done)
 {
     cudaStream_t st = c->stream;
     *done = false;
@@ -173,7 +173,7 @@ static int run_hash(mgcg_ctx *c, const Csr &A, const Csr &B, int maxprod, DevCsr
         const int gpb = threads / G;
         grid = (A.rows + gpb - 1) / gpb;
         if (grid > cap_grid) grid = cap_grid;
-        k_spgemm_symbolic<G><<<grid, threads, sm_s, st>>>(A, B, cap_s, cnt, cnt + A.rows + 2);
+        k_spgemm_symbolic<G><<<grid, threads, sm_s, st>>>(A, B, shift, cap_s, cnt, cnt + A.rows + 2);
         MGCG_LAUNCH_CHECK();
         int ov = 0;
         MGCG_CUDA(cudaMemcpyAsync(&ov, cnt + A.rows + 2, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -211,23 +211,23 @@ static int run_hash(mgcg_ctx *c, const Csr &A, const Csr &B, int maxprod, DevCsr
     const int gpb_n = threads / G;
     grid = (A.rows + gpb_n - 1) / gpb_n;
     if (grid > cap_grid) grid = cap_grid;
-    k_spgemm_numeric<G><<<grid, threads, sm_n, st>>>(A, B, cap_n, C->rowptr, C->col, C->val);
+    k_spgemm_numeric<G><<<grid, threads, sm_n, st>>>(A, B, shift, cap_n, C->rowptr, C->col, C->val);
     MGCG_LAUNCH_CHECK();
     *done = true;
     return MGCG_OK;
 }
 
 // C = A * B.  Uses the shared-memory hash kernels; falls back to spgemm_esc for rows too wide for the tables.
-int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C)
+int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C, int col_shift)
 {
     cudaStream_t st = c->stream;
-    if (A.rows <= 0 || A.nnz <= 0 || B.nnz <= 0) return spgemm_esc(c, A, B, C);
+    if ((A.rows <= 0 || A.nnz <= 0 || B.nnz <= 0) && col_shift == 0) return spgemm_esc(c, A, B, C);
     int *d_max = nullptr, maxprod = 0;
     MGCG_CUDA(cudaMalloc((void **)&d_max, sizeof(int)));
     MGCG_CUDA(cudaMemsetAsync(d_max, 0, sizeof(int), st));
     int g = (A.rows + 255) / 256;
     if (g > c->sm_count * 16) g = c->sm_count * 16;
-    k_spgemm_maxprod<<<g, 256, 0, st>>>(A, B, d_max);
+    k_spgemm_maxprod<<<g, 256, 0, st>>>(A, B, col_shift, d_max);
     MGCG_LAUNCH_CHECK();
     MGCG_CUDA(cudaMemcpyAsync(&maxprod, d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
     MGCG_CUDA(cudaStreamSynchronize(st));
@@ -235,12 +235,13 @@ int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C)
     const double avg_b = (double)B.nnz / (B.rows > 0 ? B.rows : 1);
     bool done = false;
     int s;
-    if (avg_b <= 4.5) s = run_hash<4>(c, A, B, maxprod, C, &done);
-    else if (avg_b <= 10.0) s = run_hash<8>(c, A, B, maxprod, C, &done);
-    else if (avg_b <= 20.0) s = run_hash<16>(c, A, B, maxprod, C, &done);
-    else s = run_hash<32>(c, A, B, maxprod, C, &done);
+    if (avg_b <= 4.5) s = run_hash<4>(c, A, B, col_shift, maxprod, C, &done);
+    else if (avg_b <= 10.0) s = run_hash<8>(c, A, B, col_shift, maxprod, C, &done);
+    else if (avg_b <= 20.0) s = run_hash<16>(c, A, B, col_shift, maxprod, C, &done);
+    else s = run_hash<32>(c, A, B, col_shift, maxprod, C, &done);
     MGCG_CHECK(s);
     if (done) return MGCG_OK;
+    if (col_shift != 0) { set_error("spgemm: rows too wide for the hash tables on a shifted (sharded) product"); return MGCG_ERR_UNSUPPORTED; }
     return spgemm_esc(c, A, B, C);
 }
 

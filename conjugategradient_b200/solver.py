@@ -316,3 +316,52 @@ class Mgcg:
             self.close()
         except Exception:
             pass
+
+
+class MgcgDist:
+    """One-process-per-GPU sharded solve (mgcg_comm_init / mgcg_setup_dist / mgcg_solve_dist): the native replacement of
+    ConjugateGradientParallelGpu (cs:264-594).  Rank r owns rows [row_offset, row_offset + local_count) with GLOBAL column
+    indices and row offsets rebased to 0 (Mgcg.cu:73).  The 128-byte communicator id is created on rank 0 (`unique_id`)
+    and handed to the other ranks out of band (e.g. torch.distributed.broadcast)."""
+
+    @staticmethod
+    def unique_id():
+        buf = C.create_string_buffer(128)
+        check(_lib.lib().mgcg_comm_unique_id(buf), "mgcg_comm_unique_id")
+        return buf.raw
+
+    def __init__(self, device, rank, world, id_bytes, use_torch_stream=False):
+        self.L = _lib.lib()
+        self.ctx = self.L.mgcg_create(device)
+        if not self.ctx:
+            raise RuntimeError("mgcg_create failed: " + _lib.last_error())
+        self.rank, self.world = rank, world
+        if use_torch_stream:
+            import torch
+            check(self.L.mgcg_set_stream(self.ctx, C.c_void_p(torch.cuda.current_stream(device).cuda_stream)), "mgcg_set_stream")
+        check(self.L.mgcg_comm_init(self.ctx, C.c_char_p(id_bytes), rank, world), "mgcg_comm_init")
+        self._keep = None
+
+    def setup(self, global_count, row_offset, val, rowptr, col, options=None):
+        self._keep = (val, rowptr, col)
+        self.options = options if options is not None else default_options()
+        check(self.L.mgcg_setup_dist(self.ctx, global_count, row_offset, rowptr.numel() - 1, val.numel(), _p(val), _p(rowptr), _p(col),
+                                     C.byref(self.options)), "mgcg_setup_dist")
+
+    def solve(self, b_local, x_local, raise_on_fail=True):
+        res = Result()
+        s = self.L.mgcg_solve_dist(self.ctx, _p(b_local), _p(x_local), C.byref(res))
+        if s != _lib.OK and raise_on_fail:
+            raise MgcgError(s, "mgcg_solve_dist")
+        return res
+
+    def close(self):
+        if self.ctx:
+            self.L.mgcg_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -69,7 +69,9 @@ typedef struct mgcg_options {
                                   aggregation below (0 = every level).  Smoothing widens the coarse stencils level by level. */
     int    mg_aggregate_size;        /* geometric aggregates are s x s x s grid blocks on level 0 (default 3; needs nx,ny,nz) */
     int    mg_aggregate_size_coarse; /* the same for levels >= 1 (default 2; 0 = as level 0) */
-    int    reserved[5];
+    int    dist_replicate_below;     /* sharded solve: levels with fewer global rows than this are replicated on every
+                                        rank (all-gathered right-hand side, redundant coarse solve); default 1<<20 */
+    int    reserved[4];
 } mgcg_options;
 
 typedef struct mgcg_result {

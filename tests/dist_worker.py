@@ -1,0 +1,71 @@
+"""Worker of the sharded-solve tests: run under torchrun, one rank per GPU (tests/test_gpu_dist.py launches it).
+Solves the same system (a) sharded over WORLD_SIZE GPUs and (b) on this rank's GPU alone, and compares."""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from conjugategradient_b200 import generators as g  # noqa: E402
+from conjugategradient_b200 import solver as S  # noqa: E402
+
+
+def main():
+    cfg = json.loads(sys.argv[1])
+    rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(lr)
+    dev = torch.device("cuda", lr)
+    dist.init_process_group("gloo")
+    n = cfg["n"]
+    N = n ** 3
+    if cfg.get("matrix", "p3d7") == "p3d7":
+        v, rp, c = g.poisson3d7(n)
+    else:
+        v, rp, c = g.poisson3d27_varcoef(n)
+    b = g.rhs_uniform(N, 0)
+    # plane-aligned row blocks (== the reference's floor rule, ConjugateGradientParallelGpu.cs:271-277, when world | n)
+    planes = [n // world] * world
+    planes[-1] += n - sum(planes)
+    offs = np.concatenate([[0], np.cumsum(planes)]) * n * n
+    r0, r1 = int(offs[rank]), int(offs[rank + 1])
+    e0, e1 = int(rp[r0]), int(rp[r1])
+    tv = torch.as_tensor(v[e0:e1]).to(dev)
+    tc = torch.as_tensor(c[e0:e1]).to(dev)
+    tr = torch.as_tensor((rp[r0:r1 + 1] - rp[r0]).astype(np.int32)).to(dev)
+    tb = torch.as_tensor(b[r0:r1]).to(dev)
+    tx = torch.zeros(r1 - r0, dtype=torch.float64, device=dev)
+    ids = [S.MgcgDist.unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(ids, src=0)
+    m = S.MgcgDist(lr, rank, world, ids[0])
+    kw = dict(cfg.get("options", {}))
+    if kw.get("precond", 0) == 1 and cfg.get("hint", True):
+        kw.update(nx=n, ny=n, nz=n)
+    o = S.default_options(norm=2, tolerance=1e-8, max_iteration=2000, **kw)
+    m.setup(N, r0, tv, tr, tc, o)
+    res = m.solve(tb, tx)
+    torch.cuda.synchronize()
+    # the same system on this GPU alone
+    ms = S.Mgcg(lr)
+    fv, fr, fc, fb = (torch.as_tensor(a).to(dev) for a in (v, rp, c, b))
+    fx = torch.zeros(N, dtype=torch.float64, device=dev)
+    ms.setup(fv, fr, fc, o)
+    rs = ms.solve(fb, fx)
+    torch.cuda.synchronize()
+    err = float((tx - fx[r0:r1]).abs().max() / fx.abs().max())
+    out = {"rank": rank, "it_dist": res.iterations_done, "it_single": rs.iterations_done, "err": err, "residual": res.residual,
+           "levels": res.levels, "first_replicated": res.reserved[2], "halo_exchanges": res.reserved[0], "allgathers": res.reserved[1],
+           "solve_ms": res.solve_ms, "setup_ms": res.setup_ms, "single_ms": rs.solve_ms, "launches": res.kernel_launches}
+    allo = [None] * world
+    dist.all_gather_object(allo, out)
+    if rank == 0:
+        print("DIST_RESULT " + json.dumps(allo), flush=True)
+    m.close(); ms.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
