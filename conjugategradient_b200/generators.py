@@ -63,12 +63,16 @@ def banded_sin(n, max_nonzero=160):
     return val, rp.astype(np.int32), col, b, x0
 
 
-def _stencil_csr(dims, offsets, coef_fn):
+def _stencil_csr(dims, offsets, coef_fn, zrange=None):
     """Generic structured stencil -> CSR with diagonal first. offsets: list of (dx,dy,dz) excluding (0,0,0).
-    coef_fn(mask_idx, off_index) -> off-diagonal values for the rows in mask."""
+    coef_fn(mask_idx, off_index) -> off-diagonal values for the rows in mask.
+    zrange=(z0, z1): only the rows of planes z0 <= z < z1 (a shard), column indices stay global, row offsets start at 0."""
     nx, ny, nz = dims
-    n = nx * ny * nz
-    idx = np.arange(n, dtype=np.int64)
+    if zrange is None:
+        idx = np.arange(nx * ny * nz, dtype=np.int64)
+    else:
+        idx = np.arange(zrange[0] * nx * ny, zrange[1] * nx * ny, dtype=np.int64)
+    n = len(idx)
     x = idx % nx
     y = (idx // nx) % ny
     z = idx // (nx * ny)
@@ -100,12 +104,12 @@ def poisson2d5(nx, ny):
     return val, rp.astype(np.int32), col
 
 
-def poisson3d7(nx, ny=None, nz=None):
-    """C2/C4: 3-D 7-point Poisson, diag 6, off -1, homogeneous Dirichlet eliminated."""
+def poisson3d7(nx, ny=None, nz=None, zrange=None):
+    """C2/C4: 3-D 7-point Poisson, diag 6, off -1, homogeneous Dirichlet eliminated.  zrange: see _stencil_csr."""
     ny = nx if ny is None else ny
     nz = nx if nz is None else nz
     offs = [(-1, 0, 0), (1, 0, 0), (0, -1, 0), (0, 1, 0), (0, 0, -1), (0, 0, 1)]
-    val, rp, col, n = _stencil_csr((nx, ny, nz), offs, lambda idx, o: -1.0)
+    val, rp, col, n = _stencil_csr((nx, ny, nz), offs, lambda idx, o: -1.0, zrange)
     val[rp[:-1]] = 6.0
     assert rp[-1] < 2 ** 31
     return val, rp.astype(np.int32), col
