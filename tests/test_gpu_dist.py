@@ -1,0 +1,41 @@
+"""Sharded solve (mgcg_setup_dist / mgcg_solve_dist) against the single-GPU solve of the same system; needs >= 2 GPUs.
+One process per GPU under torchrun (tests/dist_worker.py)."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _gpus():
+    import torch
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+CASES = [
+    ("plain_cg", {"n": 32, "options": {"precond": 0}}),
+    ("mg_replicated", {"n": 32, "options": {"precond": 1}}),                                  # whole hierarchy replicated
+    ("mg_two_sharded_levels", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000}}),
+    ("mg_no_grid_hint", {"n": 32, "hint": False, "options": {"precond": 1, "dist_replicate_below": 1000}}),
+]
+
+
+@pytest.mark.parametrize("name,cfg", CASES, ids=[c[0] for c in CASES])
+def test_sharded_matches_single_gpu(name, cfg):
+    if _gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29541", os.path.join(ROOT, "tests", "dist_worker.py"), json.dumps(cfg)]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    line = [l for l in out.stdout.splitlines() if l.startswith("DIST_RESULT ")]
+    assert out.returncode == 0 and line, out.stdout[-2000:] + out.stderr[-2000:]
+    res = json.loads(line[0][len("DIST_RESULT "):])
+    for r in res:
+        assert abs(r["it_dist"] - r["it_single"]) <= 1, r      # iteration count within +-1
+        assert r["err"] <= 1e-10 if r["it_dist"] == r["it_single"] else r["err"] <= 1e-6, r
+        assert r["residual"] < 1e-8
+    assert len({r["it_dist"] for r in res}) == 1 and len({r["residual"] for r in res}) == 1   # identical scalars on all ranks
