@@ -87,6 +87,7 @@ struct Csr {
 // SpMV plan: kernel choice and launch geometry for one matrix
 struct SpmvPlan {
     int kernel = MGCG_SPMV_STREAM;  // STREAM or VECTOR
+    bool tma = false;               // STREAM: use the TMA-staged variant (short rows, 16-byte aligned val/col)
     int rows_per_tile = 256;        // STREAM: rows handled per tile (<= 256)
     int lanes = 8;                  // VECTOR: lanes per row
     int grid = 0;

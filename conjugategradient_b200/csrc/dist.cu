@@ -324,6 +324,7 @@ static int dist_build_next(mgcg_ctx *c, int l, DevCsr *Ac_out)
     MGCG_CUDA(cudaMemcpy(&pn[1], L.P.rowptr + own, sizeof(int), cudaMemcpyDeviceToHost));
     L.P.nnz = pn[1] - pn[0];
     L.planP = spmv_make_plan(c, own, L.P.nnz, MGCG_SPMV_AUTO);
+    L.P.nnz = L.Pext.nnz;   // the view addresses val/col with the parent's absolute offsets
     L.planR = spmv_make_plan(c, L.R.rows, L.R.nnz, MGCG_SPMV_AUTO);
     MGCG_CUDA(cudaStreamSynchronize(st));
     cudaFree(rp_lo); cudaFree(rp_hi); cudaFree(agg); cudaFree(dinv_ext);

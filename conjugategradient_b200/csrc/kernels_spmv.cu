@@ -77,6 +77,140 @@ __global__ void __launch_bounds__(kSpmvThreads) k_spmv_stream(SpmvArgs a, int ro
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// STREAM-TMA: the same tiling, but the contiguous val/col slice of a tile is brought into shared memory by the TMA engine
+// (cp.async.bulk, 1-D, completion on an mbarrier) into a ring of stages, one or more tiles ahead of the threads that
+// consume it.  The ncu capture of the plain stream kernel shows it latency-bound on the dependent chain
+// rowptr -> (val,col) -> x[col] between block barriers (stall long_scoreboard, DRAM 50 %); here the chain is cut: row
+// pointers are prefetched a tile ahead in registers, val/col arrive asynchronously, and there is no block barrier in the
+// steady state — a thread that has finished its row only arrives on the stage's `empty` mbarrier and moves on.
+// One thread per row walks its segment from shared memory in storage order with explicit mul/add roundings.
+constexpr int kTmaRows = 256;                 // rows per tile == threads per block
+constexpr int kTmaCap = 1920;                 // non-zeros a stage can hold: 2 stages x (8+4) B x 1920 = 45 KB static smem
+constexpr int kTmaStages = 2;
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long *bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+{
+    unsigned ok;
+    do {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, unsigned bytes, unsigned long long *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+struct TmaMeta { int k0, k1, direct, pad; };
+
+template <int EPI>
+__global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles, ReduceWs ws, Scalars *sc)
+{
+    if (a.gated && sc->done) return;
+    __shared__ __align__(16) double s_val[kTmaStages][kTmaCap + 2];
+    __shared__ __align__(16) int s_col[kTmaStages][kTmaCap + 4];
+    __shared__ __align__(8) unsigned long long s_full[kTmaStages], s_empty[kTmaStages];
+    __shared__ TmaMeta s_meta[kTmaStages];
+    const int t = threadIdx.x;
+    const double *__restrict__ val = a.A.val;
+    const int *__restrict__ col = a.A.col;
+    const int *__restrict__ rowptr = a.A.rowptr;
+    const double *__restrict__ x = a.x;
+    const int rows = a.A.rows;
+    const long long nnz_end = (long long)a.A.nnz;     // entries val/col are known to hold (sub-block views pass the parent's)
+    double dsum = 0.0;
+
+    if (t == 0) {
+        for (int s = 0; s < kTmaStages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], kTmaRows); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    // the block's tiles: blockIdx.x, blockIdx.x + gridDim.x, ...
+    const int my_tiles = (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+    // producer state (thread 0): issue the slice of local tile `j` into stage j % S
+    auto issue = [&](int j) {
+        const int s = j % kTmaStages;
+        const int tile = blockIdx.x + j * gridDim.x;
+        const int r0 = tile * kTmaRows;
+        const int nr = min(kTmaRows, rows - r0);
+        const int k0 = rowptr[r0], k1 = rowptr[r0 + nr];
+        const int ka = k0 & ~1, kc = k0 & ~3;
+        const unsigned vb = (unsigned)(((k1 - ka) * 8 + 15) & ~15), cb = (unsigned)(((k1 - kc) * 4 + 15) & ~15);
+        const bool fits = (k1 - ka) <= kTmaCap && (k1 - kc) <= kTmaCap && k1 > k0 &&
+                          ((long long)ka * 8 + vb <= nnz_end * 8) && ((long long)kc * 4 + cb <= nnz_end * 4);
+        s_meta[s].k0 = k0; s_meta[s].k1 = k1; s_meta[s].direct = fits ? 0 : 1;
+        if (fits) {
+            mbar_arrive_expect_tx(&s_full[s], vb + cb);
+            tma_load_1d(&s_val[s][0], val + ka, vb, &s_full[s]);
+            tma_load_1d(&s_col[s][0], col + kc, cb, &s_full[s]);
+        } else {
+            mbar_arrive(&s_full[s]);
+        }
+    };
+    if (t == 0)
+        for (int j = 0; j < kTmaStages && j < my_tiles; ++j) issue(j);
+
+    // row pointers of this thread's row in the first tile
+    int rs_n = 0, re_n = 0;
+    {
+        const int r = blockIdx.x * kTmaRows + t;
+        if (my_tiles > 0 && r < rows) { rs_n = rowptr[r]; re_n = rowptr[r + 1]; }
+    }
+    for (int j = 0; j < my_tiles; ++j) {
+        const int s = j % kTmaStages;
+        const unsigned parity = (unsigned)((j / kTmaStages) & 1);
+        const int tile = blockIdx.x + j * gridDim.x;
+        const int row = tile * kTmaRows + t;
+        const int rs = rs_n, re = re_n;
+        // prefetch the next tile's row pointers while this one is processed
+        rs_n = re_n = 0;
+        if (j + 1 < my_tiles) {
+            const int rn = (tile + gridDim.x) * kTmaRows + t;
+            if (rn < rows) { rs_n = rowptr[rn]; re_n = rowptr[rn + 1]; }
+        }
+        mbar_wait(&s_full[s], parity);
+        double acc = 0.0;
+        if (row < rows) {
+            if (!s_meta[s].direct) {
+                const int k0 = s_meta[s].k0;
+                const double *sv = &s_val[s][0] - (k0 & ~1);
+                const int *scl = &s_col[s][0] - (k0 & ~3);
+                for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(sv[k], x[scl[k]]));
+            } else {
+                for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(__ldcs(val + k), x[__ldcs(col + k)]));
+            }
+        }
+        mbar_arrive(&s_empty[s]);                 // this thread is done with the stage
+        if (t == 0 && j + kTmaStages < my_tiles) {
+            mbar_wait(&s_empty[s], parity);       // ... and once every thread is, refill it
+            issue(j + kTmaStages);
+        }
+        if (row < rows) epilogue<EPI>(row, acc, a, dsum);
+    }
+    if (EpiTraits<EPI>::reduces) {
+        double m = 0.0;
+        block_reduce<false>(dsum, m);
+        grid_reduce_finish<false>(dsum, m, ws, a.fin, sc, a.out);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 template <int EPI, int L>
 __global__ void __launch_bounds__(kSpmvThreads) k_spmv_vector(SpmvArgs a, ReduceWs ws, Scalars *sc)
 {
@@ -118,6 +252,8 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel)
     if (cap > kMaxPartials) cap = kMaxPartials;
     if (kernel == MGCG_SPMV_AUTO) kernel = (avg <= 48.0) ? MGCG_SPMV_STREAM : MGCG_SPMV_VECTOR;
     p.kernel = kernel;
+    // short rows (a 256-row tile fits a TMA stage): the TMA-staged variant of the stream kernel
+    p.tma = (kernel == MGCG_SPMV_STREAM && avg * kTmaRows <= kTmaCap - 64);
     if (kernel == MGCG_SPMV_STREAM) {
         int per = (int)(avg + 0.999);
         if (per < 1) per = 1;
@@ -142,7 +278,13 @@ template <int EPI>
 static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
 {
     if (a.A.rows <= 0) return MGCG_OK;
-    if (plan.kernel == MGCG_SPMV_STREAM) {
+    const bool aligned = ((((uintptr_t)a.A.val) | ((uintptr_t)a.A.col)) & 15u) == 0;
+    if (plan.kernel == MGCG_SPMV_STREAM && plan.tma && aligned) {
+        const int tiles = div_up(a.A.rows, kTmaRows);
+        int grid = c->sm_count * 4;
+        if (grid > tiles) grid = tiles;
+        k_spmv_tma<EPI><<<grid, kTmaRows, 0, c->stream>>>(a, tiles, c->ws, c->d_scalars);
+    } else if (plan.kernel == MGCG_SPMV_STREAM) {
         int tiles = div_up(a.A.rows, plan.rows_per_tile);
         k_spmv_stream<EPI><<<plan.grid, kSpmvThreads, 0, c->stream>>>(a, plan.rows_per_tile, tiles, c->ws, c->d_scalars);
     } else {
