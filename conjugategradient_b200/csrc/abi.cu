@@ -105,6 +105,13 @@ mgcg_ctx *mgcg_create(int device)
     ok = ok && cudaMemset(c->ws.ticket, 0, sizeof(unsigned int)) == cudaSuccess;
     ok = ok && cudaMemset(c->d_scalars, 0, sizeof(Scalars)) == cudaSuccess;
     if (!ok) { set_error("mgcg_create: allocation failed: %s", cudaGetErrorString(cudaGetLastError())); mgcg_destroy(c); return nullptr; }
+    {   // keep freed hierarchy-build blocks in the device pool instead of returning them to the driver at every sync
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+            unsigned long long keep = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+    }
     mgcg_options_default(&c->opt);
     return c;
 }

@@ -198,6 +198,10 @@ void dist_free(mgcg_ctx *c);
 int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res);
 
 // ---- helpers
+// Stream-ordered allocation for the hierarchy build (cudaMallocAsync from the device's pool: no device-wide
+// synchronisation per call, blocks are reused between phases).  Memory obtained here may be released with cudaFree too.
+inline cudaError_t pool_alloc(void **p, size_t bytes, cudaStream_t st) { return cudaMallocAsync(p, bytes ? bytes : 1, st); }
+inline void pool_free(void *p, cudaStream_t st) { if (p) cudaFreeAsync(p, st); }
 int ctx_ensure_work(mgcg_ctx *c, int n);
 inline int div_up(int a, int b) { return (a + b - 1) / b; }
 

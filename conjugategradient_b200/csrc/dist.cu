@@ -424,6 +424,7 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
     const int W = D->world, rk = D->rank;
     const mgcg_options &o = c->opt;
     dist_free_levels(D);
+    set_alloc_stream(st);
     // ---- the partition: all-gather of the local row counts (ConjugateGradientParallelGpu.cs:271-277 is the caller's rule)
     int offs[kMaxRanks + 1];
     {

@@ -40,6 +40,7 @@ int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C, int col_shift = 0
 int coo_to_csr_sum(mgcg_ctx *c, int rows, int cols, size_t count, unsigned long long *keys, double *vals, DevCsr *out);
 int build_prolongator(mgcg_ctx *c, const Csr &A, int row_base, const int *agg, const double *dinv, bool smooth, double omega,
                       int ncoarse, DevCsr *P);
+void set_alloc_stream(cudaStream_t st);   // stream used by the build helpers' pool allocations on this host thread
 int extract_dinv(mgcg_ctx *c, const Csr &A, int row_base, double *dinv);
 int csr_transpose(mgcg_ctx *c, const Csr &A, DevCsr *T);
 

@@ -20,14 +20,18 @@ namespace mgcg {
 
 typedef unsigned long long u64;
 
+static thread_local cudaStream_t g_alloc_stream = nullptr;   // stream of the build in flight on this host thread
+void set_alloc_stream(cudaStream_t st) { g_alloc_stream = st; }
+
 template <class T>
 static int dalloc(T **p, size_t n)
 {
     *p = nullptr;
     if (n == 0) n = 1;
-    MGCG_CUDA(cudaMalloc((void **)p, n * sizeof(T)));
+    MGCG_CUDA(pool_alloc((void **)p, n * sizeof(T), g_alloc_stream));
     return MGCG_OK;
 }
+static inline void tfree(void *p) { pool_free(p, g_alloc_stream); }
 
 void DevCsr::free_all()
 {
@@ -147,9 +151,9 @@ int coo_to_csr_sum(mgcg_ctx *c, int rows, int cols, size_t count, u64 *keys, dou
     size_t tmp_bytes = 0;
     MGCG_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, (long long)count, 0, end_bit, st));
     void *tmp = nullptr;
-    MGCG_CUDA(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1));
+    MGCG_CUDA(pool_alloc(&tmp, tmp_bytes, st));
     MGCG_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, dk, dv, (long long)count, 0, end_bit, st));
-    cudaFree(tmp);
+    tfree(tmp);
     const u64 *sk = dk.Current(); const double *sv = dv.Current();
 
     int *head = nullptr, *idx = nullptr;
@@ -158,9 +162,9 @@ int coo_to_csr_sum(mgcg_ctx *c, int rows, int cols, size_t count, u64 *keys, dou
     MGCG_LAUNCH_CHECK();
     size_t sbytes = 0;
     MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, sbytes, head, idx, (long long)count, st));
-    MGCG_CUDA(cudaMalloc(&tmp, sbytes ? sbytes : 1));
+    MGCG_CUDA(pool_alloc(&tmp, sbytes, st));
     MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, sbytes, head, idx, (long long)count, st));
-    cudaFree(tmp);
+    tfree(tmp);
     int last_idx = 0, last_head = 0;
     MGCG_CUDA(cudaMemcpyAsync(&last_idx, idx + count - 1, sizeof(int), cudaMemcpyDeviceToHost, st));
     MGCG_CUDA(cudaMemcpyAsync(&last_head, head + count - 1, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -178,11 +182,11 @@ int coo_to_csr_sum(mgcg_ctx *c, int rows, int cols, size_t count, u64 *keys, dou
     k_compress<<<grid_for(uniq), 256, 0, st>>>(uniq, pos, sk, sv, out->val, out->col, rowcnt);
     MGCG_LAUNCH_CHECK();
     MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, sbytes, rowcnt, out->rowptr, rows + 1, st));
-    MGCG_CUDA(cudaMalloc(&tmp, sbytes ? sbytes : 1));
+    MGCG_CUDA(pool_alloc(&tmp, sbytes, st));
     MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, sbytes, rowcnt, out->rowptr, rows + 1, st));
     MGCG_CUDA(cudaStreamSynchronize(st));
-    cudaFree(tmp);
-    cudaFree(rowcnt); cudaFree(pos); cudaFree(head); cudaFree(idx); cudaFree(keys2); cudaFree(vals2);
+    tfree(tmp);
+    tfree(rowcnt); tfree(pos); tfree(head); tfree(idx); tfree(keys2); tfree(vals2);
     return MGCG_OK;
 }
 
@@ -234,10 +238,10 @@ int spgemm_esc(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C)
     MGCG_LAUNCH_CHECK();
     size_t sbytes = 0; void *tmp = nullptr;
     MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, sbytes, cnt, off, A.rows + 1, st));
-    MGCG_CUDA(cudaMalloc(&tmp, sbytes ? sbytes : 1));
+    MGCG_CUDA(pool_alloc(&tmp, sbytes, st));
     MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, sbytes, cnt, off, A.rows + 1, st));
     MGCG_CUDA(cudaStreamSynchronize(st));
-    cudaFree(tmp); cudaFree(cnt);
+    tfree(tmp); tfree(cnt);
     int *d_end = nullptr; long long *d_cnt = nullptr;
     MGCG_CHECK(dalloc(&d_end, 1)); MGCG_CHECK(dalloc(&d_cnt, 1));
 
@@ -259,11 +263,11 @@ int spgemm_esc(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C)
         }
         DevCsr part;
         MGCG_CHECK(coo_to_csr_sum(c, row1 - row0, B.cols, (size_t)count, keys, vals, &part));
-        cudaFree(keys); cudaFree(vals);
+        tfree(keys); tfree(vals);
         parts.push_back(part); part_row0.push_back(row0);
         row0 = row1;
     }
-    cudaFree(off); cudaFree(d_end); cudaFree(d_cnt);
+    tfree(off); tfree(d_end); tfree(d_cnt);
     // concatenate
     if (parts.size() == 1) { *C = parts[0]; C->rows = A.rows; C->cols = B.cols; return MGCG_OK; }
     long long total = 0;
@@ -303,7 +307,7 @@ int csr_transpose(mgcg_ctx *c, const Csr &A, DevCsr *T)
     k_transpose_expand<<<grid_for(A.rows), 256, 0, c->stream>>>(A, keys, vals);
     MGCG_LAUNCH_CHECK();
     int s = coo_to_csr_sum(c, A.cols, A.rows, (size_t)A.nnz, keys, vals, T);
-    cudaFree(keys); cudaFree(vals);
+    tfree(keys); tfree(vals);
     return s;
 }
 
@@ -351,7 +355,7 @@ static int dense_inverse(mgcg_ctx *c, const Csr &A, double **Minv)
     }
     MGCG_LAUNCH_CHECK();
     MGCG_CUDA(cudaStreamSynchronize(st));
-    cudaFree(colk); cudaFree(rowk);
+    tfree(colk); tfree(rowk);
     *Minv = M;
     return MGCG_OK;
 }
@@ -376,7 +380,7 @@ int build_prolongator(mgcg_ctx *c, const Csr &A, int row_base, const int *agg, c
     k_expand_sa<<<grid_for(n), 256, 0, st>>>(A, row_base, agg, dinv, omega, keys, vals);
     MGCG_LAUNCH_CHECK();
     int s = coo_to_csr_sum(c, n, ncoarse, count, keys, vals, P);
-    cudaFree(keys); cudaFree(vals);
+    tfree(keys); tfree(vals);
     return s;
 }
 
@@ -431,6 +435,7 @@ struct PhaseTrace {
 
 int mg_build(mgcg_ctx *c)
 {
+    set_alloc_stream(c->stream);
     PhaseTrace tr(c->stream);
     mg_free(c);
     tr.mark(-1, "free-old");

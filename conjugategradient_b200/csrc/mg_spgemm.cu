@@ -10,6 +10,7 @@
 // Rows whose product count exceeds the largest table fall back to the expand/sort/compress path (spgemm_esc).
 #include "mg.cuh"
 #include <cub/cub.cuh>
+#include <stdlib.h>
 
 namespace mgcg {
 
@@ -83,12 +84,33 @@ __global__ void __launch_bounds__(256) k_spgemm_symbolic(Csr A, Csr B, int shift
     extern __shared__ int sm_keys[];
     const int gpb = blockDim.x / G;
     const int lane = threadIdx.x & (G - 1);
-    int *keys = sm_keys + (size_t)(threadIdx.x / G) * cap;
+    int *keys = sm_keys + (size_t)(threadIdx.x / G) * (cap + 1);   // +1: the groups of a warp start in different banks
     const unsigned mask = group_mask<G>();
     for (int row = blockIdx.x * gpb + threadIdx.x / G; row < A.rows; row += gridDim.x * gpb) {
         for (int s = lane; s < cap; s += G) keys[s] = kEmpty;
         __syncwarp(mask);
-        int mine = spgemm_row<G, false>(A, B, shift, row, lane, mask, cap - 1, keys, nullptr, overflow);
+        // counting needs no summation order: every lane takes one entry of the A row and walks the B row it selects, so all
+        // lanes insert concurrently (the numeric phase below must go entry by entry instead)
+        int mine = 0;
+        const int cap_mask = cap - 1;
+        const int ks = A.rowptr[row], ke = A.rowptr[row + 1];
+        for (int kk = ks + lane; kk < ke; kk += G) {
+            const int j = A.col[kk] - shift;
+            const int q1 = B.rowptr[j + 1];
+            for (int q = B.rowptr[j]; q < q1; ++q) {
+                const int col = B.col[q];
+                unsigned s = hash_col(col, cap_mask);
+                int probes = 0;
+                while (true) {
+                    const int old = atomicCAS(&keys[s], kEmpty, col);
+                    if (old == kEmpty) { ++mine; break; }
+                    if (old == col) break;
+                    s = (s + 1) & cap_mask;
+                    if (++probes > 48) { *overflow = 1; break; }   // table (nearly) full: the host retries with a larger one
+                }
+            }
+        }
+        __syncwarp(mask);
 #pragma unroll
         for (int o = G / 2; o > 0; o >>= 1) mine += __shfl_down_sync(mask, mine, o, G);
         if (lane == 0) cnt[row] = mine;
@@ -104,8 +126,8 @@ __global__ void __launch_bounds__(256) k_spgemm_numeric(Csr A, Csr B, int shift,
     extern __shared__ double sm_raw[];
     const int gpb = blockDim.x / G;
     const int lane = threadIdx.x & (G - 1);
-    double *vals = sm_raw + (size_t)(threadIdx.x / G) * cap;
-    int *keys = reinterpret_cast<int *>(sm_raw + (size_t)gpb * cap) + (size_t)(threadIdx.x / G) * cap;
+    double *vals = sm_raw + (size_t)(threadIdx.x / G) * (cap + 1);   // +1: bank-conflict padding between groups
+    int *keys = reinterpret_cast<int *>(sm_raw + (size_t)gpb * (cap + 1)) + (size_t)(threadIdx.x / G) * (cap + 1);
     const unsigned mask = group_mask<G>();
     for (int row = blockIdx.x * gpb + threadIdx.x / G; row < A.rows; row += gridDim.x * gpb) {
         for (int s = lane; s < cap; s += G) { keys[s] = kEmpty; vals[s] = 0.0; }
@@ -158,16 +180,16 @@ static int run_hash(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, int maxp
     // rows of R*(A*P) have thousands of products but only a few hundred distinct columns
     long long bound = maxprod < B.cols ? maxprod : B.cols;
     int cap_s = pow2_at_least(bound + bound / 2 + 1);
-    if (cap_s > 512) cap_s = 512;
+    if (cap_s > 512 && B.cols > 4096) cap_s = 512;   // (a small column space bounds the distinct columns tightly: keep it)
     int *cnt = nullptr;
-    MGCG_CUDA(cudaMalloc((void **)&cnt, sizeof(int) * ((size_t)A.rows + 3)));
+    MGCG_CUDA(pool_alloc((void **)&cnt, sizeof(int) * ((size_t)A.rows + 3), st));
     const int cap_grid = c->sm_count * 16;
     int threads, grid;
     for (;; cap_s *= 4) {
         threads = 256;
-        while (threads > G && threads > 32 && (size_t)(threads / G) * cap_s * sizeof(int) > 96 * 1024) threads >>= 1;
-        const size_t sm_s = (size_t)(threads / G) * cap_s * sizeof(int);
-        if (sm_s > 200 * 1024) { cudaFree(cnt); return MGCG_OK; }   // too wide: caller falls back to spgemm_esc
+        while (threads > G && threads > 32 && (size_t)(threads / G) * (cap_s + 1) * sizeof(int) > 96 * 1024) threads >>= 1;
+        const size_t sm_s = (size_t)(threads / G) * (cap_s + 1) * sizeof(int);
+        if (sm_s > 200 * 1024) { pool_free(cnt, st); return MGCG_OK; }   // too wide: caller falls back to spgemm_esc
         MGCG_CUDA(cudaFuncSetAttribute(k_spgemm_symbolic<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_s));
         MGCG_CUDA(cudaMemsetAsync(cnt + A.rows, 0, 3 * sizeof(int), st));
         const int gpb = threads / G;
@@ -182,35 +204,37 @@ static int run_hash(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, int maxp
     }
     // scan + max
     C->rows = A.rows; C->cols = B.cols;
-    MGCG_CUDA(cudaMalloc((void **)&C->rowptr, sizeof(int) * ((size_t)A.rows + 1)));
+    MGCG_CUDA(pool_alloc((void **)&C->rowptr, sizeof(int) * ((size_t)A.rows + 1), st));
     size_t tb = 0, tb2 = 0;
     int *d_max = cnt + A.rows + 1;
     MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, C->rowptr, A.rows + 1, st));
     MGCG_CUDA(cub::DeviceReduce::Max(nullptr, tb2, cnt, d_max, A.rows, st));
     if (tb2 > tb) tb = tb2;
     void *tmp = nullptr;
-    MGCG_CUDA(cudaMalloc(&tmp, tb ? tb : 1));
+    MGCG_CUDA(pool_alloc(&tmp, tb, st));
     MGCG_CUDA(cub::DeviceReduce::Max(tmp, tb, cnt, d_max, A.rows, st));
     MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, C->rowptr, A.rows + 1, st));
     int h[2] = {0, 0};   // total nnz, max row length
     MGCG_CUDA(cudaMemcpyAsync(&h[0], C->rowptr + A.rows, sizeof(int), cudaMemcpyDeviceToHost, st));
     MGCG_CUDA(cudaMemcpyAsync(&h[1], d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
     MGCG_CUDA(cudaStreamSynchronize(st));
-    cudaFree(tmp); cudaFree(cnt);
+    pool_free(tmp, st); pool_free(cnt, st);
     C->nnz = h[0];
-    MGCG_CUDA(cudaMalloc((void **)&C->val, sizeof(double) * (size_t)(h[0] > 0 ? h[0] : 1)));
-    MGCG_CUDA(cudaMalloc((void **)&C->col, sizeof(int) * (size_t)(h[0] > 0 ? h[0] : 1)));
+    MGCG_CUDA(pool_alloc((void **)&C->val, sizeof(double) * (size_t)h[0], st));
+    MGCG_CUDA(pool_alloc((void **)&C->col, sizeof(int) * (size_t)h[0], st));
     // numeric table: 1.5x the longest row
     const int cap_n = pow2_at_least((long long)h[1] + h[1] / 2 + 1);
     threads = 256;
-    while (threads > G && (size_t)(threads / G) * cap_n * 12 > 160 * 1024) threads >>= 1;
+    while (threads > G && (size_t)(threads / G) * (cap_n + 1) * 12 > 160 * 1024) threads >>= 1;
     if (threads < 32) threads = 32;
-    const size_t sm_n = (size_t)(threads / G) * cap_n * 12;
+    const size_t sm_n = (size_t)(threads / G) * (cap_n + 1) * 12;
     if (sm_n > 200 * 1024) { C->free_all(); return MGCG_OK; }
     MGCG_CUDA(cudaFuncSetAttribute(k_spgemm_numeric<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_n));
     const int gpb_n = threads / G;
     grid = (A.rows + gpb_n - 1) / gpb_n;
     if (grid > cap_grid) grid = cap_grid;
+    if (getenv("MGCG_TRACE"))
+        fprintf(stderr, "[mgcg spgemm] rows %d G %d maxprod %d cap_sym %d cap_num %d (max row %d) nnz %d threads %d grid %d\n", A.rows, G, maxprod, cap_s, cap_n, h[1], h[0], threads, grid);
     k_spgemm_numeric<G><<<grid, threads, sm_n, st>>>(A, B, shift, cap_n, C->rowptr, C->col, C->val);
     MGCG_LAUNCH_CHECK();
     *done = true;
@@ -223,7 +247,7 @@ int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C, int col_shift)
     cudaStream_t st = c->stream;
     if ((A.rows <= 0 || A.nnz <= 0 || B.nnz <= 0) && col_shift == 0) return spgemm_esc(c, A, B, C);
     int *d_max = nullptr, maxprod = 0;
-    MGCG_CUDA(cudaMalloc((void **)&d_max, sizeof(int)));
+    MGCG_CUDA(pool_alloc((void **)&d_max, sizeof(int), st));
     MGCG_CUDA(cudaMemsetAsync(d_max, 0, sizeof(int), st));
     int g = (A.rows + 255) / 256;
     if (g > c->sm_count * 16) g = c->sm_count * 16;
@@ -231,7 +255,7 @@ int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C, int col_shift)
     MGCG_LAUNCH_CHECK();
     MGCG_CUDA(cudaMemcpyAsync(&maxprod, d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
     MGCG_CUDA(cudaStreamSynchronize(st));
-    cudaFree(d_max);
+    pool_free(d_max, st);
     const double avg_b = (double)B.nnz / (B.rows > 0 ? B.rows : 1);
     bool done = false;
     int s;
