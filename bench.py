@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--transport", type=int, default=0, help="sharded arm: 0 auto (peer memory on one node), 1 NCCL, 2 peer memory")
+    ap.add_argument("--replicate-below", type=int, default=0, help="sharded arm: replicate multigrid levels smaller than this (0 = library default)")
     return ap.parse_args()
 
 
@@ -354,7 +356,10 @@ def run_ours_dist(args):
     ids = [S.MgcgDist.unique_id() if rank == 0 else None]
     dist.broadcast_object_list(ids, src=0)
     m = S.MgcgDist(lr, rank, world, ids[0], use_torch_stream=True)
-    opts = S.default_options(precond=1, nx=n_side, ny=n_side, nz=n_side, norm=2, tolerance=TOL, max_iteration=1000)
+    extra = {"dist_transport": args.transport}
+    if args.replicate_below > 0:
+        extra["dist_replicate_below"] = args.replicate_below
+    opts = S.default_options(precond=1, nx=n_side, ny=n_side, nz=n_side, norm=2, tolerance=TOL, max_iteration=1000, **extra)
     m.setup(n, r0, tv, tr, tc, opts)
 
     def step():
@@ -435,7 +440,10 @@ def run_ours_dist(args):
                           "rows": n, "nnz": 7 * n - 6 * n_side * n_side,
                           "preconditioner": "smoothed-aggregation V(1,1), weighted Jacobi 0.8, built on device; coarse levels replicated",
                           "l2": "per-rank shard (matrix + vectors) larger than the 126 MB L2 at 256^3 up to 8 ranks; no flush",
-                          "parallelism": f"row-block (z-slab) shards over {world} GPUs, NCCL halo exchange + rank-ordered reductions"},
+                          "parallelism": f"row-block (z-slab) shards over {world} GPUs; halo exchange, coarse all-gather and rank-ordered "
+                                         "scalar reductions by " + ("the library's own kernels over NVLink peer memory, iteration replayed as a CUDA graph"
+                                                                    if res.reserved[3] == 2 else "NCCL send/recv + all-gather")},
+               "transport": "peer" if res.reserved[3] == 2 else "nccl", "graph": bool(res.reserved[4]),
                "iterations": res.iterations_done, "iterations_per_s": res.iterations_done / (ms * 1e-3),
                "final_relative_residual": res.residual, "setup_ms": res.setup_ms, "levels": res.levels,
                "distributed_levels": res.reserved[2], "halo_exchanges_per_solve": res.reserved[0], "allgathers_per_solve": res.reserved[1],

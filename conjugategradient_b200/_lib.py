@@ -14,6 +14,7 @@ OK, ERR_INVALID, ERR_CUDA, ERR_NOT_CONVERGED, ERR_BREAKDOWN, ERR_COMM, ERR_UNSUP
 NORM_ABS_L2, NORM_ABS_LINF, NORM_REL_L2 = 0, 1, 2
 PRECOND_NONE, PRECOND_MG = 0, 1
 SPMV_AUTO, SPMV_STREAM, SPMV_VECTOR = 0, 1, 2
+TRANSPORT_AUTO, TRANSPORT_NCCL, TRANSPORT_PEER = 0, 1, 2
 
 
 class Options(C.Structure):
@@ -24,7 +25,7 @@ class Options(C.Structure):
         ("mg_omega", C.c_double), ("mg_smoother", C.c_int), ("mg_smoothed", C.c_int), ("mg_prolong_omega", C.c_double),
         ("spmv_kernel", C.c_int), ("check_interval", C.c_int), ("use_graph", C.c_int), ("profile", C.c_int),
         ("mg_smoothed_levels", C.c_int), ("mg_aggregate_size", C.c_int), ("mg_aggregate_size_coarse", C.c_int),
-        ("dist_replicate_below", C.c_int), ("reserved", C.c_int * 4),
+        ("dist_replicate_below", C.c_int), ("dist_transport", C.c_int), ("reserved", C.c_int * 3),
     ]
 
 

@@ -33,6 +33,8 @@ int nccl_load(NcclApi **out)
     return MGCG_OK;
 }
 
+static void dist_graph_free(DistState *D);
+
 void dist_free_levels(DistState *D)
 {
     for (size_t l = 0; l < D->L.size(); ++l) {
@@ -61,6 +63,8 @@ void dist_free(mgcg_ctx *c)
 {
     DistState *D = c->dist;
     if (!D) return;
+    dist_graph_free(D);
+    peer_close(c);
     dist_free_levels(D);
     if (D->partial_send) cudaFree(D->partial_send);
     if (D->partial_all) cudaFree(D->partial_all);
@@ -75,6 +79,8 @@ int dist_halo_exchange(mgcg_ctx *c, double *v, int own, int lo, int hi, int halo
 {
     DistState *D = c->dist;
     if (D->world == 1 || halo <= 0) return MGCG_OK;
+    D->halo_exchanges++;
+    if (D->peer.active) return peer_halo_exchange(c, v, own, lo, hi, halo);
     NcclApi *a = D->api;
     double *own0 = v + lo;
     MGCG_NCCL(a, GroupStart());
@@ -87,7 +93,6 @@ int dist_halo_exchange(mgcg_ctx *c, double *v, int own, int lo, int hi, int halo
         MGCG_NCCL(a, Recv(own0 + own, (size_t)hi, ncclDouble, D->rank + 1, D->comm, c->stream));
     }
     MGCG_NCCL(a, GroupEnd());
-    D->halo_exchanges++;
     return MGCG_OK;
 }
 
@@ -416,6 +421,36 @@ static int dist_replicate(mgcg_ctx *c, int lev, const Csr &A, const int *offs, i
 
 
 // ---------------------------------------------------------------------------------------------------------
+static void dist_graph_free(DistState *D)
+{
+    if (D->graph_exec) { cudaGraphExecDestroy(D->graph_exec); D->graph_exec = nullptr; }
+    if (D->graph) { cudaGraphDestroy(D->graph); D->graph = nullptr; }
+    D->graph_b = nullptr; D->graph_x = nullptr;
+}
+
+// Choose the loop's transport once the hierarchy (hence every halo width and the gathered level's size) is known.
+// dist_transport: 0 = peer memory when every rank can map every other (one NVLink/NVSwitch node), else NCCL;
+// 1 = NCCL; 2 = peer memory or fail.  MGCG_DIST_TRANSPORT=nccl|peer overrides 0.
+static int dist_open_transport(mgcg_ctx *c)
+{
+    DistState *D = c->dist;
+    int want = c->opt.dist_transport;
+    if (want == MGCG_TRANSPORT_AUTO) {
+        const char *e = getenv("MGCG_DIST_TRANSPORT");
+        if (e && !strcmp(e, "nccl")) want = MGCG_TRANSPORT_NCCL;
+        else if (e && !strcmp(e, "peer")) want = MGCG_TRANSPORT_PEER;
+    }
+    if (D->world < 2 || want == MGCG_TRANSPORT_NCCL) return MGCG_OK;
+    int halo_cap = 0;
+    for (size_t l = 0; l < D->L.size(); ++l) if (D->L[l].halo > halo_cap && D->L[l].halo < 0x3fffffff) halo_cap = D->L[l].halo;
+    MGCG_CHECK(peer_open(c, halo_cap, D->coarse ? D->coarse_n : 0));
+    if (!D->peer.active && want == MGCG_TRANSPORT_PEER) {
+        set_error("mgcg_setup_dist: dist_transport = peer, but the ranks cannot map each other's memory (world %d, limit %d)", D->world, kPeerMax);
+        return MGCG_ERR_UNSUPPORTED;
+    }
+    return MGCG_OK;
+}
+
 static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_count, int local_nnz,
                       const double *val, const int *rowptr, const int *col)
 {
@@ -423,6 +458,8 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
     cudaStream_t st = c->stream;
     const int W = D->world, rk = D->rank;
     const mgcg_options &o = c->opt;
+    dist_graph_free(D);
+    peer_close(c);
     dist_free_levels(D);
     set_alloc_stream(st);
     // ---- the partition: all-gather of the local row counts (ConjugateGradientParallelGpu.cs:271-277 is the caller's rule)
@@ -475,7 +512,7 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
         MGCG_CUDA(cudaMemset(D->r, 0, sizeof(double) * e));
     }
     D->first_replicated = 0;
-    if (o.precond != MGCG_PRECOND_MG) return MGCG_OK;
+    if (o.precond != MGCG_PRECOND_MG) return dist_open_transport(c);
 
     // ---- hierarchy: distributed levels while they are large and their halo fits, then the replicated tail
     int cur_offs[kMaxRanks + 1];
@@ -532,39 +569,39 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
     // the private context runs on this context's scalars (its kernels are gated by the same `done` flag)
     D->coarse_scalars_orig = D->coarse->d_scalars;
     D->coarse->d_scalars = c->d_scalars;
-    return MGCG_OK;
+    return dist_open_transport(c);
 }
 
 
 // ---------------------------------------------------------------------------------------------------------
 // solve: per-rank partial sums -> all-gather -> every rank adds them in rank order (deterministic, identical on all ranks;
 // the reference sums its per-device partial dots on the host in device order, ConjugateGradientParallelGpu.cs:463,499,525)
-enum DistFin { DF_INIT_PLAIN = 0, DF_INIT_PRE, DF_PAP, DF_RR, DF_RR_RZ };
-
 __global__ void k_dist_finalize(int mode, int k, int world, const double *__restrict__ all, Scalars *sc, bool gated)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     if (gated && sc->done) return;
     double s0 = 0.0, s1 = 0.0;
     for (int r = 0; r < world; ++r) { s0 += all[r * k]; if (k > 1) s1 += all[r * k + 1]; }
-    switch (mode) {
-    case DF_INIT_PLAIN: finalize(FIN_INIT, s0, 0.0, sc, nullptr); break;
-    case DF_INIT_PRE: finalize(FIN_INIT_RR, s0, 0.0, sc, nullptr); finalize(FIN_INIT_RZ, s1, 0.0, sc, nullptr); break;
-    case DF_PAP: finalize(FIN_PAP, s0, 0.0, sc, nullptr); break;
-    case DF_RR: finalize(FIN_RR, s0, 0.0, sc, nullptr); break;
-    case DF_RR_RZ: finalize(FIN_RR_PRECOND, s0, 0.0, sc, nullptr); if (!sc->done) finalize(FIN_RZ, s1, 0.0, sc, nullptr); break;
-    }
+    dist_finalize(mode, s0, s1, sc);
 }
 
 static int dist_reduce(mgcg_ctx *c, int mode, int k, bool gated)
 {
     DistState *D = c->dist;
-    MGCG_NCCL(D->api, AllGather(D->partial_send, D->partial_all, (size_t)k, ncclDouble, D->comm, c->stream));
     D->allgathers++;
+    if (D->peer.active) return peer_reduce(c, mode, k, gated);
+    MGCG_NCCL(D->api, AllGather(D->partial_send, D->partial_all, (size_t)k, ncclDouble, D->comm, c->stream));
     k_dist_finalize<<<1, 32, 0, c->stream>>>(mode, k, D->world, D->partial_all, c->d_scalars, gated);
     c->launches++;
     MGCG_LAUNCH_CHECK();
     return MGCG_OK;
+}
+
+static int dist_gather_coarse_b(mgcg_ctx *c)
+{
+    DistState *D = c->dist;
+    if (D->peer.active) return peer_allgather(c, D->coarse_b, D->coarse_offs);
+    return allgather_v(c, D->coarse_b, D->coarse_offs, ncclDouble, sizeof(double));
 }
 
 static inline const double *shifted(const double *ext, int off, int lo) { return ext - ((ptrdiff_t)off - lo); }
@@ -593,7 +630,7 @@ static int dist_vcycle(mgcg_ctx *c, double *r_ext, double **z_own, bool fuse_fir
     double *r_own = r_ext + L0.lo;
     if (Ld == 0) {   // the whole preconditioner is replicated: gather r, cycle, take the own slice
         MGCG_CUDA(cudaMemcpyAsync(D->coarse_b + D->coarse_offs[D->rank], r_own, sizeof(double) * (size_t)L0.own, cudaMemcpyDeviceToDevice, c->stream));
-        MGCG_CHECK(allgather_v(c, D->coarse_b, D->coarse_offs, ncclDouble, sizeof(double)));
+        MGCG_CHECK(dist_gather_coarse_b(c));
         double *z = nullptr;
         MGCG_CHECK(mg_vcycle(D->coarse, D->coarse_b, &z, false, -1));
         *z_own = z + L0.off;
@@ -606,19 +643,26 @@ static int dist_vcycle(mgcg_ctx *c, double *r_ext, double **z_own, bool fuse_fir
         L.xcur = L.xa;
         if (!(l == 0 && fuse_first_done)) MGCG_CHECK(mg_jacobi_first(c, L.own, omega, L.dinv, L.b, L.xa + L.lo));
         for (int s = 1; s < pre; ++s) MGCG_CHECK(dist_jacobi_sweep(c, L, omega, nullptr));
+        dist_trace(c, l == 0 ? "L0 pre-smooth" : "L1+ pre-smooth");
         MGCG_CHECK(dist_halo_exchange(c, L.xcur, L.own, L.lo, L.hi, L.halo));
+        dist_trace(c, l == 0 ? "L0 halo(z)" : "L1+ halo(z)");
         SpmvArgs a;
         a.A = L.A; a.x = shifted(L.xcur, L.off, L.lo); a.y = L.r + L.lo; a.b = L.b; a.gated = true;
         MGCG_CHECK(spmv_launch(c, L.planA, EPI_RESID, a));
+        dist_trace(c, l == 0 ? "L0 residual" : "L1+ residual");
         MGCG_CHECK(dist_halo_exchange(c, L.r, L.own, L.lo, L.hi, L.halo));
+        dist_trace(c, l == 0 ? "L0 halo(r)" : "L1+ halo(r)");
         SpmvArgs q;
         q.A = L.R.view(); q.x = L.r; q.gated = true;
         q.y = (l + 1 < Ld) ? D->L[l + 1].b : D->coarse_b + D->coarse_offs[D->rank];
         MGCG_CHECK(spmv_launch(c, L.planR, EPI_PLAIN, q));
+        dist_trace(c, l == 0 ? "L0 restrict" : "L1+ restrict");
     }
-    MGCG_CHECK(allgather_v(c, D->coarse_b, D->coarse_offs, ncclDouble, sizeof(double)));
+    MGCG_CHECK(dist_gather_coarse_b(c));
+    dist_trace(c, "gather coarse rhs");
     double *zc = nullptr;
     MGCG_CHECK(mg_vcycle(D->coarse, D->coarse_b, &zc, false, -1));
+    dist_trace(c, "replicated tail cycle");
     for (int l = Ld - 1; l >= 0; --l) {
         DistLevel &L = D->L[l];
         const double *xn;
@@ -626,14 +670,17 @@ static int dist_vcycle(mgcg_ctx *c, double *r_ext, double **z_own, bool fuse_fir
         else {
             DistLevel &N = D->L[l + 1];
             MGCG_CHECK(dist_halo_exchange(c, N.xcur, N.own, N.lo, N.hi, N.halo));
+            dist_trace(c, "L1+ halo(xc)");
             xn = shifted(N.xcur, N.off, N.lo);
         }
         SpmvArgs a;
         a.A = L.P; a.x = xn; a.y = L.xcur + L.lo; a.alpha = 1.0; a.beta = 1.0; a.gated = true;
         MGCG_CHECK(spmv_launch(c, L.planP, EPI_AXPBY, a));
+        dist_trace(c, l == 0 ? "L0 prolong" : "L1+ prolong");
         for (int s = 0; s < post; ++s) {
             const bool last = (l == 0 && s == post - 1 && rz_out);
             MGCG_CHECK(dist_jacobi_sweep(c, L, omega, last ? rz_out : nullptr));
+            dist_trace(c, l == 0 ? "L0 post-smooth (halo + sweep)" : "L1+ post-smooth (halo + sweep)");
         }
     }
     *z_own = L0.xcur + L0.lo;
@@ -652,11 +699,15 @@ static int dist_enqueue_iteration(mgcg_ctx *c, double *x)
     const bool pre = (c->opt.precond == MGCG_PRECOND_MG);
     double *p_own = D->p + L0.lo, *r_own = D->r + L0.lo;
     // halo of p, Ap = A p, local p.Ap                                    (SyncP + Solve1, cs:470-499)
+    dist_trace(c, "update p");
     MGCG_CHECK(dist_halo_exchange(c, D->p, n, L0.lo, L0.hi, L0.halo));
+    dist_trace(c, "halo(p)");
     SpmvArgs a;
     a.A = c->A; a.x = shifted(D->p, L0.off, L0.lo); a.y = D->Ap; a.w = p_own; a.fin = FIN_STORE; a.out = D->partial_send; a.gated = true;
     MGCG_CHECK(spmv_launch(c, c->planA, EPI_DOT, a));
+    dist_trace(c, "A p + p.Ap");
     MGCG_CHECK(dist_reduce(c, DF_PAP, 1, true));
+    dist_trace(c, "reduce p.Ap");
     if (!pre) {
         MGCG_CHECK(cg_update_xr(c, n, p_own, D->Ap, x, r_own, FIN_STORE, false, 0.0, D->partial_send));   // Solve2, cs:505-525
         MGCG_CHECK(dist_reduce(c, DF_RR, 1, true));
@@ -665,12 +716,37 @@ static int dist_enqueue_iteration(mgcg_ctx *c, double *x)
         const bool fuse = D->first_replicated > 0;
         MGCG_CHECK(cg_update_xr(c, n, p_own, D->Ap, x, r_own, FIN_STORE, false, 0.0, D->partial_send,
                                 fuse ? L0.xa + L0.lo : nullptr, fuse ? L0.dinv : nullptr, c->opt.mg_omega));
+        dist_trace(c, "update x,r (+z0)");
         double *z = nullptr;
         MGCG_CHECK(dist_vcycle(c, D->r, &z, fuse, D->partial_send + 1));
         MGCG_CHECK(dist_reduce(c, DF_RR_RZ, 2, true));   // stop rule on r.r, beta from r.z: one exchange for both
+        dist_trace(c, "reduce r.r, r.z");
         MGCG_CHECK(cg_update_p(c, n, z, p_own, false, 0.0));
     }
     return MGCG_OK;
+}
+
+// phase -> total device time between consecutive trace events (the label names the phase that ENDS at the event)
+static void dist_trace_dump(mgcg_ctx *c, int iterations, float solve_ms)
+{
+    DistState *D = c->dist;
+    std::vector<std::pair<const char *, cudaEvent_t>> &ev = D->trace_ev;
+    std::vector<std::pair<std::string, std::pair<double, int>>> acc;
+    for (size_t i = 1; i < ev.size(); ++i) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, ev[i - 1].second, ev[i].second) != cudaSuccess) { cudaGetLastError(); continue; }
+        size_t j = 0;
+        for (; j < acc.size(); ++j) if (acc[j].first == ev[i].first) break;
+        if (j == acc.size()) acc.push_back({ev[i].first, {0.0, 0}});
+        acc[j].second.first += t; acc[j].second.second++;
+    }
+    if (D->rank == 0) {
+        fprintf(stderr, "[mgcg dist trace] rank 0 of %d, %d iterations, solve %.3f ms (eager launches; includes the speculative tail)\n", D->world, iterations, solve_ms);
+        for (auto &a : acc)
+            fprintf(stderr, "  %-34s n=%5d total %9.3f ms  avg %8.2f us\n", a.first.c_str(), a.second.second, a.second.first, 1e3 * a.second.first / a.second.second);
+    }
+    for (auto &e : ev) cudaEventDestroy(e.second);
+    ev.clear();
 }
 
 static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
@@ -717,8 +793,38 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     int slot = 0;
     bool finished = false, have_prev = false;
     const long long hard_cap = (long long)c->opt.max_iteration + 2;
-    while (!finished) {   // every rank sees identical scalars, so every rank enqueues the same collectives
-        for (int k = 0; k < interval; ++k) { MGCG_CHECK(dist_enqueue_iteration(c, x)); ++enq; }
+    // peer transport: the iteration is made of this library's kernels only, so it is captured once and replayed
+    {
+        const char *e = getenv("MGCG_DIST_TRACE");
+        D->trace = e && e[0] == '1';
+    }
+    const bool use_graph = D->peer.active && c->opt.use_graph && !c->opt.profile && !D->trace;
+    if (use_graph && (!D->graph_exec || D->graph_b != b || D->graph_x != x)) {
+        dist_graph_free(D);
+        const int l0 = c->launches, lc0 = D->coarse ? D->coarse->launches : 0, h0 = D->halo_exchanges, g0 = D->allgathers;
+        MGCG_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        int s = dist_enqueue_iteration(c, x);
+        cudaError_t e = cudaStreamEndCapture(st, &D->graph);
+        if (s != MGCG_OK) return s;
+        MGCG_CUDA(e);
+        MGCG_CUDA(cudaGraphInstantiate(&D->graph_exec, D->graph, 0));
+        size_t nodes = 0;
+        cudaGraphGetNodes(D->graph, nullptr, &nodes);
+        D->graph_nodes = (int)nodes; D->graph_halo = D->halo_exchanges - h0; D->graph_gather = D->allgathers - g0;
+        D->graph_b = b; D->graph_x = x;
+        c->launches = l0; D->halo_exchanges = h0; D->allgathers = g0;
+        if (D->coarse) D->coarse->launches = lc0;
+    }
+    while (!finished) {   // every rank sees identical scalars, so every rank enqueues the same exchanges
+        for (int k = 0; k < interval; ++k) {
+            if (use_graph) {
+                MGCG_CUDA(cudaGraphLaunch(D->graph_exec, st));
+                c->launches += D->graph_nodes; D->halo_exchanges += D->graph_halo; D->allgathers += D->graph_gather;
+            } else {
+                MGCG_CHECK(dist_enqueue_iteration(c, x));
+            }
+            ++enq;
+        }
         MGCG_CUDA(cudaMemcpyAsync(&c->h_scalars[slot], c->d_scalars, sizeof(Scalars), cudaMemcpyDeviceToHost, st));
         MGCG_CUDA(cudaEventRecord(evp[slot], st));
         if (have_prev) {
@@ -746,7 +852,9 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
         res->kernel_launches = c->launches + (D->coarse ? D->coarse->launches : 0);
         res->operator_complexity = 1.0;
         res->reserved[0] = D->halo_exchanges; res->reserved[1] = D->allgathers; res->reserved[2] = D->first_replicated;
+        res->reserved[3] = D->peer.active ? MGCG_TRANSPORT_PEER : MGCG_TRANSPORT_NCCL; res->reserved[4] = use_graph ? 1 : 0;
     }
+    if (D->trace) dist_trace_dump(c, fin.iteration + 1, ms);
     if (!fin.done) { set_error("mgcg_solve_dist: iteration cap reached without the device flag"); return MGCG_ERR_NOT_CONVERGED; }
     if (fin.status != MGCG_OK)
         set_error(fin.status == MGCG_ERR_NOT_CONVERGED ? "mgcg_solve_dist: Iteration > MaxIteration" : "mgcg_solve_dist: breakdown (p.Ap <= 0 or NaN)");

@@ -14,6 +14,7 @@
 // of BASELINE.json's north_star, without the scatter back.
 #pragma once
 #include "mg.cuh"
+#include "reduce.cuh"
 #include <nccl.h>
 
 namespace mgcg {
@@ -44,6 +45,31 @@ int nccl_load(NcclApi **out);   // dlopen("libnccl.so.2") once per process
     } while (0)
 
 constexpr int kMaxRanks = 64;
+
+// ---------------------------------------------------------------------------------------------------------
+// peer-memory transport (peer.cu): the loop's exchanges as this library's own kernels over NVLink peer stores
+constexpr int kPeerMax = 16;            // ranks of one NVSwitch domain served by the peer transport (NCCL beyond that)
+
+struct PeerCtl {                        // head of every rank's arena; remote ranks write xflag / rflag / rslot
+    unsigned long long xflag[kPeerMax]; // xflag[q]: sequence number of the last exchange whose data from rank q has landed
+    unsigned long long rflag[kPeerMax]; // the same for the scalar reductions
+    double rslot[2][kPeerMax][2];       // [parity][sender][value]
+    unsigned long long xseq, rseq;      // local: exchanges / reductions completed (device-resident so graphs replay)
+    unsigned int ticket1, ticket2, pad[2];
+};
+struct PeerPtrs { PeerCtl *ctl[kPeerMax]; };
+struct XchgSend { const double *src; double *dst; unsigned long long *flag; int count; int pad; };
+struct XchgRecv { const double *stage; double *dst; const unsigned long long *flag; int count; int pad; };
+struct XchgDesc { int ns, nr; size_t stage_stride; XchgSend s[kPeerMax]; XchgRecv r[kPeerMax]; };
+
+struct PeerState {
+    bool active = false;
+    void *arena = nullptr;              // this rank's arena (cudaMalloc)
+    void *peer[kPeerMax] = {};          // every rank's arena as mapped here (peer[rank] == arena)
+    bool mapped[kPeerMax] = {};         // opened with cudaIpcOpenMemHandle (to be closed)
+    size_t stage_off = 0, stage_cap = 0;   // byte offset of stage[0]; doubles per staging buffer
+    int halo_cap = 0;                   // ghost rows per side the staging holds
+};
 
 // geometry of one distributed level on every rank (host copy + device copy for the aggregate rule)
 struct LevelGeom {
@@ -98,7 +124,46 @@ struct DistState {
     double *partial_send = nullptr;         // [2]
     double *partial_all = nullptr;          // [2 * world]
     int halo_exchanges = 0, allgathers = 0; // per-solve accounting
+    PeerState peer;                         // peer-memory transport of the loop (inactive: NCCL)
+    // CUDA graph of one sharded iteration (peer transport only)
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t graph_exec = nullptr;
+    const double *graph_b = nullptr;
+    double *graph_x = nullptr;
+    int graph_halo = 0, graph_gather = 0, graph_nodes = 0;   // per-iteration counts recorded at capture
+    // MGCG_DIST_TRACE=1: phase timeline of a solve (eager launches, one CUDA event per phase boundary), printed by rank 0
+    bool trace = false;
+    std::vector<std::pair<const char *, cudaEvent_t>> trace_ev;
 };
+inline void dist_trace(mgcg_ctx *c, const char *label)
+{
+    DistState *D = c->dist;
+    if (!D || !D->trace) return;
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) return;
+    cudaEventRecord(e, c->stream);
+    D->trace_ev.emplace_back(label, e);
+}
+
+// solve: per-rank partial sums -> exchange -> every rank adds them in rank order, then the CG bookkeeping
+enum DistFin { DF_INIT_PLAIN = 0, DF_INIT_PRE, DF_PAP, DF_RR, DF_RR_RZ };
+__device__ __forceinline__ void dist_finalize(int mode, double s0, double s1, Scalars *sc)
+{
+    switch (mode) {
+    case DF_INIT_PLAIN: finalize(FIN_INIT, s0, 0.0, sc, nullptr); break;
+    case DF_INIT_PRE: finalize(FIN_INIT_RR, s0, 0.0, sc, nullptr); finalize(FIN_INIT_RZ, s1, 0.0, sc, nullptr); break;
+    case DF_PAP: finalize(FIN_PAP, s0, 0.0, sc, nullptr); break;
+    case DF_RR: finalize(FIN_RR, s0, 0.0, sc, nullptr); break;
+    case DF_RR_RZ: finalize(FIN_RR_PRECOND, s0, 0.0, sc, nullptr); if (!sc->done) finalize(FIN_RZ, s1, 0.0, sc, nullptr); break;
+    }
+}
+
+// peer.cu
+int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap);   // collective; leaves peer.active = false if any rank cannot map
+void peer_close(mgcg_ctx *c);
+int peer_halo_exchange(mgcg_ctx *c, double *v_ext, int own, int lo, int hi, int halo);
+int peer_allgather(mgcg_ctx *c, double *full, const int *offs);
+int peer_reduce(mgcg_ctx *c, int mode, int k, bool gated);
 
 // dist.cu
 int dist_halo_exchange(mgcg_ctx *c, double *v_ext, int own, int lo, int hi, int halo);

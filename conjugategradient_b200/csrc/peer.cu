@@ -1,0 +1,314 @@
+// peer.cu — peer-memory transport of the sharded solve: halo exchange, coarse right-hand-side all-gather and the scalar
+// all-reductions done by this library's own kernels with stores into the neighbours' HBM over NVLink / NVSwitch.
+//
+// Replaces, inside the CG loop, the grouped ncclSend/ncclRecv + ncclAllGather calls of the first sharded version (which
+// themselves replaced SyncP = P2Host + P2Device through a pinned host array, ConjugateGradientParallelGpu.cs:384-419,
+// Mgcg.cu:88-113, and the host-side `resultsDot.Sum()`, cs:463,499,525).  At 256^3 on 8 GPUs an iteration is ~0.25 ms of
+// sharded compute against ~11 NCCL operations of 15-25 us each, none of them capturable cheaply: the loop was latency
+// bound.  Here an exchange is ONE kernel of ours (~3-5 us) and the whole iteration is captured into a CUDA graph.
+//
+// Protocol.  Every rank owns an ARENA (cudaMalloc, exported with cudaIpcGetMemHandle and mapped by every other rank;
+// ranks that live in one process pass the raw pointer and enable peer access instead):
+//     PeerCtl   flags and the slots of the scalar reductions
+//     stage[2]  receive staging, double-buffered by the parity of the exchange sequence number
+// An exchange `s` (same number on every rank, kept on the device so a captured graph can be replayed) is
+//     phase 1  copy my send spans into the receivers' stage[s & 1] (plain stores to peer memory), __threadfence_system,
+//              and the block that takes the last ticket publishes  receiver.xflag[my rank] = s  (st.release.sys)
+//     phase 2  wait (ld.acquire.sys) until xflag[q] >= s for every rank q I receive from, then unpack stage[s & 1]
+//              into the ghost rows of the destination vector.
+// Double buffering is what makes it safe without an acknowledgement: a sender can overwrite stage[s & 1] only in
+// exchange s+2, which it reaches after waiting for MY flag of exchange s+1, which I publish after my unpack of s.
+// The scalar reduction is the same idea in one block: every rank stores its partial sums into slot[s & 1][rank] of every
+// rank, then sums the slots IN RANK ORDER (deterministic and identical everywhere, like the reference's host sum).
+// A wait that lasts longer than ~4 s marks the solve as failed (MGCG_ERR_COMM) instead of hanging the device.
+#include "dist.cuh"
+#include "reduce.cuh"
+#include <unistd.h>
+
+namespace mgcg {
+
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v)
+{
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p)
+{
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p)
+{
+    unsigned long long v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// true when the flag reached `seq`; false after ~4 s (clock64 at <= 2 GHz)
+__device__ __forceinline__ bool wait_flag(const unsigned long long *flag, unsigned long long seq)
+{
+    const long long t0 = clock64();
+    while (ld_acquire_sys(flag) < seq) {
+        if (clock64() - t0 > 8000000000ll) return false;
+        __nanosleep(32);
+    }
+    return true;
+}
+
+__device__ __forceinline__ void copy_span(double *__restrict__ dst, const double *__restrict__ src, int count, int gtid, int gsize,
+                                          bool src_remote_written)
+{
+    if (count <= 0) return;
+    if (((((uintptr_t)dst) | ((uintptr_t)src)) & 15u) == 0) {
+        const int n2 = count >> 1;
+        const double2 *s2 = reinterpret_cast<const double2 *>(src);
+        double2 *d2 = reinterpret_cast<double2 *>(dst);
+        // staging is written by another GPU: read it through L2 (never from a stale L1 line)
+        for (int i = gtid; i < n2; i += gsize) d2[i] = src_remote_written ? __ldcg(s2 + i) : s2[i];
+        if ((count & 1) && gtid == 0) dst[count - 1] = src_remote_written ? __ldcg(src + count - 1) : src[count - 1];
+    } else {
+        for (int i = gtid; i < count; i += gsize) dst[i] = src_remote_written ? __ldcg(src + i) : src[i];
+    }
+}
+
+__global__ void __launch_bounds__(256) k_peer_exchange(XchgDesc d, PeerCtl *ctl, Scalars *sc, bool gated)
+{
+    if (gated && sc->done) return;
+    __shared__ int s_last;
+    __shared__ int s_fail;
+    const int t = threadIdx.x;
+    const int gtid = blockIdx.x * blockDim.x + t, gsize = gridDim.x * blockDim.x;
+    const unsigned long long seq = ld_volatile_u64(&ctl->xseq) + 1ull;   // every block reads it before the last one advances it
+    const size_t par = (size_t)(seq & 1ull) * d.stage_stride;
+    if (t == 0) s_fail = 0;
+    // ---- phase 1: push
+    for (int i = 0; i < d.ns; ++i) copy_span(d.s[i].dst + par, d.s[i].src, d.s[i].count, gtid, gsize, false);
+    __threadfence_system();
+    __syncthreads();
+    if (t == 0) {
+        const unsigned int k = atomicAdd(&ctl->ticket1, 1u);
+        s_last = (k == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (s_last && t < d.ns) {
+        __threadfence_system();
+        st_release_sys(d.s[t].flag, seq);
+    }
+    // ---- phase 2: wait for the senders, unpack
+    if (t < d.nr && !wait_flag(d.r[t].flag, seq)) s_fail = 1;
+    __syncthreads();
+    for (int i = 0; i < d.nr; ++i) copy_span(d.r[i].dst, d.r[i].stage + par, d.r[i].count, gtid, gsize, true);
+    __syncthreads();
+    if (t == 0) {
+        if (s_fail) { sc->status = MGCG_ERR_COMM; sc->done = 1; }
+        __threadfence();
+        const unsigned int k = atomicAdd(&ctl->ticket2, 1u);
+        if (k == gridDim.x - 1) {   // every block has read xseq and finished: advance
+            ctl->ticket1 = 0u; ctl->ticket2 = 0u;
+            __threadfence();
+            ctl->xseq = seq;
+        }
+    }
+}
+
+// scalar all-reduction + the CG bookkeeping that follows it, one block.  `mine` holds this rank's k partial sums.
+__global__ void __launch_bounds__(64) k_peer_reduce(int mode, int k, int rank, int world, PeerPtrs pp, const double *__restrict__ mine,
+                                                   Scalars *sc, bool gated)
+{
+    if (gated && sc->done) return;
+    __shared__ double s_v[kPeerMax][2];
+    __shared__ int s_fail;
+    const int t = threadIdx.x;
+    PeerCtl *me = pp.ctl[rank];
+    const unsigned long long seq = ld_volatile_u64(&me->rseq) + 1ull;
+    const int par = (int)(seq & 1ull);
+    if (t == 0) s_fail = 0;
+    __syncthreads();
+    if (t < world) {
+        PeerCtl *q = pp.ctl[t];
+        q->rslot[par][rank][0] = mine[0];
+        q->rslot[par][rank][1] = k > 1 ? mine[1] : 0.0;
+        __threadfence_system();
+        st_release_sys(&q->rflag[rank], seq);
+        if (!wait_flag(&me->rflag[t], seq)) s_fail = 1;
+        s_v[t][0] = __ldcg(&me->rslot[par][t][0]);
+        s_v[t][1] = __ldcg(&me->rslot[par][t][1]);
+    }
+    __syncthreads();
+    if (t != 0) return;
+    if (s_fail) { sc->status = MGCG_ERR_COMM; sc->done = 1; me->rseq = seq; return; }
+    double s0 = 0.0, s1 = 0.0;
+    for (int r = 0; r < world; ++r) { s0 += s_v[r][0]; s1 += s_v[r][1]; }   // rank order (cs:463 resultsDot.Sum())
+    dist_finalize(mode, s0, s1, sc);
+    me->rseq = seq;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+static int grid_for(long long doubles, int sm_count)
+{
+    long long g = (doubles + 4095) / 4096;   // >= 16 doubles (2 x 128-bit stores in flight... per thread at 256 threads)
+    if (g < 1) g = 1;
+    if (g > sm_count) g = sm_count;           // all blocks must be co-resident: they spin on the flags
+    return (int)g;
+}
+
+int peer_exchange_launch(mgcg_ctx *c, const XchgDesc &d, bool gated)
+{
+    DistState *D = c->dist;
+    long long vol = 0;
+    for (int i = 0; i < d.ns; ++i) vol += d.s[i].count;
+    long long rv = 0;
+    for (int i = 0; i < d.nr; ++i) rv += d.r[i].count;
+    if (rv > vol) vol = rv;
+    k_peer_exchange<<<grid_for(vol, c->sm_count), 256, 0, c->stream>>>(d, (PeerCtl *)D->peer.arena, c->d_scalars, gated);
+    c->launches++;
+    MGCG_LAUNCH_CHECK();
+    return MGCG_OK;
+}
+
+int peer_halo_exchange(mgcg_ctx *c, double *v, int own, int lo, int hi, int halo)
+{
+    DistState *D = c->dist;
+    PeerState &P = D->peer;
+    if (halo > P.halo_cap) { set_error("peer_halo_exchange: halo %d exceeds the staging capacity %d", halo, P.halo_cap); return MGCG_ERR_INVALID; }
+    XchgDesc d;
+    memset(&d, 0, sizeof(d));
+    d.stage_stride = P.stage_cap;
+    double *own0 = v + lo;
+    const int rk = D->rank, W = D->world;
+    auto stage0 = [&](int q) { return (double *)((char *)P.peer[q] + P.stage_off); };
+    auto ctl = [&](int q) { return (PeerCtl *)P.peer[q]; };
+    if (rk > 0) {            // my first `halo` rows are rank-1's high ghosts
+        d.s[d.ns].src = own0; d.s[d.ns].dst = stage0(rk - 1) + P.halo_cap; d.s[d.ns].flag = &ctl(rk - 1)->xflag[rk]; d.s[d.ns].count = halo; d.ns++;
+        d.r[d.nr].stage = stage0(rk); d.r[d.nr].dst = v; d.r[d.nr].flag = &ctl(rk)->xflag[rk - 1]; d.r[d.nr].count = lo; d.nr++;
+    }
+    if (rk < W - 1) {
+        d.s[d.ns].src = own0 + own - halo; d.s[d.ns].dst = stage0(rk + 1); d.s[d.ns].flag = &ctl(rk + 1)->xflag[rk]; d.s[d.ns].count = halo; d.ns++;
+        d.r[d.nr].stage = stage0(rk) + P.halo_cap; d.r[d.nr].dst = own0 + own; d.r[d.nr].flag = &ctl(rk)->xflag[rk + 1]; d.r[d.nr].count = hi; d.nr++;
+    }
+    return peer_exchange_launch(c, d, true);
+}
+
+// all-gather of a vector laid out by `offs` (own block already in place): every rank pushes its block to all others
+int peer_allgather(mgcg_ctx *c, double *full, const int *offs)
+{
+    DistState *D = c->dist;
+    PeerState &P = D->peer;
+    const int rk = D->rank, W = D->world;
+    if ((size_t)offs[W] > P.stage_cap) { set_error("peer_allgather: %d rows exceed the staging capacity", offs[W]); return MGCG_ERR_INVALID; }
+    XchgDesc d;
+    memset(&d, 0, sizeof(d));
+    d.stage_stride = P.stage_cap;
+    for (int q = 0; q < W; ++q) {
+        if (q == rk) continue;
+        double *stq = (double *)((char *)P.peer[q] + P.stage_off), *stme = (double *)((char *)P.peer[rk] + P.stage_off);
+        d.s[d.ns].src = full + offs[rk]; d.s[d.ns].dst = stq + offs[rk]; d.s[d.ns].flag = &((PeerCtl *)P.peer[q])->xflag[rk];
+        d.s[d.ns].count = offs[rk + 1] - offs[rk]; d.ns++;
+        d.r[d.nr].stage = stme + offs[q]; d.r[d.nr].dst = full + offs[q]; d.r[d.nr].flag = &((PeerCtl *)P.peer[rk])->xflag[q];
+        d.r[d.nr].count = offs[q + 1] - offs[q]; d.nr++;
+    }
+    return peer_exchange_launch(c, d, true);
+}
+
+int peer_reduce(mgcg_ctx *c, int mode, int k, bool gated)
+{
+    DistState *D = c->dist;
+    PeerPtrs pp;
+    for (int q = 0; q < kPeerMax; ++q) pp.ctl[q] = (PeerCtl *)(q < D->world ? D->peer.peer[q] : nullptr);
+    k_peer_reduce<<<1, 64, 0, c->stream>>>(mode, k, D->rank, D->world, pp, D->partial_send, c->d_scalars, gated);
+    c->launches++;
+    MGCG_LAUNCH_CHECK();
+    return MGCG_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// arena life cycle
+void peer_close(mgcg_ctx *c)
+{
+    DistState *D = c->dist;
+    if (!D) return;
+    PeerState &P = D->peer;
+    for (int q = 0; q < kPeerMax; ++q) {
+        if (P.peer[q] && P.mapped[q]) cudaIpcCloseMemHandle(P.peer[q]);
+        P.peer[q] = nullptr; P.mapped[q] = false;
+    }
+    if (P.arena) cudaFree(P.arena);
+    P = PeerState();
+}
+
+struct PeerHello {
+    cudaIpcMemHandle_t handle;
+    long long pid;
+    unsigned long long ptr;
+    int device;
+    int ok;
+};
+
+// Collective: allocate the arena for `halo_cap` ghost rows per side and `gather_cap` gathered rows, exchange the handles
+// (over NCCL: this is setup, not the loop) and map every peer.  Leaves P.active = true only if EVERY rank succeeded.
+int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
+{
+    DistState *D = c->dist;
+    PeerState &P = D->peer;
+    cudaStream_t st = c->stream;
+    const int W = D->world, rk = D->rank;
+    peer_close(c);
+    if (W < 2 || W > kPeerMax) return MGCG_OK;
+    halo_cap = (halo_cap + 1) & ~1;
+    size_t cap = (size_t)2 * halo_cap;
+    if ((size_t)gather_cap > cap) cap = (size_t)gather_cap;
+    cap = (cap + 1) & ~(size_t)1;
+    P.halo_cap = halo_cap; P.stage_cap = cap;
+    P.stage_off = (sizeof(PeerCtl) + 255) & ~(size_t)255;
+    const size_t bytes = P.stage_off + sizeof(double) * 2 * cap;
+    PeerHello me;
+    memset(&me, 0, sizeof(me));
+    me.ok = 1;
+    if (cudaMalloc(&P.arena, bytes) != cudaSuccess) { cudaGetLastError(); P.arena = nullptr; me.ok = 0; }
+    if (me.ok) {
+        MGCG_CUDA(cudaMemsetAsync(P.arena, 0, bytes, st));
+        if (cudaIpcGetMemHandle(&me.handle, P.arena) != cudaSuccess) { cudaGetLastError(); me.ok = 0; }
+    }
+    me.pid = (long long)getpid(); me.ptr = (unsigned long long)(uintptr_t)P.arena; me.device = c->device;
+    // hellos of every rank
+    PeerHello *d_all = nullptr;
+    MGCG_CUDA(cudaMalloc((void **)&d_all, sizeof(PeerHello) * (size_t)(W + 1)));
+    MGCG_CUDA(cudaMemcpyAsync(d_all + W, &me, sizeof(me), cudaMemcpyHostToDevice, st));
+    MGCG_NCCL(D->api, AllGather(d_all + W, d_all, sizeof(PeerHello), ncclChar, D->comm, st));
+    std::vector<PeerHello> all((size_t)W);
+    MGCG_CUDA(cudaMemcpyAsync(all.data(), d_all, sizeof(PeerHello) * (size_t)W, cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    int ok = 1;
+    for (int q = 0; q < W; ++q) ok = ok && all[q].ok;
+    if (ok) {
+        for (int q = 0; q < W && ok; ++q) {
+            if (q == rk) { P.peer[q] = P.arena; continue; }
+            if (all[q].pid == me.pid) {   // same process (one host thread per GPU): the pointer itself, with peer access on
+                int can = 0;
+                if (all[q].device == c->device) can = 1;
+                else if (cudaDeviceCanAccessPeer(&can, c->device, all[q].device) == cudaSuccess && can) {
+                    cudaError_t e = cudaDeviceEnablePeerAccess(all[q].device, 0);
+                    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) can = 0;
+                    cudaGetLastError();
+                }
+                if (can) P.peer[q] = (void *)(uintptr_t)all[q].ptr; else ok = 0;
+            } else {
+                void *p = nullptr;
+                if (cudaIpcOpenMemHandle(&p, all[q].handle, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess) { P.peer[q] = p; P.mapped[q] = true; }
+                else { cudaGetLastError(); ok = 0; }
+            }
+        }
+    }
+    // agreement: everyone or no one.  The all-reduce is also the barrier that orders the arena memsets before any push.
+    int *d_ok = (int *)d_all;
+    MGCG_CUDA(cudaMemcpyAsync(d_ok, &ok, sizeof(int), cudaMemcpyHostToDevice, st));
+    MGCG_NCCL(D->api, AllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, D->comm, st));
+    MGCG_CUDA(cudaMemcpyAsync(&ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    cudaFree(d_all);
+    if (!ok) { peer_close(c); return MGCG_OK; }
+    P.active = true;
+    return MGCG_OK;
+}
+
+}  // namespace mgcg

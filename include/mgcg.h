@@ -41,6 +41,7 @@ enum {
 enum { MGCG_PRECOND_NONE = 0, MGCG_PRECOND_MG = 1 };
 enum { MGCG_SMOOTHER_JACOBI = 0, MGCG_SMOOTHER_RBGS = 1 };
 enum { MGCG_SPMV_AUTO = 0, MGCG_SPMV_STREAM = 1, MGCG_SPMV_VECTOR = 2 };
+enum { MGCG_TRANSPORT_AUTO = 0, MGCG_TRANSPORT_NCCL = 1, MGCG_TRANSPORT_PEER = 2 };
 
 typedef struct mgcg_options {
     /* CG control — same meaning as the reference's ctor arguments (ConjugateGradient.cs:41-50) */
@@ -71,7 +72,9 @@ typedef struct mgcg_options {
     int    mg_aggregate_size_coarse; /* the same for levels >= 1 (default 2; 0 = as level 0) */
     int    dist_replicate_below;     /* sharded solve: levels with fewer global rows than this are replicated on every
                                         rank (all-gathered right-hand side, redundant coarse solve); default 1<<20 */
-    int    reserved[4];
+    int    dist_transport;           /* sharded solve, exchanges inside the CG loop: MGCG_TRANSPORT_AUTO (peer memory when
+                                        every rank can map every other, else NCCL), _NCCL, _PEER (or fail) */
+    int    reserved[3];
 } mgcg_options;
 
 typedef struct mgcg_result {
@@ -149,7 +152,9 @@ int mgcg_partition_offsets(int count, int device_count, int *offsets /* [device_
 
 /* ---- one-process-per-GPU sharded solve (replaces the host-threaded ConjugateGradientParallelGpu.Solve,
  *      cs:424-565): each rank owns rows [row_offset, row_offset+local_count); column indices are GLOBAL;
- *      local row offsets are rebased to 0 (Mgcg.cu:73).  Halo exchange of p and the scalar reductions go over NCCL. */
+ *      local row offsets are rebased to 0 (Mgcg.cu:73).  Setup traffic goes over NCCL; inside the CG loop the halo
+ *      exchanges, the coarse all-gather and the scalar reductions are this library's own kernels storing into the
+ *      neighbours' memory over NVLink (peer transport, one node), or NCCL calls where peers cannot be mapped. */
 int mgcg_comm_unique_id(void *out128);             /* rank 0: 128-byte NCCL id to broadcast out of band */
 int mgcg_comm_init(mgcg_ctx *c, const void *id128, int rank, int world);
 int mgcg_setup_dist(mgcg_ctx *c, int global_count, int row_offset, int local_count, int local_elements_count,

@@ -47,6 +47,10 @@ def main():
     o = S.default_options(norm=2, tolerance=1e-8, max_iteration=2000, **kw)
     m.setup(N, r0, tv, tr, tc, o)
     res = m.solve(tb, tx)
+    for _ in range(cfg.get("solves", 1) - 1):     # repeated solves replay the captured iteration; results must not move
+        x_first = tx.clone()
+        res2 = m.solve(tb, tx.zero_())
+        assert res2.iterations_done == res.iterations_done and torch.equal(tx, x_first), "repeated sharded solve differs"
     torch.cuda.synchronize()
     # the same system on this GPU alone
     ms = S.Mgcg(lr)
@@ -58,7 +62,8 @@ def main():
     err = float((tx - fx[r0:r1]).abs().max() / fx.abs().max())
     out = {"rank": rank, "it_dist": res.iterations_done, "it_single": rs.iterations_done, "err": err, "residual": res.residual,
            "levels": res.levels, "first_replicated": res.reserved[2], "halo_exchanges": res.reserved[0], "allgathers": res.reserved[1],
-           "solve_ms": res.solve_ms, "setup_ms": res.setup_ms, "single_ms": rs.solve_ms, "launches": res.kernel_launches}
+           "solve_ms": res.solve_ms, "setup_ms": res.setup_ms, "single_ms": rs.solve_ms, "launches": res.kernel_launches,
+           "transport": res.reserved[3], "graph": res.reserved[4]}
     allo = [None] * world
     dist.all_gather_object(allo, out)
     if rank == 0:

@@ -21,6 +21,15 @@ CASES = [
     ("mg_replicated", {"n": 32, "options": {"precond": 1}}),                                  # whole hierarchy replicated
     ("mg_two_sharded_levels", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000}}),
     ("mg_no_grid_hint", {"n": 32, "hint": False, "options": {"precond": 1, "dist_replicate_below": 1000}}),
+    # the same paths with the loop's exchanges forced onto NCCL (transport 1) / onto peer memory (2, fails if unavailable)
+    ("plain_cg_nccl", {"n": 32, "options": {"precond": 0, "dist_transport": 1}}),
+    ("mg_two_sharded_levels_nccl", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 1}}),
+    ("plain_cg_peer", {"n": 32, "options": {"precond": 0, "dist_transport": 2}, "transport": 2}),
+    ("mg_replicated_peer", {"n": 32, "options": {"precond": 1, "dist_transport": 2}, "transport": 2}),
+    ("mg_two_sharded_levels_peer", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2}, "transport": 2,
+                                    "solves": 3}),
+    ("mg_27pt_peer_eager", {"n": 24, "matrix": "p27", "options": {"precond": 1, "dist_replicate_below": 500, "dist_transport": 2, "use_graph": 0},
+                            "transport": 2}),
 ]
 
 
@@ -38,4 +47,6 @@ def test_sharded_matches_single_gpu(name, cfg):
         assert abs(r["it_dist"] - r["it_single"]) <= 1, r      # iteration count within +-1
         assert r["err"] <= 1e-10 if r["it_dist"] == r["it_single"] else r["err"] <= 1e-6, r
         assert r["residual"] < 1e-8
+    if "transport" in cfg:
+        assert all(r["transport"] == cfg["transport"] for r in res), res
     assert len({r["it_dist"] for r in res}) == 1 and len({r["residual"] for r in res}) == 1   # identical scalars on all ranks
