@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--device-gen", action="store_true", help="assemble the matrix on the device (mgcg_generate_poisson3d7); implied for --size > 256, "
+                    "where the e2e and CPU legs (which need the host copy) are skipped")
     ap.add_argument("--transport", type=int, default=0, help="sharded arm: 0 auto (peer memory on one node), 1 NCCL, 2 peer memory")
     ap.add_argument("--replicate-below", type=int, default=0, help="sharded arm: replicate multigrid levels smaller than this (0 = library default)")
     return ap.parse_args()
@@ -208,17 +210,27 @@ def run_ours_single(args):
     torch.cuda.set_stream(torch.cuda.Stream(dev))   # a real (capturable) stream shared by torch's events and the library
     n_side = args.size
     n = n_side ** 3
-    problem = make_problem(n_side)
-    val, rp, col, b = problem
-    nnz = int(rp[-1])
-    # pinned host copies (the e2e leg uploads from these)
-    hv, hr, hc, hb = (torch.from_numpy(a).pin_memory() for a in (val, rp, col, b))
-    hx = torch.zeros(n, dtype=torch.float64).pin_memory()
-    tv, tr, tc, tb = (t.to(dev, non_blocking=True) for t in (hv, hr, hc, hb))
+    m = S.Mgcg(0, use_torch_stream=True)     # run on torch's current stream so torch.cuda.Event brackets the library's work
+    device_gen = args.device_gen or n_side > 256
+    if device_gen:
+        from conjugategradient_b200 import device_generators as dg
+        from conjugategradient_b200 import generators as g
+        tv, tr, tc = dg.poisson3d7(m.ctx, n_side, device=dev)
+        tb = torch.from_numpy(g.rhs_uniform(n, 0)).to(dev)
+        nnz = tv.numel()
+        problem = None
+        args.no_e2e = True; args.no_cpu = True
+    else:
+        problem = make_problem(n_side)
+        val, rp, col, b = problem
+        nnz = int(rp[-1])
+        # pinned host copies (the e2e leg uploads from these)
+        hv, hr, hc, hb = (torch.from_numpy(a).pin_memory() for a in (val, rp, col, b))
+        hx = torch.zeros(n, dtype=torch.float64).pin_memory()
+        tv, tr, tc, tb = (t.to(dev, non_blocking=True) for t in (hv, hr, hc, hb))
     tx = torch.zeros(n, dtype=torch.float64, device=dev)
     torch.cuda.synchronize()
 
-    m = S.Mgcg(0, use_torch_stream=True)     # run on torch's current stream so torch.cuda.Event brackets the library's work
     opts = S.default_options(precond=1, nx=n_side, ny=n_side, nz=n_side, norm=2, tolerance=TOL, max_iteration=1000, use_graph=1)
     m.setup(tv, tr, tc, opts)
 
@@ -305,7 +317,8 @@ def run_ours_single(args):
            "data": "synthetic",
            "config": {"workload": f"3-D 7-point Poisson {n_side}^3 MGCG, fp64, b~U(-1,1) seed 0, x0=0, relative residual 1e-8",
                       "rows": n, "nnz": nnz, "preconditioner": "smoothed-aggregation V(1,1), weighted Jacobi 0.8, built on device",
-                      "l2": "inputs (1.6 GB matrix + 128 MiB vectors) larger than the 126 MB L2; no flush",
+                      "l2": "inputs (1.6 GB matrix + 128 MiB vectors at 256^3) larger than the 126 MB L2; no flush",
+                      "matrix_assembly": "device (mgcg_generate_poisson3d7)" if device_gen else "host numpy, uploaded",
                       "parallelism": "1 GPU"},
            "iterations": iters, "iterations_per_s": iters / (ms * 1e-3), "final_relative_residual": res.residual,
            "true_relative_residual": true_rel, "setup_ms": setup_ms, "levels": res.levels,
@@ -347,15 +360,23 @@ def run_ours_dist(args):
     zo = np.concatenate([[0], np.cumsum(planes)])
     z0, z1 = int(zo[rank]), int(zo[rank + 1])
     r0, r1 = z0 * n_side * n_side, z1 * n_side * n_side
-    val, rp, col = g.poisson3d7(n_side, zrange=(z0, z1))
-    b = g.rhs_uniform(n, 0)[r0:r1].copy()
-    nnz_local = int(rp[-1])
-    hv, hr, hc, hb = (torch.from_numpy(a).pin_memory() for a in (val, rp, col, b))
-    tv, tr, tc, tb = (t.to(dev, non_blocking=True) for t in (hv, hr, hc, hb))
-    tx = torch.zeros(r1 - r0, dtype=torch.float64, device=dev)
     ids = [S.MgcgDist.unique_id() if rank == 0 else None]
     dist.broadcast_object_list(ids, src=0)
     m = S.MgcgDist(lr, rank, world, ids[0], use_torch_stream=True)
+    b = g.rhs_uniform(n, 0)[r0:r1].copy()
+    device_gen = args.device_gen or n_side > 256
+    if device_gen:
+        from conjugategradient_b200 import device_generators as dg
+        tv, tr, tc = dg.poisson3d7(m.ctx, n_side, zrange=(z0, z1), device=dev)
+        tb = torch.from_numpy(b).to(dev)
+        nnz_local = tv.numel()
+        args.no_e2e = True
+    else:
+        val, rp, col = g.poisson3d7(n_side, zrange=(z0, z1))
+        nnz_local = int(rp[-1])
+        hv, hr, hc, hb = (torch.from_numpy(a).pin_memory() for a in (val, rp, col, b))
+        tv, tr, tc, tb = (t.to(dev, non_blocking=True) for t in (hv, hr, hc, hb))
+    tx = torch.zeros(r1 - r0, dtype=torch.float64, device=dev)
     extra = {"dist_transport": args.transport}
     if args.replicate_below > 0:
         extra["dist_replicate_below"] = args.replicate_below
@@ -387,6 +408,8 @@ def run_ours_dist(args):
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     clk = clocks.stop() if rank == 0 else None
+    micro = (C.c_double * 3)()
+    S.check(m.L.mgcg_dist_microbench(m.ctx, 200, micro), "mgcg_dist_microbench")
     # local SpMV(+p.Ap) in isolation on this rank's shard (x = a [lo|own|hi]-sized vector addressed globally, like p)
     L = m.L
     halo = n_side * n_side
@@ -444,6 +467,7 @@ def run_ours_dist(args):
                                          "scalar reductions by " + ("the library's own kernels over NVLink peer memory, iteration replayed as a CUDA graph"
                                                                     if res.reserved[3] == 2 else "NCCL send/recv + all-gather")},
                "transport": "peer" if res.reserved[3] == 2 else "nccl", "graph": bool(res.reserved[4]),
+               "exchange_us": {"halo_level0": micro[0], "coarse_allgather": micro[1], "scalar_reduction": micro[2]},
                "iterations": res.iterations_done, "iterations_per_s": res.iterations_done / (ms * 1e-3),
                "final_relative_residual": res.residual, "setup_ms": res.setup_ms, "levels": res.levels,
                "distributed_levels": res.reserved[2], "halo_exchanges_per_solve": res.reserved[0], "allgathers_per_solve": res.reserved[1],

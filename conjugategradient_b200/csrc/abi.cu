@@ -72,11 +72,11 @@ void mgcg_options_default(mgcg_options *o)
     o->mg_smoothed = 1;
     o->mg_aggregate_size = 3;          /* 3x3x3 on the finest level, 2x2x2 below: fewest total bytes per digit of residual */
     o->mg_aggregate_size_coarse = 2;
-    o->dist_replicate_below = 1 << 20;
+    o->dist_replicate_below = 1 << 18;
     o->mg_prolong_omega = 2.0 / 3.0;
     o->spmv_kernel = MGCG_SPMV_AUTO;
     o->check_interval = 8;
-    o->use_graph = 1;
+    o->use_graph = 2;
     o->profile = 0;
 }
 

@@ -4,6 +4,7 @@
 // written by the last block of each reducing kernel, the host enqueues iterations ahead and polls a `done` flag
 // with a lag (kernels enqueued past convergence see `done` and return immediately, so the result is exact).
 #include "common.cuh"
+#include <string.h>
 
 namespace mgcg {
 
@@ -39,6 +40,49 @@ static int enqueue_iteration(mgcg_ctx *c, const double *b, double *x, std::vecto
         MGCG_CHECK(cg_update_p(c, n, z, c->p, false, 0.0)); // p = z + beta p
     }
     return MGCG_OK;
+}
+
+__global__ void k_loop_condition(cudaGraphConditionalHandle h, const Scalars *sc)
+{
+    if (threadIdx.x == 0) cudaGraphSetConditional(h, sc->done ? 0u : 1u);
+}
+
+int graph_build_while(mgcg_ctx *c, int (*enqueue)(mgcg_ctx *, void *), void *arg, cudaGraph_t *graph, cudaGraphExec_t *exec, int *body_nodes)
+{
+    cudaStream_t st = c->stream;
+    cudaGraph_t g = nullptr;
+    MGCG_CUDA(cudaGraphCreate(&g, 0));
+    cudaGraphConditionalHandle h;
+    cudaGraphNodeParams p = {};
+    cudaGraphNode_t node;
+    if (cudaGraphConditionalHandleCreate(&h, g, 1, cudaGraphCondAssignDefault) != cudaSuccess) { cudaGetLastError(); cudaGraphDestroy(g); return MGCG_ERR_UNSUPPORTED; }
+    p.type = cudaGraphNodeTypeConditional;
+    p.conditional.handle = h; p.conditional.type = cudaGraphCondTypeWhile; p.conditional.size = 1;
+    if (cudaGraphAddNode(&node, g, nullptr, 0, &p) != cudaSuccess) { cudaGetLastError(); cudaGraphDestroy(g); return MGCG_ERR_UNSUPPORTED; }
+    cudaGraph_t body = p.conditional.phGraph_out[0];
+    if (cudaStreamBeginCaptureToGraph(st, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+        cudaGetLastError(); cudaGraphDestroy(g); return MGCG_ERR_UNSUPPORTED;
+    }
+    int s = enqueue(c, arg);
+    k_loop_condition<<<1, 32, 0, st>>>(h, c->d_scalars);
+    cudaGraph_t got = nullptr;
+    cudaError_t e = cudaStreamEndCapture(st, &got);
+    if (s != MGCG_OK) { cudaGraphDestroy(g); return s; }
+    if (e != cudaSuccess) { set_error("graph_build_while: capture failed: %s", cudaGetErrorString(e)); cudaGetLastError(); cudaGraphDestroy(g); return MGCG_ERR_CUDA; }
+    size_t nodes = 0;
+    cudaGraphGetNodes(body, nullptr, &nodes);
+    e = cudaGraphInstantiate(exec, g, 0);
+    if (e != cudaSuccess) { set_error("graph_build_while: instantiate failed: %s", cudaGetErrorString(e)); cudaGetLastError(); cudaGraphDestroy(g); return MGCG_ERR_UNSUPPORTED; }
+    *graph = g;
+    *body_nodes = (int)nodes;
+    return MGCG_OK;
+}
+
+struct IterArgs { const double *b; double *x; };
+static int enqueue_iteration_thunk(mgcg_ctx *c, void *arg)
+{
+    IterArgs *a = (IterArgs *)arg;
+    return enqueue_iteration(c, a->b, a->x);
 }
 
 int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
@@ -89,25 +133,44 @@ int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     float spmv_ms = 0.f;
     int spmv_n = 0;
 
-    if (use_graph && (!c->graph_exec || c->graph_b != b || c->graph_x != x)) {
+    const int want_mode = use_graph ? (c->opt.use_graph >= 2 ? 2 : 1) : 0;
+    if (use_graph && (!c->graph_exec || c->graph_b != b || c->graph_x != x || (c->graph_mode != want_mode && c->graph_mode != -want_mode))) {
         if (c->graph_exec) { cudaGraphExecDestroy(c->graph_exec); c->graph_exec = nullptr; }
         if (c->graph) { cudaGraphDestroy(c->graph); c->graph = nullptr; }
         int saved = c->launches;
-        MGCG_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        int s = enqueue_iteration(c, b, x);
-        cudaError_t e = cudaStreamEndCapture(st, &c->graph);
-        if (s != MGCG_OK) return s;
-        MGCG_CUDA(e);
-        MGCG_CUDA(cudaGraphInstantiate(&c->graph_exec, c->graph, 0));
+        c->graph_mode = 0;
+        if (want_mode == 2) {   // the whole loop as one launch: WHILE(!done) { iteration } on the device
+            IterArgs ia{b, x};
+            int s = graph_build_while(c, enqueue_iteration_thunk, &ia, &c->graph, &c->graph_exec, &c->graph_body_nodes);
+            if (s == MGCG_OK) c->graph_mode = 2;
+            else if (s != MGCG_ERR_UNSUPPORTED) return s;
+        }
+        if (c->graph_mode == 0) {
+            MGCG_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            int s = enqueue_iteration(c, b, x);
+            cudaError_t e = cudaStreamEndCapture(st, &c->graph);
+            if (s != MGCG_OK) return s;
+            MGCG_CUDA(e);
+            MGCG_CUDA(cudaGraphInstantiate(&c->graph_exec, c->graph, 0));
+            size_t nodes = 0;
+            cudaGraphGetNodes(c->graph, nullptr, &nodes);
+            c->graph_body_nodes = (int)nodes;
+            c->graph_mode = want_mode == 2 ? -2 : 1;   // -2: asked for the while loop, the driver cannot; do not retry every solve
+        }
         c->graph_b = b; c->graph_x = x;
         c->launches = saved;
     }
+    const bool while_loop = use_graph && c->graph_mode == 2;
     long long enq = 0;
     int slot = 0;
     bool finished = false;
     bool have_prev = false;
     Scalars fin{};
     const long long hard_cap = (long long)c->opt.max_iteration + 2;
+    if (while_loop) {   // one launch: the device decides when to stop
+        MGCG_CUDA(cudaGraphLaunch(c->graph_exec, st));
+        finished = true;
+    }
     while (!finished) {
         for (int k = 0; k < interval; ++k) {
             if (use_graph) {
@@ -133,11 +196,8 @@ int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     MGCG_CUDA(cudaEventRecord(ev1, st));
     MGCG_CUDA(cudaEventSynchronize(ev1));
     fin = c->h_scalars[0];
-    if (use_graph) {
-        size_t nodes = 0;
-        cudaGraphGetNodes(c->graph, nullptr, &nodes);
-        c->launches += (int)(nodes * enq);
-    }
+    if (while_loop) c->launches += c->graph_body_nodes * (fin.iteration + 1);
+    else if (use_graph) c->launches += (int)(c->graph_body_nodes * enq);
 
     float ms = 0.f;
     MGCG_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));

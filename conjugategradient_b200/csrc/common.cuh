@@ -153,6 +153,8 @@ struct mgcg_ctx {
     cudaGraphExec_t graph_exec = nullptr;
     const double *graph_b = nullptr;
     double *graph_x = nullptr;
+    int graph_mode = 0;                  // 1: one iteration per launch; 2: device-side while loop (conditional node)
+    int graph_body_nodes = 0;            // kernels of one iteration
     // host-pointer path buffers (mgcg_solve_host)
     void *host_path = nullptr;
 };
@@ -196,6 +198,10 @@ void dist_free(mgcg_ctx *c);
 
 // ---- cg.cu
 int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res);
+// Build `*graph` = WHILE(!Scalars.done) { body }: `enqueue` is captured into the body of a conditional node, followed by a
+// one-thread kernel that feeds the loop condition from the device-side `done` flag.  MGCG_ERR_UNSUPPORTED if the driver
+// has no conditional nodes (callers fall back to one iteration per launch).
+int graph_build_while(mgcg_ctx *c, int (*enqueue)(mgcg_ctx *, void *), void *arg, cudaGraph_t *graph, cudaGraphExec_t *exec, int *body_nodes);
 
 // ---- helpers
 // Stream-ordered allocation for the hierarchy build (cudaMallocAsync from the device's pool: no device-wide

@@ -227,6 +227,8 @@ static int dist_build_next(mgcg_ctx *c, int l, DevCsr *Ac_out)
     const int W = D->world, rk = D->rank, B = L.halo, own = L.own;
     const int e_lo = rk > 0 ? 2 * B : 0, e_hi = rk < W - 1 ? 2 * B : 0;
     const int lo1 = L.lo, hi1 = L.hi;
+    PhaseTrace tr(st);
+    if (rk != 0) tr.on = false;
     // ---- fetch the ghost rows: row pointers first (fixed size), then the entries
     int *rp_lo = nullptr, *rp_hi = nullptr;
     MGCG_CUDA(cudaMalloc((void **)&rp_lo, sizeof(int) * ((size_t)e_lo + 1)));
@@ -277,6 +279,7 @@ static int dist_build_next(mgcg_ctx *c, int l, DevCsr *Ac_out)
     MGCG_CUDA(cudaMemcpyAsync(E.val + nnz_lo, L.A.val + h[0], sizeof(double) * (size_t)nnz_own, cudaMemcpyDeviceToDevice, st));
     k_ext_rowptr<<<gridn(E.rows + 1), 256, 0, st>>>(e_lo, own, e_hi, rp_lo, L.A.rowptr, rp_hi, nnz_lo, nnz_own, E.rowptr);
     MGCG_LAUNCH_CHECK();
+    tr.mark(l, "d:ghost rows");
     const int e0 = L.off - e_lo;                       // global index of extended row 0
     // ---- aggregate ids for every column the extended rows can reference
     int g0 = e0 - B; if (g0 < 0) g0 = 0;
@@ -294,11 +297,13 @@ static int dist_build_next(mgcg_ctx *c, int l, DevCsr *Ac_out)
     const bool smooth_here = o.mg_smoothed && (o.mg_smoothed_levels <= 0 || l < o.mg_smoothed_levels);
     const int nc_glob = g.coff[W], coff = g.coff[rk], cown = g.coff[rk + 1] - g.coff[rk];
     MGCG_CHECK(build_prolongator(c, E.view(), e0, agg_sh, dinv_ext, smooth_here, o.mg_prolong_omega, nc_glob, &L.Pext));
+    tr.mark(l, "d:P ext");
     // ---- A*P for rows [own +- halo]
     Csr Av = E.view();
     Av.rows = lo1 + own + hi1; Av.rowptr = E.rowptr + (e_lo - lo1);
     DevCsr AP;
     MGCG_CHECK(spgemm(c, Av, L.Pext.view(), &AP, e0));
+    tr.mark(l, "d:A*P");
     // ---- R = (P rows [own +- halo])^T restricted to the owned aggregates
     Csr Pv = L.Pext.view();
     Pv.rows = Av.rows; Pv.rowptr = L.Pext.rowptr + (e_lo - lo1);
@@ -317,10 +322,12 @@ static int dist_build_next(mgcg_ctx *c, int l, DevCsr *Ac_out)
     int rn = 0;
     MGCG_CUDA(cudaMemcpy(&rn, L.R.rowptr + cown, sizeof(int), cudaMemcpyDeviceToHost));
     L.R.rows = cown; L.R.nnz = rn;                      // drop the dump row
+    tr.mark(l, "d:R");
     // ---- Galerkin rows of the owned aggregates
     MGCG_CHECK(spgemm(c, L.R.view(), AP.view(), Ac_out, 0));
     Ac_out->cols = nc_glob;
     AP.free_all();
+    tr.mark(l, "d:R*(AP)");
     // ---- solve-time views
     L.P = L.Pext.view();
     L.P.rows = own; L.P.rowptr = L.Pext.rowptr + e_lo;
@@ -334,6 +341,7 @@ static int dist_build_next(mgcg_ctx *c, int l, DevCsr *Ac_out)
     MGCG_CUDA(cudaStreamSynchronize(st));
     cudaFree(rp_lo); cudaFree(rp_hi); cudaFree(agg); cudaFree(dinv_ext);
     E.free_all();
+    tr.mark(l, "d:finish");
     return MGCG_OK;
 }
 
@@ -364,6 +372,8 @@ static int dist_replicate(mgcg_ctx *c, int lev, const Csr &A, const int *offs, i
     cudaStream_t st = c->stream;
     const int W = D->world, rk = D->rank;
     const int n = offs[W], own = offs[rk + 1] - offs[rk];
+    PhaseTrace tr(st);
+    if (rk != 0) tr.on = false;
     // non-zero counts of every rank
     int my[2] = {0, 0};
     MGCG_CUDA(cudaMemcpy(&my[0], A.rowptr, sizeof(int), cudaMemcpyDeviceToHost));
@@ -396,6 +406,7 @@ static int dist_replicate(mgcg_ctx *c, int lev, const Csr &A, const int *offs, i
     MGCG_CHECK(allgather_v(c, F.col, zoff, ncclInt, sizeof(int)));
     MGCG_CHECK(allgather_v(c, F.val, zoff, ncclDouble, sizeof(double)));
     MGCG_CUDA(cudaStreamSynchronize(st));
+    tr.mark(lev, "d:replicate A");
     // right-hand side buffer of the replicated level
     D->coarse_n = n;
     for (int r = 0; r <= W; ++r) D->coarse_offs[r] = offs[r];
@@ -416,6 +427,7 @@ static int dist_replicate(mgcg_ctx *c, int lev, const Csr &A, const int *offs, i
         if (o.mg_max_levels > 0) { o.mg_max_levels -= lev; if (o.mg_max_levels < 1) o.mg_max_levels = 1; }
     }
     MGCG_CHECK(mgcg_setup(D->coarse, n, F.nnz, F.val, F.rowptr, F.col, &o));
+    tr.mark(lev, "d:tail setup");
     return MGCG_OK;
 }
 
@@ -458,10 +470,13 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
     cudaStream_t st = c->stream;
     const int W = D->world, rk = D->rank;
     const mgcg_options &o = c->opt;
+    PhaseTrace tr(st);
+    if (rk != 0) tr.on = false;
     dist_graph_free(D);
     peer_close(c);
     dist_free_levels(D);
     set_alloc_stream(st);
+    tr.mark(-1, "d:free old");
     // ---- the partition: all-gather of the local row counts (ConjugateGradientParallelGpu.cs:271-277 is the caller's rule)
     int offs[kMaxRanks + 1];
     {
@@ -488,7 +503,7 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
     int nx = 0, ny = 0;
     if (o.nx > 0 && o.ny > 0 && o.nz > 0 && (long long)o.nx * o.ny * o.nz == global_count) { nx = o.nx; ny = o.ny; }
     const int max_levels = o.mg_max_levels > 0 ? o.mg_max_levels : 12;
-    const int replicate_below = o.dist_replicate_below > 0 ? o.dist_replicate_below : (1 << 20);
+    const int replicate_below = o.dist_replicate_below > 0 ? o.dist_replicate_below : (1 << 18);
 
     D->L.emplace_back();
     {
@@ -512,6 +527,7 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
         MGCG_CUDA(cudaMemset(D->r, 0, sizeof(double) * e));
     }
     D->first_replicated = 0;
+    tr.mark(0, "d:level0 init");
     if (o.precond != MGCG_PRECOND_MG) return dist_open_transport(c);
 
     // ---- hierarchy: distributed levels while they are large and their halo fits, then the replicated tail
@@ -569,7 +585,10 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
     // the private context runs on this context's scalars (its kernels are gated by the same `done` flag)
     D->coarse_scalars_orig = D->coarse->d_scalars;
     D->coarse->d_scalars = c->d_scalars;
-    return dist_open_transport(c);
+    tr.mark(-1, "d:levels");
+    int s_ = dist_open_transport(c);
+    tr.mark(-1, "d:transport");
+    return s_;
 }
 
 
@@ -749,6 +768,8 @@ static void dist_trace_dump(mgcg_ctx *c, int iterations, float solve_ms)
     ev.clear();
 }
 
+static int dist_enqueue_thunk(mgcg_ctx *c, void *x) { return dist_enqueue_iteration(c, (double *)x); }
+
 static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
 {
     DistState *D = c->dist;
@@ -799,21 +820,39 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
         D->trace = e && e[0] == '1';
     }
     const bool use_graph = D->peer.active && c->opt.use_graph && !c->opt.profile && !D->trace;
-    if (use_graph && (!D->graph_exec || D->graph_b != b || D->graph_x != x)) {
+    const int want_mode = use_graph ? (c->opt.use_graph >= 2 ? 2 : 1) : 0;
+    if (use_graph && (!D->graph_exec || D->graph_b != b || D->graph_x != x || (D->graph_mode != want_mode && D->graph_mode != -want_mode))) {
         dist_graph_free(D);
         const int l0 = c->launches, lc0 = D->coarse ? D->coarse->launches : 0, h0 = D->halo_exchanges, g0 = D->allgathers;
-        MGCG_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        int s = dist_enqueue_iteration(c, x);
-        cudaError_t e = cudaStreamEndCapture(st, &D->graph);
-        if (s != MGCG_OK) return s;
-        MGCG_CUDA(e);
-        MGCG_CUDA(cudaGraphInstantiate(&D->graph_exec, D->graph, 0));
-        size_t nodes = 0;
-        cudaGraphGetNodes(D->graph, nullptr, &nodes);
-        D->graph_nodes = (int)nodes; D->graph_halo = D->halo_exchanges - h0; D->graph_gather = D->allgathers - g0;
+        D->graph_mode = 0;
+        if (want_mode == 2) {   // WHILE(!done) { iteration } on the device: every rank leaves the loop at the same iteration
+            int s = graph_build_while(c, dist_enqueue_thunk, x, &D->graph, &D->graph_exec, &D->graph_nodes);
+            if (s == MGCG_OK) D->graph_mode = 2;
+            else if (s != MGCG_ERR_UNSUPPORTED) return s;
+        }
+        if (D->graph_mode == 0) {
+            c->launches = l0; D->halo_exchanges = h0; D->allgathers = g0;
+            if (D->coarse) D->coarse->launches = lc0;
+            MGCG_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            int s = dist_enqueue_iteration(c, x);
+            cudaError_t e = cudaStreamEndCapture(st, &D->graph);
+            if (s != MGCG_OK) return s;
+            MGCG_CUDA(e);
+            MGCG_CUDA(cudaGraphInstantiate(&D->graph_exec, D->graph, 0));
+            size_t nodes = 0;
+            cudaGraphGetNodes(D->graph, nullptr, &nodes);
+            D->graph_nodes = (int)nodes;
+            D->graph_mode = want_mode == 2 ? -2 : 1;
+        }
+        D->graph_halo = D->halo_exchanges - h0; D->graph_gather = D->allgathers - g0;
         D->graph_b = b; D->graph_x = x;
         c->launches = l0; D->halo_exchanges = h0; D->allgathers = g0;
         if (D->coarse) D->coarse->launches = lc0;
+    }
+    const bool while_loop = use_graph && D->graph_mode == 2;
+    if (while_loop) {
+        MGCG_CUDA(cudaGraphLaunch(D->graph_exec, st));
+        finished = true;
     }
     while (!finished) {   // every rank sees identical scalars, so every rank enqueues the same exchanges
         for (int k = 0; k < interval; ++k) {
@@ -839,6 +878,10 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     MGCG_CUDA(cudaEventRecord(ev1, st));
     MGCG_CUDA(cudaEventSynchronize(ev1));
     const Scalars fin = c->h_scalars[0];
+    if (while_loop) {
+        const int its = fin.iteration + 1;
+        c->launches += D->graph_nodes * its; D->halo_exchanges += D->graph_halo * its; D->allgathers += D->graph_gather * its;
+    }
     float ms = 0.f;
     MGCG_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
     cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(evp[0]); cudaEventDestroy(evp[1]);
@@ -852,7 +895,7 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
         res->kernel_launches = c->launches + (D->coarse ? D->coarse->launches : 0);
         res->operator_complexity = 1.0;
         res->reserved[0] = D->halo_exchanges; res->reserved[1] = D->allgathers; res->reserved[2] = D->first_replicated;
-        res->reserved[3] = D->peer.active ? MGCG_TRANSPORT_PEER : MGCG_TRANSPORT_NCCL; res->reserved[4] = use_graph ? 1 : 0;
+        res->reserved[3] = D->peer.active ? MGCG_TRANSPORT_PEER : MGCG_TRANSPORT_NCCL; res->reserved[4] = use_graph ? (while_loop ? 2 : 1) : 0;
     }
     if (D->trace) dist_trace_dump(c, fin.iteration + 1, ms);
     if (!fin.done) { set_error("mgcg_solve_dist: iteration cap reached without the device flag"); return MGCG_ERR_NOT_CONVERGED; }

@@ -130,6 +130,7 @@ struct DistState {
     cudaGraphExec_t graph_exec = nullptr;
     const double *graph_b = nullptr;
     double *graph_x = nullptr;
+    int graph_mode = 0;                     // 1: one iteration per launch; 2: device-side while loop; -2: asked for 2, unsupported
     int graph_halo = 0, graph_gather = 0, graph_nodes = 0;   // per-iteration counts recorded at capture
     // MGCG_DIST_TRACE=1: phase timeline of a solve (eager launches, one CUDA event per phase boundary), printed by rank 0
     bool trace = false;

@@ -1,6 +1,8 @@
 // mg.cuh — multigrid hierarchy data structures (device-resident).
 #pragma once
 #include "common.cuh"
+#include <chrono>
+#include <stdlib.h>
 
 namespace mgcg {
 
@@ -43,5 +45,19 @@ int build_prolongator(mgcg_ctx *c, const Csr &A, int row_base, const int *agg, c
 void set_alloc_stream(cudaStream_t st);   // stream used by the build helpers' pool allocations on this host thread
 int extract_dinv(mgcg_ctx *c, const Csr &A, int row_base, double *dinv);
 int csr_transpose(mgcg_ctx *c, const Csr &A, DevCsr *T);
+
+// MGCG_TRACE=1: wall-clock phase marks of the hierarchy build on stderr (synchronises the stream at every mark)
+struct PhaseTrace {
+    bool on; cudaStream_t st; std::chrono::steady_clock::time_point t0;
+    PhaseTrace(cudaStream_t s) : on(getenv("MGCG_TRACE") != nullptr), st(s) { if (on) { cudaStreamSynchronize(st); t0 = std::chrono::steady_clock::now(); } }
+    void mark(int level, const char *what)
+    {
+        if (!on) return;
+        cudaStreamSynchronize(st);
+        auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[mgcg setup] level %d %-12s %8.3f ms\n", level, what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
 
 }  // namespace mgcg

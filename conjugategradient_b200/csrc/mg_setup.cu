@@ -420,18 +420,6 @@ void mg_free(mgcg_ctx *c)
 }
 
 // MGCG_TRACE=1: wall-clock of every phase of the hierarchy build on stderr (synchronises the stream at each mark)
-struct PhaseTrace {
-    bool on; cudaStream_t st; std::chrono::steady_clock::time_point t0;
-    PhaseTrace(cudaStream_t s) : on(getenv("MGCG_TRACE") != nullptr), st(s) { if (on) { cudaStreamSynchronize(st); t0 = std::chrono::steady_clock::now(); } }
-    void mark(int level, const char *what)
-    {
-        if (!on) return;
-        cudaStreamSynchronize(st);
-        auto t1 = std::chrono::steady_clock::now();
-        fprintf(stderr, "[mgcg setup] level %d %-12s %8.3f ms\n", level, what, std::chrono::duration<double, std::milli>(t1 - t0).count());
-        t0 = t1;
-    }
-};
 
 int mg_build(mgcg_ctx *c)
 {

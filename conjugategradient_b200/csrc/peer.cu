@@ -139,14 +139,16 @@ __global__ void __launch_bounds__(64) k_peer_reduce(int mode, int k, int rank, i
     if (s_fail) { sc->status = MGCG_ERR_COMM; sc->done = 1; me->rseq = seq; return; }
     double s0 = 0.0, s1 = 0.0;
     for (int r = 0; r < world; ++r) { s0 += s_v[r][0]; s1 += s_v[r][1]; }   // rank order (cs:463 resultsDot.Sum())
-    dist_finalize(mode, s0, s1, sc);
+    if (mode >= 0) dist_finalize(mode, s0, s1, sc);
     me->rseq = seq;
 }
 
 // ---------------------------------------------------------------------------------------------------------
 static int grid_for(long long doubles, int sm_count)
 {
-    long long g = (doubles + 4095) / 4096;   // >= 16 doubles (2 x 128-bit stores in flight... per thread at 256 threads)
+    static int per_block = 0;
+    if (!per_block) { const char *e = getenv("MGCG_PEER_DOUBLES_PER_BLOCK"); per_block = e ? atoi(e) : 4096; if (per_block < 256) per_block = 256; }
+    long long g = (doubles + per_block - 1) / per_block;   // >= 16 doubles (2 x 128-bit stores in flight... per thread at 256 threads)
     if (g < 1) g = 1;
     if (g > sm_count) g = sm_count;           // all blocks must be co-resident: they spin on the flags
     return (int)g;
@@ -312,3 +314,31 @@ int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
 }
 
 }  // namespace mgcg
+
+using namespace mgcg;
+
+// Collective micro-benchmark of the loop's exchanges (all ranks call it after mgcg_setup_dist): `reps` back-to-back level-0
+// halo exchanges, coarse all-gathers and scalar reductions; out_us[0..2] = microseconds per operation on this rank.
+extern "C" int mgcg_dist_microbench(mgcg_ctx *c, int reps, double *out_us)
+{
+    if (!c || !c->dist || c->dist->L.empty() || !out_us || reps < 1) { set_error("mgcg_dist_microbench: bad argument / not set up"); return MGCG_ERR_INVALID; }
+    DistState *D = c->dist;
+    MGCG_CUDA(cudaSetDevice(c->device));
+    MGCG_CUDA(cudaMemsetAsync(c->d_scalars, 0, sizeof(Scalars), c->stream));
+    cudaEvent_t e[4];
+    for (int i = 0; i < 4; ++i) MGCG_CUDA(cudaEventCreate(&e[i]));
+    DistLevel &L0 = D->L[0];
+    for (int w = 0; w < 2; ++w) {      // pass 0 warms up
+        MGCG_CUDA(cudaEventRecord(e[0], c->stream));
+        for (int i = 0; i < reps; ++i) MGCG_CHECK(dist_halo_exchange(c, D->p, L0.own, L0.lo, L0.hi, L0.halo));
+        MGCG_CUDA(cudaEventRecord(e[1], c->stream));
+        if (D->coarse) for (int i = 0; i < reps; ++i) MGCG_CHECK(D->peer.active ? peer_allgather(c, D->coarse_b, D->coarse_offs) : MGCG_OK);
+        MGCG_CUDA(cudaEventRecord(e[2], c->stream));
+        if (D->peer.active) for (int i = 0; i < reps; ++i) MGCG_CHECK(peer_reduce(c, -1, 2, false));
+        MGCG_CUDA(cudaEventRecord(e[3], c->stream));
+        MGCG_CUDA(cudaStreamSynchronize(c->stream));
+    }
+    for (int i = 0; i < 3; ++i) { float ms = 0.f; cudaEventElapsedTime(&ms, e[i], e[i + 1]); out_us[i] = 1e3 * ms / reps; }
+    for (int i = 0; i < 4; ++i) cudaEventDestroy(e[i]);
+    return MGCG_OK;
+}

@@ -64,14 +64,17 @@ typedef struct mgcg_options {
     /* execution */
     int    spmv_kernel;      /* MGCG_SPMV_* */
     int    check_interval;   /* host polls the device-side convergence flag every this many iterations (default 8) */
-    int    use_graph;        /* 1: capture one iteration into a CUDA graph and replay it */
+    int    use_graph;        /* 0: eager launches; 1: one iteration captured into a CUDA graph, replayed check_interval times
+                                between host polls; 2 (default): the whole loop as ONE launch — a conditional WHILE node
+                                whose condition is the device-side convergence flag (falls back to 1 on old drivers) */
     int    profile;          /* 1: time the fine-level SpMV launches with CUDA events (disables the graph) */
     int    mg_smoothed_levels; /* with mg_smoothed: smooth the prolongator on the finest this-many levels only, plain
                                   aggregation below (0 = every level).  Smoothing widens the coarse stencils level by level. */
     int    mg_aggregate_size;        /* geometric aggregates are s x s x s grid blocks on level 0 (default 3; needs nx,ny,nz) */
     int    mg_aggregate_size_coarse; /* the same for levels >= 1 (default 2; 0 = as level 0) */
     int    dist_replicate_below;     /* sharded solve: levels with fewer global rows than this are replicated on every
-                                        rank (all-gathered right-hand side, redundant coarse solve); default 1<<20 */
+                                        rank (all-gathered right-hand side, redundant coarse solve); default 1<<18: sharding a
+                                        level pays for its four halo exchanges per cycle above ~2e5 rows */
     int    dist_transport;           /* sharded solve, exchanges inside the CG loop: MGCG_TRANSPORT_AUTO (peer memory when
                                         every rank can map every other, else NCCL), _NCCL, _PEER (or fail) */
     int    reserved[3];
@@ -147,6 +150,19 @@ int mgcg_mg_level_aggregates(mgcg_ctx *c, int level, int *agg);
 /* z = M r : one V-cycle applied to a device vector */
 int mgcg_mg_apply(mgcg_ctx *c, const double *d_r, double *d_z);
 
+/* ---- synthetic stencil matrices assembled in device memory, one z-slab [z0, z1) of an nx*ny*nz grid at a time (SURVEY.md
+ *      §8(f)2: the step before the path; the reference's generators are host loops, MgcgMain.cs:51-104).  Row layout of the
+ *      reference: diagonal first (MgcgMain.cs:59-60), global 0-based columns, row offsets rebased to the slab (Mgcg.cu:73).
+ *      *_nnz returns the slab's non-zero count (-1: bad arguments) so the caller can size the arrays. */
+long long mgcg_generate_poisson3d7_nnz(int nx, int ny, int nz, int z0, int z1);
+int mgcg_generate_poisson3d7(mgcg_ctx *c, int nx, int ny, int nz, int z0, int z1,
+                             double *d_elements, int *d_row_offsets, int *d_column_indeces);
+long long mgcg_generate_poisson3d27_nnz(int nx, int ny, int nz, int z0, int z1);
+/* 27-point variable coefficient: d_kblk = cell coefficients on block^3 cells (ceil(nx/block)*ceil(ny/block)*ceil(nz/block)),
+ * aniso3 = host array of the three axis weights */
+int mgcg_generate_poisson3d27(mgcg_ctx *c, int nx, int ny, int nz, int z0, int z1, int block, const double *d_kblk,
+                              const double *aniso3, double *d_elements, int *d_row_offsets, int *d_column_indeces);
+
 /* ---- row-block partition rule of the reference (bit-exact): ConjugateGradientParallelGpu.cs:271-277 */
 int mgcg_partition_offsets(int count, int device_count, int *offsets /* [device_count+1] */);
 
@@ -161,6 +177,9 @@ int mgcg_setup_dist(mgcg_ctx *c, int global_count, int row_offset, int local_cou
                     const double *d_elements, const int *d_row_offsets, const int *d_column_indeces,
                     const mgcg_options *opt);
 int mgcg_solve_dist(mgcg_ctx *c, const double *d_b_local, double *d_x_local, mgcg_result *res);
+/* collective micro-benchmark of the loop's exchanges after mgcg_setup_dist: microseconds per level-0 halo exchange,
+ * per coarse all-gather and per scalar reduction (back to back, `reps` each) */
+int mgcg_dist_microbench(mgcg_ctx *c, int reps, double *out_us /* [3] */);
 
 #ifdef __cplusplus
 }

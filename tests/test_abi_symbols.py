@@ -62,4 +62,12 @@ def test_options_struct_layout(L):
     from conjugategradient_b200.solver import default_options
     o = default_options()
     assert o.tolerance == 1e-8 and o.norm == 0 and o.precond == 0 and o.mg_pre_sweeps == 1 and abs(o.mg_omega - 0.8) < 1e-15
-    assert o.check_interval == 8 and o.use_graph == 1 and abs(o.mg_prolong_omega - 2 / 3) < 1e-15
+    assert o.check_interval == 8 and o.use_graph == 2 and abs(o.mg_prolong_omega - 2 / 3) < 1e-15
+
+
+def test_generator_sizes_host_side():
+    from conjugategradient_b200 import _lib
+    L = _lib.lib()
+    assert L.mgcg_generate_poisson3d7_nnz(4, 4, 4, 2, 2) == -1 and L.mgcg_generate_poisson3d7_nnz(4, 4, 4, 0, 5) == -1
+    assert L.mgcg_generate_poisson3d7_nnz(256, 256, 256, 0, 256) == 117047296          # SURVEY.md §8 size table, C4
+    assert L.mgcg_generate_poisson3d27_nnz(512, 512, 512, 0, 512) == 3609741304        # C5: exceeds int32 globally

@@ -150,11 +150,14 @@ def test_graph_and_eager_agree_bitwise(gen):
     b = gen.rhs_uniform(n, 1)
     tv, tr, tc, tb = (torch.as_tensor(a).cuda() for a in (v, rp, c, b))
     xs = []
-    for graph, interval in ((0, 1), (1, 8), (1, 3), (0, 16)):
+    for graph, interval in ((0, 1), (1, 8), (1, 3), (0, 16), (2, 8)):   # 2: device-side while loop, one launch
         m = S.Mgcg(0)
         m.setup(tv, tr, tc, S.default_options(use_graph=graph, check_interval=interval))
         tx = torch.zeros(n, dtype=torch.float64, device="cuda")
         res = m.solve(tb, tx)
+        if graph == 2:      # no speculative iterations: exactly iterations x (3 kernels + the loop-condition kernel) + the 2 init kernels
+            assert res.kernel_launches == 4 * res.iterations_done + 2, res.kernel_launches
+            res = m.solve(tb, tx.zero_())    # replay
         xs.append((res.iteration, tx.cpu().numpy()))
         m.close()
     for it, x in xs[1:]:

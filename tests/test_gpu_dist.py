@@ -28,6 +28,8 @@ CASES = [
     ("mg_replicated_peer", {"n": 32, "options": {"precond": 1, "dist_transport": 2}, "transport": 2}),
     ("mg_two_sharded_levels_peer", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2}, "transport": 2,
                                     "solves": 3}),
+    ("mg_two_sharded_levels_peer_graph1", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "use_graph": 1},
+                                           "transport": 2}),
     ("mg_27pt_peer_eager", {"n": 24, "matrix": "p27", "options": {"precond": 1, "dist_replicate_below": 500, "dist_transport": 2, "use_graph": 0},
                             "transport": 2}),
 ]

@@ -114,7 +114,7 @@ def test_mgcg_graph_vs_eager_bitwise(gen):
     v, rp, c = gen.poisson3d7(n)
     b = gen.rhs_uniform(n ** 3, 4)
     out = []
-    for graph in (0, 1):
+    for graph in (0, 1, 2):
         m = _setup(S, torch, v, rp, c, nx=n, ny=n, nz=n, norm=2, use_graph=graph, check_interval=4)
         tb, tx = torch.as_tensor(b).cuda(), torch.zeros(n ** 3, dtype=torch.float64, device="cuda")
         res = m.solve(tb, tx)
@@ -122,7 +122,7 @@ def test_mgcg_graph_vs_eager_bitwise(gen):
         assert res2.iteration == res.iteration
         out.append((res.iteration, tx.cpu().numpy()))
         m.close()
-    assert out[0][0] == out[1][0] and np.array_equal(out[0][1], out[1][1])
+    assert out[0][0] == out[1][0] == out[2][0] and np.array_equal(out[0][1], out[1][1]) and np.array_equal(out[0][1], out[2][1])
 
 
 def test_compat_solve_with_preconditioner_switch(oracle, gen):
