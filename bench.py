@@ -45,6 +45,8 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--device-gen", action="store_true", help="assemble the matrix on the device (mgcg_generate_poisson3d7); implied for --size > 256, "
                     "where the e2e and CPU legs (which need the host copy) are skipped")
+    ap.add_argument("--graph", type=int, default=-1, help="use_graph option: 0 eager, 1 one iteration per graph launch, 2 device-side while loop "
+                    "(library default); profilers want 0")
     ap.add_argument("--transport", type=int, default=0, help="sharded arm: 0 auto (peer memory on one node), 1 NCCL, 2 peer memory")
     ap.add_argument("--replicate-below", type=int, default=0, help="sharded arm: replicate multigrid levels smaller than this (0 = library default)")
     return ap.parse_args()
@@ -231,7 +233,8 @@ def run_ours_single(args):
     tx = torch.zeros(n, dtype=torch.float64, device=dev)
     torch.cuda.synchronize()
 
-    opts = S.default_options(precond=1, nx=n_side, ny=n_side, nz=n_side, norm=2, tolerance=TOL, max_iteration=1000, use_graph=1)
+    gopt = {} if args.graph < 0 else {"use_graph": args.graph}
+    opts = S.default_options(precond=1, nx=n_side, ny=n_side, nz=n_side, norm=2, tolerance=TOL, max_iteration=1000, **gopt)
     m.setup(tv, tr, tc, opts)
 
     def step():
@@ -378,6 +381,8 @@ def run_ours_dist(args):
         tv, tr, tc, tb = (t.to(dev, non_blocking=True) for t in (hv, hr, hc, hb))
     tx = torch.zeros(r1 - r0, dtype=torch.float64, device=dev)
     extra = {"dist_transport": args.transport}
+    if args.graph >= 0:
+        extra["use_graph"] = args.graph
     if args.replicate_below > 0:
         extra["dist_replicate_below"] = args.replicate_below
     opts = S.default_options(precond=1, nx=n_side, ny=n_side, nz=n_side, norm=2, tolerance=TOL, max_iteration=1000, **extra)

@@ -25,7 +25,7 @@ class Options(C.Structure):
         ("mg_omega", C.c_double), ("mg_smoother", C.c_int), ("mg_smoothed", C.c_int), ("mg_prolong_omega", C.c_double),
         ("spmv_kernel", C.c_int), ("check_interval", C.c_int), ("use_graph", C.c_int), ("profile", C.c_int),
         ("mg_smoothed_levels", C.c_int), ("mg_aggregate_size", C.c_int), ("mg_aggregate_size_coarse", C.c_int),
-        ("dist_replicate_below", C.c_int), ("dist_transport", C.c_int), ("reserved", C.c_int * 3),
+        ("dist_replicate_below", C.c_int), ("dist_transport", C.c_int), ("mg_tail_rows", C.c_int), ("reserved", C.c_int * 2),
     ]
 
 

@@ -67,7 +67,7 @@ void mgcg_options_default(mgcg_options *o)
     o->mg_coarse_size = 512;
     o->mg_pre_sweeps = 1;
     o->mg_post_sweeps = 1;
-    o->mg_omega = 0.8;
+    o->mg_omega = 0.85;   /* ~6/7, the optimal Jacobi damping of the 3-D 7-point stencil: one iteration fewer than 0.8 at 256^3 */
     o->mg_smoother = MGCG_SMOOTHER_JACOBI;
     o->mg_smoothed = 1;
     o->mg_aggregate_size = 3;          /* 3x3x3 on the finest level, 2x2x2 below: fewest total bytes per digit of residual */
@@ -102,6 +102,8 @@ mgcg_ctx *mgcg_create(int device)
     ok = ok && cudaMalloc((void **)&c->ws.ticket, sizeof(unsigned int)) == cudaSuccess;
     ok = ok && cudaMalloc((void **)&c->d_tmp_scalar, sizeof(double) * 4) == cudaSuccess;
     ok = ok && cudaMallocHost((void **)&c->h_tmp_scalar, sizeof(double) * 4) == cudaSuccess;
+    ok = ok && cudaMalloc((void **)&c->tail_barrier, 2 * sizeof(unsigned int)) == cudaSuccess;
+    ok = ok && cudaMemset(c->tail_barrier, 0, 2 * sizeof(unsigned int)) == cudaSuccess;
     ok = ok && cudaMemset(c->ws.ticket, 0, sizeof(unsigned int)) == cudaSuccess;
     ok = ok && cudaMemset(c->d_scalars, 0, sizeof(Scalars)) == cudaSuccess;
     if (!ok) { set_error("mgcg_create: allocation failed: %s", cudaGetErrorString(cudaGetLastError())); mgcg_destroy(c); return nullptr; }
@@ -133,6 +135,7 @@ void mgcg_destroy(mgcg_ctx *c)
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     if (c->ws.partial) cudaFree(c->ws.partial);
     if (c->ws.ticket) cudaFree(c->ws.ticket);
+    if (c->tail_barrier) cudaFree(c->tail_barrier);
     if (c->d_tmp_scalar) cudaFree(c->d_tmp_scalar);
     if (c->h_tmp_scalar) cudaFreeHost(c->h_tmp_scalar);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);

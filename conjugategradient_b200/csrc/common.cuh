@@ -88,6 +88,7 @@ struct Csr {
 struct SpmvPlan {
     int kernel = MGCG_SPMV_STREAM;  // STREAM or VECTOR
     bool tma = false;               // STREAM: use the TMA-staged variant (short rows, 16-byte aligned val/col)
+    bool tma_short = false;         // ... with twice the stages of half the size (very short rows)
     int rows_per_tile = 256;        // STREAM: rows handled per tile (<= 256)
     int lanes = 8;                  // VECTOR: lanes per row
     int grid = 0;
@@ -133,6 +134,7 @@ struct mgcg_ctx {
     mgcg::Scalars *d_scalars = nullptr;
     mgcg::Scalars *h_scalars = nullptr;  // pinned, 2 slots
     mgcg::ReduceWs ws{};
+    unsigned int *tail_barrier = nullptr; // {count, generation} of the persistent tail kernel's grid barrier
     double *d_tmp_scalar = nullptr;      // scratch device scalar for the standalone dot / maxabs calls
     double *h_tmp_scalar = nullptr;      // pinned
     // problem

@@ -86,7 +86,12 @@ __global__ void __launch_bounds__(kSpmvThreads) k_spmv_stream(SpmvArgs a, int ro
 // One thread per row walks its segment from shared memory in storage order with explicit mul/add roundings.
 constexpr int kTmaRows = 256;                 // rows per tile == threads per block
 constexpr int kTmaCap = 1920;                 // non-zeros a stage can hold: 2 stages x (8+4) B x 1920 = 45 KB static smem
-constexpr int kTmaStages = 2;
+constexpr int kTmaStagesLong = 2;
+// very short rows (prolongators: ~3 per row): a tile is only a few KB, so the same shared memory is cut into twice as
+// many stages of half the size — more TMA copies in flight per SM (the ncu capture of the 2-stage kernel on P showed 53 %
+// of DRAM peak against 73-75 % on the 7-per-row operator)
+constexpr int kTmaCapShort = 960;
+constexpr int kTmaStagesShort = 4;
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
@@ -117,7 +122,7 @@ __device__ __forceinline__ void tma_load_1d(void *dst, const void *src, unsigned
 
 struct TmaMeta { int k0, k1, direct, pad; };
 
-template <int EPI>
+template <int EPI, int kTmaCap, int kTmaStages>
 __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles, ReduceWs ws, Scalars *sc)
 {
     if (a.gated && sc->done) return;
@@ -254,6 +259,7 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel)
     p.kernel = kernel;
     // short rows (a 256-row tile fits a TMA stage): the TMA-staged variant of the stream kernel
     p.tma = (kernel == MGCG_SPMV_STREAM && avg * kTmaRows <= kTmaCap - 64);
+    p.tma_short = p.tma && avg * kTmaRows <= kTmaCapShort - 64;
     if (kernel == MGCG_SPMV_STREAM) {
         int per = (int)(avg + 0.999);
         if (per < 1) per = 1;
@@ -283,7 +289,8 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
         const int tiles = div_up(a.A.rows, kTmaRows);
         int grid = c->sm_count * 4;
         if (grid > tiles) grid = tiles;
-        k_spmv_tma<EPI><<<grid, kTmaRows, 0, c->stream>>>(a, tiles, c->ws, c->d_scalars);
+        if (plan.tma_short) k_spmv_tma<EPI, kTmaCapShort, kTmaStagesShort><<<grid, kTmaRows, 0, c->stream>>>(a, tiles, c->ws, c->d_scalars);
+        else k_spmv_tma<EPI, kTmaCap, kTmaStagesLong><<<grid, kTmaRows, 0, c->stream>>>(a, tiles, c->ws, c->d_scalars);
     } else if (plan.kernel == MGCG_SPMV_STREAM) {
         int tiles = div_up(a.A.rows, plan.rows_per_tile);
         k_spmv_stream<EPI><<<plan.grid, kSpmvThreads, 0, c->stream>>>(a, plan.rows_per_tile, tiles, c->ws, c->d_scalars);

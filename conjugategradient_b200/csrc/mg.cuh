@@ -28,7 +28,27 @@ struct MgLevel {
     int dims[3] = {0, 0, 0};
 };
 
+// arguments of the persistent coarse-tail kernel (mg_tail.cu)
+constexpr int kTailMaxLevels = 8;
+struct TailLevel {
+    Csr A, P, R;
+    const double *dinv;
+    double *xa, *xb, *b, *r;
+    double *xfinal;              // buffer that holds the level's x when the cycle leaves it
+    int lanesA, lanesP, lanesR;
+};
+struct TailArgs {
+    int nl;                      // levels in the tail; the last one is the dense coarsest level
+    TailLevel L[kTailMaxLevels];
+    const double *coarse_inv;
+    int coarse_n;
+    double omega;
+    int pre, post;
+    unsigned int *barrier;       // {arrival count, generation}
+};
+
 struct Hierarchy {
+    int tail_first = -1;            // first level handled by the persistent tail kernel (-1: none)
     std::vector<MgLevel> L;
     double *coarse_inv = nullptr;   // dense inverse of the coarsest operator (n x n row-major)
     int coarse_n = 0;
@@ -45,6 +65,9 @@ int build_prolongator(mgcg_ctx *c, const Csr &A, int row_base, const int *agg, c
 void set_alloc_stream(cudaStream_t st);   // stream used by the build helpers' pool allocations on this host thread
 int extract_dinv(mgcg_ctx *c, const Csr &A, int row_base, double *dinv);
 int csr_transpose(mgcg_ctx *c, const Csr &A, DevCsr *T);
+// ---- mg_tail.cu
+void mg_tail_plan(mgcg_ctx *c);
+int mg_tail_run(mgcg_ctx *c, int first, double **x_out);
 
 // MGCG_TRACE=1: wall-clock phase marks of the hierarchy build on stderr (synchronises the stream at every mark)
 struct PhaseTrace {

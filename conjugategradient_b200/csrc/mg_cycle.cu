@@ -36,8 +36,14 @@ int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done
         *z_out = L.xb;
         return MGCG_OK;
     }
+    // the coarse tail runs as one persistent kernel (mg_tail.cu).  It may start at level 0 only for a pure application
+    // (level 0's fused first sweep and fused r.z belong to the CG kernels)
+    int t0 = H->tail_first;
+    if (t0 == 0 && (fuse_first_done || rz_fin >= 0)) t0 = 1;
+    if (t0 > nl - 2) t0 = -1;
+    const int down_end = t0 >= 0 ? t0 : nl - 1;
     // ---- down
-    for (int l = 0; l < nl - 1; ++l) {
+    for (int l = 0; l < down_end; ++l) {
         MgLevel &L = H->L[l];
         L.xcur = L.xa;
         if (!(l == 0 && fuse_first_done)) MGCG_CHECK(mg_jacobi_first(c, L.A.rows, omega, L.dinv, L.b, L.xa));
@@ -49,14 +55,17 @@ int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done
         q.A = L.R.view(); q.x = L.r; q.y = H->L[l + 1].b; q.gated = true;
         MGCG_CHECK(spmv_launch(c, L.planR, EPI_PLAIN, q));
     }
-    // ---- coarsest
-    {
+    if (t0 >= 0) {
+        double *xt = nullptr;
+        MGCG_CHECK(mg_tail_run(c, t0, &xt));
+        if (t0 == 0) { *z_out = xt; return MGCG_OK; }
+    } else {   // ---- coarsest
         MgLevel &L = H->L[nl - 1];
         MGCG_CHECK(mg_dense_apply(c, L.A.rows, H->coarse_inv, L.b, L.xa));
         L.xcur = L.xa;
     }
     // ---- up
-    for (int l = nl - 2; l >= 0; --l) {
+    for (int l = down_end - 1; l >= 0; --l) {
         MgLevel &L = H->L[l];
         SpmvArgs a;
         a.A = L.P.view(); a.x = H->L[l + 1].xcur; a.y = L.xcur; a.alpha = 1.0; a.beta = 1.0; a.gated = true;

@@ -506,6 +506,7 @@ int mg_build(mgcg_ctx *c)
     MGCG_CHECK(dense_inverse(c, Lc.A, &H->coarse_inv));
     tr.mark((int)H->L.size() - 1, "dense-inverse");
     H->op_complexity = nnz_sum / (double)(c->A.nnz > 0 ? c->A.nnz : 1);
+    mg_tail_plan(c);
     MGCG_CUDA(cudaStreamSynchronize(st));
     return MGCG_OK;
 }

@@ -57,7 +57,7 @@ typedef struct mgcg_options {
     int    mg_coarse_size;   /* stop coarsening at <= this many rows; dense inverse there (default 512) */
     int    mg_pre_sweeps;    /* default 1 */
     int    mg_post_sweeps;   /* default 1 (keep == pre for an SPD preconditioner) */
-    double mg_omega;         /* Jacobi damping, default 0.8 */
+    double mg_omega;         /* Jacobi damping, default 0.85 */
     int    mg_smoother;      /* MGCG_SMOOTHER_* */
     int    mg_smoothed;      /* 1: smoothed-aggregation prolongator P=(I-w D^-1 A)T; 0: plain aggregation */
     double mg_prolong_omega; /* default 2/3 */
@@ -77,7 +77,10 @@ typedef struct mgcg_options {
                                         level pays for its four halo exchanges per cycle above ~2e5 rows */
     int    dist_transport;           /* sharded solve, exchanges inside the CG loop: MGCG_TRANSPORT_AUTO (peer memory when
                                         every rank can map every other, else NCCL), _NCCL, _PEER (or fail) */
-    int    reserved[3];
+    int    mg_tail_rows;             /* > 0: multigrid levels with at most this many rows (the coarse tail of the cycle) run as
+                                        ONE persistent kernel with grid barriers between the steps.  Default 0 = off: measured
+                                        no faster than graph-replayed launches on B200 (mg_tail.cu) */
+    int    reserved[2];
 } mgcg_options;
 
 typedef struct mgcg_result {

@@ -173,12 +173,12 @@ class MgRef:
         lib().mg_ref_level_agg(self.h, l, agg)
         return agg
 
-    def apply(self, r, pre=1, post=1, omega=0.8):
+    def apply(self, r, pre=1, post=1, omega=0.85):
         z = np.empty(self.n)
         lib().mg_ref_apply(self.h, pre, post, omega, np.ascontiguousarray(r, dtype=np.float64), z)
         return z
 
-    def pcg(self, b, x0=None, tol=1e-8, min_iteration=0, max_iteration=None, norm=NORM_ABS_L2, min_strict=False, pre=1, post=1, omega=0.8):
+    def pcg(self, b, x0=None, tol=1e-8, min_iteration=0, max_iteration=None, norm=NORM_ABS_L2, min_strict=False, pre=1, post=1, omega=0.85):
         x = np.zeros(self.n) if x0 is None else np.array(x0, dtype=np.float64, copy=True)
         it, res = C.c_int(0), C.c_double(0)
         st = lib().mg_ref_pcg(self.h, pre, post, omega, np.ascontiguousarray(b, dtype=np.float64), x, tol, min_iteration,

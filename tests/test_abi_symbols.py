@@ -61,7 +61,7 @@ def test_fails_loudly_without_gpu(L):
 def test_options_struct_layout(L):
     from conjugategradient_b200.solver import default_options
     o = default_options()
-    assert o.tolerance == 1e-8 and o.norm == 0 and o.precond == 0 and o.mg_pre_sweeps == 1 and abs(o.mg_omega - 0.8) < 1e-15
+    assert o.tolerance == 1e-8 and o.norm == 0 and o.precond == 0 and o.mg_pre_sweeps == 1 and abs(o.mg_omega - 0.85) < 1e-15
     assert o.check_interval == 8 and o.use_graph == 2 and abs(o.mg_prolong_omega - 2 / 3) < 1e-15
 
 
