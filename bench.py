@@ -62,6 +62,26 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def ncu_traffic(kernel_substr, n_side):
+    """DRAM bytes (read + write) of one launch of the dominant kernel from the committed `ncu --set full` capture of this
+    workload (profiles/r01_ncu_full_spmv_tma_256.csv, taken at 256^3); None for other sizes or if the file is absent."""
+    import csv
+    p = os.path.join(ROOT, "profiles", "r01_ncu_full_spmv_tma_256.csv")
+    if n_side != 256 or not os.path.exists(p):
+        return None
+    try:
+        rows = list(csv.reader(open(p)))
+        hdr, units = rows[0], rows[1]
+        ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
+        for r in rows[2:]:
+            if kernel_substr in r[0]:
+                return float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]]
+    except Exception:
+        return None
+    return None
+
+
 class ClockSampler:
     """nvidia-smi clocks + throttle reasons sampled every 200 ms during the timed region (B200_PROFILING.md)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -285,8 +305,10 @@ def run_ours_single(args):
     spmv_bytes = 12.0 * nnz + 20.0 * n
     peak, peak_how = measured_peak()
     achieved = spmv_bytes / (spmv_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_spmv_stream<EPI_DOT> (fine-level A*p with fused p.Ap)", "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "frac_of_8TBs_nominal": achieved / 8000.0, "traffic": None,
+    roofline = {"bound": "hbm", "kernel": "k_spmv_tma<EPI_DOT> (fine-level A*p with fused p.Ap, TMA-staged stream kernel)", "achieved": achieved,
+                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "frac_of_8TBs_nominal": achieved / 8000.0,
+                "traffic": ncu_traffic("k_spmv_tma<2>", n_side),
+                "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r01_ncu_full_spmv_tma_256.csv)",
                 "peak_source": peak_how, "bytes_per_launch": spmv_bytes, "ms_per_launch": spmv_ms,
                 "launches_timed": pres.spmv_launches, "isolated_ms_per_launch": spmv_iso_ms,
                 "isolated_gbs": spmv_bytes / (spmv_iso_ms * 1e-3) / 1e9}
@@ -477,7 +499,7 @@ def run_ours_dist(args):
                "final_relative_residual": res.residual, "setup_ms": res.setup_ms, "levels": res.levels,
                "distributed_levels": res.reserved[2], "halo_exchanges_per_solve": res.reserved[0], "allgathers_per_solve": res.reserved[1],
                "spmv_gbs": achieved * world, "gpu_launches": launches, "clocks": clk,
-               "roofline": {"bound": "hbm", "kernel": "k_spmv_stream<EPI_DOT> on rank 0's shard (isolated, back to back)", "achieved": achieved,
+               "roofline": {"bound": "hbm", "kernel": "k_spmv_tma<EPI_DOT> on rank 0's shard (isolated, back to back)", "achieved": achieved,
                             "peak": peak, "unit": "GB/s", "frac": achieved / peak, "frac_of_8TBs_nominal": achieved / 8000.0, "traffic": None,
                             "peak_source": peak_how, "bytes_per_launch": spmv_bytes, "ms_per_launch": spmv_ms},
                "cpu_baseline": None, "e2e": e2e}

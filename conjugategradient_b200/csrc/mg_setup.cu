@@ -360,6 +360,111 @@ static int dense_inverse(mgcg_ctx *c, const Csr &A, double **Minv)
     return MGCG_OK;
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// Smoothed prolongator WITHOUT the global sort, for matrices whose rows are short (row length + 1 <= MAXM): one thread per
+// row keeps the row's (aggregate, value) pairs in registers, emits the distinct aggregates in ascending order and sums the
+// duplicates of each in storage order — the same order and roundings as k_expand_sa + stable sort + k_compress (and as the
+// CPU twin, oracle/mg_ref.c b_row), so P is bit-identical.  Replaces a 64-bit radix sort of nnz(A)+n pairs (12 ms of the
+// 87 ms hierarchy build at 256^3) by two streaming passes over A.
+template <int MAXM>
+__device__ __forceinline__ int psa_load(const Csr &A, int i, int row_base, const int *__restrict__ agg, const double *__restrict__ dinv, double w,
+                                        int (&cc)[MAXM], double (&vv)[MAXM], bool with_values)
+{
+    const int ks = A.rowptr[i], m = A.rowptr[i + 1] - ks + 1;
+    const double f = with_values ? -__dmul_rn(w, dinv[i]) : 0.0;
+#pragma unroll
+    for (int k = 0; k < MAXM; ++k) {
+        cc[k] = 0x7fffffff; vv[k] = 0.0;
+        if (k == 0) { cc[0] = agg[i + row_base]; vv[0] = 1.0; }
+        else if (k < m) {
+            cc[k] = agg[A.col[ks + k - 1]];
+            if (with_values) vv[k] = __dmul_rn(f, A.val[ks + k - 1]);
+        }
+    }
+    return m;
+}
+
+template <int MAXM>
+__global__ void __launch_bounds__(256) k_psa_count(Csr A, int row_base, const int *__restrict__ agg, int *__restrict__ cnt)
+{
+    int cc[MAXM]; double vv[MAXM];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x) {
+        psa_load<MAXM>(A, i, row_base, agg, nullptr, 0.0, cc, vv, false);
+        int distinct = 0;
+#pragma unroll
+        for (int k = 0; k < MAXM; ++k) {
+            bool first = cc[k] != 0x7fffffff;
+#pragma unroll
+            for (int j = 0; j < k; ++j) first = first && (cc[j] != cc[k]);
+            distinct += first ? 1 : 0;
+        }
+        cnt[i] = distinct;
+    }
+}
+
+template <int MAXM>
+__global__ void __launch_bounds__(256) k_psa_fill(Csr A, int row_base, const int *__restrict__ agg, const double *__restrict__ dinv, double w,
+                                                  const int *__restrict__ p_rowptr, int *__restrict__ p_col, double *__restrict__ p_val)
+{
+    int cc[MAXM]; double vv[MAXM];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x) {
+        psa_load<MAXM>(A, i, row_base, agg, dinv, w, cc, vv, true);
+        const int o0 = p_rowptr[i], n_out = p_rowptr[i + 1] - o0;
+        int last = -1;
+        for (int o = 0; o < n_out; ++o) {
+            int cur = 0x7fffffff;
+#pragma unroll
+            for (int k = 0; k < MAXM; ++k) if (cc[k] > last && cc[k] < cur) cur = cc[k];
+            double sum = 0.0;
+            bool have = false;
+#pragma unroll
+            for (int k = 0; k < MAXM; ++k)
+                if (cc[k] == cur) { sum = have ? __dadd_rn(sum, vv[k]) : vv[k]; have = true; }
+            p_col[o0 + o] = cur; p_val[o0 + o] = sum;
+            last = cur;
+        }
+    }
+}
+
+__global__ void k_max_row(Csr A, int *out)
+{
+    int m = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x) m = max(m, A.rowptr[i + 1] - A.rowptr[i]);
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_down_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(out, m);
+}
+
+template <int MAXM>
+static int psa_direct(mgcg_ctx *c, const Csr &A, int row_base, const int *agg, const double *dinv, double omega, int ncoarse, DevCsr *P)
+{
+    cudaStream_t st = c->stream;
+    const int n = A.rows;
+    int *cnt = nullptr;
+    MGCG_CHECK(dalloc(&cnt, (size_t)n + 1));
+    MGCG_CUDA(cudaMemsetAsync(cnt + n, 0, sizeof(int), st));
+    int g = grid_for(n);
+    if (g > c->sm_count * 32) g = c->sm_count * 32;
+    k_psa_count<MAXM><<<g, 256, 0, st>>>(A, row_base, agg, cnt);
+    MGCG_LAUNCH_CHECK();
+    P->rows = n; P->cols = ncoarse;
+    MGCG_CHECK(dalloc(&P->rowptr, (size_t)n + 1));
+    size_t tb = 0;
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, P->rowptr, n + 1, st));
+    void *tmp = nullptr;
+    MGCG_CUDA(pool_alloc(&tmp, tb, st));
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, P->rowptr, n + 1, st));
+    int nnz = 0;
+    MGCG_CUDA(cudaMemcpyAsync(&nnz, P->rowptr + n, sizeof(int), cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    tfree(tmp); tfree(cnt);
+    P->nnz = nnz;
+    MGCG_CHECK(dalloc(&P->val, (size_t)nnz)); MGCG_CHECK(dalloc(&P->col, (size_t)nnz));
+    k_psa_fill<MAXM><<<g, 256, 0, st>>>(A, row_base, agg, dinv, omega, P->rowptr, P->col, P->val);
+    MGCG_LAUNCH_CHECK();
+    return MGCG_OK;
+}
+
 // P = T (plain aggregation) or (I - w D^-1 A) T (smoothed) for the rows of A.  `agg` is indexed by GLOBAL row / column id
 // (row i of A is global row i + row_base); columns of P are aggregate ids.
 int build_prolongator(mgcg_ctx *c, const Csr &A, int row_base, const int *agg, const double *dinv, bool smooth, double omega,
@@ -373,6 +478,19 @@ int build_prolongator(mgcg_ctx *c, const Csr &A, int row_base, const int *agg, c
         k_build_T<<<grid_for(n + 1), 256, 0, st>>>(n, row_base, agg, P->val, P->rowptr, P->col);
         MGCG_LAUNCH_CHECK();
         return MGCG_OK;
+    }
+    {   // short rows: no global sort
+        int *d_max = nullptr, maxrow = 0;
+        MGCG_CHECK(dalloc(&d_max, 1));
+        MGCG_CUDA(cudaMemsetAsync(d_max, 0, sizeof(int), st));
+        k_max_row<<<grid_for(n) > 4096 ? 4096 : grid_for(n), 256, 0, st>>>(A, d_max);
+        MGCG_LAUNCH_CHECK();
+        MGCG_CUDA(cudaMemcpyAsync(&maxrow, d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
+        MGCG_CUDA(cudaStreamSynchronize(st));
+        tfree(d_max);
+        if (maxrow + 1 <= 8) return psa_direct<8>(c, A, row_base, agg, dinv, omega, ncoarse, P);
+        if (maxrow + 1 <= 16) return psa_direct<16>(c, A, row_base, agg, dinv, omega, ncoarse, P);
+        if (maxrow + 1 <= 32) return psa_direct<32>(c, A, row_base, agg, dinv, omega, ncoarse, P);
     }
     const size_t count = (size_t)A.nnz + n;
     u64 *keys = nullptr; double *vals = nullptr;

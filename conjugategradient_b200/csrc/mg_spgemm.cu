@@ -169,6 +169,130 @@ __global__ void k_spgemm_maxprod(Csr A, Csr B, int shift, int *out_max)
     if ((threadIdx.x & 31) == 0) atomicMax(out_max, m);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// FEW, VERY LONG rows (the coarsest levels: a few hundred to a few thousand rows whose products run to 10^5 per row, all
+// columns within a few thousand): one BLOCK per row with a dense accumulator over the column space in shared memory.
+// The A row is still walked entry by entry in storage order (a block barrier per entry orders the adds to one c_ij), the
+// 256 threads take the entries of the selected B row (distinct columns, no conflicts), so the sums and roundings are the
+// ones of the hash kernels and of the CPU twin.  No hashing, no sort: the output is read off the accumulator in column
+// order.  With 32 lanes per row these levels took 3-6 ms per product (9 300 dependent hash steps per row at 216 rows).
+constexpr int kDenseThreads = 256;
+constexpr int kDenseChunk = 256;      // A-row entries staged per pass
+
+template <bool NUMERIC>
+__global__ void __launch_bounds__(kDenseThreads) k_spgemm_dense_row(Csr A, Csr B, int shift, int cols, int *__restrict__ cnt,
+                                                                    const int *__restrict__ c_rowptr, int *__restrict__ c_col,
+                                                                    double *__restrict__ c_val)
+{
+    extern __shared__ double sm_dense[];
+    double *acc = sm_dense;                                             // [cols]              (NUMERIC)
+    unsigned char *mark = reinterpret_cast<unsigned char *>(sm_dense + (NUMERIC ? cols : 0));   // [cols]
+    __shared__ int s_q0[kDenseChunk], s_q1[kDenseChunk];
+    __shared__ double s_a[kDenseChunk];
+    __shared__ int s_scan[kDenseThreads];
+    const int t = threadIdx.x;
+    for (int c = t; c < cols; c += kDenseThreads) { if (NUMERIC) acc[c] = 0.0; mark[c] = 0; }
+    __syncthreads();
+    for (int row = blockIdx.x; row < A.rows; row += gridDim.x) {
+        const int ks = A.rowptr[row], ke = A.rowptr[row + 1];
+        for (int kb = ks; kb < ke; kb += kDenseChunk) {
+            const int nk = min(kDenseChunk, ke - kb);
+            if (t < nk) {
+                const int j = A.col[kb + t] - shift;
+                s_q0[t] = B.rowptr[j]; s_q1[t] = B.rowptr[j + 1];
+                if (NUMERIC) s_a[t] = A.val[kb + t];
+            }
+            __syncthreads();
+            if (!NUMERIC) {   // counting needs no order: every thread takes whole B rows
+                for (int e = t; e < nk; e += kDenseThreads)
+                    for (int q = s_q0[e]; q < s_q1[e]; ++q) mark[B.col[q]] = 1;
+            } else {
+                int q0 = s_q0[0], q1 = s_q1[0];
+                int c_cur = 0; double v_cur = 0.0;
+                if (q0 + t < q1) { c_cur = B.col[q0 + t]; v_cur = B.val[q0 + t]; }
+                for (int e = 0; e < nk; ++e) {
+                    const double a = s_a[e];
+                    int q0n = 0, q1n = 0, c_nxt = 0; double v_nxt = 0.0;
+                    if (e + 1 < nk) {   // the next B row's first entries are in flight while this one is added
+                        q0n = s_q0[e + 1]; q1n = s_q1[e + 1];
+                        if (q0n + t < q1n) { c_nxt = B.col[q0n + t]; v_nxt = B.val[q0n + t]; }
+                    }
+                    for (int q = q0 + t; q < q1; q += kDenseThreads) {
+                        int col = c_cur; double bv = v_cur;
+                        if (q != q0 + t) { col = B.col[q]; bv = B.val[q]; }
+                        acc[col] = __dadd_rn(acc[col], __dmul_rn(a, bv));      // first product: 0 + prod == prod exactly
+                        mark[col] = 1;
+                    }
+                    __syncthreads();      // orders this entry's adds before the next entry's
+                    q0 = q0n; q1 = q1n; c_cur = c_nxt; v_cur = v_nxt;
+                }
+            }
+            __syncthreads();
+        }
+        // ---- read the row off in column order: thread t owns the contiguous slice [c0, c1)
+        const int per = (cols + kDenseThreads - 1) / kDenseThreads;
+        const int c0 = min(t * per, cols), c1 = min(c0 + per, cols);
+        int mine = 0;
+        for (int c = c0; c < c1; ++c) mine += mark[c];
+        s_scan[t] = mine;
+        __syncthreads();
+        for (int o = 1; o < kDenseThreads; o <<= 1) {      // inclusive Hillis-Steele scan
+            const int v = (t >= o) ? s_scan[t - o] : 0;
+            __syncthreads();
+            s_scan[t] += v;
+            __syncthreads();
+        }
+        if (!NUMERIC) {
+            if (t == kDenseThreads - 1) cnt[row] = s_scan[t];
+            for (int c = c0; c < c1; ++c) mark[c] = 0;
+        } else {
+            int o = c_rowptr[row] + s_scan[t] - mine;
+            for (int c = c0; c < c1; ++c)
+                if (mark[c]) { c_col[o] = c; c_val[o] = acc[c]; ++o; acc[c] = 0.0; mark[c] = 0; }
+        }
+        __syncthreads();
+    }
+}
+
+// C = A*B for few long rows over a small column space.  *done = false when the shape does not qualify.
+static int run_dense_rows(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, int maxprod, DevCsr *C, bool *done)
+{
+    cudaStream_t st = c->stream;
+    *done = false;
+    const int cols = B.cols;
+    int min_prod = 16384;      // below this the 32-lane hash kernels are faster (MGCG_SPGEMM_DENSE_MIN: tests force the path)
+    if (const char *e = getenv("MGCG_SPGEMM_DENSE_MIN")) min_prod = atoi(e);
+    if (A.rows > 2048 || cols > 8192 || maxprod < min_prod) return MGCG_OK;
+    const size_t sm_s = (size_t)cols + 16, sm_n = (size_t)cols * 9 + 16;
+    MGCG_CUDA(cudaFuncSetAttribute(k_spgemm_dense_row<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_n));
+    int *cnt = nullptr;
+    MGCG_CUDA(pool_alloc((void **)&cnt, sizeof(int) * ((size_t)A.rows + 1), st));
+    MGCG_CUDA(cudaMemsetAsync(cnt + A.rows, 0, sizeof(int), st));
+    int grid = A.rows < c->sm_count * 2 ? A.rows : c->sm_count * 2;
+    k_spgemm_dense_row<false><<<grid, kDenseThreads, sm_s, st>>>(A, B, shift, cols, cnt, nullptr, nullptr, nullptr);
+    MGCG_LAUNCH_CHECK();
+    C->rows = A.rows; C->cols = B.cols;
+    MGCG_CUDA(pool_alloc((void **)&C->rowptr, sizeof(int) * ((size_t)A.rows + 1), st));
+    size_t tb = 0;
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, C->rowptr, A.rows + 1, st));
+    void *tmp = nullptr;
+    MGCG_CUDA(pool_alloc(&tmp, tb, st));
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, C->rowptr, A.rows + 1, st));
+    int nnz = 0;
+    MGCG_CUDA(cudaMemcpyAsync(&nnz, C->rowptr + A.rows, sizeof(int), cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    pool_free(tmp, st); pool_free(cnt, st);
+    C->nnz = nnz;
+    MGCG_CUDA(pool_alloc((void **)&C->val, sizeof(double) * (size_t)(nnz > 0 ? nnz : 1), st));
+    MGCG_CUDA(pool_alloc((void **)&C->col, sizeof(int) * (size_t)(nnz > 0 ? nnz : 1), st));
+    if (getenv("MGCG_TRACE")) fprintf(stderr, "[mgcg spgemm] rows %d dense-row kernel, cols %d maxprod %d nnz %d grid %d\n", A.rows, cols, maxprod, nnz, grid);
+    k_spgemm_dense_row<true><<<grid, kDenseThreads, sm_n, st>>>(A, B, shift, cols, nullptr, C->rowptr, C->col, C->val);
+    MGCG_LAUNCH_CHECK();
+    *done = true;
+    return MGCG_OK;
+}
+
 static int pow2_at_least(long long v) { int p = 32; while (p < v) p <<= 1; return p; }
 
 template <int G>
@@ -258,6 +382,8 @@ int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C, int col_shift)
     pool_free(d_max, st);
     const double avg_b = (double)B.nnz / (B.rows > 0 ? B.rows : 1);
     bool done = false;
+    MGCG_CHECK(run_dense_rows(c, A, B, col_shift, maxprod, C, &done));
+    if (done) return MGCG_OK;
     int s;
     if (avg_b <= 4.5) s = run_hash<4>(c, A, B, col_shift, maxprod, C, &done);
     else if (avg_b <= 10.0) s = run_hash<8>(c, A, B, col_shift, maxprod, C, &done);

@@ -16,8 +16,10 @@
 //              and the block that takes the last ticket publishes  receiver.xflag[my rank] = s  (st.release.sys)
 //     phase 2  wait (ld.acquire.sys) until xflag[q] >= s for every rank q I receive from, then unpack stage[s & 1]
 //              into the ghost rows of the destination vector.
-// Double buffering is what makes it safe without an acknowledgement: a sender can overwrite stage[s & 1] only in
-// exchange s+2, which it reaches after waiting for MY flag of exchange s+1, which I publish after my unpack of s.
+// Double buffering is what makes it safe without an acknowledgement: a NEIGHBOUR can overwrite its halo slot of
+// stage[s & 1] only in exchange s+2, which it reaches after waiting for MY flag of exchange s+1, which I publish after my
+// unpack of s.  The all-gather is pushed by every rank (not only neighbours): it has its own staging region, and two
+// gathers are always separated by a scalar reduction, which is a full barrier (every rank waits for every rank).
 // The scalar reduction is the same idea in one block: every rank stores its partial sums into slot[s & 1][rank] of every
 // rank, then sums the slots IN RANK ORDER (deterministic and identical everywhere, like the reference's host sum).
 // A wait that lasts longer than ~4 s marks the solve as failed (MGCG_ERR_COMM) instead of hanging the device.
@@ -197,13 +199,14 @@ int peer_allgather(mgcg_ctx *c, double *full, const int *offs)
     DistState *D = c->dist;
     PeerState &P = D->peer;
     const int rk = D->rank, W = D->world;
-    if ((size_t)offs[W] > P.stage_cap) { set_error("peer_allgather: %d rows exceed the staging capacity", offs[W]); return MGCG_ERR_INVALID; }
+    if ((size_t)2 * P.halo_cap + (size_t)offs[W] > P.stage_cap) { set_error("peer_allgather: %d rows exceed the staging capacity", offs[W]); return MGCG_ERR_INVALID; }
     XchgDesc d;
     memset(&d, 0, sizeof(d));
     d.stage_stride = P.stage_cap;
     for (int q = 0; q < W; ++q) {
         if (q == rk) continue;
-        double *stq = (double *)((char *)P.peer[q] + P.stage_off), *stme = (double *)((char *)P.peer[rk] + P.stage_off);
+        double *stq = (double *)((char *)P.peer[q] + P.stage_off) + 2 * (size_t)P.halo_cap;
+        double *stme = (double *)((char *)P.peer[rk] + P.stage_off) + 2 * (size_t)P.halo_cap;
         d.s[d.ns].src = full + offs[rk]; d.s[d.ns].dst = stq + offs[rk]; d.s[d.ns].flag = &((PeerCtl *)P.peer[q])->xflag[rk];
         d.s[d.ns].count = offs[rk + 1] - offs[rk]; d.ns++;
         d.r[d.nr].stage = stme + offs[q]; d.r[d.nr].dst = full + offs[q]; d.r[d.nr].flag = &((PeerCtl *)P.peer[rk])->xflag[q];
@@ -257,8 +260,10 @@ int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
     peer_close(c);
     if (W < 2 || W > kPeerMax) return MGCG_OK;
     halo_cap = (halo_cap + 1) & ~1;
-    size_t cap = (size_t)2 * halo_cap;
-    if ((size_t)gather_cap > cap) cap = (size_t)gather_cap;
+    // halo and gather staging are DISJOINT: a gather is pushed by every rank, also by ranks that are not this rank's
+    // neighbours and have therefore not synchronised with it in the halo exchanges just before — their blocks must not land
+    // where a slower rank may still be unpacking a halo of two exchanges ago (seen as a changed iteration count at 8 GPUs)
+    size_t cap = (size_t)2 * halo_cap + (size_t)gather_cap;
     cap = (cap + 1) & ~(size_t)1;
     P.halo_cap = halo_cap; P.stage_cap = cap;
     P.stage_off = (sizeof(PeerCtl) + 255) & ~(size_t)255;

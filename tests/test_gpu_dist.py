@@ -30,16 +30,22 @@ CASES = [
                                     "solves": 3}),
     ("mg_two_sharded_levels_peer_graph1", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "use_graph": 1},
                                            "transport": 2}),
+    # four ranks: ranks that are not neighbours push into each other's staging only in the all-gather (eager launches drift most)
+    ("mg_two_sharded_levels_peer_eager_w4", {"n": 48, "world": 4, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "use_graph": 0},
+                                             "transport": 2, "solves": 3}),
+    ("mg_one_sharded_level_peer_w4", {"n": 48, "world": 4, "options": {"precond": 1, "dist_replicate_below": 50000, "dist_transport": 2}, "transport": 2,
+                                      "solves": 3}),
     ("mg_27pt_peer_eager", {"n": 24, "matrix": "p27", "options": {"precond": 1, "dist_replicate_below": 500, "dist_transport": 2, "use_graph": 0},
-                            "transport": 2}),
+                            "transport": 2, "err_tol": 1e-9}),   # high-contrast coefficients (1e6): rounding-order differences are amplified
 ]
 
 
 @pytest.mark.parametrize("name,cfg", CASES, ids=[c[0] for c in CASES])
 def test_sharded_matches_single_gpu(name, cfg):
-    if _gpus() < 2:
-        pytest.skip("needs 2 GPUs")
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+    world = cfg.get("world", 2)
+    if _gpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
            "--master-port", "29541", os.path.join(ROOT, "tests", "dist_worker.py"), json.dumps(cfg)]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     line = [l for l in out.stdout.splitlines() if l.startswith("DIST_RESULT ")]
@@ -47,7 +53,7 @@ def test_sharded_matches_single_gpu(name, cfg):
     res = json.loads(line[0][len("DIST_RESULT "):])
     for r in res:
         assert abs(r["it_dist"] - r["it_single"]) <= 1, r      # iteration count within +-1
-        assert r["err"] <= 1e-10 if r["it_dist"] == r["it_single"] else r["err"] <= 1e-6, r
+        assert r["err"] <= cfg.get("err_tol", 1e-10) if r["it_dist"] == r["it_single"] else r["err"] <= 1e-6, r
         assert r["residual"] < 1e-8
     if "transport" in cfg:
         assert all(r["transport"] == cfg["transport"] for r in res), res

@@ -35,6 +35,24 @@ def test_hierarchy_bit_exact(oracle, gen, smoothed, dims):
     m.close(); H.close()
 
 
+def test_hierarchy_bit_exact_dense_row_spgemm(oracle, gen, monkeypatch):
+    """The block-per-row SpGEMM of the coarsest levels (few, very long rows) gives the same bits as the twin: forced on here
+    for every product with <= 2048 rows (at full size it serves products above 16384 terms per row)."""
+    import torch
+    from conjugategradient_b200 import solver as S
+    monkeypatch.setenv("MGCG_SPGEMM_DENSE_MIN", "0")
+    nx, ny, nz = 24, 20, 16
+    v, rp, c = gen.poisson3d7(nx, ny, nz)
+    m = _setup(S, torch, v, rp, c, nx=nx, ny=ny, nz=nz, mg_coarse_size=20)
+    H = oracle.MgRef(v, rp, c, nx, ny, nz, coarse_size=20)
+    assert m.levels() == H.levels() >= 3
+    for l in range(m.levels()):
+        gv, gr, gc = m.level(l)
+        hv, hr, hc = H.level(l)
+        assert np.array_equal(gr, hr) and np.array_equal(gc, hc) and np.array_equal(gv, hv), f"level {l}"
+    m.close(); H.close()
+
+
 def test_hierarchy_no_hint_blocks(oracle, gen):
     import torch
     from conjugategradient_b200 import solver as S
