@@ -293,6 +293,96 @@ static int run_dense_rows(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, in
     return MGCG_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// SHORT A rows (<= MAXA entries, the stencil levels): one THREAD per row does a k-way merge of the B rows its A entries
+// select.  B rows are sorted by column (every producer in this library emits them so), so the smallest head column is the
+// next output column, and adding the heads that carry it IN k ORDER is exactly the storage-order sum of the hash kernels
+// and of the CPU twin.  No table, no sort, no shared memory: two streaming passes (count, fill).  At 256^3 the fine-level
+// A*P (16.7 M rows, 105 M outputs) took 3.7 + 13.0 ms with the 4-lane hash kernels.
+template <int MAXA, bool NUMERIC>
+__global__ void __launch_bounds__(128) k_spgemm_merge(Csr A, Csr B, int shift, int *__restrict__ cnt, const int *__restrict__ c_rowptr,
+                                                      int *__restrict__ c_col, double *__restrict__ c_val)
+{
+    constexpr int kEnd = 0x7fffffff;
+    for (int row = blockIdx.x * blockDim.x + threadIdx.x; row < A.rows; row += gridDim.x * blockDim.x) {
+        int q[MAXA], qe[MAXA], hc[MAXA];
+        double a[MAXA];
+        const int ks = A.rowptr[row], m = A.rowptr[row + 1] - ks;
+#pragma unroll
+        for (int k = 0; k < MAXA; ++k) {
+            q[k] = 0; qe[k] = 0; hc[k] = kEnd; a[k] = 0.0;
+            if (k < m) {
+                const int j = A.col[ks + k] - shift;
+                q[k] = B.rowptr[j]; qe[k] = B.rowptr[j + 1];
+                if (NUMERIC) a[k] = A.val[ks + k];
+                if (q[k] < qe[k]) hc[k] = B.col[q[k]];
+            }
+        }
+        int o = NUMERIC ? c_rowptr[row] : 0;
+        while (true) {
+            int cur = kEnd;
+#pragma unroll
+            for (int k = 0; k < MAXA; ++k) cur = min(cur, hc[k]);
+            if (cur == kEnd) break;
+            double s = 0.0;
+            bool have = false;
+#pragma unroll
+            for (int k = 0; k < MAXA; ++k)
+                if (hc[k] == cur) {
+                    if (NUMERIC) {
+                        const double pr = __dmul_rn(a[k], B.val[q[k]]);
+                        s = have ? __dadd_rn(s, pr) : pr;
+                        have = true;
+                    }
+                    ++q[k];
+                    hc[k] = q[k] < qe[k] ? B.col[q[k]] : kEnd;
+                }
+            if (NUMERIC) { c_col[o] = cur; c_val[o] = s; }
+            ++o;
+        }
+        if (!NUMERIC) cnt[row] = o;
+    }
+}
+
+__global__ void k_spgemm_maxlen(Csr A, int *out_max)
+{
+    int m = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x) m = max(m, A.rowptr[i + 1] - A.rowptr[i]);
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_down_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(out_max, m);
+}
+
+template <int MAXA>
+static int run_merge(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, DevCsr *C)
+{
+    cudaStream_t st = c->stream;
+    int *cnt = nullptr;
+    MGCG_CUDA(pool_alloc((void **)&cnt, sizeof(int) * ((size_t)A.rows + 1), st));
+    MGCG_CUDA(cudaMemsetAsync(cnt + A.rows, 0, sizeof(int), st));
+    int grid = (A.rows + 127) / 128;
+    if (grid > c->sm_count * 64) grid = c->sm_count * 64;
+    k_spgemm_merge<MAXA, false><<<grid, 128, 0, st>>>(A, B, shift, cnt, nullptr, nullptr, nullptr);
+    MGCG_LAUNCH_CHECK();
+    C->rows = A.rows; C->cols = B.cols;
+    MGCG_CUDA(pool_alloc((void **)&C->rowptr, sizeof(int) * ((size_t)A.rows + 1), st));
+    size_t tb = 0;
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, C->rowptr, A.rows + 1, st));
+    void *tmp = nullptr;
+    MGCG_CUDA(pool_alloc(&tmp, tb, st));
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, C->rowptr, A.rows + 1, st));
+    int nnz = 0;
+    MGCG_CUDA(cudaMemcpyAsync(&nnz, C->rowptr + A.rows, sizeof(int), cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    pool_free(tmp, st); pool_free(cnt, st);
+    C->nnz = nnz;
+    MGCG_CUDA(pool_alloc((void **)&C->val, sizeof(double) * (size_t)(nnz > 0 ? nnz : 1), st));
+    MGCG_CUDA(pool_alloc((void **)&C->col, sizeof(int) * (size_t)(nnz > 0 ? nnz : 1), st));
+    if (getenv("MGCG_TRACE")) fprintf(stderr, "[mgcg spgemm] rows %d merge kernel MAXA %d nnz %d grid %d\n", A.rows, MAXA, nnz, grid);
+    k_spgemm_merge<MAXA, true><<<grid, 128, 0, st>>>(A, B, shift, nullptr, C->rowptr, C->col, C->val);
+    MGCG_LAUNCH_CHECK();
+    return MGCG_OK;
+}
+
 static int pow2_at_least(long long v) { int p = 32; while (p < v) p <<= 1; return p; }
 
 template <int G>
@@ -370,16 +460,23 @@ int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C, int col_shift)
 {
     cudaStream_t st = c->stream;
     if ((A.rows <= 0 || A.nnz <= 0 || B.nnz <= 0) && col_shift == 0) return spgemm_esc(c, A, B, C);
-    int *d_max = nullptr, maxprod = 0;
-    MGCG_CUDA(pool_alloc((void **)&d_max, sizeof(int), st));
-    MGCG_CUDA(cudaMemsetAsync(d_max, 0, sizeof(int), st));
+    int *d_max = nullptr, hmax[2] = {0, 0};
+    MGCG_CUDA(pool_alloc((void **)&d_max, 2 * sizeof(int), st));
+    MGCG_CUDA(cudaMemsetAsync(d_max, 0, 2 * sizeof(int), st));
     int g = (A.rows + 255) / 256;
     if (g > c->sm_count * 16) g = c->sm_count * 16;
     k_spgemm_maxprod<<<g, 256, 0, st>>>(A, B, col_shift, d_max);
+    k_spgemm_maxlen<<<g, 256, 0, st>>>(A, d_max + 1);
     MGCG_LAUNCH_CHECK();
-    MGCG_CUDA(cudaMemcpyAsync(&maxprod, d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaMemcpyAsync(hmax, d_max, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
     MGCG_CUDA(cudaStreamSynchronize(st));
     pool_free(d_max, st);
+    const int maxprod = hmax[0], maxlen = hmax[1];
+    if (!getenv("MGCG_SPGEMM_NO_MERGE")) {   // short A rows: per-thread k-way merge
+        if (maxlen <= 8) return run_merge<8>(c, A, B, col_shift, C);
+        if (maxlen <= 16) return run_merge<16>(c, A, B, col_shift, C);
+        if (maxlen <= 32) return run_merge<32>(c, A, B, col_shift, C);
+    }
     const double avg_b = (double)B.nnz / (B.rows > 0 ? B.rows : 1);
     bool done = false;
     MGCG_CHECK(run_dense_rows(c, A, B, col_shift, maxprod, C, &done));
