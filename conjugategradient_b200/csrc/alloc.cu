@@ -1,0 +1,111 @@
+// alloc.cu — size-bucketed block cache under the hierarchy build.
+// The build allocates and frees gigabyte-sized transients (sort buffers, A*P) and, on every re-setup, the level operators
+// themselves.  Through cudaMallocAsync's pool the same request sequence did NOT reach a steady state: block sizes differ
+// from phase to phase, the pool fragments and grows by mapping fresh physical memory at ~75 ms per GB — seen as sporadic
+// 90-700 ms stalls inside `R = P^T` / `A*P` of an otherwise 46 ms build (profiles/r01_setup_trace_256.txt).  Here freed
+// blocks are kept in per-(device, stream, rounded size) free lists and handed back to the next request of that bucket:
+// from the second setup of a given problem on, the build makes no driver allocation at all.
+// Reuse is stream-ordered: a block is only re-issued to work on the stream it was allocated for (the build runs on one
+// stream, and a free in host order is a free in stream order).  Sizes are rounded up to 1/8 of their power of two (<= 12.5 %).
+#include "common.cuh"
+#include <map>
+#include <mutex>
+#include <tuple>
+
+namespace mgcg {
+
+namespace {
+struct Block { size_t bytes; int device; cudaStream_t stream; };
+typedef std::tuple<int, cudaStream_t, size_t> Key;
+std::mutex g_mu;
+std::map<void *, Block> g_live;                  // blocks handed out
+std::map<Key, std::vector<void *>> g_free;       // blocks waiting for the next request of their bucket
+size_t g_cached_bytes = 0;
+
+size_t round_up(size_t bytes)
+{
+    if (bytes <= 4096) return 4096;
+    size_t p2 = 4096;
+    while ((p2 << 1) <= bytes) p2 <<= 1;
+    const size_t step = p2 >> 3;
+    return (bytes + step - 1) / step * step;
+}
+
+void drop_cached_locked(int device, bool any_stream = true, cudaStream_t stream = nullptr)
+{
+    for (auto it = g_free.begin(); it != g_free.end();) {
+        if ((device < 0 || std::get<0>(it->first) == device) && (any_stream || std::get<1>(it->first) == stream)) {
+            for (void *p : it->second) { cudaFree(p); g_cached_bytes -= std::get<2>(it->first); }
+            it = g_free.erase(it);
+        } else ++it;
+    }
+}
+}  // namespace
+
+cudaError_t pool_alloc(void **p, size_t bytes, cudaStream_t st)
+{
+    *p = nullptr;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    const size_t rb = round_up(bytes ? bytes : 1);
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_free.find(Key(dev, st, rb));
+    if (it != g_free.end() && !it->second.empty()) {
+        *p = it->second.back();
+        it->second.pop_back();
+        g_cached_bytes -= rb;
+    } else {
+        e = cudaMalloc(p, rb);
+        if (e != cudaSuccess) {          // out of memory: give the cached blocks back and try once more
+            cudaGetLastError();
+            drop_cached_locked(dev);
+            e = cudaMalloc(p, rb);
+            if (e != cudaSuccess) return e;
+        }
+    }
+    g_live[*p] = Block{rb, dev, st};
+    return cudaSuccess;
+}
+
+// Free a block obtained from pool_alloc (kept for reuse), or anything else (cudaFree).  Safe for work still queued on the
+// block's stream: it is only re-issued to that stream.
+void pool_release(void *p)
+{
+    if (!p) return;
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        auto it = g_live.find(p);
+        if (it != g_live.end()) {
+            const Block b = it->second;
+            g_live.erase(it);
+            g_free[Key(b.device, b.stream, b.bytes)].push_back(p);
+            g_cached_bytes += b.bytes;
+            return;
+        }
+    }
+    cudaFree(p);
+}
+
+void pool_free(void *p, cudaStream_t) { pool_release(p); }
+
+void pool_trim(int device)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    drop_cached_locked(device);
+}
+
+// a context is going away: blocks cached for its stream can never be re-issued
+void pool_trim_stream(int device, cudaStream_t st)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    drop_cached_locked(device, false, st);
+}
+
+size_t pool_cached_bytes()
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    return g_cached_bytes;
+}
+
+}  // namespace mgcg

@@ -206,10 +206,14 @@ int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res);
 int graph_build_while(mgcg_ctx *c, int (*enqueue)(mgcg_ctx *, void *), void *arg, cudaGraph_t *graph, cudaGraphExec_t *exec, int *body_nodes);
 
 // ---- helpers
-// Stream-ordered allocation for the hierarchy build (cudaMallocAsync from the device's pool: no device-wide
-// synchronisation per call, blocks are reused between phases).  Memory obtained here may be released with cudaFree too.
-inline cudaError_t pool_alloc(void **p, size_t bytes, cudaStream_t st) { return cudaMallocAsync(p, bytes ? bytes : 1, st); }
-inline void pool_free(void *p, cudaStream_t st) { if (p) cudaFreeAsync(p, st); }
+// Allocation for the hierarchy build (alloc.cu): a size-bucketed block cache — freed blocks are re-issued to the next
+// request of the same rounded size on the same stream, so a repeated build makes no driver allocation.
+cudaError_t pool_alloc(void **p, size_t bytes, cudaStream_t st);
+void pool_free(void *p, cudaStream_t st);
+void pool_release(void *p);          // block of pool_alloc -> cache; any other device pointer -> cudaFree
+void pool_trim_stream(int device, cudaStream_t st);
+void pool_trim(int device);          // give the cached blocks of a device (-1: all) back to the driver
+size_t pool_cached_bytes();
 int ctx_ensure_work(mgcg_ctx *c, int n);
 inline int div_up(int a, int b) { return (a + b - 1) / b; }
 

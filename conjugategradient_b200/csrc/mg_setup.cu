@@ -35,9 +35,9 @@ static inline void tfree(void *p) { pool_free(p, g_alloc_stream); }
 
 void DevCsr::free_all()
 {
-    if (val) cudaFree(val);
-    if (rowptr) cudaFree(rowptr);
-    if (col) cudaFree(col);
+    pool_release(val);
+    pool_release(rowptr);
+    pool_release(col);
     val = nullptr; rowptr = nullptr; col = nullptr; rows = cols = nnz = 0;
 }
 
@@ -291,24 +291,56 @@ int spgemm_esc(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C)
     return MGCG_OK;
 }
 
-__global__ void k_transpose_expand(Csr A, u64 *keys, double *vals)
+
+// Transposition has no duplicates and its input is already ordered by row, so a STABLE sort by column alone (32-bit keys,
+// only the bits the column count needs: 3 radix passes at 256^3 instead of 6 over 64-bit (col,row) keys) leaves every
+// output row ordered by its column = the input row; the row pointers are read off the sorted keys.
+struct RowVal { int row; int pad; double val; };
+
+__global__ void k_transpose_expand32(Csr A, unsigned *keys, RowVal *rv)
 {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x)
         for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k) {
-            keys[k] = ((u64)(unsigned)A.col[k] << 32) | (unsigned)i;
-            vals[k] = A.val[k];
+            keys[k] = (unsigned)A.col[k];
+            RowVal e; e.row = i; e.pad = 0; e.val = A.val[k];
+            rv[k] = e;
         }
+}
+__global__ void k_transpose_finish(size_t count, int rows_t, const unsigned *__restrict__ keys, const RowVal *__restrict__ rv,
+                                   int *__restrict__ rowptr, int *__restrict__ col, double *__restrict__ val)
+{
+    for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < count; k += (size_t)gridDim.x * blockDim.x) {
+        const int cur = (int)keys[k], prev = k > 0 ? (int)keys[k - 1] : -1;
+        for (int r = prev + 1; r <= cur; ++r) rowptr[r] = (int)k;
+        if (k == count - 1) for (int r = cur + 1; r <= rows_t; ++r) rowptr[r] = (int)count;
+        col[k] = rv[k].row; val[k] = rv[k].val;
+    }
 }
 
 int csr_transpose(mgcg_ctx *c, const Csr &A, DevCsr *T)
 {
-    u64 *keys = nullptr; double *vals = nullptr;
-    MGCG_CHECK(dalloc(&keys, (size_t)A.nnz)); MGCG_CHECK(dalloc(&vals, (size_t)A.nnz));
-    k_transpose_expand<<<grid_for(A.rows), 256, 0, c->stream>>>(A, keys, vals);
+    cudaStream_t st = c->stream;
+    const size_t count = (size_t)A.nnz;
+    T->rows = A.cols; T->cols = A.rows; T->nnz = A.nnz;
+    MGCG_CHECK(dalloc(&T->rowptr, (size_t)A.cols + 1));
+    MGCG_CHECK(dalloc(&T->val, count)); MGCG_CHECK(dalloc(&T->col, count));
+    if (count == 0) { MGCG_CUDA(cudaMemsetAsync(T->rowptr, 0, sizeof(int) * ((size_t)A.cols + 1), st)); return MGCG_OK; }
+    unsigned *k1 = nullptr, *k2 = nullptr; RowVal *v1 = nullptr, *v2 = nullptr;
+    MGCG_CHECK(dalloc(&k1, count)); MGCG_CHECK(dalloc(&k2, count)); MGCG_CHECK(dalloc(&v1, count)); MGCG_CHECK(dalloc(&v2, count));
+    k_transpose_expand32<<<grid_for(A.rows), 256, 0, st>>>(A, k1, v1);
     MGCG_LAUNCH_CHECK();
-    int s = coo_to_csr_sum(c, A.cols, A.rows, (size_t)A.nnz, keys, vals, T);
-    tfree(keys); tfree(vals);
-    return s;
+    cub::DoubleBuffer<unsigned> dk(k1, k2);
+    cub::DoubleBuffer<RowVal> dv(v1, v2);
+    const int end_bit = bits_for((unsigned)(A.cols > 0 ? A.cols - 1 : 0));
+    size_t tb = 0;
+    MGCG_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, dk, dv, (long long)count, 0, end_bit, st));
+    void *tmp = nullptr;
+    MGCG_CUDA(pool_alloc(&tmp, tb, st));
+    MGCG_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, dk, dv, (long long)count, 0, end_bit, st));   // LSD radix sort: stable
+    k_transpose_finish<<<grid_for((long long)count), 256, 0, st>>>(count, A.cols, dk.Current(), dv.Current(), T->rowptr, T->col, T->val);
+    MGCG_LAUNCH_CHECK();
+    tfree(tmp); tfree(k1); tfree(k2); tfree(v1); tfree(v2);
+    return MGCG_OK;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -525,14 +557,14 @@ void mg_free(mgcg_ctx *c)
     for (size_t l = 0; l < H->L.size(); ++l) {
         MgLevel &L = H->L[l];
         L.Aown.free_all(); L.P.free_all(); L.R.free_all();
-        if (L.agg) cudaFree(L.agg);
-        if (L.dinv) cudaFree(L.dinv);
-        if (L.xa) cudaFree(L.xa);
-        if (L.xb) cudaFree(L.xb);
-        if (L.r) cudaFree(L.r);
-        if (l > 0 && L.b) cudaFree(L.b);
+        pool_release(L.agg);
+        pool_release(L.dinv);
+        pool_release(L.xa);
+        pool_release(L.xb);
+        pool_release(L.r);
+        if (l > 0) pool_release(L.b);
     }
-    if (H->coarse_inv) cudaFree(H->coarse_inv);
+    pool_release(H->coarse_inv);
     delete H;
     c->mg = nullptr;
 }
