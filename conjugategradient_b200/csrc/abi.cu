@@ -125,7 +125,7 @@ void mgcg_destroy(mgcg_ctx *c)
     if (c->stream) cudaStreamSynchronize(c->stream);
     dist_free(c);
     mg_free(c);
-    pool_trim_stream(c->device, c->stream);
+    if (!c->child) pool_trim_stream(c->device, c->stream);
     if (c->graph_exec) cudaGraphExecDestroy(c->graph_exec);
     if (c->graph) cudaGraphDestroy(c->graph);
     if (c->host_path) { ((HostPath *)c->host_path)->release(); delete (HostPath *)c->host_path; }

@@ -130,6 +130,7 @@ struct mgcg_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    bool child = false;            // private context of a sharded solve (shares the parent's stream and block cache)
     int sm_count = 148;
     mgcg::Scalars *d_scalars = nullptr;
     mgcg::Scalars *h_scalars = nullptr;  // pinned, 2 slots

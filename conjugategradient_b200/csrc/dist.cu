@@ -35,28 +35,39 @@ int nccl_load(NcclApi **out)
 
 static void dist_graph_free(DistState *D);
 
+// one int from device memory, ordered after the work queued on the context's (non-blocking) stream
+static int fetch_int(mgcg_ctx *c, int *h, const int *d)
+{
+    MGCG_CUDA(cudaMemcpyAsync(h, d, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    MGCG_CUDA(cudaStreamSynchronize(c->stream));
+    return MGCG_OK;
+}
+
+
 void dist_free_levels(DistState *D)
 {
     for (size_t l = 0; l < D->L.size(); ++l) {
         DistLevel &L = D->L[l];
         L.Aown.free_all(); L.Pext.free_all(); L.R.free_all();
-        if (L.dinv) cudaFree(L.dinv);
-        if (L.xa) cudaFree(L.xa);
-        if (L.xb) cudaFree(L.xb);
-        if (L.r) cudaFree(L.r);
-        if (l > 0 && L.b) cudaFree(L.b);
+        if (L.dinv) pool_release(L.dinv);
+        if (L.xa) pool_release(L.xa);
+        if (L.xb) pool_release(L.xb);
+        if (L.r) pool_release(L.r);
+        if (l > 0 && L.b) pool_release(L.b);
     }
     D->L.clear();
-    if (D->coarse) {
+    if (D->coarse) {     // kept for the next setup: creating a context costs pinned allocations and a dozen driver calls
         if (D->coarse_scalars_orig) D->coarse->d_scalars = D->coarse_scalars_orig;
         D->coarse_scalars_orig = nullptr;
-        mgcg_destroy(D->coarse); D->coarse = nullptr;
+        mg_free(D->coarse);
+        if (D->coarse_spare) mgcg_destroy(D->coarse_spare);
+        D->coarse_spare = D->coarse; D->coarse = nullptr;
     }
     D->coarse_A.free_all();
-    if (D->coarse_b) { cudaFree(D->coarse_b); D->coarse_b = nullptr; }
-    if (D->p) { cudaFree(D->p); D->p = nullptr; }
-    if (D->r) { cudaFree(D->r); D->r = nullptr; }
-    if (D->Ap) { cudaFree(D->Ap); D->Ap = nullptr; }
+    if (D->coarse_b) { pool_release(D->coarse_b); D->coarse_b = nullptr; }
+    if (D->p) { pool_release(D->p); D->p = nullptr; }
+    if (D->r) { pool_release(D->r); D->r = nullptr; }
+    if (D->Ap) { pool_release(D->Ap); D->Ap = nullptr; }
 }
 
 void dist_free(mgcg_ctx *c)
@@ -66,6 +77,7 @@ void dist_free(mgcg_ctx *c)
     dist_graph_free(D);
     peer_close(c);
     dist_free_levels(D);
+    if (D->coarse_spare) { mgcg_destroy(D->coarse_spare); D->coarse_spare = nullptr; }
     if (D->partial_send) cudaFree(D->partial_send);
     if (D->partial_all) cudaFree(D->partial_all);
     if (D->comm && D->api) D->api->CommDestroy(D->comm);
@@ -188,27 +200,27 @@ static int level_halfband(mgcg_ctx *c, const Csr &A, int row_base, int *out)
 {
     DistState *D = c->dist;
     int *d = nullptr;
-    MGCG_CUDA(cudaMalloc((void **)&d, sizeof(int)));
+    MGCG_CUDA(pool_alloc((void **)&d, sizeof(int), c->stream));
     MGCG_CUDA(cudaMemsetAsync(d, 0, sizeof(int), c->stream));
     if (A.rows > 0) { k_halfband<<<gridn(A.rows), 256, 0, c->stream>>>(A, row_base, d); MGCG_LAUNCH_CHECK(); }
     MGCG_NCCL(D->api, AllReduce(d, d, 1, ncclInt, ncclMax, D->comm, c->stream));
     MGCG_CUDA(cudaMemcpyAsync(out, d, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     MGCG_CUDA(cudaStreamSynchronize(c->stream));
-    cudaFree(d);
+    pool_release(d);
     return MGCG_OK;
 }
 
-static int alloc_level_vectors_dist(DistLevel &L, bool level0)
+static int alloc_level_vectors_dist(DistLevel &L, bool level0, cudaStream_t st)
 {
     const size_t e = (size_t)L.lo + L.own + L.hi + 1;
-    MGCG_CUDA(cudaMalloc((void **)&L.xa, sizeof(double) * e));
-    MGCG_CUDA(cudaMalloc((void **)&L.xb, sizeof(double) * e));
-    MGCG_CUDA(cudaMemset(L.xa, 0, sizeof(double) * e));
-    MGCG_CUDA(cudaMemset(L.xb, 0, sizeof(double) * e));
-    MGCG_CUDA(cudaMalloc((void **)&L.r, sizeof(double) * e));
-    MGCG_CUDA(cudaMemset(L.r, 0, sizeof(double) * e));
-    if (!level0) MGCG_CUDA(cudaMalloc((void **)&L.b, sizeof(double) * ((size_t)L.own + 1)));
-    MGCG_CUDA(cudaMalloc((void **)&L.dinv, sizeof(double) * ((size_t)L.own + 1)));
+    MGCG_CUDA(pool_alloc((void **)&L.xa, sizeof(double) * e, st));
+    MGCG_CUDA(pool_alloc((void **)&L.xb, sizeof(double) * e, st));
+    MGCG_CUDA(cudaMemsetAsync(L.xa, 0, sizeof(double) * e, st));
+    MGCG_CUDA(cudaMemsetAsync(L.xb, 0, sizeof(double) * e, st));
+    MGCG_CUDA(pool_alloc((void **)&L.r, sizeof(double) * e, st));
+    MGCG_CUDA(cudaMemsetAsync(L.r, 0, sizeof(double) * e, st));
+    if (!level0) MGCG_CUDA(pool_alloc((void **)&L.b, sizeof(double) * ((size_t)L.own + 1), st));
+    MGCG_CUDA(pool_alloc((void **)&L.dinv, sizeof(double) * ((size_t)L.own + 1), st));
     return MGCG_OK;
 }
 
@@ -231,8 +243,8 @@ static int dist_build_next(mgcg_ctx *c, int l, DevCsr *Ac_out)
     if (rk != 0) tr.on = false;
     // ---- fetch the ghost rows: row pointers first (fixed size), then the entries
     int *rp_lo = nullptr, *rp_hi = nullptr;
-    MGCG_CUDA(cudaMalloc((void **)&rp_lo, sizeof(int) * ((size_t)e_lo + 1)));
-    MGCG_CUDA(cudaMalloc((void **)&rp_hi, sizeof(int) * ((size_t)e_hi + 1)));
+    MGCG_CUDA(pool_alloc((void **)&rp_lo, sizeof(int) * ((size_t)e_lo + 1), c->stream));
+    MGCG_CUDA(pool_alloc((void **)&rp_hi, sizeof(int) * ((size_t)e_hi + 1), c->stream));
     MGCG_CUDA(cudaMemsetAsync(rp_lo, 0, sizeof(int) * ((size_t)e_lo + 1), st));
     MGCG_CUDA(cudaMemsetAsync(rp_hi, 0, sizeof(int) * ((size_t)e_hi + 1), st));
     MGCG_NCCL(a, GroupStart());
@@ -258,9 +270,9 @@ static int dist_build_next(mgcg_ctx *c, int l, DevCsr *Ac_out)
     const int nnz_own = h[3] - h[0], nnz_lo = h[5] - h[4], nnz_hi = h[7] - h[6];
     DevCsr E;   // the extended block
     E.rows = e_lo + own + e_hi; E.cols = L.n_glob; E.nnz = nnz_lo + nnz_own + nnz_hi;
-    MGCG_CUDA(cudaMalloc((void **)&E.rowptr, sizeof(int) * ((size_t)E.rows + 1)));
-    MGCG_CUDA(cudaMalloc((void **)&E.col, sizeof(int) * ((size_t)E.nnz + 1)));
-    MGCG_CUDA(cudaMalloc((void **)&E.val, sizeof(double) * ((size_t)E.nnz + 1)));
+    MGCG_CUDA(pool_alloc((void **)&E.rowptr, sizeof(int) * ((size_t)E.rows + 1), c->stream));
+    MGCG_CUDA(pool_alloc((void **)&E.col, sizeof(int) * ((size_t)E.nnz + 1), c->stream));
+    MGCG_CUDA(pool_alloc((void **)&E.val, sizeof(double) * ((size_t)E.nnz + 1), c->stream));
     MGCG_NCCL(a, GroupStart());
     if (rk > 0) {
         MGCG_NCCL(a, Send(L.A.col + h[0], (size_t)(h[1] - h[0]), ncclInt, rk - 1, D->comm, st));
@@ -285,12 +297,12 @@ static int dist_build_next(mgcg_ctx *c, int l, DevCsr *Ac_out)
     int g0 = e0 - B; if (g0 < 0) g0 = 0;
     int g1 = e0 + E.rows + B; if (g1 > L.n_glob) g1 = L.n_glob;
     int *agg = nullptr;
-    MGCG_CUDA(cudaMalloc((void **)&agg, sizeof(int) * (size_t)(g1 - g0)));
+    MGCG_CUDA(pool_alloc((void **)&agg, sizeof(int) * (size_t)(g1 - g0), c->stream));
     k_fill_agg<<<gridn(g1 - g0), 256, 0, st>>>(g, g0, g1 - g0, agg);
     MGCG_LAUNCH_CHECK();
     const int *agg_sh = agg - g0;                      // indexed by global row id
     double *dinv_ext = nullptr;
-    MGCG_CUDA(cudaMalloc((void **)&dinv_ext, sizeof(double) * ((size_t)E.rows + 1)));
+    MGCG_CUDA(pool_alloc((void **)&dinv_ext, sizeof(double) * ((size_t)E.rows + 1), c->stream));
     MGCG_CHECK(extract_dinv(c, E.view(), e0, dinv_ext));
     // ---- prolongator rows of the whole extended block (global coarse columns)
     const mgcg_options &o = c->opt;
@@ -313,14 +325,14 @@ static int dist_build_next(mgcg_ctx *c, int l, DevCsr *Ac_out)
     MGCG_CUDA(cudaStreamSynchronize(st));
     const size_t cnt = (size_t)(pr[1] - pr[0]);
     unsigned long long *keys = nullptr; double *vals = nullptr;
-    MGCG_CUDA(cudaMalloc((void **)&keys, sizeof(unsigned long long) * (cnt + 1)));
-    MGCG_CUDA(cudaMalloc((void **)&vals, sizeof(double) * (cnt + 1)));
+    MGCG_CUDA(pool_alloc((void **)&keys, sizeof(unsigned long long) * (cnt + 1), c->stream));
+    MGCG_CUDA(pool_alloc((void **)&vals, sizeof(double) * (cnt + 1), c->stream));
     k_transpose_expand_filtered<<<gridn(Pv.rows), 256, 0, st>>>(Pv, coff, cown, keys, vals);
     MGCG_LAUNCH_CHECK();
     MGCG_CHECK(coo_to_csr_sum(c, cown + 1, Pv.rows, cnt, keys, vals, &L.R));
-    cudaFree(keys); cudaFree(vals);
+    pool_release(keys); pool_release(vals);
     int rn = 0;
-    MGCG_CUDA(cudaMemcpy(&rn, L.R.rowptr + cown, sizeof(int), cudaMemcpyDeviceToHost));
+    MGCG_CHECK(fetch_int(c, &rn, L.R.rowptr + cown));
     L.R.rows = cown; L.R.nnz = rn;                      // drop the dump row
     tr.mark(l, "d:R");
     // ---- Galerkin rows of the owned aggregates
@@ -332,14 +344,14 @@ static int dist_build_next(mgcg_ctx *c, int l, DevCsr *Ac_out)
     L.P = L.Pext.view();
     L.P.rows = own; L.P.rowptr = L.Pext.rowptr + e_lo;
     int pn[2] = {0, 0};
-    MGCG_CUDA(cudaMemcpy(&pn[0], L.P.rowptr, sizeof(int), cudaMemcpyDeviceToHost));
-    MGCG_CUDA(cudaMemcpy(&pn[1], L.P.rowptr + own, sizeof(int), cudaMemcpyDeviceToHost));
+    MGCG_CHECK(fetch_int(c, &pn[0], L.P.rowptr));
+    MGCG_CHECK(fetch_int(c, &pn[1], L.P.rowptr + own));
     L.P.nnz = pn[1] - pn[0];
     L.planP = spmv_make_plan(c, own, L.P.nnz, MGCG_SPMV_AUTO);
     L.P.nnz = L.Pext.nnz;   // the view addresses val/col with the parent's absolute offsets
     L.planR = spmv_make_plan(c, L.R.rows, L.R.nnz, MGCG_SPMV_AUTO);
     MGCG_CUDA(cudaStreamSynchronize(st));
-    cudaFree(rp_lo); cudaFree(rp_hi); cudaFree(agg); cudaFree(dinv_ext);
+    pool_release(rp_lo); pool_release(rp_hi); pool_release(agg); pool_release(dinv_ext);
     E.free_all();
     tr.mark(l, "d:finish");
     return MGCG_OK;
@@ -376,26 +388,26 @@ static int dist_replicate(mgcg_ctx *c, int lev, const Csr &A, const int *offs, i
     if (rk != 0) tr.on = false;
     // non-zero counts of every rank
     int my[2] = {0, 0};
-    MGCG_CUDA(cudaMemcpy(&my[0], A.rowptr, sizeof(int), cudaMemcpyDeviceToHost));
-    MGCG_CUDA(cudaMemcpy(&my[1], A.rowptr + own, sizeof(int), cudaMemcpyDeviceToHost));
+    MGCG_CHECK(fetch_int(c, &my[0], A.rowptr));
+    MGCG_CHECK(fetch_int(c, &my[1], A.rowptr + own));
     int *d_cnt = nullptr;
-    MGCG_CUDA(cudaMalloc((void **)&d_cnt, sizeof(int) * (size_t)(W + 1)));
+    MGCG_CUDA(pool_alloc((void **)&d_cnt, sizeof(int) * (size_t)(W + 1), c->stream));
     const int mynnz = my[1] - my[0];
     MGCG_CUDA(cudaMemcpyAsync(d_cnt + W, &mynnz, sizeof(int), cudaMemcpyHostToDevice, st));
     MGCG_NCCL(D->api, AllGather(d_cnt + W, d_cnt, 1, ncclInt, D->comm, st));
     int cnts[kMaxRanks], zoff[kMaxRanks + 1];
     MGCG_CUDA(cudaMemcpyAsync(cnts, d_cnt, sizeof(int) * (size_t)W, cudaMemcpyDeviceToHost, st));
     MGCG_CUDA(cudaStreamSynchronize(st));
-    cudaFree(d_cnt);
+    pool_release(d_cnt);
     zoff[0] = 0;
     long long tot = 0;
     for (int r = 0; r < W; ++r) { tot += cnts[r]; zoff[r + 1] = (int)tot; }
     if (tot >= (1ll << 31)) { set_error("dist_replicate: replicated level exceeds int32 non-zeros"); return MGCG_ERR_UNSUPPORTED; }
     DevCsr &F = D->coarse_A;
     F.rows = n; F.cols = n; F.nnz = (int)tot;
-    MGCG_CUDA(cudaMalloc((void **)&F.rowptr, sizeof(int) * ((size_t)n + 1)));
-    MGCG_CUDA(cudaMalloc((void **)&F.col, sizeof(int) * ((size_t)tot + 1)));
-    MGCG_CUDA(cudaMalloc((void **)&F.val, sizeof(double) * ((size_t)tot + 1)));
+    MGCG_CUDA(pool_alloc((void **)&F.rowptr, sizeof(int) * ((size_t)n + 1), c->stream));
+    MGCG_CUDA(pool_alloc((void **)&F.col, sizeof(int) * ((size_t)tot + 1), c->stream));
+    MGCG_CUDA(pool_alloc((void **)&F.val, sizeof(double) * ((size_t)tot + 1), c->stream));
     // own block in place: row pointers rebased to the global non-zero numbering
     MGCG_CUDA(cudaMemcpyAsync(F.rowptr + offs[rk], A.rowptr, sizeof(int) * (size_t)own, cudaMemcpyDeviceToDevice, st));
     if (own > 0) { k_add_int<<<gridn(own), 256, 0, st>>>(own, F.rowptr + offs[rk], zoff[rk] - my[0]); MGCG_LAUNCH_CHECK(); }
@@ -410,11 +422,13 @@ static int dist_replicate(mgcg_ctx *c, int lev, const Csr &A, const int *offs, i
     // right-hand side buffer of the replicated level
     D->coarse_n = n;
     for (int r = 0; r <= W; ++r) D->coarse_offs[r] = offs[r];
-    MGCG_CUDA(cudaMalloc((void **)&D->coarse_b, sizeof(double) * ((size_t)n + 1)));
+    MGCG_CUDA(pool_alloc((void **)&D->coarse_b, sizeof(double) * ((size_t)n + 1), c->stream));
     // the private context
-    D->coarse = mgcg_create(c->device);
+    if (D->coarse_spare) { D->coarse = D->coarse_spare; D->coarse_spare = nullptr; }
+    else D->coarse = mgcg_create(c->device);
     if (!D->coarse) return MGCG_ERR_CUDA;
     MGCG_CHECK(mgcg_set_stream(D->coarse, (void *)st));
+    D->coarse->child = true;        // its cached blocks live under the parent's stream: the parent trims them
     mgcg_options o = c->opt;
     o.precond = MGCG_PRECOND_MG;
     o.nx = nx; o.ny = ny; o.nz = nz_total;
@@ -452,7 +466,7 @@ static int dist_open_transport(mgcg_ctx *c)
         if (e && !strcmp(e, "nccl")) want = MGCG_TRANSPORT_NCCL;
         else if (e && !strcmp(e, "peer")) want = MGCG_TRANSPORT_PEER;
     }
-    if (D->world < 2 || want == MGCG_TRANSPORT_NCCL) return MGCG_OK;
+    if (D->world < 2 || want == MGCG_TRANSPORT_NCCL) { peer_close(c); return MGCG_OK; }
     int halo_cap = 0;
     for (size_t l = 0; l < D->L.size(); ++l) if (D->L[l].halo > halo_cap && D->L[l].halo < 0x3fffffff) halo_cap = D->L[l].halo;
     MGCG_CHECK(peer_open(c, halo_cap, D->coarse ? D->coarse_n : 0));
@@ -473,7 +487,7 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
     PhaseTrace tr(st);
     if (rk != 0) tr.on = false;
     dist_graph_free(D);
-    peer_close(c);
+    D->peer.active = false;          // setup traffic goes over NCCL; the arena is kept for dist_open_transport to reuse
     dist_free_levels(D);
     set_alloc_stream(st);
     tr.mark(-1, "d:free old");
@@ -481,13 +495,13 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
     int offs[kMaxRanks + 1];
     {
         int *d = nullptr;
-        MGCG_CUDA(cudaMalloc((void **)&d, sizeof(int) * (size_t)(W + 1)));
+        MGCG_CUDA(pool_alloc((void **)&d, sizeof(int) * (size_t)(W + 1), c->stream));
         MGCG_CUDA(cudaMemcpyAsync(d + W, &local_count, sizeof(int), cudaMemcpyHostToDevice, st));
         MGCG_NCCL(D->api, AllGather(d + W, d, 1, ncclInt, D->comm, st));
         int cnt[kMaxRanks];
         MGCG_CUDA(cudaMemcpyAsync(cnt, d, sizeof(int) * (size_t)W, cudaMemcpyDeviceToHost, st));
         MGCG_CUDA(cudaStreamSynchronize(st));
-        cudaFree(d);
+        pool_release(d);
         offs[0] = 0;
         for (int r = 0; r < W; ++r) offs[r + 1] = offs[r] + cnt[r];
     }
@@ -517,14 +531,14 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
                 return MGCG_ERR_UNSUPPORTED;
             }
         L.lo = rk > 0 ? L.halo : 0; L.hi = rk < W - 1 ? L.halo : 0;
-        MGCG_CHECK(alloc_level_vectors_dist(L, true));
+        MGCG_CHECK(alloc_level_vectors_dist(L, true, st));
         MGCG_CHECK(extract_dinv(c, L.A, L.off, L.dinv));
         const size_t e = (size_t)L.lo + L.own + L.hi + 1;
-        MGCG_CUDA(cudaMalloc((void **)&D->p, sizeof(double) * e));
-        MGCG_CUDA(cudaMalloc((void **)&D->r, sizeof(double) * e));
-        MGCG_CUDA(cudaMalloc((void **)&D->Ap, sizeof(double) * ((size_t)L.own + 1)));
-        MGCG_CUDA(cudaMemset(D->p, 0, sizeof(double) * e));
-        MGCG_CUDA(cudaMemset(D->r, 0, sizeof(double) * e));
+        MGCG_CUDA(pool_alloc((void **)&D->p, sizeof(double) * e, c->stream));
+        MGCG_CUDA(pool_alloc((void **)&D->r, sizeof(double) * e, c->stream));
+        MGCG_CUDA(pool_alloc((void **)&D->Ap, sizeof(double) * ((size_t)L.own + 1), c->stream));
+        MGCG_CUDA(cudaMemsetAsync(D->p, 0, sizeof(double) * e, st));
+        MGCG_CUDA(cudaMemsetAsync(D->r, 0, sizeof(double) * e, st));
     }
     D->first_replicated = 0;
     tr.mark(0, "d:level0 init");
@@ -554,11 +568,11 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
             D->first_replicated = l;
             if (l > 0) {   // level l lives in the private context only: drop its distributed shell (the matrix was copied)
                 D->L[l].Aown.free_all();
-                if (D->L[l].dinv) cudaFree(D->L[l].dinv);
-                if (D->L[l].xa) cudaFree(D->L[l].xa);
-                if (D->L[l].xb) cudaFree(D->L[l].xb);
-                if (D->L[l].r) cudaFree(D->L[l].r);
-                if (D->L[l].b) cudaFree(D->L[l].b);
+                if (D->L[l].dinv) pool_release(D->L[l].dinv);
+                if (D->L[l].xa) pool_release(D->L[l].xa);
+                if (D->L[l].xb) pool_release(D->L[l].xb);
+                if (D->L[l].r) pool_release(D->L[l].r);
+                if (D->L[l].b) pool_release(D->L[l].b);
                 D->L.pop_back();
             }
             break;
@@ -577,7 +591,7 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
         const bool halo_fits = nmin >= N.halo;
         N.lo = (rk > 0 && halo_fits) ? N.halo : 0; N.hi = (rk < W - 1 && halo_fits) ? N.halo : 0;
         if (!halo_fits) N.halo = 0x3fffffff;   // forces replication of this level on the next pass
-        MGCG_CHECK(alloc_level_vectors_dist(N, false));
+        MGCG_CHECK(alloc_level_vectors_dist(N, false, st));
         MGCG_CHECK(extract_dinv(c, N.A, N.off, N.dinv));
         memcpy(cur_offs, g.coff, sizeof(int) * (size_t)(W + 1));
         if (g.structured) { cur_nx = g.cx; cur_ny = g.cy; } else { cur_nx = cur_ny = 0; }

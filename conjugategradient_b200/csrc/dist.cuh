@@ -63,7 +63,8 @@ struct XchgRecv { const double *stage; double *dst; const unsigned long long *fl
 struct XchgDesc { int ns, nr; size_t stage_stride; XchgSend s[kPeerMax]; XchgRecv r[kPeerMax]; };
 
 struct PeerState {
-    bool active = false;
+    bool active = false;                // the loop of the CURRENT setup runs over peer memory
+    bool ready = false;                 // arena allocated and every peer mapped (survives a re-setup that fits)
     void *arena = nullptr;              // this rank's arena (cudaMalloc)
     void *peer[kPeerMax] = {};          // every rank's arena as mapped here (peer[rank] == arena)
     bool mapped[kPeerMax] = {};         // opened with cudaIpcOpenMemHandle (to be closed)
@@ -111,6 +112,7 @@ struct DistState {
     // replicated tail: a private single-GPU context that owns the all-gathered operator and its hierarchy
     mgcg_ctx *coarse = nullptr;
     Scalars *coarse_scalars_orig = nullptr; // the private context's own scalar block (it runs on the parent's during solves)
+    mgcg_ctx *coarse_spare = nullptr;       // the private context of the previous setup, reused by the next one
     int first_replicated = 0;               // level index of the replicated tail (0: the whole preconditioner is replicated)
     DevCsr coarse_A;
     double *coarse_b = nullptr;             // all-gathered right-hand side (global length of the first replicated level)

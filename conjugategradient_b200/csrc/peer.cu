@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(64) k_peer_reduce(int mode, int k, int rank, i
 static int grid_for(long long doubles, int sm_count)
 {
     static int per_block = 0;
-    if (!per_block) { const char *e = getenv("MGCG_PEER_DOUBLES_PER_BLOCK"); per_block = e ? atoi(e) : 1024; if (per_block < 256) per_block = 256;   // 1024: 13.6 us per 256^2-double halo, 4096: 16.1, 16384: 27.8 }
+    if (!per_block) { const char *e = getenv("MGCG_PEER_DOUBLES_PER_BLOCK"); per_block = e ? atoi(e) : 1024; if (per_block < 256) per_block = 256; }   // measured per 256^2-double halo: 1024 -> 13.6 us, 4096 -> 16.1, 16384 -> 27.8
     long long g = (doubles + per_block - 1) / per_block;   // >= 16 doubles (2 x 128-bit stores in flight... per thread at 256 threads)
     if (g < 1) g = 1;
     if (g > sm_count) g = sm_count;           // all blocks must be co-resident: they spin on the flags
@@ -257,9 +257,25 @@ int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
     PeerState &P = D->peer;
     cudaStream_t st = c->stream;
     const int W = D->world, rk = D->rank;
-    peer_close(c);
-    if (W < 2 || W > kPeerMax) return MGCG_OK;
+    P.active = false;
+    if (W < 2 || W > kPeerMax) { peer_close(c); return MGCG_OK; }
     halo_cap = (halo_cap + 1) & ~1;
+    // A re-setup keeps the arena and its mappings when the new hierarchy fits (allocating and IPC-mapping with 7 peers costs
+    // tens of milliseconds): every rank clears its own flags / sequence numbers, and the all-reduce that takes the decision
+    // is also the barrier that orders those memsets before anybody's first push.
+    {
+        int reuse = (P.ready && P.arena && halo_cap <= P.halo_cap && (size_t)2 * P.halo_cap + (size_t)gather_cap <= P.stage_cap) ? 1 : 0;
+        int *d_flag = nullptr;
+        MGCG_CUDA(pool_alloc((void **)&d_flag, sizeof(int), st));
+        if (reuse) MGCG_CUDA(cudaMemsetAsync(P.arena, 0, P.stage_off, st));
+        MGCG_CUDA(cudaMemcpyAsync(d_flag, &reuse, sizeof(int), cudaMemcpyHostToDevice, st));
+        MGCG_NCCL(D->api, AllReduce(d_flag, d_flag, 1, ncclInt, ncclMin, D->comm, st));
+        MGCG_CUDA(cudaMemcpyAsync(&reuse, d_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+        MGCG_CUDA(cudaStreamSynchronize(st));
+        pool_release(d_flag);
+        if (reuse) { P.active = true; return MGCG_OK; }
+    }
+    peer_close(c);
     // halo and gather staging are DISJOINT: a gather is pushed by every rank, also by ranks that are not this rank's
     // neighbours and have therefore not synchronised with it in the halo exchanges just before — their blocks must not land
     // where a slower rank may still be unpacking a halo of two exchanges ago (seen as a changed iteration count at 8 GPUs)
@@ -314,7 +330,7 @@ int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
     MGCG_CUDA(cudaStreamSynchronize(st));
     cudaFree(d_all);
     if (!ok) { peer_close(c); return MGCG_OK; }
-    P.active = true;
+    P.active = true; P.ready = true;
     return MGCG_OK;
 }
 

@@ -47,6 +47,12 @@ def main():
     o = S.default_options(norm=2, tolerance=1e-8, max_iteration=2000, **kw)
     m.setup(N, r0, tv, tr, tc, o)
     res = m.solve(tb, tx)
+    for _ in range(cfg.get("setups", 1) - 1):     # a re-setup reuses the peer arena, the private coarse context and cached blocks
+        x_first = tx.clone()
+        m.setup(N, r0, tv, tr, tc, o)
+        res2 = m.solve(tb, tx.zero_())
+        assert res2.iterations_done == res.iterations_done and torch.equal(tx, x_first), "solve after a re-setup differs"
+        res = res2
     for _ in range(cfg.get("solves", 1) - 1):     # repeated solves replay the captured iteration; results must not move
         x_first = tx.clone()
         res2 = m.solve(tb, tx.zero_())

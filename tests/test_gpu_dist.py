@@ -27,14 +27,14 @@ CASES = [
     ("plain_cg_peer", {"n": 32, "options": {"precond": 0, "dist_transport": 2}, "transport": 2}),
     ("mg_replicated_peer", {"n": 32, "options": {"precond": 1, "dist_transport": 2}, "transport": 2}),
     ("mg_two_sharded_levels_peer", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2}, "transport": 2,
-                                    "solves": 3}),
+                                    "solves": 3, "setups": 3}),
     ("mg_two_sharded_levels_peer_graph1", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "use_graph": 1},
                                            "transport": 2}),
     # four ranks: ranks that are not neighbours push into each other's staging only in the all-gather (eager launches drift most)
     ("mg_two_sharded_levels_peer_eager_w4", {"n": 48, "world": 4, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "use_graph": 0},
                                              "transport": 2, "solves": 3}),
     ("mg_one_sharded_level_peer_w4", {"n": 48, "world": 4, "options": {"precond": 1, "dist_replicate_below": 50000, "dist_transport": 2}, "transport": 2,
-                                      "solves": 3}),
+                                      "solves": 3, "setups": 2}),
     ("mg_27pt_peer_eager", {"n": 24, "matrix": "p27", "options": {"precond": 1, "dist_replicate_below": 500, "dist_transport": 2, "use_graph": 0},
                             "transport": 2, "err_tol": 1e-9}),   # high-contrast coefficients (1e6): rounding-order differences are amplified
 ]
