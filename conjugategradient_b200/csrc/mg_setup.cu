@@ -101,6 +101,25 @@ __global__ void k_expand_sa(Csr A, int row_base, const int *agg, const double *d
     }
 }
 
+// The same expansion with one WARP per row, for the coarse levels (a few thousand rows of hundreds of entries: one thread
+// per row left 6 blocks busy for a millisecond).  Every entry goes to the same position with the same value.
+__global__ void k_expand_sa_warp(Csr A, int row_base, const int *agg, const double *dinv, double w, u64 *keys, double *vals)
+{
+    const int nz0 = A.rowptr[0];
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (int i = warp; i < A.rows; i += nwarps) {
+        const int ks = A.rowptr[i], ke = A.rowptr[i + 1];
+        const size_t o0 = (size_t)(ks - nz0) + i;
+        if (lane == 0) { keys[o0] = ((u64)i << 32) | (unsigned)agg[i + row_base]; vals[o0] = 1.0; }
+        const double f = -__dmul_rn(w, dinv[i]);
+        for (int k = ks + lane; k < ke; k += 32) {
+            keys[o0 + 1 + (size_t)(k - ks)] = ((u64)i << 32) | (unsigned)agg[A.col[k]];
+            vals[o0 + 1 + (size_t)(k - ks)] = __dmul_rn(f, A.val[k]);
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // COO (key = row<<32 | col) -> CSR with ordered duplicate summation
 __global__ void k_mark_heads(size_t count, const u64 *keys, int *head)
@@ -344,50 +363,52 @@ int csr_transpose(mgcg_ctx *c, const Csr &A, DevCsr *T)
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// dense coarsest level: M = A^-1 by in-place Gauss-Jordan, two launches per pivot
+// dense coarsest level: M = A^-1 by Gauss-Jordan without pivoting (SPD), one launch per pivot
 __global__ void k_csr_to_dense(Csr A, double *M)
 {
     const int n = A.rows;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
         for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k) M[(size_t)i * n + A.col[k]] = A.val[k];
 }
-__global__ void k_gj_pivot(int n, int k, const double *M, double *colk, double *rowk)
+// One launch per pivot, out of place (Min -> Mout, the buffers swap): every element recomputes its entry of the normalised
+// pivot row instead of reading it from a second kernel's output, so nothing it reads is written in the same launch.
+// Per element:  row k: m_kj / p (1 / p on the diagonal);  column k: -(m_ik * (1 / p));  else m_ij - m_ik * (m_kj / p).
+__global__ void k_gj_step(int n, int k, const double *__restrict__ Min, double *__restrict__ Mout)
 {
-    const double p = M[(size_t)k * n + k];
-    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
-        colk[j] = M[(size_t)j * n + k];
-        rowk[j] = (j == k) ? 1.0 / p : M[(size_t)k * n + j] / p;
-    }
-}
-__global__ void k_gj_update(int n, int k, double *M, const double *colk, const double *rowk)
-{
+    const double p = Min[(size_t)k * n + k];
     const long long nn = (long long)n * n;
     for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < nn; e += (long long)gridDim.x * blockDim.x) {
         const int i = (int)(e / n), j = (int)(e % n);
+        const double rkj = (j == k) ? 1.0 / p : Min[(size_t)k * n + j] / p;
         double v;
-        if (i == k) v = rowk[j];
-        else if (j == k) v = -__dmul_rn(colk[i], rowk[k]);
-        else v = __dadd_rn(M[e], -__dmul_rn(colk[i], rowk[j]));
-        M[e] = v;
+        if (i == k) v = rkj;
+        else {
+            const double ci = Min[(size_t)i * n + k];
+            v = (j == k) ? -__dmul_rn(ci, rkj) : __dadd_rn(Min[e], -__dmul_rn(ci, rkj));
+        }
+        Mout[e] = v;
     }
 }
 
+// (Measured and dropped: the elimination in ONE block with the pivot row/column in shared memory and a block barrier per
+// pivot.  Every update is an L2 round trip for the one SM doing the work: 2.0-3.0 ms at n = 216 against 1.85 ms with two
+// launches per pivot.)
 static int dense_inverse(mgcg_ctx *c, const Csr &A, double **Minv)
 {
     const int n = A.rows;
     cudaStream_t st = c->stream;
-    double *M = nullptr, *colk = nullptr, *rowk = nullptr;
-    MGCG_CHECK(dalloc(&M, (size_t)n * n)); MGCG_CHECK(dalloc(&colk, (size_t)n)); MGCG_CHECK(dalloc(&rowk, (size_t)n));
+    double *M = nullptr, *M2 = nullptr;
+    MGCG_CHECK(dalloc(&M, (size_t)n * n)); MGCG_CHECK(dalloc(&M2, (size_t)n * n));
     MGCG_CUDA(cudaMemsetAsync(M, 0, sizeof(double) * (size_t)n * n, st));
     k_csr_to_dense<<<grid_for(n), 256, 0, st>>>(A, M);
     MGCG_LAUNCH_CHECK();
     for (int k = 0; k < n; ++k) {
-        k_gj_pivot<<<grid_for(n), 256, 0, st>>>(n, k, M, colk, rowk);
-        k_gj_update<<<grid_for((long long)n * n), 256, 0, st>>>(n, k, M, colk, rowk);
+        k_gj_step<<<grid_for((long long)n * n), 256, 0, st>>>(n, k, M, M2);
+        double *t = M; M = M2; M2 = t;
     }
     MGCG_LAUNCH_CHECK();
     MGCG_CUDA(cudaStreamSynchronize(st));
-    tfree(colk); tfree(rowk);
+    tfree(M2);
     *Minv = M;
     return MGCG_OK;
 }
@@ -527,7 +548,8 @@ int build_prolongator(mgcg_ctx *c, const Csr &A, int row_base, const int *agg, c
     const size_t count = (size_t)A.nnz + n;
     u64 *keys = nullptr; double *vals = nullptr;
     MGCG_CHECK(dalloc(&keys, count)); MGCG_CHECK(dalloc(&vals, count));
-    k_expand_sa<<<grid_for(n), 256, 0, st>>>(A, row_base, agg, dinv, omega, keys, vals);
+    if ((double)A.nnz >= 16.0 * n) k_expand_sa_warp<<<grid_for((long long)n * 32), 256, 0, st>>>(A, row_base, agg, dinv, omega, keys, vals);
+    else k_expand_sa<<<grid_for(n), 256, 0, st>>>(A, row_base, agg, dinv, omega, keys, vals);
     MGCG_LAUNCH_CHECK();
     int s = coo_to_csr_sum(c, n, ncoarse, count, keys, vals, P);
     tfree(keys); tfree(vals);
