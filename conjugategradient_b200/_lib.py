@@ -47,6 +47,12 @@ NATIVE_SYMBOLS = [
     "mgcg_comm_unique_id", "mgcg_comm_init", "mgcg_setup_dist", "mgcg_solve_dist", "mgcg_dist_microbench",
     "mgcg_generate_poisson3d7_nnz", "mgcg_generate_poisson3d7", "mgcg_generate_poisson3d27_nnz", "mgcg_generate_poisson3d27",
 ]
+# every symbol include/mgcg_formats.h declares (ELL input, Write/Solve/Read/Iteration object)
+FORMAT_SYMBOLS = [
+    "mgcg_ell_nnz", "mgcg_ell_to_csr", "mgcg_solve_host_ell", "mgcg_computer_create", "mgcg_computer_destroy",
+    "mgcg_computer_set_preconditioner", "mgcg_computer_write", "mgcg_computer_solve", "mgcg_computer_read",
+    "mgcg_computer_iteration", "mgcg_computer_result",
+]
 # the reference's 32 MgcgGpu.dll exports (+ the C entry of SolveGpu and the preconditioner switch)
 COMPAT_SYMBOLS = [
     "GetDeviceCount", "SetDevice", "CreateBlas", "DestroyBlas", "CreateSparse", "DestroySparse", "CreateMatDescr",
@@ -112,6 +118,17 @@ def lib():
     L.mgcg_generate_poisson3d27_nnz.argtypes = [ci] * 5; L.mgcg_generate_poisson3d27_nnz.restype = C.c_longlong
     L.mgcg_generate_poisson3d27.argtypes = [vp] + [ci] * 6 + [vp, dp, vp, vp, vp]
     # compat exports
+    L.mgcg_ell_nnz.argtypes = [vp, ci, ci, vp]; L.mgcg_ell_nnz.restype = C.c_longlong
+    L.mgcg_ell_to_csr.argtypes = [vp, ci, ci, vp, vp, vp, vp, vp, vp]
+    L.mgcg_solve_host_ell.argtypes = [vp, ci, ci, vp, vp, vp, vp, vp, C.POINTER(Options), C.POINTER(Result)]
+    L.mgcg_computer_create.argtypes = [ci, ci]; L.mgcg_computer_create.restype = vp
+    L.mgcg_computer_destroy.argtypes = [vp]; L.mgcg_computer_destroy.restype = None
+    L.mgcg_computer_set_preconditioner.argtypes = [vp, ci, ci, ci, ci]
+    L.mgcg_computer_write.argtypes = [vp, vp, vp, vp, ci, vp, vp]
+    L.mgcg_computer_solve.argtypes = [vp, cd, ci, ci]
+    L.mgcg_computer_read.argtypes = [vp, vp]
+    L.mgcg_computer_iteration.argtypes = [vp]
+    L.mgcg_computer_result.argtypes = [vp, C.POINTER(Result)]
     L.GetDeviceCount.restype = ci
     L.SetDevice.argtypes = [ci]; L.SetDevice.restype = None
     for n in ("CreateBlas", "CreateSparse", "CreateMatDescr"):

@@ -160,6 +160,7 @@ struct mgcg_ctx {
     int graph_body_nodes = 0;            // kernels of one iteration
     // host-pointer path buffers (mgcg_solve_host)
     void *host_path = nullptr;
+    void *ell_path = nullptr;        // device system owned by mgcg_solve_host_ell (formats.cu)
 };
 
 namespace mgcg {
@@ -192,6 +193,7 @@ int spmv_launch(mgcg_ctx *c, const SpmvPlan &plan, int epi, const SpmvArgs &a);
 // ---- mg_setup.cu / mg_cycle.cu
 int mg_build(mgcg_ctx *c);
 void mg_free(mgcg_ctx *c);
+void formats_free(mgcg_ctx *c);
 int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done, int rz_fin);
 double *mg_level0_first_x(mgcg_ctx *c);   // buffer that receives the fused first pre-smoothing sweep
 const double *mg_level0_dinv(mgcg_ctx *c);

@@ -305,3 +305,68 @@ int ref_gen_banded_sin(int n, int max_nonzero, double *elements, int *column_ind
     for (int i = 0; i < n; i++) { b[i] = cos((double)i) * 10; x0[i] = (double)i / 100; }
     return row_offsets[n];
 }
+
+/* ---- the OpenCL variant's ELL container and solver (Mgcg/HandmadeCL/MgcgCL) --------------------------- */
+
+/* SparseMatrix.Multiply — Mgcg/HandmadeCL/MgcgCL/SparseMatrix.cs:202-224: answer[i] = 0, then the row's slots
+ * k = 0 .. NonzeroCounts[i]-1 in order (slot 0 is the diagonal, :74-92), element index i*MaxNonzeroCountPerRow + k. */
+void ref_ell_multiply(int rows, int max_nonzero, const double *elements, const int *column_indeces,
+                      const int *nonzero_counts, const double *vector, double *answer)
+{
+    for (int i = 0; i < rows; i++) {
+        answer[i] = 0;
+        for (int k = 0; k < nonzero_counts[i]; k++) {
+            size_t index = (size_t)i * (size_t)max_nonzero + (size_t)k;      /* GetGlobalIndex, :191-194 */
+            int j = column_indeces[index];
+            answer[i] += elements[index] * vector[j];
+        }
+    }
+}
+
+/* Index bookkeeping only: the used slots of every row, in slot order, as CSR.  Returns the entry count. */
+int ref_ell_to_csr(int rows, int max_nonzero, const double *elements, const int *column_indeces, const int *nonzero_counts,
+                   double *csr_elements, int *row_offsets, int *csr_column_indeces)
+{
+    int o = 0;
+    for (int i = 0; i < rows; i++) {
+        row_offsets[i] = o;
+        for (int k = 0; k < nonzero_counts[i]; k++, o++) {
+            size_t index = (size_t)i * (size_t)max_nonzero + (size_t)k;
+            csr_elements[o] = elements[index];
+            csr_column_indeces[o] = column_indeces[index];
+        }
+    }
+    row_offsets[rows] = o;
+    return o;
+}
+
+/* ConjugateGradientSingleGpu.Solve of the OpenCL variant — Mgcg/HandmadeCL/MgcgCL/ConjugateGradientSingleGpu.cs:226-296,
+ * with its kernels as the sequential loops they parallelise (Mgcg.cl:15-33 result = left + C*right; :35-108 dot by
+ * multiply + tree sum, restated left to right; :110-160 max |.|).  rr is recomputed at the top of every pass (:261),
+ * Residual = max|r_i| (:268), IsConverged as ConjugateGradient.cs of that variant (Iteration < Min -> no;
+ * Iteration > Max -> throw; Residual < Allowable).  x holds the initial guess (:217, :246). */
+int ref_cg_solve_ell(int n, int max_nonzero, const double *elements, const int *column_indeces, const int *nonzero_counts,
+                     double *x, const double *b, double *r, double *p, double *Ap,
+                     double allowable_residual, int min_iteration, int max_iteration, int *iteration, double *residual)
+{
+    ref_ell_multiply(n, max_nonzero, elements, column_indeces, nonzero_counts, x, Ap);      /* :246 */
+    ref_set_added(n, r, b, Ap, -1);                                                         /* :247 */
+    memcpy(p, r, sizeof(double) * (size_t)n);                                               /* :248 */
+    int it;
+    for (it = 0;; it++) {                                                                   /* :251 */
+        double rr = ref_dot(n, r, r);                                                       /* :261 */
+        ref_ell_multiply(n, max_nonzero, elements, column_indeces, nonzero_counts, p, Ap);  /* :262 */
+        double alpha = rr / ref_dot(n, p, Ap);                                              /* :263 */
+        ref_set_added(n, x, x, p, alpha);                                                   /* :264 */
+        ref_set_added(n, r, r, Ap, -alpha);                                                 /* :265 */
+        *residual = ref_max_absolute(n, r);                                                 /* :268 */
+        int c = ref_is_converged(it, min_iteration, max_iteration, *residual, allowable_residual);
+        if (c < 0) { *iteration = it; return REF_MAX_ITERATION_EXCEEDED; }
+        if (c) break;                                                                       /* :271-275 */
+        double rrNew = ref_dot(n, r, r);                                                    /* :285 */
+        double beta = rrNew / rr;                                                           /* :286 */
+        ref_set_added(n, p, r, p, beta);                                                    /* :287 */
+    }
+    *iteration = it;
+    return REF_OK;
+}

@@ -51,6 +51,11 @@ def lib():
                                       C.c_double, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double)]
         L.ref_cg_solve_mt.restype = C.c_int
         L.ref_mt_max_threads.restype = C.c_int
+        L.ref_ell_multiply.argtypes = [C.c_int, C.c_int, c_dp, c_ip, c_ip, c_dp, c_dp]
+        L.ref_ell_to_csr.argtypes = [C.c_int, C.c_int, c_dp, c_ip, c_ip, c_dp, c_ip, c_ip]; L.ref_ell_to_csr.restype = C.c_int
+        L.ref_cg_solve_ell.argtypes = [C.c_int, C.c_int, c_dp, c_ip, c_ip, c_dp, c_dp, c_dp, c_dp, c_dp,
+                                       C.c_double, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double)]
+        L.ref_cg_solve_ell.restype = C.c_int
         _LIB = L
     return _LIB
 
@@ -87,6 +92,33 @@ def cg_solve_mt(val, rowptr, col, b, x0=None, tol=1e-8, min_iteration=0, max_ite
     it, res = C.c_int(0), C.c_double(0)
     st = lib().ref_cg_solve_mt(threads, n, val, rowptr, col, x, np.ascontiguousarray(b, dtype=np.float64), r, p, Ap, tol,
                                min_iteration, n if max_iteration is None else max_iteration, norm, C.byref(it), C.byref(res))
+    return x, it.value, res.value, st
+
+
+def ell_multiply(elements, columns, counts, max_nonzero, x):
+    """SparseMatrix.Multiply of the OpenCL variant (HandmadeCL/MgcgCL/SparseMatrix.cs:202-224)."""
+    n = len(counts)
+    y = np.empty(n)
+    lib().ref_ell_multiply(n, max_nonzero, elements, columns, counts, np.ascontiguousarray(x, dtype=np.float64), y)
+    return y
+
+
+def ell_to_csr(elements, columns, counts, max_nonzero):
+    n = len(counts)
+    total = int(np.sum(counts))
+    val, rp, col = np.empty(total), np.empty(n + 1, dtype=np.int32), np.empty(total, dtype=np.int32)
+    assert lib().ref_ell_to_csr(n, max_nonzero, elements, columns, counts, val, rp, col) == total
+    return val, rp, col
+
+
+def cg_solve_ell(elements, columns, counts, max_nonzero, b, x0=None, tol=1e-8, min_iteration=0, max_iteration=None):
+    """ConjugateGradientSingleGpu.Solve of the OpenCL variant (ELL matrix, max|r| stop). Returns (x, iteration_index, residual, status)."""
+    n = len(counts)
+    x = np.zeros(n) if x0 is None else np.array(x0, dtype=np.float64, copy=True)
+    r, p, Ap = np.empty(n), np.empty(n), np.empty(n)
+    it, res = C.c_int(0), C.c_double(0)
+    st = lib().ref_cg_solve_ell(n, max_nonzero, elements, columns, counts, x, np.ascontiguousarray(b, dtype=np.float64), r, p, Ap, tol,
+                                min_iteration, n if max_iteration is None else max_iteration, C.byref(it), C.byref(res))
     return x, it.value, res.value, st
 
 

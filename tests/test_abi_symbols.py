@@ -41,6 +41,15 @@ def test_reference_export_names(L):
         assert hasattr(L, n), n
 
 
+def test_format_symbols_exported(L):
+    # ELL input + the four-call object of the reference's other variants (include/mgcg_formats.h)
+    from conjugategradient_b200 import _lib
+    decl = _declared("mgcg_formats.h")
+    assert set(decl) == set(_lib.FORMAT_SYMBOLS), set(decl) ^ set(_lib.FORMAT_SYMBOLS)
+    for n in decl:
+        assert hasattr(L, n), n
+
+
 def test_version_and_partition_rule(L):
     import numpy as np
     assert L.mgcg_version() == 100
