@@ -31,6 +31,34 @@ __device__ __forceinline__ void epilogue(int row, double s, const SpmvArgs &a, d
     }
 }
 
+// The epilogue's operands that do not depend on the row sum, loaded BEFORE the wait for the tile's matrix slice so that their
+// latency overlaps it (the prolongator's 3-entry rows leave nothing else to hide a y[row] round trip behind).  Same
+// expressions as epilogue<EPI>, operand for operand.
+struct EpiPre { double e0, e1, e2; };
+template <int EPI>
+__device__ __forceinline__ void epi_prefetch(int row, const SpmvArgs &a, EpiPre &p)
+{
+    p.e0 = 0.0; p.e1 = 0.0; p.e2 = 0.0;
+    if (EPI == EPI_AXPBY) { if (a.beta != 0.0) p.e0 = a.y[row]; }
+    else if (EPI == EPI_DOT) p.e0 = a.w[row];
+    else if (EPI == EPI_RESID) p.e0 = a.b[row];
+    else if (EPI == EPI_JACOBI || EPI == EPI_JACOBI_DOT) { p.e0 = a.b[row]; p.e1 = (a.xrow ? a.xrow : a.x)[row]; p.e2 = a.dinv[row]; }
+}
+template <int EPI>
+__device__ __forceinline__ void epilogue_pre(int row, double s, const SpmvArgs &a, double &dsum, const EpiPre &p)
+{
+    if (EPI == EPI_PLAIN) a.y[row] = s;
+    else if (EPI == EPI_AXPBY) a.y[row] = (a.beta == 0.0) ? a.alpha * s : a.alpha * s + a.beta * p.e0;
+    else if (EPI == EPI_DOT) { a.y[row] = s; dsum += p.e0 * s; }
+    else if (EPI == EPI_RESID) a.y[row] = p.e0 - s;
+    else if (EPI == EPI_JACOBI || EPI == EPI_JACOBI_DOT) {
+        const double bi = p.e0;
+        const double yi = p.e1 + a.omega * p.e2 * (bi - s);
+        a.y[row] = yi;
+        if (EPI == EPI_JACOBI_DOT) dsum += bi * yi;
+    }
+}
+
 template <int EPI> struct EpiTraits { static constexpr bool reduces = (EPI == EPI_DOT || EPI == EPI_JACOBI_DOT); };
 
 // ---------------------------------------------------------------------------------------------------------
@@ -189,6 +217,8 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
             const int rn = (tile + gridDim.x) * kTmaRows + t;
             if (rn < rows) { rs_n = rowptr[rn]; re_n = rowptr[rn + 1]; }
         }
+        EpiPre pre;
+        if (row < rows) epi_prefetch<EPI>(row, a, pre);
         mbar_wait(&s_full[s], parity);
         double acc = 0.0;
         if (row < rows) {
@@ -206,7 +236,7 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
             mbar_wait(&s_empty[s], parity);       // ... and once every thread is, refill it
             issue(j + kTmaStages);
         }
-        if (row < rows) epilogue<EPI>(row, acc, a, dsum);
+        if (row < rows) epilogue_pre<EPI>(row, acc, a, dsum, pre);
     }
     if (EpiTraits<EPI>::reduces) {
         double m = 0.0;
