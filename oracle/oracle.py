@@ -19,7 +19,7 @@ OK, MAX_ITERATION_EXCEEDED = 0, 3
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("cg_ref.c", "mg_ref.c", "cg_ref_mt.c") if os.path.exists(os.path.join(_HERE, f))]
+    srcs = [os.path.join(_HERE, f) for f in ("cg_ref.c", "mg_ref.c", "cg_ref_mt.c", "mps_ref.c") if os.path.exists(os.path.join(_HERE, f))]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-s", "-C", _HERE, "-B", "liboracle.so"])
     return so
@@ -51,6 +51,9 @@ def lib():
                                       C.c_double, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double)]
         L.ref_cg_solve_mt.restype = C.c_int
         L.ref_mt_max_threads.restype = C.c_int
+        L.ref_mps_cell_order.argtypes = [C.c_int, c_dp, C.c_double, c_ip, C.c_void_p, C.c_int]; L.ref_mps_cell_order.restype = C.c_int
+        L.ref_mps_assemble.argtypes = [C.c_int, c_dp, C.c_double, C.c_double, C.c_int, c_ip, C.c_void_p, C.c_void_p]
+        L.ref_mps_assemble.restype = C.c_longlong
         L.ref_ell_multiply.argtypes = [C.c_int, C.c_int, c_dp, c_ip, c_ip, c_dp, c_dp]
         L.ref_ell_to_csr.argtypes = [C.c_int, C.c_int, c_dp, c_ip, c_ip, c_dp, c_ip, c_ip]; L.ref_ell_to_csr.restype = C.c_int
         L.ref_cg_solve_ell.argtypes = [C.c_int, C.c_int, c_dp, c_ip, c_ip, c_dp, c_dp, c_dp, c_dp, c_dp,
@@ -120,6 +123,23 @@ def cg_solve_ell(elements, columns, counts, max_nonzero, b, x0=None, tol=1e-8, m
     st = lib().ref_cg_solve_ell(n, max_nonzero, elements, columns, counts, x, np.ascontiguousarray(b, dtype=np.float64), r, p, Ap, tol,
                                 min_iteration, n if max_iteration is None else max_iteration, C.byref(it), C.byref(res))
     return x, it.value, res.value, st
+
+
+def mps_assemble(pos, re, shift_abs=0.0, max_per_row=160):
+    """oracle/mps_ref.c: cell-list neighbour search -> CSR (diagonal first, neighbours ascending).  pos: (n, 3) in any order.
+    Returns (val, rowptr, col, order) with order[k] = input index of the particle numbered k."""
+    pos = np.ascontiguousarray(pos, dtype=np.float64)
+    n = pos.shape[0]
+    order = np.empty(n, dtype=np.int32)
+    assert lib().ref_mps_cell_order(n, pos.reshape(-1), re, order, None, 0) > 0
+    p = np.ascontiguousarray(pos[order]).reshape(-1)
+    rp = np.empty(n + 1, dtype=np.int32)
+    nnz = lib().ref_mps_assemble(n, p, re, shift_abs, max_per_row, rp, None, None)
+    if nnz < 0:
+        raise ValueError(f"ref_mps_assemble: {nnz}")
+    val, col = np.empty(nnz), np.empty(nnz, dtype=np.int32)
+    assert lib().ref_mps_assemble(n, p, re, shift_abs, max_per_row, rp, val.ctypes.data_as(C.c_void_p), col.ctypes.data_as(C.c_void_p)) == nnz
+    return val, rp, col, order
 
 
 def max_threads():
