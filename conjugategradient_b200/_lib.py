@@ -15,6 +15,7 @@ NORM_ABS_L2, NORM_ABS_LINF, NORM_REL_L2 = 0, 1, 2
 PRECOND_NONE, PRECOND_MG = 0, 1
 SPMV_AUTO, SPMV_STREAM, SPMV_VECTOR = 0, 1, 2
 TRANSPORT_AUTO, TRANSPORT_NCCL, TRANSPORT_PEER = 0, 1, 2
+AGG_AUTO, AGG_BLOCKS, AGG_MIS2 = 0, 1, 2
 
 
 class Options(C.Structure):
@@ -25,7 +26,8 @@ class Options(C.Structure):
         ("mg_omega", C.c_double), ("mg_smoother", C.c_int), ("mg_smoothed", C.c_int), ("mg_prolong_omega", C.c_double),
         ("spmv_kernel", C.c_int), ("check_interval", C.c_int), ("use_graph", C.c_int), ("profile", C.c_int),
         ("mg_smoothed_levels", C.c_int), ("mg_aggregate_size", C.c_int), ("mg_aggregate_size_coarse", C.c_int),
-        ("dist_replicate_below", C.c_int), ("dist_transport", C.c_int), ("mg_tail_rows", C.c_int), ("reserved", C.c_int * 2),
+        ("dist_replicate_below", C.c_int), ("dist_transport", C.c_int), ("mg_tail_rows", C.c_int), ("mg_aggregation", C.c_int),
+        ("reserved0", C.c_int), ("mg_strength_theta", C.c_double), ("reserved", C.c_int * 6),
     ]
 
 
@@ -46,6 +48,7 @@ NATIVE_SYMBOLS = [
     "mgcg_mg_level_get", "mgcg_mg_level_aggregates", "mgcg_mg_apply", "mgcg_partition_offsets",
     "mgcg_comm_unique_id", "mgcg_comm_init", "mgcg_setup_dist", "mgcg_solve_dist", "mgcg_dist_microbench",
     "mgcg_generate_poisson3d7_nnz", "mgcg_generate_poisson3d7", "mgcg_generate_poisson3d27_nnz", "mgcg_generate_poisson3d27",
+    "mgcg_mps_order", "mgcg_mps_count", "mgcg_mps_fill", "mgcg_test_scan_counts",
 ]
 # every symbol include/mgcg_formats.h declares (ELL input, Write/Solve/Read/Iteration object)
 FORMAT_SYMBOLS = [
@@ -118,6 +121,10 @@ def lib():
     L.mgcg_generate_poisson3d27_nnz.argtypes = [ci] * 5; L.mgcg_generate_poisson3d27_nnz.restype = C.c_longlong
     L.mgcg_generate_poisson3d27.argtypes = [vp] + [ci] * 6 + [vp, dp, vp, vp, vp]
     # compat exports
+    L.mgcg_mps_order.argtypes = [vp, ci, vp, cd, vp, vp]; L.mgcg_mps_order.restype = C.c_longlong
+    L.mgcg_mps_count.argtypes = [vp, ci, vp, cd, ci, vp]; L.mgcg_mps_count.restype = C.c_longlong
+    L.mgcg_mps_fill.argtypes = [vp, ci, vp, cd, cd, vp, vp, vp]
+    L.mgcg_test_scan_counts.argtypes = [vp, ci, ci, C.POINTER(C.c_longlong)]
     L.mgcg_ell_nnz.argtypes = [vp, ci, ci, vp]; L.mgcg_ell_nnz.restype = C.c_longlong
     L.mgcg_ell_to_csr.argtypes = [vp, ci, ci, vp, vp, vp, vp, vp, vp]
     L.mgcg_solve_host_ell.argtypes = [vp, ci, ci, vp, vp, vp, vp, vp, C.POINTER(Options), C.POINTER(Result)]

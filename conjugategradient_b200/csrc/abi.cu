@@ -78,6 +78,8 @@ void mgcg_options_default(mgcg_options *o)
     o->check_interval = 8;
     o->use_graph = 2;
     o->profile = 0;
+    o->mg_aggregation = MGCG_AGG_AUTO;
+    o->mg_strength_theta = 0.5;
 }
 
 mgcg_ctx *mgcg_create(int device)

@@ -432,6 +432,9 @@ static int dist_replicate(mgcg_ctx *c, int lev, const Csr &A, const int *offs, i
     mgcg_options o = c->opt;
     o.precond = MGCG_PRECOND_MG;
     o.nx = nx; o.ny = ny; o.nz = nz_total;
+    // the sharded levels above aggregate without a grid by blocks of 8 rows of each rank's block (agg_of): keep the same rule
+    // in the replicated tail so that the sharded hierarchy equals the single-GPU one built with MGCG_AGG_BLOCKS
+    if (o.mg_aggregation == MGCG_AGG_AUTO) o.mg_aggregation = MGCG_AGG_BLOCKS;
     if (lev > 0) {
         if (o.mg_aggregate_size_coarse > 0) o.mg_aggregate_size = o.mg_aggregate_size_coarse;
         if (o.mg_smoothed && o.mg_smoothed_levels > 0) {
@@ -967,6 +970,10 @@ extern "C" int mgcg_setup_dist(mgcg_ctx *c, int global_count, int row_offset, in
     if (opt) c->opt = *opt;
     if (c->opt.norm == MGCG_NORM_ABS_LINF) { set_error("mgcg_setup_dist: the max-norm stop rule is not available on the sharded path"); return MGCG_ERR_UNSUPPORTED; }
     if (c->opt.mg_smoother != MGCG_SMOOTHER_JACOBI) { set_error("mgcg_setup_dist: only the weighted-Jacobi smoother is implemented"); return MGCG_ERR_UNSUPPORTED; }
+    if (c->opt.precond == MGCG_PRECOND_MG && c->opt.mg_aggregation == MGCG_AGG_MIS2) {
+        set_error("mgcg_setup_dist: MIS-2 aggregation is single-GPU only (sharded levels aggregate by grid blocks or blocks of 8 rows)");
+        return MGCG_ERR_UNSUPPORTED;
+    }
     c->is_setup = false;
     cudaEvent_t e0, e1;
     MGCG_CUDA(cudaEventCreate(&e0)); MGCG_CUDA(cudaEventCreate(&e1));

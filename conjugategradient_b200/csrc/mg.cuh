@@ -65,6 +65,11 @@ int build_prolongator(mgcg_ctx *c, const Csr &A, int row_base, const int *agg, c
 void set_alloc_stream(cudaStream_t st);   // stream used by the build helpers' pool allocations on this host thread
 int extract_dinv(mgcg_ctx *c, const Csr &A, int row_base, double *dinv);
 int csr_transpose(mgcg_ctx *c, const Csr &A, DevCsr *T);
+// cnt[0..rows) (cnt[rows] == 0) -> rowptr[0..rows], total in 64 bits; MGCG_ERR_UNSUPPORTED when it does not fit int32 (mg_spgemm.cu)
+int scan_counts_checked(mgcg_ctx *c, const int *cnt, int rows, int *rowptr, int *nnz, const char *what);
+// ---- mg_aggregate.cu: aggregation without a grid — strength filter (A -> A_F, 1/diag(A_F)) and MIS-2 aggregates on A_F
+int strength_filter(mgcg_ctx *c, const Csr &A, double theta, DevCsr *F, double **dinvF);
+int mis2_aggregate(mgcg_ctx *c, const Csr &F, int *agg, int *ncoarse, int *rounds_out);
 // ---- mg_tail.cu
 void mg_tail_plan(mgcg_ctx *c);
 int mg_tail_run(mgcg_ctx *c, int first, double **x_out);

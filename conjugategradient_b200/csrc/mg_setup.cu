@@ -161,7 +161,7 @@ int coo_to_csr_sum(mgcg_ctx *c, int rows, int cols, size_t count, u64 *keys, dou
         MGCG_CHECK(dalloc(&out->val, 1)); MGCG_CHECK(dalloc(&out->col, 1));
         return MGCG_OK;
     }
-    if (count >= 0xfffffff0ull) { set_error("coo_to_csr_sum: chunk too large"); return MGCG_ERR_UNSUPPORTED; }
+    if (count >= (1ull << 31)) { set_error("coo_to_csr_sum: %llu entries exceed the int32 index range", (unsigned long long)count); return MGCG_ERR_UNSUPPORTED; }
     u64 *keys2 = nullptr; double *vals2 = nullptr;
     MGCG_CHECK(dalloc(&keys2, count)); MGCG_CHECK(dalloc(&vals2, count));
     cub::DoubleBuffer<u64> dk(keys, keys2);
@@ -502,15 +502,12 @@ static int psa_direct(mgcg_ctx *c, const Csr &A, int row_base, const int *agg, c
     MGCG_LAUNCH_CHECK();
     P->rows = n; P->cols = ncoarse;
     MGCG_CHECK(dalloc(&P->rowptr, (size_t)n + 1));
-    size_t tb = 0;
-    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, P->rowptr, n + 1, st));
-    void *tmp = nullptr;
-    MGCG_CUDA(pool_alloc(&tmp, tb, st));
-    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, P->rowptr, n + 1, st));
     int nnz = 0;
-    MGCG_CUDA(cudaMemcpyAsync(&nnz, P->rowptr + n, sizeof(int), cudaMemcpyDeviceToHost, st));
-    MGCG_CUDA(cudaStreamSynchronize(st));
-    tfree(tmp); tfree(cnt);
+    {
+        const int s_ = scan_counts_checked(c, cnt, n, P->rowptr, &nnz, "prolongator");
+        tfree(cnt);
+        MGCG_CHECK(s_);
+    }
     P->nnz = nnz;
     MGCG_CHECK(dalloc(&P->val, (size_t)nnz)); MGCG_CHECK(dalloc(&P->col, (size_t)nnz));
     k_psa_fill<MAXM><<<g, 256, 0, st>>>(A, row_base, agg, dinv, omega, P->rowptr, P->col, P->val);
@@ -629,23 +626,43 @@ int mg_build(mgcg_ctx *c)
         int nc;
         int cd[3] = {0, 0, 0};
         MGCG_CHECK(dalloc(&L.agg, (size_t)n));
-        if (L.dims[0] > 0) {
+        // aggregation: AUTO = geometric blocks with a grid hint, strength filter + MIS-2 without; BLOCKS = 8 consecutive rows
+        // without a hint (== cells of cell-sorted particles; the round-1 rule); MIS2 = algebraic even with a hint
+        const bool geometric = L.dims[0] > 0 && o.mg_aggregation != MGCG_AGG_MIS2;
+        const bool filtered = (o.mg_aggregation == MGCG_AGG_MIS2) || (L.dims[0] <= 0 && o.mg_aggregation != MGCG_AGG_BLOCKS);
+        DevCsr F;
+        double *dinvF = nullptr;
+        if (geometric) {
             int a = (l == 0 || o.mg_aggregate_size_coarse <= 0) ? o.mg_aggregate_size : o.mg_aggregate_size_coarse;
             if (a < 2) a = 2;
             cd[0] = (L.dims[0] + a - 1) / a; cd[1] = (L.dims[1] + a - 1) / a; cd[2] = (L.dims[2] + a - 1) / a;
             nc = cd[0] * cd[1] * cd[2];
             k_agg_geometric<<<grid_for(n), 256, 0, st>>>(L.dims[0], L.dims[1], L.dims[2], cd[0], cd[1], a, L.agg);
-        } else {
+        } else if (!filtered) {
             nc = (n + 7) / 8;
             k_agg_blocks<<<grid_for(n), 256, 0, st>>>(n, 8, L.agg);
+        } else {
+            const double theta = o.mg_strength_theta > 0.0 ? o.mg_strength_theta : 0.5;
+            int rounds = 0;
+            MGCG_CHECK(strength_filter(c, L.A, theta, &F, &dinvF));
+            tr.mark(l, "filter");
+            int s_ = mis2_aggregate(c, F.view(), L.agg, &nc, &rounds);
+            if (s_ != MGCG_OK) { F.free_all(); pool_release(dinvF); return s_; }
+            if (tr.on) fprintf(stderr, "[mgcg setup] level %d MIS-2: %d rows -> %d aggregates in %d rounds, %.1f strong entries per row\n",
+                               l, n, nc, rounds, (double)(F.nnz - n) / n);
         }
         MGCG_LAUNCH_CHECK();
-        if (nc >= n) break;   // cannot coarsen further
+        if (nc >= n) { F.free_all(); pool_release(dinvF); break; }   // cannot coarsen further
         tr.mark(l, "aggregate");
 
-        // ---- prolongator
+        // ---- prolongator (smoothed with the level operator, or with its strength-filtered version under MIS-2)
         const bool smooth_here = o.mg_smoothed && (o.mg_smoothed_levels <= 0 || l < o.mg_smoothed_levels);
-        MGCG_CHECK(build_prolongator(c, L.A, 0, L.agg, L.dinv, smooth_here, o.mg_prolong_omega, nc, &L.P));
+        {
+            const int s_ = filtered ? build_prolongator(c, F.view(), 0, L.agg, dinvF, smooth_here, o.mg_prolong_omega, nc, &L.P)
+                                    : build_prolongator(c, L.A, 0, L.agg, L.dinv, smooth_here, o.mg_prolong_omega, nc, &L.P);
+            F.free_all(); pool_release(dinvF);
+            MGCG_CHECK(s_);
+        }
         tr.mark(l, "P");
         MGCG_CHECK(csr_transpose(c, L.P.view(), &L.R));
         tr.mark(l, "R=P^T");

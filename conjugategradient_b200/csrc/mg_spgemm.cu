@@ -169,6 +169,47 @@ __global__ void k_spgemm_maxprod(Csr A, Csr B, int shift, int *out_max)
     if ((threadIdx.x & 31) == 0) atomicMax(out_max, m);
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Row counts -> row pointers with the total accumulated in 64 bits.  A*P and R*(A*P) hold 2-3x nnz(A) entries, so a
+// problem that itself fits int32 can produce a product that does not; the int32 exclusive scan would wrap silently and
+// size C->val / C->col from the wrapped total.  The total is summed separately as unsigned long long and any level with
+// >= 2^31 entries is refused (MGCG_ERR_UNSUPPORTED) before anything is allocated from it.
+__global__ void __launch_bounds__(256) k_sum_counts64(const int *__restrict__ cnt, int n, unsigned long long *out)
+{
+    unsigned long long s = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) s += (unsigned long long)(unsigned)cnt[i];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0 && s) atomicAdd(out, s);
+}
+
+// cnt[0..rows) -> rowptr[0..rows] (cnt[rows] must be 0); *nnz = total.  Synchronises the stream.
+int scan_counts_checked(mgcg_ctx *c, const int *cnt, int rows, int *rowptr, int *nnz, const char *what)
+{
+    cudaStream_t st = c->stream;
+    unsigned long long *d_total = nullptr, h_total = 0;
+    MGCG_CUDA(pool_alloc((void **)&d_total, sizeof(unsigned long long), st));
+    MGCG_CUDA(cudaMemsetAsync(d_total, 0, sizeof(unsigned long long), st));
+    int g = (rows + 255) / 256;
+    if (g > c->sm_count * 8) g = c->sm_count * 8;
+    if (g < 1) g = 1;
+    k_sum_counts64<<<g, 256, 0, st>>>(cnt, rows, d_total);
+    MGCG_LAUNCH_CHECK();
+    size_t tb = 0;
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, rowptr, rows + 1, st));
+    void *tmp = nullptr;
+    MGCG_CUDA(pool_alloc(&tmp, tb, st));
+    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, rowptr, rows + 1, st));
+    MGCG_CUDA(cudaMemcpyAsync(&h_total, d_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    pool_free(tmp, st); pool_free(d_total, st);
+    if (h_total >= (1ull << 31)) {
+        set_error("%s: %llu entries exceed the int32 index range of a level operator (2^31 - 1)", what, h_total);
+        return MGCG_ERR_UNSUPPORTED;
+    }
+    *nnz = (int)h_total;
+    return MGCG_OK;
+}
+
 
 // ---------------------------------------------------------------------------------------------------------
 // FEW, VERY LONG rows (the coarsest levels: a few hundred to a few thousand rows whose products run to 10^5 per row, all
@@ -274,15 +315,12 @@ static int run_dense_rows(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, in
     MGCG_LAUNCH_CHECK();
     C->rows = A.rows; C->cols = B.cols;
     MGCG_CUDA(pool_alloc((void **)&C->rowptr, sizeof(int) * ((size_t)A.rows + 1), st));
-    size_t tb = 0;
-    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, C->rowptr, A.rows + 1, st));
-    void *tmp = nullptr;
-    MGCG_CUDA(pool_alloc(&tmp, tb, st));
-    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, C->rowptr, A.rows + 1, st));
     int nnz = 0;
-    MGCG_CUDA(cudaMemcpyAsync(&nnz, C->rowptr + A.rows, sizeof(int), cudaMemcpyDeviceToHost, st));
-    MGCG_CUDA(cudaStreamSynchronize(st));
-    pool_free(tmp, st); pool_free(cnt, st);
+    {
+        const int s_ = scan_counts_checked(c, cnt, A.rows, C->rowptr, &nnz, "spgemm");
+        pool_free(cnt, st);
+        if (s_ != MGCG_OK) { pool_free(C->rowptr, st); C->rowptr = nullptr; return s_; }
+    }
     C->nnz = nnz;
     MGCG_CUDA(pool_alloc((void **)&C->val, sizeof(double) * (size_t)(nnz > 0 ? nnz : 1), st));
     MGCG_CUDA(pool_alloc((void **)&C->col, sizeof(int) * (size_t)(nnz > 0 ? nnz : 1), st));
@@ -365,15 +403,12 @@ static int run_merge(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, DevCsr 
     MGCG_LAUNCH_CHECK();
     C->rows = A.rows; C->cols = B.cols;
     MGCG_CUDA(pool_alloc((void **)&C->rowptr, sizeof(int) * ((size_t)A.rows + 1), st));
-    size_t tb = 0;
-    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, C->rowptr, A.rows + 1, st));
-    void *tmp = nullptr;
-    MGCG_CUDA(pool_alloc(&tmp, tb, st));
-    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, C->rowptr, A.rows + 1, st));
     int nnz = 0;
-    MGCG_CUDA(cudaMemcpyAsync(&nnz, C->rowptr + A.rows, sizeof(int), cudaMemcpyDeviceToHost, st));
-    MGCG_CUDA(cudaStreamSynchronize(st));
-    pool_free(tmp, st); pool_free(cnt, st);
+    {
+        const int s_ = scan_counts_checked(c, cnt, A.rows, C->rowptr, &nnz, "spgemm");
+        pool_free(cnt, st);
+        if (s_ != MGCG_OK) { pool_free(C->rowptr, st); C->rowptr = nullptr; return s_; }
+    }
     C->nnz = nnz;
     MGCG_CUDA(pool_alloc((void **)&C->val, sizeof(double) * (size_t)(nnz > 0 ? nnz : 1), st));
     MGCG_CUDA(pool_alloc((void **)&C->col, sizeof(int) * (size_t)(nnz > 0 ? nnz : 1), st));
@@ -469,15 +504,12 @@ static int run_wmerge(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, DevCsr
     MGCG_LAUNCH_CHECK();
     C->rows = A.rows; C->cols = B.cols;
     MGCG_CUDA(pool_alloc((void **)&C->rowptr, sizeof(int) * ((size_t)A.rows + 1), st));
-    size_t tb = 0;
-    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, C->rowptr, A.rows + 1, st));
-    void *tmp = nullptr;
-    MGCG_CUDA(pool_alloc(&tmp, tb, st));
-    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, C->rowptr, A.rows + 1, st));
     int nnz = 0;
-    MGCG_CUDA(cudaMemcpyAsync(&nnz, C->rowptr + A.rows, sizeof(int), cudaMemcpyDeviceToHost, st));
-    MGCG_CUDA(cudaStreamSynchronize(st));
-    pool_free(tmp, st); pool_free(cnt, st);
+    {
+        const int s_ = scan_counts_checked(c, cnt, A.rows, C->rowptr, &nnz, "spgemm");
+        pool_free(cnt, st);
+        if (s_ != MGCG_OK) { pool_free(C->rowptr, st); C->rowptr = nullptr; return s_; }
+    }
     C->nnz = nnz;
     MGCG_CUDA(pool_alloc((void **)&C->val, sizeof(double) * (size_t)(nnz > 0 ? nnz : 1), st));
     MGCG_CUDA(pool_alloc((void **)&C->col, sizeof(int) * (size_t)(nnz > 0 ? nnz : 1), st));
@@ -523,20 +555,19 @@ static int run_hash(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, int maxp
     // scan + max
     C->rows = A.rows; C->cols = B.cols;
     MGCG_CUDA(pool_alloc((void **)&C->rowptr, sizeof(int) * ((size_t)A.rows + 1), st));
-    size_t tb = 0, tb2 = 0;
+    size_t tb = 0;
     int *d_max = cnt + A.rows + 1;
-    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, C->rowptr, A.rows + 1, st));
-    MGCG_CUDA(cub::DeviceReduce::Max(nullptr, tb2, cnt, d_max, A.rows, st));
-    if (tb2 > tb) tb = tb2;
+    MGCG_CUDA(cub::DeviceReduce::Max(nullptr, tb, cnt, d_max, A.rows, st));
     void *tmp = nullptr;
     MGCG_CUDA(pool_alloc(&tmp, tb, st));
     MGCG_CUDA(cub::DeviceReduce::Max(tmp, tb, cnt, d_max, A.rows, st));
-    MGCG_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, C->rowptr, A.rows + 1, st));
     int h[2] = {0, 0};   // total nnz, max row length
-    MGCG_CUDA(cudaMemcpyAsync(&h[0], C->rowptr + A.rows, sizeof(int), cudaMemcpyDeviceToHost, st));
     MGCG_CUDA(cudaMemcpyAsync(&h[1], d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
-    MGCG_CUDA(cudaStreamSynchronize(st));
-    pool_free(tmp, st); pool_free(cnt, st);
+    {
+        const int s_ = scan_counts_checked(c, cnt, A.rows, C->rowptr, &h[0], "spgemm");   // synchronises
+        pool_free(tmp, st); pool_free(cnt, st);
+        if (s_ != MGCG_OK) { pool_free(C->rowptr, st); C->rowptr = nullptr; return s_; }
+    }
     C->nnz = h[0];
     MGCG_CUDA(pool_alloc((void **)&C->val, sizeof(double) * (size_t)h[0], st));
     MGCG_CUDA(pool_alloc((void **)&C->col, sizeof(int) * (size_t)h[0], st));
@@ -599,3 +630,27 @@ int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C, int col_shift)
 }
 
 }  // namespace mgcg
+
+// ---- test hook (tests/test_gpu_mg.py): run the 64-bit-checked count scan on `rows` rows of `per_row` entries each
+// without building a product of that size.  Returns the status; *nnz_out = total when it fits.
+namespace mgcg {
+__global__ void k_fill_int(int n, int v, int *a)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i <= n; i += gridDim.x * blockDim.x) a[i] = i < n ? v : 0;
+}
+}
+extern "C" int mgcg_test_scan_counts(mgcg_ctx *c, int rows, int per_row, long long *nnz_out)
+{
+    using namespace mgcg;
+    if (!c || rows <= 0 || per_row < 0) { set_error("mgcg_test_scan_counts: bad argument"); return MGCG_ERR_INVALID; }
+    MGCG_CUDA(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    int *cnt = nullptr, *rp = nullptr, nnz = 0;
+    MGCG_CUDA(pool_alloc((void **)&cnt, sizeof(int) * ((size_t)rows + 1), st));
+    MGCG_CUDA(pool_alloc((void **)&rp, sizeof(int) * ((size_t)rows + 1), st));
+    k_fill_int<<<(rows + 256) / 256, 256, 0, st>>>(rows, per_row, cnt);
+    const int s = scan_counts_checked(c, cnt, rows, rp, &nnz, "mgcg_test_scan_counts");
+    pool_free(cnt, st); pool_free(rp, st);
+    if (nnz_out) *nnz_out = (s == MGCG_OK) ? nnz : -1;
+    return s;
+}

@@ -53,3 +53,26 @@ def poisson3d27_varcoef(ctx, nx, ny=None, nz=None, zrange=None, seed=3, block=8,
     an = (C.c_double * 3)(*aniso)
     check(L.mgcg_generate_poisson3d27(ctx, nx, ny, nz, z0, z1, block, _p(kblk), an, _p(val), _p(rp), _p(col)), "mgcg_generate_poisson3d27")
     return val, rp, col
+
+
+def mps_particles(ctx, pos, re, shift_abs=0.0, max_per_row=160):
+    """Particle (MPS) pressure-Poisson matrix from positions `pos` (torch CUDA tensor n x 3, fp64, any order), assembled on the
+    device by a cell-list neighbour search (mgcg_mps_order / _count / _fill; semantics of oracle/mps_ref.c).
+    -> (elements, row_offsets, column_indeces, order, pos_sorted); order[k] = input index of the particle numbered k."""
+    import torch
+    L = _lib.lib()
+    pos = pos.contiguous()
+    n = pos.shape[0]
+    order = torch.empty(n, dtype=torch.int32, device=pos.device)
+    sorted_pos = torch.empty_like(pos)
+    cells = L.mgcg_mps_order(ctx, n, _p(pos), re, _p(order), _p(sorted_pos))
+    if cells <= 0:
+        raise _lib.MgcgError(int(-cells), "mgcg_mps_order")
+    rp = torch.empty(n + 1, dtype=torch.int32, device=pos.device)
+    nnz = L.mgcg_mps_count(ctx, n, _p(sorted_pos), re, max_per_row, _p(rp))
+    if nnz < 0:
+        raise _lib.MgcgError(int(-nnz), "mgcg_mps_count")
+    val = torch.empty(nnz, dtype=torch.float64, device=pos.device)
+    col = torch.empty(nnz, dtype=torch.int32, device=pos.device)
+    check(L.mgcg_mps_fill(ctx, n, _p(sorted_pos), re, shift_abs, _p(rp), _p(val), _p(col)), "mgcg_mps_fill")
+    return val, rp, col, order, sorted_pos

@@ -17,7 +17,7 @@
 extern "C" {
 #endif
 
-#define MGCG_VERSION 100
+#define MGCG_VERSION 200
 
 /* ---- status codes (the reference reports no errors at all: every CUDA/cuBLAS/cuSPARSE status is dropped,
  *      Runtime.cu:23,37, Mgcg.cu:17; only the C# side throws on Iteration > MaxIteration, ConjugateGradient.cs:70-74) */
@@ -42,6 +42,10 @@ enum { MGCG_PRECOND_NONE = 0, MGCG_PRECOND_MG = 1 };
 enum { MGCG_SMOOTHER_JACOBI = 0, MGCG_SMOOTHER_RBGS = 1 };
 enum { MGCG_SPMV_AUTO = 0, MGCG_SPMV_STREAM = 1, MGCG_SPMV_VECTOR = 2 };
 enum { MGCG_TRANSPORT_AUTO = 0, MGCG_TRANSPORT_NCCL = 1, MGCG_TRANSPORT_PEER = 2 };
+/* aggregation of the multigrid hierarchy: AUTO = geometric blocks when nx,ny,nz are given, else strength-of-connection filter +
+ * MIS-2 aggregates (caller-supplied CSR without a grid, e.g. particle matrices); BLOCKS = 8 consecutive rows when there is no
+ * grid (cells of cell-sorted particles); MIS2 = algebraic even when a grid hint is present */
+enum { MGCG_AGG_AUTO = 0, MGCG_AGG_BLOCKS = 1, MGCG_AGG_MIS2 = 2 };
 
 typedef struct mgcg_options {
     /* CG control — same meaning as the reference's ctor arguments (ConjugateGradient.cs:41-50) */
@@ -80,7 +84,10 @@ typedef struct mgcg_options {
     int    mg_tail_rows;             /* > 0: multigrid levels with at most this many rows (the coarse tail of the cycle) run as
                                         ONE persistent kernel with grid barriers between the steps.  Default 0 = off: measured
                                         no faster than graph-replayed launches on B200 (mg_tail.cu) */
-    int    reserved[2];
+    int    mg_aggregation;           /* MGCG_AGG_* */
+    int    reserved0;
+    double mg_strength_theta;        /* MIS-2: a_ij is a strong connection when |a_ij| >= theta * min(max_k|a_ik|, max_k|a_jk|); default 0.5 */
+    int    reserved[6];
 } mgcg_options;
 
 typedef struct mgcg_result {
@@ -150,6 +157,9 @@ int mgcg_mg_level_size(mgcg_ctx *c, int level, int *rows, int *nnz);
 int mgcg_mg_level_get(mgcg_ctx *c, int level, double *elements, int *row_offsets, int *column_indeces);
 /* copy the fine->coarse aggregate map of `level` (rows entries) */
 int mgcg_mg_level_aggregates(mgcg_ctx *c, int level, int *agg);
+/* test hook: the 64-bit-checked scan that sizes every level operator, on `rows` rows of `per_row` entries (no product is built);
+ * MGCG_ERR_UNSUPPORTED when the total does not fit the int32 index range of a level */
+int mgcg_test_scan_counts(mgcg_ctx *c, int rows, int per_row, long long *nnz_out);
 /* z = M r : one V-cycle applied to a device vector */
 int mgcg_mg_apply(mgcg_ctx *c, const double *d_r, double *d_z);
 
@@ -165,6 +175,16 @@ long long mgcg_generate_poisson3d27_nnz(int nx, int ny, int nz, int z0, int z1);
  * aniso3 = host array of the three axis weights */
 int mgcg_generate_poisson3d27(mgcg_ctx *c, int nx, int ny, int nz, int z0, int z1, int block, const double *d_kblk,
                               const double *aniso3, double *d_elements, int *d_row_offsets, int *d_column_indeces);
+
+/* ---- particle (MPS) pressure-Poisson matrix assembled in device memory by a cell-list neighbour search (the
+ * reference receives this matrix from its particle-method caller, <= 160 entries per row, MgcgMain.cs:20).  Semantics = oracle/mps_ref.c:
+ * cells of edge re, particles numbered in cell order, neighbours r < re, a_ij = -(re/r - 1), a_ii = sum_j w_ij + shift_abs, rows with
+ * the diagonal first and then ascending columns.  Three calls: order the particles, size the matrix, fill it.
+ * Negative return values of the two long long functions are -MGCG_ERR_*. */
+long long mgcg_mps_order(mgcg_ctx *c, int n, const double *d_pos /* n x 3 */, double re, int *d_order /* n */, double *d_pos_sorted /* n x 3 */);
+long long mgcg_mps_count(mgcg_ctx *c, int n, const double *d_pos_sorted, double re, int max_per_row, int *d_row_offsets /* n + 1 */);
+int mgcg_mps_fill(mgcg_ctx *c, int n, const double *d_pos_sorted, double re, double shift_abs, const int *d_row_offsets,
+                  double *d_elements, int *d_column_indeces);
 
 /* ---- row-block partition rule of the reference (bit-exact): ConjugateGradientParallelGpu.cs:271-277 */
 int mgcg_partition_offsets(int count, int device_count, int *offsets /* [device_count+1] */);

@@ -130,6 +130,126 @@ static double *dense_inverse(const csr_t *A)
     return M;
 }
 
+
+/* ---- strength-of-connection filter + MIS-2 aggregation for matrices without a grid hint (device: csrc/mg_aggregate.cu).
+ * Every step is a synchronous (Jacobi-style) sweep over the rows so that the sequential twin and the one-thread-per-row
+ * device kernels produce the same integers.
+ *   rowmax_i   = max_{col_k != i} |a_ik|
+ *   strong(i,k): col_k != i, a_ik != 0, |a_ik| >= theta * min(rowmax_i, rowmax_col_k)      (symmetric for symmetric A)
+ *   filtered matrix A_F: row i = [ (i, d_F) , the strong entries in storage order ], d_F = (sum of the diagonal entries)
+ *                + (the weak entries, added in storage order) when that stays positive, else the diagonal alone.
+ *   MIS-2 of the strong graph by rounds: T = (state, hash(i), i) packed in 64 bits; two max-propagation hops; an
+ *                undecided node that is the maximum of its 2-hop neighbourhood joins the set, one that sees a member
+ *                leaves it.   Roots are numbered in index order; two passes attach every other node to the aggregate of
+ *                the strong neighbour with the largest |a_ij| (first in storage order on ties); leftovers are singletons. */
+static uint32_t mix32(uint32_t x)
+{
+    x *= 0x9E3779B1u; x ^= x >> 16; x *= 0x85EBCA6Bu; x ^= x >> 13; x *= 0xC2B2AE35u; x ^= x >> 16;
+    return x;
+}
+
+static csr_t strength_filter(const csr_t *A, double theta, double **dinvF_out)
+{
+    int n = A->rows;
+    double *rowmax = (double *)calloc((size_t)(n > 0 ? n : 1), sizeof(double));
+    for (int i = 0; i < n; i++) {
+        double m = 0.0;
+        for (int k = A->rowptr[i]; k < A->rowptr[i + 1]; k++)
+            if (A->col[k] != i) { double a = fabs(A->val[k]); if (a > m) m = a; }
+        rowmax[i] = m;
+    }
+    csr_t F; F.rows = n; F.cols = n;
+    F.rowptr = (int *)calloc((size_t)n + 1, sizeof(int));
+    for (int i = 0; i < n; i++) {
+        int cnt = 1;
+        for (int k = A->rowptr[i]; k < A->rowptr[i + 1]; k++) {
+            int j = A->col[k];
+            if (j == i) continue;
+            double a = A->val[k], mm = rowmax[i] < rowmax[j] ? rowmax[i] : rowmax[j];
+            if (a != 0.0 && fabs(a) >= theta * mm) cnt++;
+        }
+        F.rowptr[i + 1] = F.rowptr[i] + cnt;
+    }
+    F.nnz = F.rowptr[n];
+    F.val = (double *)malloc(sizeof(double) * (size_t)(F.nnz > 0 ? F.nnz : 1));
+    F.col = (int *)malloc(sizeof(int) * (size_t)(F.nnz > 0 ? F.nnz : 1));
+    double *dinvF = (double *)malloc(sizeof(double) * (size_t)(n > 0 ? n : 1));
+    for (int i = 0; i < n; i++) {
+        int o = F.rowptr[i] + 1;
+        double d = 0.0;
+        for (int k = A->rowptr[i]; k < A->rowptr[i + 1]; k++) if (A->col[k] == i) d = d + A->val[k];
+        double l = d;
+        for (int k = A->rowptr[i]; k < A->rowptr[i + 1]; k++) {
+            int j = A->col[k];
+            if (j == i) continue;
+            double a = A->val[k], mm = rowmax[i] < rowmax[j] ? rowmax[i] : rowmax[j];
+            if (a != 0.0 && fabs(a) >= theta * mm) { F.val[o] = a; F.col[o] = j; o++; }
+            else l = l + a;
+        }
+        double dF = (l > 0.0) ? l : d;
+        if (dF == 0.0) dF = 1.0;
+        F.val[F.rowptr[i]] = dF; F.col[F.rowptr[i]] = i;
+        dinvF[i] = 1.0 / dF;
+    }
+    free(rowmax);
+    *dinvF_out = dinvF;
+    return F;
+}
+
+/* F: filtered matrix (diagonal first).  Returns the number of aggregates; agg[i] filled. */
+static int mis2_aggregate(const csr_t *F, int *agg)
+{
+    int n = F->rows;
+    size_t nn = (size_t)(n > 0 ? n : 1);
+    uint64_t *T0 = (uint64_t *)malloc(8 * nn), *T1 = (uint64_t *)malloc(8 * nn), *T2 = (uint64_t *)malloc(8 * nn);
+    unsigned char *state = (unsigned char *)malloc(nn);
+    for (int i = 0; i < n; i++) state[i] = 1;
+    for (int round = 0; round < 256; round++) {
+        int undecided = 0;
+        for (int i = 0; i < n; i++) {
+            T0[i] = ((uint64_t)state[i] << 62) | ((uint64_t)(mix32((uint32_t)i) >> 2) << 32) | (uint32_t)i;
+            undecided += state[i] == 1;
+        }
+        if (!undecided) break;
+        for (int i = 0; i < n; i++) {
+            uint64_t m = T0[i];
+            for (int k = F->rowptr[i] + 1; k < F->rowptr[i + 1]; k++) if (T0[F->col[k]] > m) m = T0[F->col[k]];
+            T1[i] = m;
+        }
+        for (int i = 0; i < n; i++) {
+            uint64_t m = T1[i];
+            for (int k = F->rowptr[i] + 1; k < F->rowptr[i + 1]; k++) if (T1[F->col[k]] > m) m = T1[F->col[k]];
+            T2[i] = m;
+        }
+        for (int i = 0; i < n; i++)
+            if (state[i] == 1) {
+                if (T2[i] == T0[i]) state[i] = 2;
+                else if ((T2[i] >> 62) == 2) state[i] = 0;
+            }
+    }
+    int nroots = 0;
+    for (int i = 0; i < n; i++) agg[i] = (state[i] == 2) ? nroots++ : -1;
+    int *src = (int *)malloc(sizeof(int) * nn);
+    for (int pass = 0; pass < 2; pass++) {
+        memcpy(src, agg, sizeof(int) * nn);
+        for (int i = 0; i < n; i++) {
+            if (src[i] >= 0) continue;
+            double best = -1.0; int pick = -1;
+            for (int k = F->rowptr[i] + 1; k < F->rowptr[i + 1]; k++) {
+                int j = F->col[k];
+                if (src[j] < 0) continue;
+                double a = fabs(F->val[k]);
+                if (a > best) { best = a; pick = src[j]; }
+            }
+            agg[i] = pick;
+        }
+    }
+    int nc = nroots;
+    for (int i = 0; i < n; i++) if (agg[i] < 0) agg[i] = nc++;
+    free(src); free(state); free(T0); free(T1); free(T2);
+    return nc;
+}
+
 static void level_vectors(level_t *L)
 {
     size_t n = (size_t)L->A.rows;
@@ -145,7 +265,7 @@ static void level_vectors(level_t *L)
 
 mg_ref_t *mg_ref_build(int n, int nnz, const double *val, const int *rowptr, const int *col,
                        int nx, int ny, int nz, int max_levels, int coarse_size, int smoothed, double prolong_omega,
-                       int smoothed_levels, int agg_size, int agg_size_coarse)
+                       int smoothed_levels, int agg_size, int agg_size_coarse, int aggregation, double theta)
 {
     mg_ref_t *H = (mg_ref_t *)calloc(1, sizeof(mg_ref_t));
     if (max_levels <= 0) max_levels = 12;
@@ -164,7 +284,7 @@ mg_ref_t *mg_ref_build(int n, int nnz, const double *val, const int *rowptr, con
         if (m <= coarse_size || l + 1 >= max_levels) break;
         int nc, cd[3] = {0, 0, 0};
         L->agg = (int *)malloc(sizeof(int) * (size_t)m);
-        if (L->dims[0] > 0) {
+        if (L->dims[0] > 0 && aggregation != 2) {
             int a = (l == 0 || agg_size_coarse <= 0) ? agg_size : agg_size_coarse;
             if (a < 2) a = 2;
             cd[0] = (L->dims[0] + a - 1) / a; cd[1] = (L->dims[1] + a - 1) / a; cd[2] = (L->dims[2] + a - 1) / a;
@@ -173,27 +293,41 @@ mg_ref_t *mg_ref_build(int n, int nnz, const double *val, const int *rowptr, con
                 int x = i % L->dims[0], y = (i / L->dims[0]) % L->dims[1], z = i / (L->dims[0] * L->dims[1]);
                 L->agg[i] = (x / a) + cd[0] * ((y / a) + cd[1] * (z / a));
             }
-        } else {
+        } else if (aggregation == 1) {
             nc = (m + 7) / 8;
             for (int i = 0; i < m; i++) L->agg[i] = i / 8;
+        } else {
+            nc = -1;   /* MIS-2 below */
         }
-        if (nc >= m) break;
-        /* prolongator */
+        /* aggregation: 0 auto (geometric with a hint, MIS-2 without), 1 blocks of 8 rows without a hint, 2 MIS-2 always */
+        csr_t F; memset(&F, 0, sizeof(F));
+        double *dinvF = NULL;
+        const int filtered = (aggregation == 2) || (L->dims[0] <= 0 && aggregation != 1);
+        if (filtered) {
+            F = strength_filter(&L->A, theta, &dinvF);
+            nc = mis2_aggregate(&F, L->agg);
+            cd[0] = cd[1] = cd[2] = 0;
+        }
+        if (nc >= m) { csr_free(&F); free(dinvF); break; }
+        /* prolongator: smoothed with the level operator, or with its strength-filtered version under MIS-2 */
+        const csr_t *Asm = filtered ? &F : &L->A;
+        const double *dsm = filtered ? dinvF : L->dinv;
         builder_t bp; b_init(&bp, m, nc);
         size_t cap = 256; ent_t *e = (ent_t *)malloc(cap * sizeof(ent_t));
         for (int i = 0; i < m; i++) {
             int cnt = 0;
             e[cnt].col = L->agg[i]; e[cnt].v = 1.0; cnt++;
             if (smoothed && (smoothed_levels <= 0 || l < smoothed_levels)) {
-                double f = -(prolong_omega * L->dinv[i]);
-                for (int k = L->A.rowptr[i]; k < L->A.rowptr[i + 1]; k++) {
+                double f = -(prolong_omega * dsm[i]);
+                for (int k = Asm->rowptr[i]; k < Asm->rowptr[i + 1]; k++) {
                     if ((size_t)cnt + 1 > cap) { cap *= 2; e = (ent_t *)realloc(e, cap * sizeof(ent_t)); }
-                    e[cnt].col = L->agg[L->A.col[k]]; e[cnt].v = f * L->A.val[k]; cnt++;
+                    e[cnt].col = L->agg[Asm->col[k]]; e[cnt].v = f * Asm->val[k]; cnt++;
                 }
             }
             b_row(&bp, i, e, cnt);
         }
         free(e);
+        csr_free(&F); free(dinvF);
         L->P = bp.m;
         L->R = transpose(&L->P);
         csr_t AP = spgemm(&L->A, &L->P);

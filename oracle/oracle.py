@@ -191,10 +191,10 @@ def gen_banded_sin(n, max_nonzero=160):
 # ---- multigrid CPU twin (oracle/mg_ref.c; parity unpinned: the reference has no multigrid) ------------------
 class MgRef:
     def __init__(self, val, rowptr, col, nx=0, ny=0, nz=0, max_levels=12, coarse_size=512, smoothed=1, prolong_omega=2.0 / 3.0,
-                 smoothed_levels=0, agg_size=3, agg_size_coarse=2):
+                 smoothed_levels=0, agg_size=3, agg_size_coarse=2, aggregation=0, theta=0.5):
         L = lib()
         L.mg_ref_build.restype = C.c_void_p
-        L.mg_ref_build.argtypes = [C.c_int, C.c_int, c_dp, c_ip, c_ip, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int]
+        L.mg_ref_build.argtypes = [C.c_int, C.c_int, c_dp, c_ip, c_ip, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double]
         L.mg_ref_free.argtypes = [C.c_void_p]
         L.mg_ref_levels.argtypes = [C.c_void_p]
         L.mg_ref_level_size.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -206,7 +206,7 @@ class MgRef:
         self._keep = (np.ascontiguousarray(val, dtype=np.float64), np.ascontiguousarray(rowptr, dtype=np.int32),
                       np.ascontiguousarray(col, dtype=np.int32))
         self.n = len(rowptr) - 1
-        self.h = L.mg_ref_build(self.n, len(val), *self._keep, nx, ny, nz, max_levels, coarse_size, smoothed, prolong_omega, smoothed_levels, agg_size, agg_size_coarse)
+        self.h = L.mg_ref_build(self.n, len(val), *self._keep, nx, ny, nz, max_levels, coarse_size, smoothed, prolong_omega, smoothed_levels, agg_size, agg_size_coarse, aggregation, theta)
 
     def levels(self):
         return lib().mg_ref_levels(self.h)

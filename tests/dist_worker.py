@@ -44,6 +44,8 @@ def main():
     kw = dict(cfg.get("options", {}))
     if kw.get("precond", 0) == 1 and cfg.get("hint", True):
         kw.update(nx=n, ny=n, nz=n)
+    elif kw.get("precond", 0) == 1:
+        kw.update(mg_aggregation=1)     # without a grid the sharded hierarchy aggregates by blocks of 8 rows (csrc/dist.cu agg_of)
     o = S.default_options(norm=2, tolerance=1e-8, max_iteration=2000, **kw)
     m.setup(N, r0, tv, tr, tc, o)
     res = m.solve(tb, tx)

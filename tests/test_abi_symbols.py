@@ -52,7 +52,7 @@ def test_format_symbols_exported(L):
 
 def test_version_and_partition_rule(L):
     import numpy as np
-    assert L.mgcg_version() == 100
+    assert L.mgcg_version() == 200
     off = np.zeros(5, dtype=np.int32)
     assert L.mgcg_partition_offsets(207402, 4, off.ctypes.data_as(ctypes.c_void_p)) == 0
     assert off.tolist() == [0, 51850, 103700, 155550, 207402]   # ConjugateGradientParallelGpu.cs:271-277

@@ -57,8 +57,8 @@ def test_hierarchy_no_hint_blocks(oracle, gen):
     import torch
     from conjugategradient_b200 import solver as S
     v, rp, c = gen.mps_particles(12)
-    m = _setup(S, torch, v, rp, c, mg_coarse_size=64)
-    H = oracle.MgRef(v, rp, c, coarse_size=64)
+    m = _setup(S, torch, v, rp, c, mg_coarse_size=64, mg_aggregation=1)      # MGCG_AGG_BLOCKS: 8 consecutive rows
+    H = oracle.MgRef(v, rp, c, coarse_size=64, aggregation=1)
     assert m.levels() == H.levels() >= 2
     assert np.array_equal(m.aggregates(0), np.arange(12 ** 3) // 8)
     for l in range(m.levels()):
@@ -165,3 +165,99 @@ def test_compat_solve_with_preconditioner_switch(oracle, gen):
     cg.close()
     assert cg.Iteration < plain_it / 3
     assert np.abs(cg.x - x_plain).max() / np.abs(x_plain).max() < 1e-6
+
+
+def _random_spd(n, per_row, seed):
+    """Irregular symmetric M-matrix (random graph, random weights over three decades), diagonal first, columns ascending."""
+    import scipy.sparse as sp
+    rng = np.random.default_rng(seed)
+    i = rng.integers(0, n, n * per_row // 2); j = rng.integers(0, n, n * per_row // 2)
+    keep = i != j
+    i, j = i[keep], j[keep]
+    w = 10.0 ** rng.uniform(-2, 1, len(i))
+    W = sp.coo_matrix((w, (i, j)), shape=(n, n)).tocsr()
+    W = (W + W.T).tocsr(); W.sum_duplicates(); W.sort_indices()
+    d = np.asarray(W.sum(axis=1)).ravel() + 0.01
+    cnt = np.diff(W.indptr) + 1
+    rp = np.zeros(n + 1, dtype=np.int64); np.cumsum(cnt, out=rp[1:])
+    val = np.empty(rp[-1]); col = np.empty(rp[-1], dtype=np.int32)
+    val[rp[:-1]] = d; col[rp[:-1]] = np.arange(n)
+    off = np.ones(rp[-1], dtype=bool); off[rp[:-1]] = False
+    val[off] = -W.data; col[off] = W.indices
+    return val, rp.astype(np.int32), col
+
+
+MIS2_CASES = [("mps12_r21", 0.5), ("mps12_r21", 0.25), ("mps10_r31", 0.5), ("p3d_forced", 0.5), ("p27_forced", 0.25), ("random", 0.5)]
+
+
+@pytest.mark.parametrize("name,theta", MIS2_CASES)
+def test_hierarchy_mis2_bit_exact(oracle, gen, name, theta):
+    """Strength filter + MIS-2 aggregation on the device: aggregate maps (integers) and every level operator equal the CPU
+    twin's bit for bit — irregular particle matrices (38 and 124 entries per row), grids with the hint ignored, a random graph."""
+    import torch
+    from conjugategradient_b200 import solver as S
+    dims, agg = (0, 0, 0), 0
+    if name == "mps12_r21":
+        v, rp, c = gen.mps_particles(12, re_over_l0=2.1)
+    elif name == "mps10_r31":
+        v, rp, c = gen.mps_particles(10, re_over_l0=3.1)
+    elif name == "p3d_forced":
+        dims, agg = (14, 11, 9), 2; v, rp, c = gen.poisson3d7(*dims)
+    elif name == "p27_forced":
+        dims, agg = (12, 12, 12), 2; v, rp, c = gen.poisson3d27_varcoef(12)
+    else:
+        v, rp, c = _random_spd(3000, 12, 5)
+    m = _setup(S, torch, v, rp, c, nx=dims[0], ny=dims[1], nz=dims[2], mg_coarse_size=40, mg_aggregation=agg, mg_strength_theta=theta)
+    H = oracle.MgRef(v, rp, c, *dims, coarse_size=40, aggregation=agg, theta=theta)
+    assert m.levels() == H.levels() >= 2
+    for l in range(m.levels()):
+        if l + 1 < m.levels():
+            ga, ha = m.aggregates(l), H.aggregates(l)
+            assert np.array_equal(ga, ha), f"level {l} aggregates differ at {np.flatnonzero(ga != ha)[:5]}"
+            sizes = np.bincount(ga)
+            assert sizes.min() >= 1 and ga.max() + 1 == len(sizes)
+        gv, gr, gc = m.level(l)
+        hv, hr, hc = H.level(l)
+        assert np.array_equal(gr, hr) and np.array_equal(gc, hc), f"level {l} structure"
+        assert np.array_equal(gv, hv), f"level {l} values: max diff {np.abs(gv - hv).max()}"
+    m.close(); H.close()
+
+
+@pytest.mark.parametrize("re,theta", [(2.1, 0.5), (3.1, 0.5)])
+def test_mgcg_mis2_particles(oracle, gen, re, theta):
+    """MGCG with algebraic aggregation on a particle matrix: iterations within +-1 of the twin, solution to 1e-10, far fewer
+    iterations than plain CG, operator complexity bounded."""
+    import torch
+    from conjugategradient_b200 import solver as S
+    v, rp, c = gen.mps_particles(20, re_over_l0=re)
+    n = len(rp) - 1
+    b = gen.rhs_uniform(n, 2)
+    m = _setup(S, torch, v, rp, c, norm=2, tolerance=1e-8, max_iteration=500, mg_strength_theta=theta)
+    tb, tx = torch.as_tensor(b).cuda(), torch.zeros(n, dtype=torch.float64, device="cuda")
+    res = m.solve(tb, tx)
+    H = oracle.MgRef(v, rp, c, theta=theta)
+    xt, itt, _, st = H.pcg(b, tol=1e-8, norm=oracle.NORM_REL_L2, max_iteration=500)
+    assert st == 0 and abs(res.iteration - itt) <= 1, (res.iteration, itt)
+    x = tx.cpu().numpy()
+    if res.iteration == itt:
+        assert np.abs(x - xt).max() / np.abs(xt).max() <= 1e-10
+    xo, ito, _, _ = oracle.cg_solve(v, rp, c, b, tol=1e-8, norm=oracle.NORM_REL_L2)
+    assert res.iteration * 3 < ito
+    assert res.operator_complexity < 1.3
+    m.close(); H.close()
+
+
+def test_level_size_overflow_is_refused():
+    """the entry count of a level operator is summed in 64 bits; a product past 2^31 - 1 entries is refused instead
+    of wrapping the int32 scan (2^20 rows x 4096 = 2^32 entries; nothing of that size is allocated)."""
+    from conjugategradient_b200 import _lib
+    import ctypes as C
+    L = _lib.lib()
+    ctx = L.mgcg_create(0)
+    nnz = C.c_longlong(0)
+    assert L.mgcg_test_scan_counts(ctx, 1 << 20, 1000, C.byref(nnz)) == _lib.OK and nnz.value == 1000 << 20
+    assert L.mgcg_test_scan_counts(ctx, 1 << 20, 2047, C.byref(nnz)) == _lib.OK and nnz.value == 2047 << 20
+    assert L.mgcg_test_scan_counts(ctx, 1 << 20, 2048, C.byref(nnz)) == _lib.ERR_UNSUPPORTED
+    assert L.mgcg_test_scan_counts(ctx, 1 << 20, 4096, C.byref(nnz)) == _lib.ERR_UNSUPPORTED      # wraps to 0 in 32 bits
+    assert b"int32" in L.mgcg_last_error()
+    L.mgcg_destroy(ctx)
