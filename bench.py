@@ -1,18 +1,29 @@
 #!/usr/bin/env python
-"""bench.py — BASELINE.json's metric on its own workload: MGCG time-to-1e-8 (+ SpMV HBM GB/s) on the 3-D 7-point Poisson
-256^3 system, fp64, at 1/2/4/8 B200 (row-block sharded for N > 1).
+"""bench.py — BASELINE.json's metric on its own workloads: MGCG time-to-1e-8 (+ SpMV HBM GB/s), fp64.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--size 256]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c4|c2|c3|c5] [--size n] [--re 2.1]
 
+  --config c4 (default): 3-D 7-point Poisson 256^3 at 1/2/4/8 B200 (row-block sharded for N > 1) — the configuration the metric
+                         is quoted on.  c2: the same at 128^3, one GPU.  c3: particle (MPS) pressure matrix, 160^3 = 4 096 000
+                         particles, neighbour radius --re (2.1 or 3.1 lattice spacings), assembled on the device, no grid given to
+                         the solver (strength filter + MIS-2 aggregation), one GPU.  c5: 27-point variable-coefficient 512^3,
+                         sharded (needs N >= 2: the global matrix has 3.6e9 non-zeros), assembled per shard on the device.
 A "step" is ONE complete solve of the system to 1e-8 relative residual (x0 = 0).  One JSON line is printed by rank 0:
   value / ms_per_step : solve time with the matrix, the hierarchy and b resident in HBM (CUDA events, max over ranks)
-  e2e                 : the same solve through the host-pointer C-ABI call (mgcg_solve_host): pinned host CSR + b in,
-                        x out, upload + hierarchy build + solve + download all inside the timed region
+  e2e                 : the same solve through ONE host-pointer C-ABI call (mgcg_solve_host / mgcg_solve_host_dist): pinned host
+                        CSR + b in, x out; upload + hierarchy build + solve + download inside the timed region.  e2e_cold is the
+                        first such call of the process (allocations, peer mappings, graph instantiation included).
   roofline            : the fine-level SpMV(+p.Ap) kernel, algorithmic bytes 12*nnz + 20*N per launch, timed live with CUDA
                         events inside a solve, against MEASURED_PEAKS.json's HBM copy bandwidth
-  cpu_baseline        : the reference's CPU path (oracle port of ConjugateGradientCpu.Solve: plain, unpreconditioned,
-                        single-threaded like the reference runs it) on a bounded sample of the same system
-`--impl reference` times that CPU path alone (the reference has no multigrid and cannot be compiled here).
+  parity              : x of the timed solve against a 1e-12 solve of the same system on the same device (the CPU twin at 256^3
+                        takes minutes: it is compared at 128^3 in tests/test_gpu_parity_c2.py and once at 256^3 by
+                        tools/parity_c4.py -> profiles/); the plain-CG iteration count measured on the GPU; N > 1: the sharded
+                        x against the single-GPU x of the same system (dist_x_rel_err)
+  cpu_baseline        : the reference's CPU path (oracle port of ConjugateGradientCpu.Solve: plain, unpreconditioned) on the host
+                        cores: one COMPLETE solve when that fits the time budget, else a bounded number of iterations scaled to
+                        the iteration count MEASURED by the GPU plain-CG run of the same system in this run
+`--impl reference` times that CPU path alone (the reference has no multigrid and cannot be compiled here): the
+first warm-up step is one complete CPU solve (which measures the iteration count), every other step a bounded sample.
 """
 import argparse
 import ctypes as C
@@ -29,8 +40,9 @@ if ROOT not in sys.path:
 
 import numpy as np  # noqa: E402
 
-METRIC = "mgcg_time_to_1e-8_poisson3d7"
 TOL = 1e-8
+NCU_FULL = os.path.join("profiles", "r02_ncu_full_kernels_256.csv")       # refreshed capture of the shipped kernels
+NCU_FULL_OLD = os.path.join("profiles", "r01_ncu_full_spmv_tma_256.csv")
 
 
 def parse():
@@ -39,17 +51,42 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--size", type=int, default=256, help="grid points per side (BASELINE: 256)")
-    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the bounded CPU sample")
+    ap.add_argument("--config", default="c4", choices=["c2", "c3", "c4", "c5"])
+    ap.add_argument("--size", type=int, default=0, help="grid points / particles per side (default: the config's own: 128 / 160 / 256 / 512)")
+    ap.add_argument("--re", type=float, default=2.1, help="c3: neighbour radius in lattice spacings (2.1: ~38 per row, 3.1: ~123 per row)")
+    ap.add_argument("--theta", type=float, default=0.0, help="c3: strength threshold of the MIS-2 aggregation (0 = library default 0.5)")
+    ap.add_argument("--cpu-seconds", type=float, default=30.0, help="budget of the CPU baseline leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--device-gen", action="store_true", help="assemble the matrix on the device (mgcg_generate_poisson3d7); implied for --size > 256, "
-                    "where the e2e and CPU legs (which need the host copy) are skipped")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity block (tight solve, plain-CG count, sharded-vs-single)")
+    ap.add_argument("--device-gen", action="store_true", help="assemble the matrix on the device; implied for c3, c5 and --size > 256")
     ap.add_argument("--graph", type=int, default=-1, help="use_graph option: 0 eager, 1 one iteration per graph launch, 2 device-side while loop "
                     "(library default); profilers want 0")
     ap.add_argument("--transport", type=int, default=0, help="sharded arm: 0 auto (peer memory on one node), 1 NCCL, 2 peer memory")
     ap.add_argument("--replicate-below", type=int, default=0, help="sharded arm: replicate multigrid levels smaller than this (0 = library default)")
-    return ap.parse_args()
+    ap.add_argument("--smoother", type=int, default=-1, help="multigrid smoother (-1 = library default)")
+    ap.add_argument("--opt", action="append", default=[], help="extra mgcg_options field, name=value (repeatable)")
+    a = ap.parse_args()
+    if a.size <= 0:
+        a.size = {"c2": 128, "c3": 160, "c4": 256, "c5": 512}[a.config]
+    return a
+
+
+def metric_name(cfg):
+    return {"c2": "mgcg_time_to_1e-8_poisson3d7", "c4": "mgcg_time_to_1e-8_poisson3d7", "c3": "mgcg_time_to_1e-8_mps_particles",
+            "c5": "mgcg_time_to_1e-8_poisson3d27_varcoef"}[cfg]
+
+
+def workload_text(args):
+    n = args.size
+    if args.config in ("c2", "c4"):
+        return f"3-D 7-point Poisson {n}^3 MGCG, fp64, b~U(-1,1) seed 0, x0=0, relative residual 1e-8"
+    if args.config == "c3":
+        return (f"MPS particle pressure Poisson, {n}^3 = {n ** 3} particles on a unit lattice jittered by U(-0.2,0.2) (seed 1), neighbours r < "
+                f"{args.re} l0, a_ij = -(re/r - 1), diagonal = sum + 1e-3 * mean diagonal; cell-ordered; MGCG fp64, b~U(-1,1) seed 2, x0=0, "
+                "relative residual 1e-8")
+    return (f"3-D 27-point variable-coefficient Poisson {n}^3 (k = 10^U(-3,3) on 8^3 blocks, seed 3, anisotropy 1:1:0.01) MGCG, fp64, "
+            "b~U(-1,1) seed 0, x0=0, relative residual 1e-8")
 
 
 def measured_peak():
@@ -62,24 +99,28 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic(kernel_substr, n_side):
-    """DRAM bytes (read + write) of one launch of the dominant kernel from the committed `ncu --set full` capture of this
-    workload (profiles/r01_ncu_full_spmv_tma_256.csv, taken at 256^3); None for other sizes or if the file is absent."""
+def ncu_traffic(kernel_substr, args):
+    """DRAM bytes (read + write) of one launch of the dominant kernel from the committed `ncu --set full` capture of the c4
+    workload; None for other workloads or if no capture is committed."""
     import csv
-    p = os.path.join(ROOT, "profiles", "r01_ncu_full_spmv_tma_256.csv")
-    if n_side != 256 or not os.path.exists(p):
-        return None
-    try:
-        rows = list(csv.reader(open(p)))
-        hdr, units = rows[0], rows[1]
-        ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
-        scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
-        for r in rows[2:]:
-            if kernel_substr in r[0]:
-                return float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]]
-    except Exception:
-        return None
-    return None
+    if args.config != "c4" or args.size != 256:
+        return None, None
+    for rel in (NCU_FULL, NCU_FULL_OLD):
+        p = os.path.join(ROOT, rel)
+        if not os.path.exists(p):
+            continue
+        try:
+            rows = list(csv.reader(open(p)))
+            hdr, units = rows[0], rows[1]
+            ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+            ik = hdr.index("Kernel Name") if "Kernel Name" in hdr else 0
+            scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
+            for r in rows[2:]:
+                if kernel_substr in r[ik]:
+                    return float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]], rel
+        except Exception:
+            continue
+    return None, None
 
 
 class ClockSampler:
@@ -131,29 +172,91 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------------------------------
-# workload (synthetic): 3-D 7-point Poisson, diag 6 / off -1, diagonal stored first, b ~ U(-1,1) seed 0
-def make_problem(n_side):
+# workloads (synthetic)
+def mps_positions(n_side, jitter=0.2, seed=1):
+    rng = np.random.default_rng(seed)
+    g = np.arange(n_side, dtype=np.float64)
+    zz, yy, xx = np.meshgrid(g, g, g, indexing="ij")
+    pos = np.stack([xx.ravel(), yy.ravel(), zz.ravel()], axis=1)
+    pos += rng.uniform(-jitter, jitter, size=pos.shape)
+    return pos
+
+
+def host_problem(args):
+    """(val, rowptr, col, b) as numpy arrays — only for workloads whose host copy is cheap to build (7-point grids <= 256^3)."""
     from conjugategradient_b200 import generators as g
-    val, rp, col = g.poisson3d7(n_side)
-    b = g.rhs_uniform(n_side ** 3, 0)
-    return val, rp, col, b
+    n = args.size
+    assert args.config in ("c2", "c4")
+    val, rp, col = g.poisson3d7(n)
+    return val, rp, col, g.rhs_uniform(n ** 3, 0)
 
 
-# Iterations the reference's (unpreconditioned) CG needs for ||r||/||r0|| < 1e-8 on this workload.  Measured with this
-# repo's GPU plain-CG path, whose iteration count is parity-tested (+-1) against the oracle (tests/test_gpu_cg.py); the
-# CPU legs time a bounded number of iterations and scale to this count ("time a fixed number of
-# iterations and extrapolate, stated as such").
-PLAIN_CG_ITERATIONS = {32: 111, 48: 177, 64: 230, 128: 445}
+def device_problem(args, m, dev, zrange=None):
+    """Assemble the workload (or the z-slab `zrange` of it) in device memory.  -> (tv, tr, tc, tb_full_or_local, info)."""
+    import torch
+    from conjugategradient_b200 import device_generators as dg
+    from conjugategradient_b200 import generators as g
+    n = args.size
+    if args.config in ("c2", "c4"):
+        tv, tr, tc = dg.poisson3d7(m.ctx, n, zrange=zrange, device=dev)
+        b = g.rhs_uniform(n ** 3, 0)
+    elif args.config == "c5":
+        tv, tr, tc = dg.poisson3d27_varcoef(m.ctx, n, zrange=zrange, device=dev)
+        b = g.rhs_uniform(n ** 3, 0)
+    else:
+        assert zrange is None
+        pos = torch.from_numpy(mps_positions(n)).to(dev)
+        t0 = time.perf_counter()
+        try:       # the reference's container holds at most 160 entries per row (MgcgMain.cs:20)
+            tv, tr, tc, order, _ = dg.mps_particles(m.ctx, pos, args.re, shift_abs=0.0, max_per_row=160)
+            device_problem.row_cap = 160
+        except Exception:
+            tv, tr, tc, order, _ = dg.mps_particles(m.ctx, pos, args.re, shift_abs=0.0, max_per_row=1 << 20)
+            device_problem.row_cap = None
+        diag = tv[tr[:-1].long()]
+        tv[tr[:-1].long()] = diag + 1e-3 * float(diag.mean())          # the stand-in for the free-surface Dirichlet rows (SURVEY §8d)
+        torch.cuda.synchronize()
+        device_problem.assembly_ms = (time.perf_counter() - t0) * 1e3
+        del pos, order, diag
+        b = g.rhs_uniform(n ** 3, 2)
+    if zrange is not None:
+        r0, r1 = zrange[0] * n * n, zrange[1] * n * n
+        b = b[r0:r1].copy()
+    return tv, tr, tc, torch.from_numpy(b).to(dev)
 
 
-def plain_cg_iterations(n_side):
-    if n_side in PLAIN_CG_ITERATIONS:
-        return PLAIN_CG_ITERATIONS[n_side], "table"
-    return int(round(3.48 * n_side)), "estimate 3.48*n (fit to 64/128)"
+device_problem.assembly_ms = None
+device_problem.row_cap = None
 
 
-def cpu_sample(problem, n_side, iters, threads):
-    """Run `iters` iterations of the reference CPU CG (oracle port) and return seconds per iteration."""
+def solver_options(args, S, **extra):
+    n = args.size
+    kw = dict(precond=1, norm=2, tolerance=TOL, max_iteration=5000)
+    if args.config != "c3":
+        kw.update(nx=n, ny=n, nz=n)
+    elif args.theta > 0:
+        kw.update(mg_strength_theta=args.theta)
+    if args.graph >= 0:
+        kw["use_graph"] = args.graph
+    if args.smoother >= 0:
+        kw["mg_smoother"] = args.smoother
+    for kv in args.opt:
+        k, v = kv.split("=")
+        kw[k] = float(v) if ("." in v or "e" in v.lower()) else int(v)
+    kw.update(extra)
+    return S.default_options(**kw)
+
+
+def precond_text(args):
+    if args.config == "c3":
+        return "smoothed aggregation on strength-filtered MIS-2 aggregates (no grid given), V(1,1), weighted Jacobi 0.85, built on device"
+    return "smoothed-aggregation V(1,1) on geometric aggregates (grid hint), weighted Jacobi 0.85, built on device"
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# CPU legs (the only places that execute oracle/)
+def cpu_sample(problem, iters, threads):
+    """Run `iters` iterations of the reference CPU CG (oracle port); -> (seconds per iteration, iterations done)."""
     from oracle import oracle as o
     val, rp, col, b = problem
     t0 = time.perf_counter()
@@ -166,54 +269,84 @@ def cpu_sample(problem, n_side, iters, threads):
     return dt / done, done
 
 
-def cpu_baseline_leg(problem, n_side, budget_s):
-    """cpu_baseline object: the reference's CPU path, all host cores, bounded sample, scaled to time-to-1e-8."""
+def cpu_full_solve(problem, threads):
+    """One COMPLETE solve to 1e-8 relative residual with the reference's CPU CG; -> (seconds, iterations performed, status)."""
+    from oracle import oracle as o
+    val, rp, col, b = problem
+    t0 = time.perf_counter()
+    _, it, _, st = o.cg_solve_mt(val, rp, col, b, tol=TOL, norm=o.NORM_REL_L2, threads=threads)
+    return time.perf_counter() - t0, it + 1, st
+
+
+def cpu_baseline_leg(problem, label, budget_s, gpu_plain_iterations):
+    """cpu_baseline object.  A complete CPU solve when it fits the budget (nothing extrapolated); else a bounded sample scaled
+    to the plain-CG iteration count measured on the GPU in this run."""
     from oracle import oracle as o
     cores = o.max_threads()
-    per_it, _ = cpu_sample(problem, n_side, 3, cores)                  # calibration
+    per_it, _ = cpu_sample(problem, 3, cores)                  # calibration
+    need = gpu_plain_iterations
+    base = {"unit": "ms", "cores": cores, "kind": "port"}
+    if need is not None and per_it * need <= budget_s:
+        secs, done, st = cpu_full_solve(problem, cores)
+        base.update({"value": secs * 1e3, "iterations": done, "ms_per_iteration": secs * 1e3 / done, "extrapolated": False,
+                     "sample": f"one COMPLETE solve of the same {label} system by the reference's unpreconditioned CPU CG (oracle/cg_ref_mt.c, "
+                               f"OpenMP over its commented-out Parallel.For loops, {cores} threads): {done} iterations to 1e-8 "
+                               f"(GPU plain CG of this run: {need}); the reference has no multigrid (SURVEY F1)"})
+        return base
     iters = max(3, min(200, int(budget_s / max(per_it, 1e-6))))
-    per_it, done = cpu_sample(problem, n_side, iters, cores)
-    need, how = plain_cg_iterations(n_side)
-    per_it1, done1 = cpu_sample(problem, n_side, max(3, min(20, int(0.3 * budget_s / max(per_it * cores, 1e-6)) or 3)), 1)
-    return {"value": per_it * (need + 1) * 1e3, "unit": "ms", "cores": cores, "kind": "port",
-            "sample": f"{done} iterations of the reference's unpreconditioned CPU CG (oracle/cg_ref_mt.c, OpenMP over its "
-                      f"commented-out Parallel.For loops) on the same {n_side}^3 system, {per_it * 1e3:.1f} ms/iteration, scaled to "
-                      f"the {need + 1} iterations plain CG needs for 1e-8 ({how}); the reference has no multigrid (SURVEY F1)",
-            "ms_per_iteration": per_it * 1e3,
-            "single_thread_ms_per_iteration": per_it1 * 1e3,
-            "single_thread_value": per_it1 * (need + 1) * 1e3}
+    per_it, done = cpu_sample(problem, iters, cores)
+    how = "measured by this run's GPU plain-CG solve" if need is not None else "unknown: per-iteration time only"
+    base.update({"value": per_it * need * 1e3 if need is not None else None, "ms_per_iteration": per_it * 1e3, "extrapolated": True,
+                 "iterations": need,
+                 "sample": f"{done} iterations of the reference's unpreconditioned CPU CG (oracle/cg_ref_mt.c, {cores} threads) on the same "
+                           f"{label} system, {per_it * 1e3:.1f} ms/iteration, scaled to the {need} iterations plain CG needs for 1e-8 ({how})"})
+    return base
 
 
 def run_reference(args):
     """--impl reference: the reference's own CPU implementation of the path (oracle port; the C#/boost/CUDA-5 sources cannot
-    be compiled here) on the box's host cores.  Each step = a bounded number of CG iterations on the same
-    system, scaled to the iteration count plain CG needs for 1e-8."""
+    be compiled here) on the box's host cores, all threads.  The first warm-up step is one COMPLETE solve — it
+    measures the iteration count plain CG needs; every other step times a bounded number of iterations and scales to it."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     from oracle import oracle as o
+    if args.config not in ("c2", "c4") or args.size > 256:
+        print(json.dumps({"impl": "reference", "unavailable": f"config {args.config} at size {args.size} has no host-assembled matrix for the CPU arm "
+                          "(assembled on the device only); run --config c4 / c2"}), flush=True)
+        return 0
     n = args.size
-    problem = make_problem(n)
+    problem = host_problem(args)
     cores = o.max_threads()
-    need, how = plain_cg_iterations(n)
-    per_it, _ = cpu_sample(problem, n, 3, cores)
+    t_full, need, st = cpu_full_solve(problem, cores)          # warm-up step 1: complete solve, measures the iteration count
+    per_it_full = t_full / need
     total_steps = args.steps + args.warmup
-    iters = max(3, min(100, int(120.0 / total_steps / max(per_it, 1e-6))))
-    for _ in range(args.warmup):
-        cpu_sample(problem, n, iters, cores)
-    t = []
-    for _ in range(args.steps):
-        p, done = cpu_sample(problem, n, iters, cores)
-        t.append(p)
-    per_it = float(np.mean(t))
-    value = per_it * (need + 1) * 1e3
-    sample = (f"{iters} iterations per step of the reference's unpreconditioned CPU CG (oracle/cg_ref_mt.c) on {n}^3, "
-              f"{per_it * 1e3:.1f} ms/iteration x {need + 1} iterations to 1e-8 ({how})")
-    out = {"impl": "reference", "metric": METRIC, "value": value, "unit": "ms", "n_gpus": args.gpus, "steps": args.steps,
+    iters = max(3, min(100, int(90.0 / max(total_steps, 1) / max(per_it_full, 1e-6))))
+    if t_full * (total_steps - 1) <= 100.0:        # every step a COMPLETE solve: nothing is scaled
+        for _ in range(max(args.warmup - 1, 0)):
+            cpu_full_solve(problem, cores)
+        t = [cpu_full_solve(problem, cores)[0] for _ in range(args.steps)]
+        value = float(np.mean(t)) * 1e3
+        sample = (f"every step is one COMPLETE solve ({need} iterations to 1e-8) by the reference's unpreconditioned CPU CG "
+                  f"(oracle/cg_ref_mt.c, {cores} threads) on {n}^3; nothing extrapolated")
+    else:
+        for _ in range(max(args.warmup - 1, 0)):
+            cpu_sample(problem, iters, cores)
+        t = []
+        for _ in range(args.steps):
+            p, done = cpu_sample(problem, iters, cores)
+            t.append(p)
+        per_it = float(np.mean(t))
+        value = per_it * need * 1e3
+        sample = (f"{iters} iterations per step of the reference's unpreconditioned CPU CG (oracle/cg_ref_mt.c, {cores} threads) on {n}^3, "
+                  f"{per_it * 1e3:.1f} ms/iteration x {need} iterations to 1e-8; the iteration count is MEASURED by one complete CPU solve in "
+                  f"this run (first warm-up step: {t_full:.1f} s = {t_full * 1e3 / need:.1f} ms/iteration, status {st})")
+    out = {"impl": "reference", "metric": metric_name(args.config), "value": value, "unit": "ms", "n_gpus": args.gpus, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": value, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
            "dtype": "f64", "data": "synthetic",
-           "config": {"workload": f"3-D 7-point Poisson {n}^3, fp64, b~U(-1,1) seed 0, x0=0, relative residual 1e-8",
-                      "rows": n ** 3, "nnz": int(problem[1][-1]), "preconditioner": "none (the reference has none)"},
+           "config": {"workload": workload_text(args).replace(" MGCG", ""), "rows": n ** 3, "nnz": int(problem[1][-1]),
+                      "preconditioner": "none (the reference has none)"},
+           "plain_cg_iterations": need, "complete_solve_ms": t_full * 1e3,
            "cpu_baseline": {"value": value, "unit": "ms", "cores": cores, "kind": "port", "sample": sample},
            "e2e": {"value": value, "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
@@ -222,46 +355,66 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------------------------------------------------
+def gpu_plain_cg_iterations(S, m, tv, tr, tc, tb, tx, opts_mg):
+    """Iterations the reference's algorithm (unpreconditioned CG) needs for 1e-8 on this system, measured on the GPU outside the
+    timed region (its +-1 parity with the CPU oracle is tested in tests/test_gpu_cg.py and tests/test_gpu_parity_c2.py)."""
+    o = S.default_options(precond=0, norm=2, tolerance=TOL, max_iteration=200000)
+    m.setup(tv, tr, tc, o)
+    tx.zero_()
+    res = m.solve(tb, tx, raise_on_fail=False)
+    out = (res.iterations_done, res.solve_ms, tx.clone()) if res.status == 0 else (None, res.solve_ms, None)
+    m.setup(tv, tr, tc, opts_mg)
+    return out
+
+
 def run_ours_single(args):
     """N = 1: the whole system on cuda:0 through the C ABI (mgcg_setup / mgcg_solve / mgcg_solve_host)."""
     import torch
     from conjugategradient_b200 import solver as S
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    if args.config == "c5":
+        raise SystemExit("config c5 (27-point 512^3: 3.6e9 non-zeros) needs --gpus >= 2; per-rank shards must stay below 2^31 entries")
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
     torch.cuda.set_stream(torch.cuda.Stream(dev))   # a real (capturable) stream shared by torch's events and the library
     n_side = args.size
     n = n_side ** 3
     m = S.Mgcg(0, use_torch_stream=True)     # run on torch's current stream so torch.cuda.Event brackets the library's work
-    device_gen = args.device_gen or n_side > 256
+    device_gen = args.device_gen or args.config == "c3" or n_side > 256
+    problem = None
     if device_gen:
-        from conjugategradient_b200 import device_generators as dg
-        from conjugategradient_b200 import generators as g
-        tv, tr, tc = dg.poisson3d7(m.ctx, n_side, device=dev)
-        tb = torch.from_numpy(g.rhs_uniform(n, 0)).to(dev)
+        tv, tr, tc, tb = device_problem(args, m, dev)
         nnz = tv.numel()
-        problem = None
-        args.no_e2e = True; args.no_cpu = True
+        if not args.no_e2e or not args.no_cpu:     # the host legs need a host copy: bring the device-assembled system back once
+            hv, hr, hc, hb = (torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in (tv, tr, tc, tb))
+            for h, t in ((hv, tv), (hr, tr), (hc, tc), (hb, tb)):
+                h.copy_(t)
+            problem = (hv.numpy(), hr.numpy(), hc.numpy(), hb.numpy())
     else:
-        problem = make_problem(n_side)
+        problem = host_problem(args)
         val, rp, col, b = problem
         nnz = int(rp[-1])
-        # pinned host copies (the e2e leg uploads from these)
-        hv, hr, hc, hb = (torch.from_numpy(a).pin_memory() for a in (val, rp, col, b))
-        hx = torch.zeros(n, dtype=torch.float64).pin_memory()
+        hv, hr, hc, hb = (torch.from_numpy(a).pin_memory() for a in (val, rp, col, b))   # pinned host copies (the e2e leg uploads from these)
         tv, tr, tc, tb = (t.to(dev, non_blocking=True) for t in (hv, hr, hc, hb))
+    hx = torch.zeros(n, dtype=torch.float64).pin_memory()
     tx = torch.zeros(n, dtype=torch.float64, device=dev)
     torch.cuda.synchronize()
 
-    gopt = {} if args.graph < 0 else {"use_graph": args.graph}
-    opts = S.default_options(precond=1, nx=n_side, ny=n_side, nz=n_side, norm=2, tolerance=TOL, max_iteration=1000, **gopt)
+    opts = solver_options(args, S)
+    t0 = time.perf_counter()
     m.setup(tv, tr, tc, opts)
+    torch.cuda.synchronize()
+    setup_cold_ms = (time.perf_counter() - t0) * 1e3            # first hierarchy build of the process: allocations included
 
     def step():
         tx.zero_()
         return m.solve(tb, tx)
 
-    for _ in range(args.warmup):
+    t0 = time.perf_counter()
+    res = step()
+    torch.cuda.synchronize()
+    solve_cold_ms = (time.perf_counter() - t0) * 1e3            # first solve: graph capture + instantiation included
+    for _ in range(max(args.warmup - 1, 0)):
         res = step()
     torch.cuda.synchronize()
     clocks = ClockSampler(0)
@@ -277,20 +430,43 @@ def run_ours_single(args):
     ms = e0.elapsed_time(e1) / args.steps
     clk = clocks.stop()
     iters = res.iterations_done
-    setup_ms = res.setup_ms
+    x_timed = tx.clone()
+    # steady-state setup (a second build reuses the cached blocks)
+    m.setup(tv, tr, tc, opts)
+    setup_ms = step().setup_ms
     # true residual check of the last solve (not timed): ||b - A x|| / ||b||
     ty = torch.empty_like(tx)
-    S.check(m.L.mgcg_spmv(m.ctx, n, n, nnz, S._p(tv), S._p(tr), S._p(tc), S._p(tx), S._p(ty), 1.0, 0.0, 0), "mgcg_spmv")
+    S.check(m.L.mgcg_spmv(m.ctx, n, n, nnz, S._p(tv), S._p(tr), S._p(tc), S._p(x_timed), S._p(ty), 1.0, 0.0, 0), "mgcg_spmv")
     torch.cuda.synchronize()
     true_rel = float(torch.linalg.vector_norm(tb - ty) / torch.linalg.vector_norm(tb))
 
+    # parity block (not timed)
+    parity, plain_it = None, None
+    if not args.no_parity:
+        tight = solver_options(args, S, tolerance=1e-12)
+        m.setup(tv, tr, tc, tight)
+        tx.zero_()
+        rt = m.solve(tb, tx)
+        x_tight = tx.clone()
+        scale = float(x_tight.abs().max())
+        m.setup(tv, tr, tc, opts)
+        plain_it, plain_ms, x_plain = gpu_plain_cg_iterations(S, m, tv, tr, tc, tb, tx, opts)
+        parity = {"x_rel_err_vs_tight_solve": float((x_timed - x_tight).abs().max()) / scale,
+                  "reference_solution": "1e-12 relative-residual MGCG solve of the same system on the same device (not the CPU twin: it takes "
+                                        "minutes at this size; twin parity is tested at 128^3 and recorded once at 256^3 under profiles/)",
+                  "tight_iterations": rt.iterations_done, "tight_relative_residual": rt.residual,
+                  "plain_cg_iterations_gpu": plain_it, "plain_cg_solve_ms_gpu": plain_ms,
+                  "x_rel_err_plain_cg_vs_tight_solve": (float((x_plain - x_tight).abs().max()) / scale) if x_plain is not None else None,
+                  "norm": "max|dx| / max|x|"}
+        del x_tight, x_plain
+
     # roofline leg: the fine-level SpMV(+p.Ap) launches timed with CUDA events inside one more solve (profile=1)
-    popts = S.default_options(precond=1, nx=n_side, ny=n_side, nz=n_side, norm=2, tolerance=TOL, max_iteration=1000, profile=1)
+    popts = solver_options(args, S, profile=1)
     m.setup(tv, tr, tc, popts)
     tx.zero_()
     pres = m.solve(tb, tx)
     spmv_ms = pres.spmv_ms_total / max(pres.spmv_launches, 1)
-    # ... and back-to-back in isolation (inputs 1.6 GB >> 126 MB L2, so no flush is needed)
+    # ... and back-to-back in isolation (inputs >> 126 MB L2, so no flush is needed)
     td = torch.zeros(1, dtype=torch.float64, device=dev)
     for _ in range(3):
         m.L.mgcg_spmv_dot(m.ctx, n, n, nnz, S._p(tv), S._p(tr), S._p(tc), S._p(tb), S._p(ty), S._p(tb), S._p(td), 0)
@@ -305,20 +481,30 @@ def run_ours_single(args):
     spmv_bytes = 12.0 * nnz + 20.0 * n
     peak, peak_how = measured_peak()
     achieved = spmv_bytes / (spmv_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_spmv_tma<EPI_DOT> (fine-level A*p with fused p.Ap, TMA-staged stream kernel)", "achieved": achieved,
+    kname = pres.reserved[5]
+    kernel_text = {1: "k_spmv_tma<EPI_DOT> (fine-level A*p with fused p.Ap, TMA-staged stream kernel)",
+                   2: "k_spmv_vector<EPI_DOT> (fine-level A*p with fused p.Ap, lanes-per-row kernel)",
+                   3: "k_spmv_rowblock<EPI_DOT> (fine-level A*p with fused p.Ap, TMA-staged long-row kernel)",
+                   0: "k_spmv_stream<EPI_DOT>"}.get(kname, "fine-level SpMV + p.Ap")
+    traffic, traffic_src = ncu_traffic("k_spmv_tma<2", args)
+    roofline = {"bound": "hbm", "kernel": kernel_text, "achieved": achieved,
                 "peak": peak, "unit": "GB/s", "frac": achieved / peak, "frac_of_8TBs_nominal": achieved / 8000.0,
-                "traffic": ncu_traffic("k_spmv_tma<2>", n_side),
-                "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r01_ncu_full_spmv_tma_256.csv)",
+                "traffic": traffic,
+                "traffic_source": f"dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full ({traffic_src})" if traffic else None,
                 "peak_source": peak_how, "bytes_per_launch": spmv_bytes, "ms_per_launch": spmv_ms,
                 "launches_timed": pres.spmv_launches, "isolated_ms_per_launch": spmv_iso_ms,
                 "isolated_gbs": spmv_bytes / (spmv_iso_ms * 1e-3) / 1e9}
+    m.setup(tv, tr, tc, opts)
 
     # e2e leg: host CSR + b in, x out, everything (upload, hierarchy, solve, download) inside the timed region
     e2e = None
     if not args.no_e2e:
         m2 = S.Mgcg(0, use_torch_stream=True)
         hx.zero_()
-        m2.solve_host(hv.numpy(), hr.numpy(), hc.numpy(), hb.numpy(), hx.numpy(), opts)     # warm-up (allocations)
+        t0 = time.perf_counter()
+        rc = m2.solve_host(hv.numpy(), hr.numpy(), hc.numpy(), hb.numpy(), hx.numpy(), opts)     # the first call of a fresh context
+        torch.cuda.synchronize()
+        e2e_cold = (time.perf_counter() - t0) * 1e3
         k = max(1, min(args.steps, 3))
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
@@ -332,23 +518,27 @@ def run_ours_single(args):
         e2e = {"value": max(g0.elapsed_time(g1) / k, wall), "unit": "ms",
                "h2d_bytes_per_step": int(12 * nnz + 4 * (n + 1) + 16 * n), "d2h_bytes_per_step": int(8 * n),
                "setup_ms": r2.setup_ms, "solve_ms": r2.solve_ms, "iterations": r2.iterations_done,
+               "e2e_cold_ms": e2e_cold, "cold_iterations": rc.iterations_done,
+               "x_rel_err_vs_device_path": float((torch.from_numpy(hx.numpy()).to(dev) - x_timed).abs().max() / x_timed.abs().max()),
                "api": "mgcg_solve_host (include/mgcg.h): pinned host CSR + b + x0 -> x"}
         assert abs(r2.iterations_done - iters) <= 1
         m2.close()
 
-    cpu = None if args.no_cpu else cpu_baseline_leg(problem, n_side, args.cpu_seconds)
-    out = {"metric": METRIC, "value": ms, "unit": "ms", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+    label = f"{args.config} {n_side}^3"
+    cpu = None if (args.no_cpu or problem is None) else cpu_baseline_leg(problem, label, args.cpu_seconds, plain_it)
+    out = {"metric": metric_name(args.config), "value": ms, "unit": "ms", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
            "data": "synthetic",
-           "config": {"workload": f"3-D 7-point Poisson {n_side}^3 MGCG, fp64, b~U(-1,1) seed 0, x0=0, relative residual 1e-8",
-                      "rows": n, "nnz": nnz, "preconditioner": "smoothed-aggregation V(1,1), weighted Jacobi 0.85, built on device",
-                      "l2": "inputs (1.6 GB matrix + 128 MiB vectors at 256^3) larger than the 126 MB L2; no flush",
-                      "matrix_assembly": "device (mgcg_generate_poisson3d7)" if device_gen else "host numpy, uploaded",
+           "config": {"workload": workload_text(args), "name": args.config,
+                      "rows": n, "nnz": nnz, "preconditioner": precond_text(args),
+                      "l2": f"inputs ({12 * nnz / 1e9:.2f} GB matrix + {8 * n / 2 ** 20:.0f} MiB vectors) larger than the 126 MB L2; no flush",
+                      "matrix_assembly": "device" if device_gen else "host numpy, uploaded",
                       "parallelism": "1 GPU"},
            "iterations": iters, "iterations_per_s": iters / (ms * 1e-3), "final_relative_residual": res.residual,
-           "true_relative_residual": true_rel, "setup_ms": setup_ms, "levels": res.levels,
-           "operator_complexity": res.operator_complexity, "spmv_gbs": achieved,
-           "gpu_launches": launches, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e}
+           "true_relative_residual": true_rel, "setup_ms": setup_ms, "setup_cold_ms": setup_cold_ms, "first_solve_ms": solve_cold_ms,
+           "levels": res.levels, "operator_complexity": res.operator_complexity, "spmv_gbs": achieved,
+           "assembly_ms": device_problem.assembly_ms,
+           "gpu_launches": launches, "clocks": clk, "roofline": roofline, "parity": parity, "cpu_baseline": cpu, "e2e": e2e}
     print(json.dumps(out), flush=True)
     m.close()
     return 0
@@ -366,11 +556,12 @@ def main():
 
 def run_ours_dist(args):
     """N > 1 (torchrun, one rank per GPU): the SAME system row-block sharded over the ranks (strong scaling): z-slab shards,
-    halo exchange of p and of the multigrid level vectors plus rank-ordered scalar reductions over NCCL."""
+    halo exchange of p and of the multigrid level vectors plus rank-ordered scalar reductions over NVLink."""
     import torch
     import torch.distributed as dist
-    from conjugategradient_b200 import generators as g
     from conjugategradient_b200 import solver as S
+    if args.config == "c3":
+        raise SystemExit("config c3 (particle matrix, MIS-2 aggregation) is a single-GPU configuration (BASELINE.json); run it with --gpus 1")
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     lr = int(os.environ.get("LOCAL_RANK", "0"))
     assert torch.cuda.is_available(), "bench.py needs CUDA devices (there is no CPU fallback)"
@@ -387,34 +578,41 @@ def run_ours_dist(args):
     r0, r1 = z0 * n_side * n_side, z1 * n_side * n_side
     ids = [S.MgcgDist.unique_id() if rank == 0 else None]
     dist.broadcast_object_list(ids, src=0)
+    t0 = time.perf_counter()
     m = S.MgcgDist(lr, rank, world, ids[0], use_torch_stream=True)
-    b = g.rhs_uniform(n, 0)[r0:r1].copy()
-    device_gen = args.device_gen or n_side > 256
+    comm_init_ms = (time.perf_counter() - t0) * 1e3
+    device_gen = args.device_gen or args.config == "c5" or n_side > 256
     if device_gen:
-        from conjugategradient_b200 import device_generators as dg
-        tv, tr, tc = dg.poisson3d7(m.ctx, n_side, zrange=(z0, z1), device=dev)
-        tb = torch.from_numpy(b).to(dev)
+        tv, tr, tc, tb = device_problem(args, m, dev, zrange=(z0, z1))
         nnz_local = tv.numel()
         args.no_e2e = True
     else:
+        from conjugategradient_b200 import generators as g
         val, rp, col = g.poisson3d7(n_side, zrange=(z0, z1))
+        b = g.rhs_uniform(n, 0)[r0:r1].copy()
         nnz_local = int(rp[-1])
         hv, hr, hc, hb = (torch.from_numpy(a).pin_memory() for a in (val, rp, col, b))
         tv, tr, tc, tb = (t.to(dev, non_blocking=True) for t in (hv, hr, hc, hb))
     tx = torch.zeros(r1 - r0, dtype=torch.float64, device=dev)
     extra = {"dist_transport": args.transport}
-    if args.graph >= 0:
-        extra["use_graph"] = args.graph
     if args.replicate_below > 0:
         extra["dist_replicate_below"] = args.replicate_below
-    opts = S.default_options(precond=1, nx=n_side, ny=n_side, nz=n_side, norm=2, tolerance=TOL, max_iteration=1000, **extra)
+    opts = solver_options(args, S, **extra)
+    torch.cuda.synchronize(); dist.barrier()
+    t0 = time.perf_counter()
     m.setup(n, r0, tv, tr, tc, opts)
+    torch.cuda.synchronize()
+    setup_cold_ms = (time.perf_counter() - t0) * 1e3            # first sharded setup: peer arena + IPC mappings included
 
     def step():
         tx.zero_()
         return m.solve(tb, tx)
 
-    for _ in range(args.warmup):
+    t0 = time.perf_counter()
+    res = step()
+    torch.cuda.synchronize()
+    solve_cold_ms = (time.perf_counter() - t0) * 1e3
+    for _ in range(max(args.warmup - 1, 0)):
         res = step()
     torch.cuda.synchronize()
     dist.barrier()
@@ -431,10 +629,13 @@ def run_ours_dist(args):
     e1.record()
     torch.cuda.synchronize()
     dist.barrier()
-    t = torch.tensor([e0.elapsed_time(e1) / args.steps], dtype=torch.float64, device=dev)
+    t = torch.tensor([e0.elapsed_time(e1) / args.steps, setup_cold_ms, solve_cold_ms], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
+    ms, setup_cold_ms, solve_cold_ms = (float(v) for v in t.tolist())
     clk = clocks.stop() if rank == 0 else None
+    x_timed = tx.clone()
+    m.setup(n, r0, tv, tr, tc, opts)             # steady-state setup time (arena, mappings and cached blocks reused)
+    setup_ms = step().setup_ms
     micro = (C.c_double * 3)()
     S.check(m.L.mgcg_dist_microbench(m.ctx, 200, micro), "mgcg_dist_microbench")
     # local SpMV(+p.Ap) in isolation on this rank's shard (x = a [lo|own|hi]-sized vector addressed globally, like p)
@@ -458,51 +659,89 @@ def run_ours_dist(args):
     spmv_bytes = 12.0 * nnz_local + 20.0 * (r1 - r0)
     peak, peak_how = measured_peak()
     achieved = spmv_bytes / (spmv_ms * 1e-3) / 1e9
+    del tp, ty
 
-    # e2e: pinned host shard -> device, hierarchy build, solve, x back to the host, all inside the timed region
+    # parity: the sharded x against the single-GPU solve of the SAME system, run on rank 0's GPU after the timed region
+    parity = None
+    nnz_global = torch.tensor([nnz_local], dtype=torch.int64, device=dev)
+    dist.all_reduce(nnz_global)
+    nnz_global = int(nnz_global.item())
+    if not args.no_parity and nnz_global < 2 ** 31:
+        parts = [torch.empty(int(zo[q + 1] - zo[q]) * n_side * n_side, dtype=torch.float64, device=dev) for q in range(world)] if rank == 0 else None
+        if rank == 0:
+            parts[0].copy_(x_timed)
+            reqs = [dist.irecv(parts[q], src=q) for q in range(1, world)]
+            for r_ in reqs:
+                r_.wait()
+        else:
+            dist.send(x_timed, dst=0)
+        if rank == 0:
+            xd = torch.cat(parts)
+            del parts
+            ms1 = S.Mgcg(lr, use_torch_stream=True)
+            fv, fr, fc, fb = device_problem(args, ms1, dev)
+            fx = torch.zeros(n, dtype=torch.float64, device=dev)
+            o1 = solver_options(args, S)
+            ms1.setup(fv, fr, fc, o1)
+            r1g = ms1.solve(fb, fx)
+            scale = float(fx.abs().max())
+            err = float((xd - fx).abs().max()) / scale
+            ms1.setup(fv, fr, fc, solver_options(args, S, tolerance=1e-12))
+            ft = torch.zeros(n, dtype=torch.float64, device=dev)
+            ms1.solve(fb, ft)
+            parity = {"dist_x_rel_err": err, "single_gpu_iterations": r1g.iterations_done, "single_gpu_solve_ms": r1g.solve_ms,
+                      "dist_x_rel_err_vs_tight_solve": float((xd - ft).abs().max()) / scale,
+                      "single_x_rel_err_vs_tight_solve": float((fx - ft).abs().max()) / scale,
+                      "norm": "max|dx| / max|x|; single-GPU solves of the same device-assembled system on rank 0's GPU, outside the timed region"}
+            ms1.close()
+            del xd, fx, ft, fv, fr, fc, fb
+        dist.barrier()
+
+    # e2e: ONE C-ABI call per rank on pinned host shards (mgcg_solve_host_dist): upload + hierarchy + solve + download timed
     e2e = None
     if not args.no_e2e:
         hx = torch.zeros(r1 - r0, dtype=torch.float64).pin_memory()
         k = max(1, min(args.steps, 3))
+        m.solve_host(n, r0, hv.numpy(), hr.numpy(), hc.numpy(), hb.numpy(), hx.numpy(), opts)      # allocates the context's device copies
         dist.barrier()
         torch.cuda.synchronize()
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         g0.record()
         for _ in range(k):
-            dv, dr, dc, db = (h.to(dev, non_blocking=True) for h in (hv, hr, hc, hb))
-            dx = torch.zeros(r1 - r0, dtype=torch.float64, device=dev)
-            m.setup(n, r0, dv, dr, dc, opts)
-            r2 = m.solve(db, dx)
-            hx.copy_(dx, non_blocking=True)
+            hx.zero_()
+            r2 = m.solve_host(n, r0, hv.numpy(), hr.numpy(), hc.numpy(), hb.numpy(), hx.numpy(), opts)
         g1.record()
         torch.cuda.synchronize()
         wall = (time.perf_counter() - t0) * 1e3 / k
         t2 = torch.tensor([max(g0.elapsed_time(g1) / k, wall)], dtype=torch.float64, device=dev)
         dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-        e2e = {"value": float(t2.item()), "unit": "ms", "h2d_bytes_per_step": int(12 * nnz_local + 4 * (r1 - r0 + 1) + 8 * (r1 - r0)),
+        e2e = {"value": float(t2.item()), "unit": "ms", "h2d_bytes_per_step": int(12 * nnz_local + 4 * (r1 - r0 + 1) + 16 * (r1 - r0)),
                "d2h_bytes_per_step": int(8 * (r1 - r0)), "setup_ms": r2.setup_ms, "solve_ms": r2.solve_ms, "iterations": r2.iterations_done,
-               "api": "MgcgDist.setup + solve (mgcg_setup_dist / mgcg_solve_dist) from pinned host shards; bytes are per rank"}
+               "e2e_cold_ms": comm_init_ms + setup_cold_ms + solve_cold_ms,
+               "e2e_cold_note": "communicator init + first sharded setup (peer arena, IPC mappings) + first solve (graph capture), wall clock, max over ranks",
+               "api": "mgcg_solve_host_dist (include/mgcg.h): one call per rank on its pinned host row block; bytes are per rank"}
     if rank == 0:
-        out = {"metric": METRIC, "value": ms, "unit": "ms", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        out = {"metric": metric_name(args.config), "value": ms, "unit": "ms", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                "ms_per_step": ms, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-               "config": {"workload": f"3-D 7-point Poisson {n_side}^3 MGCG, fp64, b~U(-1,1) seed 0, x0=0, relative residual 1e-8",
-                          "rows": n, "nnz": 7 * n - 6 * n_side * n_side,
-                          "preconditioner": "smoothed-aggregation V(1,1), weighted Jacobi 0.85, built on device; coarse levels replicated",
+               "config": {"workload": workload_text(args), "name": args.config,
+                          "rows": n, "nnz": nnz_global,
+                          "preconditioner": precond_text(args) + "; coarse levels replicated",
                           "l2": "per-rank shard (matrix + vectors) larger than the 126 MB L2 at 256^3 up to 8 ranks; no flush",
                           "parallelism": f"row-block (z-slab) shards over {world} GPUs; halo exchange, coarse all-gather and rank-ordered "
                                          "scalar reductions by " + ("the library's own kernels over NVLink peer memory, iteration replayed as a CUDA graph"
                                                                     if res.reserved[3] == 2 else "NCCL send/recv + all-gather")},
-               "transport": "peer" if res.reserved[3] == 2 else "nccl", "graph": bool(res.reserved[4]),
+               "transport": "peer" if res.reserved[3] == 2 else "nccl", "graph": int(res.reserved[4]),
                "exchange_us": {"halo_level0": micro[0], "coarse_allgather": micro[1], "scalar_reduction": micro[2]},
                "iterations": res.iterations_done, "iterations_per_s": res.iterations_done / (ms * 1e-3),
-               "final_relative_residual": res.residual, "setup_ms": res.setup_ms, "levels": res.levels,
+               "final_relative_residual": res.residual, "setup_ms": setup_ms, "setup_cold_ms": setup_cold_ms, "first_solve_ms": solve_cold_ms,
+               "comm_init_ms": comm_init_ms, "levels": res.levels,
                "distributed_levels": res.reserved[2], "halo_exchanges_per_solve": res.reserved[0], "allgathers_per_solve": res.reserved[1],
                "spmv_gbs": achieved * world, "gpu_launches": launches, "clocks": clk,
                "roofline": {"bound": "hbm", "kernel": "k_spmv_tma<EPI_DOT> on rank 0's shard (isolated, back to back)", "achieved": achieved,
                             "peak": peak, "unit": "GB/s", "frac": achieved / peak, "frac_of_8TBs_nominal": achieved / 8000.0, "traffic": None,
                             "peak_source": peak_how, "bytes_per_launch": spmv_bytes, "ms_per_launch": spmv_ms},
-               "cpu_baseline": None, "e2e": e2e}
+               "parity": parity, "cpu_baseline": None, "e2e": e2e}
         print(json.dumps(out), flush=True)
     m.close()
     dist.barrier()

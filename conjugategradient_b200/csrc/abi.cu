@@ -132,6 +132,7 @@ void mgcg_destroy(mgcg_ctx *c)
     if (c->graph) cudaGraphDestroy(c->graph);
     if (c->host_path) { ((HostPath *)c->host_path)->release(); delete (HostPath *)c->host_path; }
     formats_free(c);
+    dist_host_path_free(c);
     if (c->r) cudaFree(c->r);
     if (c->p) cudaFree(c->p);
     if (c->Ap) cudaFree(c->Ap);

@@ -42,6 +42,17 @@ static int enqueue_iteration(mgcg_ctx *c, const double *b, double *x, std::vecto
     return MGCG_OK;
 }
 
+// "No limit" (the library default 1 << 30, or <= 0) is replaced by a finite bound: with the whole loop running as one
+// device-side WHILE graph the host cannot cancel a solve that stagnates above the tolerance (a tolerance below what fp64
+// can reach, a semi-definite system), so the device-side Iteration > MaxIteration test must be able to fire.  20 n + 1000
+// is far above anything CG needs on an SPD system (exact arithmetic: n; the reference's own 65 536-row stress input: 2 n).
+int effective_max_iteration(int requested, int n)
+{
+    if (requested > 0 && requested < (1 << 30)) return requested;
+    const long long cap = 20LL * n + 1000;
+    return (int)(cap < (1LL << 30) ? cap : (1LL << 30));
+}
+
 __global__ void k_loop_condition(cudaGraphConditionalHandle h, const Scalars *sc)
 {
     if (threadIdx.x == 0) cudaGraphSetConditional(h, sc->done ? 0u : 1u);
@@ -92,18 +103,23 @@ int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     const bool pre = (c->opt.precond == MGCG_PRECOND_MG) && c->mg;
     MGCG_CHECK(ctx_ensure_work(c, n));
     cudaStream_t st = c->stream;
-    cudaEvent_t ev0, ev1, evp[2];
-    MGCG_CUDA(cudaEventCreate(&ev0));
-    MGCG_CUDA(cudaEventCreate(&ev1));
-    MGCG_CUDA(cudaEventCreateWithFlags(&evp[0], cudaEventDisableTiming));
-    MGCG_CUDA(cudaEventCreateWithFlags(&evp[1], cudaEventDisableTiming));
+    struct Events {   // destroyed on every exit path (the early returns of MGCG_CHECK / MGCG_CUDA included)
+        cudaEvent_t e[4] = {nullptr, nullptr, nullptr, nullptr};
+        ~Events() { for (auto &x : e) if (x) cudaEventDestroy(x); }
+    } evs;
+    MGCG_CUDA(cudaEventCreate(&evs.e[0]));
+    MGCG_CUDA(cudaEventCreate(&evs.e[1]));
+    MGCG_CUDA(cudaEventCreateWithFlags(&evs.e[2], cudaEventDisableTiming));
+    MGCG_CUDA(cudaEventCreateWithFlags(&evs.e[3], cudaEventDisableTiming));
+    cudaEvent_t &ev0 = evs.e[0], &ev1 = evs.e[1];
+    cudaEvent_t *evp = &evs.e[2];
     c->launches = 0;
 
     // scalars
     Scalars h{};
     h.tolerance = c->opt.tolerance;
     h.min_iteration = c->opt.min_iteration;
-    h.max_iteration = c->opt.max_iteration;
+    h.max_iteration = effective_max_iteration(c->opt.max_iteration, n);
     h.norm = c->opt.norm;
     h.min_strict = c->opt.min_strict;
     c->h_scalars[0] = h;
@@ -166,7 +182,7 @@ int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     bool finished = false;
     bool have_prev = false;
     Scalars fin{};
-    const long long hard_cap = (long long)c->opt.max_iteration + 2;
+    const long long hard_cap = (long long)h.max_iteration + 2;
     if (while_loop) {   // one launch: the device decides when to stop
         MGCG_CUDA(cudaGraphLaunch(c->graph_exec, st));
         finished = true;
@@ -208,7 +224,6 @@ int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
         if ((int)(i / 2) <= fin.iteration) { spmv_ms += t; spmv_n++; }
         cudaEventDestroy(pev[i]); cudaEventDestroy(pev[i + 1]);
     }
-    cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(evp[0]); cudaEventDestroy(evp[1]);
 
     if (res) {
         res->status = fin.done ? fin.status : MGCG_ERR_NOT_CONVERGED;
@@ -223,6 +238,7 @@ int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
         res->kernel_launches = c->launches;
         res->spmv_ms_total = spmv_ms;
         res->spmv_launches = spmv_n;
+        res->reserved[5] = spmv_kernel_id(c->planA, c->A);   // kernel family of the fine-level SpMV (bench.py names it)
     }
     if (!fin.done) { set_error("cg_solve: iteration cap reached without the device flag"); return MGCG_ERR_NOT_CONVERGED; }
     if (fin.status != MGCG_OK) {

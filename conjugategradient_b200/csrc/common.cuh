@@ -161,6 +161,7 @@ struct mgcg_ctx {
     // host-pointer path buffers (mgcg_solve_host)
     void *host_path = nullptr;
     void *ell_path = nullptr;        // device system owned by mgcg_solve_host_ell (formats.cu)
+    void *host_path_dist = nullptr;  // device copies owned by mgcg_solve_host_dist (dist.cu)
 };
 
 namespace mgcg {
@@ -189,6 +190,7 @@ int mg_dense_apply(mgcg_ctx *c, int n, const double *Minv, const double *b, doub
 // ---- kernels_spmv.cu
 SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel);
 int spmv_launch(mgcg_ctx *c, const SpmvPlan &plan, int epi, const SpmvArgs &a);
+int spmv_kernel_id(const SpmvPlan &plan, const Csr &A);
 
 // ---- mg_setup.cu / mg_cycle.cu
 int mg_build(mgcg_ctx *c);
@@ -200,9 +202,11 @@ const double *mg_level0_dinv(mgcg_ctx *c);
 
 // ---- dist.cu
 void dist_free(mgcg_ctx *c);
+void dist_host_path_free(mgcg_ctx *c);
 
 // ---- cg.cu
 int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res);
+int effective_max_iteration(int requested, int n);   // the option's "no limit" (>= 1 << 30 or <= 0) -> 20 n + 1000
 // Build `*graph` = WHILE(!Scalars.done) { body }: `enqueue` is captured into the body of a conditional node, followed by a
 // one-thread kernel that feeds the loop condition from the device-side `done` flag.  MGCG_ERR_UNSUPPORTED if the driver
 // has no conditional nodes (callers fall back to one iteration per launch).

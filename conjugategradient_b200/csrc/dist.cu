@@ -795,14 +795,19 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     const int n = L0.own;
     const bool pre = (c->opt.precond == MGCG_PRECOND_MG);
     cudaStream_t st = c->stream;
-    cudaEvent_t ev0, ev1, evp[2];
-    MGCG_CUDA(cudaEventCreate(&ev0)); MGCG_CUDA(cudaEventCreate(&ev1));
-    MGCG_CUDA(cudaEventCreateWithFlags(&evp[0], cudaEventDisableTiming));
-    MGCG_CUDA(cudaEventCreateWithFlags(&evp[1], cudaEventDisableTiming));
+    struct Events {   // destroyed on every exit path
+        cudaEvent_t e[4] = {nullptr, nullptr, nullptr, nullptr};
+        ~Events() { for (auto &x : e) if (x) cudaEventDestroy(x); }
+    } evs;
+    MGCG_CUDA(cudaEventCreate(&evs.e[0])); MGCG_CUDA(cudaEventCreate(&evs.e[1]));
+    MGCG_CUDA(cudaEventCreateWithFlags(&evs.e[2], cudaEventDisableTiming));
+    MGCG_CUDA(cudaEventCreateWithFlags(&evs.e[3], cudaEventDisableTiming));
+    cudaEvent_t &ev0 = evs.e[0], &ev1 = evs.e[1];
+    cudaEvent_t *evp = &evs.e[2];
     c->launches = 0; D->halo_exchanges = 0; D->allgathers = 0;
     if (D->coarse) D->coarse->launches = 0;
     Scalars h{};
-    h.tolerance = c->opt.tolerance; h.min_iteration = c->opt.min_iteration; h.max_iteration = c->opt.max_iteration;
+    h.tolerance = c->opt.tolerance; h.min_iteration = c->opt.min_iteration; h.max_iteration = effective_max_iteration(c->opt.max_iteration, D->n_glob);
     h.norm = c->opt.norm; h.min_strict = c->opt.min_strict;
     c->h_scalars[0] = h;
     MGCG_CUDA(cudaMemcpyAsync(c->d_scalars, &c->h_scalars[0], sizeof(Scalars), cudaMemcpyHostToDevice, st));
@@ -830,7 +835,7 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     long long enq = 0;
     int slot = 0;
     bool finished = false, have_prev = false;
-    const long long hard_cap = (long long)c->opt.max_iteration + 2;
+    const long long hard_cap = (long long)h.max_iteration + 2;
     // peer transport: the iteration is made of this library's kernels only, so it is captured once and replayed
     {
         const char *e = getenv("MGCG_DIST_TRACE");
@@ -901,7 +906,6 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     }
     float ms = 0.f;
     MGCG_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
-    cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(evp[0]); cudaEventDestroy(evp[1]);
     if (res) {
         memset(res, 0, sizeof(*res));
         res->status = fin.done ? fin.status : MGCG_ERR_NOT_CONVERGED;
@@ -995,5 +999,72 @@ extern "C" int mgcg_solve_dist(mgcg_ctx *c, const double *d_b_local, double *d_x
     MGCG_CUDA(cudaSetDevice(c->device));
     int s = dist_solve(c, d_b_local, d_x_local, res);
     if (res) res->status = s;
+    return s;
+}
+
+// ---- sharded solve on HOST pointers: this rank's row block in host arrays (the reference's multi-device class hands host
+// arrays to the native side, ConjugateGradientParallelGpu.cs:358-379 -> Initialize, Mgcg.cu:57-85: elements / column indices
+// of the block, row offsets of the block — rebased here like Mgcg.cu:73 when they are not — x and b slices), one call:
+// upload + hierarchy build + solve + download.  Device copies are owned by the context and reused by the next call that fits.
+namespace mgcg {
+struct HostPathDist {
+    double *val = nullptr; int *rowptr = nullptr; int *col = nullptr; double *b = nullptr; double *x = nullptr;
+    size_t cap_n = 0, cap_nnz = 0;
+    void release()
+    {
+        cudaFree(val); cudaFree(rowptr); cudaFree(col); cudaFree(b); cudaFree(x);
+        val = nullptr; rowptr = nullptr; col = nullptr; b = nullptr; x = nullptr; cap_n = cap_nnz = 0;
+    }
+};
+__global__ void k_rebase_rowptr(int n, int *rp, int base)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) rp[i] -= base;
+}
+void dist_host_path_free(mgcg_ctx *c)
+{
+    if (!c->host_path_dist) return;
+    HostPathDist *h = (HostPathDist *)c->host_path_dist;
+    h->release();
+    delete h;
+    c->host_path_dist = nullptr;
+}
+}  // namespace mgcg
+
+extern "C" int mgcg_solve_host_dist(mgcg_ctx *c, int global_count, int row_offset, int local_count, int local_elements_count,
+                                    const double *elements, const int *row_offsets, const int *column_indeces,
+                                    const double *b_local, double *x_local, const mgcg_options *opt, mgcg_result *res)
+{
+    if (!c || !c->dist) { set_error("mgcg_solve_host_dist: call mgcg_comm_init first"); return MGCG_ERR_INVALID; }
+    if (!elements || !row_offsets || !column_indeces || !b_local || !x_local || local_count <= 0 || local_elements_count < 0) {
+        set_error("mgcg_solve_host_dist: null or empty argument");
+        return MGCG_ERR_INVALID;
+    }
+    MGCG_CUDA(cudaSetDevice(c->device));
+    if (!c->host_path_dist) c->host_path_dist = new HostPathDist();
+    HostPathDist *h = (HostPathDist *)c->host_path_dist;
+    const size_t n = (size_t)local_count, nnz = (size_t)local_elements_count;
+    if (h->cap_n < n || h->cap_nnz < nnz) {
+        h->release();
+        MGCG_CUDA(cudaMalloc((void **)&h->val, sizeof(double) * (nnz > 0 ? nnz : 1)));
+        MGCG_CUDA(cudaMalloc((void **)&h->col, sizeof(int) * (nnz > 0 ? nnz : 1)));
+        MGCG_CUDA(cudaMalloc((void **)&h->rowptr, sizeof(int) * (n + 1)));
+        MGCG_CUDA(cudaMalloc((void **)&h->b, sizeof(double) * n));
+        MGCG_CUDA(cudaMalloc((void **)&h->x, sizeof(double) * n));
+        h->cap_n = n; h->cap_nnz = nnz;
+    }
+    cudaStream_t st = c->stream;
+    MGCG_CUDA(cudaMemcpyAsync(h->val, elements, sizeof(double) * nnz, cudaMemcpyHostToDevice, st));
+    MGCG_CUDA(cudaMemcpyAsync(h->col, column_indeces, sizeof(int) * nnz, cudaMemcpyHostToDevice, st));
+    MGCG_CUDA(cudaMemcpyAsync(h->rowptr, row_offsets, sizeof(int) * (n + 1), cudaMemcpyHostToDevice, st));
+    if (row_offsets[0] != 0) {   // offsets of the block inside the global array: rebase to the block (Mgcg.cu:73)
+        k_rebase_rowptr<<<(local_count + 256) / 256, 256, 0, st>>>(local_count + 1, h->rowptr, row_offsets[0]);
+        MGCG_LAUNCH_CHECK();
+    }
+    MGCG_CUDA(cudaMemcpyAsync(h->b, b_local, sizeof(double) * n, cudaMemcpyHostToDevice, st));
+    MGCG_CUDA(cudaMemcpyAsync(h->x, x_local, sizeof(double) * n, cudaMemcpyHostToDevice, st));
+    MGCG_CHECK(mgcg_setup_dist(c, global_count, row_offset, local_count, local_elements_count, h->val, h->rowptr, h->col, opt));
+    const int s = mgcg_solve_dist(c, h->b, h->x, res);
+    MGCG_CUDA(cudaMemcpyAsync(x_local, h->x, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
     return s;
 }

@@ -337,6 +337,14 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
     return MGCG_OK;
 }
 
+// which kernel family spmv_launch picks for this plan / matrix: 0 stream, 1 TMA-staged stream, 2 lanes-per-row vector
+int spmv_kernel_id(const SpmvPlan &plan, const Csr &A)
+{
+    const bool aligned = ((((uintptr_t)A.val) | ((uintptr_t)A.col)) & 15u) == 0;
+    if (plan.kernel == MGCG_SPMV_STREAM) return (plan.tma && aligned) ? 1 : 0;
+    return 2;
+}
+
 int spmv_launch(mgcg_ctx *c, const SpmvPlan &plan, int epi, const SpmvArgs &a)
 {
     switch (epi) {

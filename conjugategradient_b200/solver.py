@@ -355,6 +355,17 @@ class MgcgDist:
             raise MgcgError(s, "mgcg_solve_dist")
         return res
 
+    def solve_host(self, global_count, row_offset, val, rowptr, col, b_local, x_local, options=None, raise_on_fail=True):
+        """numpy (ideally pinned) host arrays of this rank's row block in, x_local updated in place: one C-ABI call
+        (mgcg_solve_host_dist) doing upload + setup + solve + download."""
+        res = Result()
+        o = options if options is not None else default_options()
+        s = self.L.mgcg_solve_host_dist(self.ctx, global_count, row_offset, len(rowptr) - 1, len(val), _p(val), _p(rowptr), _p(col),
+                                        _p(b_local), _p(x_local), C.byref(o), C.byref(res))
+        if s != _lib.OK and raise_on_fail:
+            raise MgcgError(s, "mgcg_solve_host_dist")
+        return res
+
     def close(self):
         if self.ctx:
             self.L.mgcg_destroy(self.ctx)

@@ -200,6 +200,12 @@ int mgcg_setup_dist(mgcg_ctx *c, int global_count, int row_offset, int local_cou
                     const double *d_elements, const int *d_row_offsets, const int *d_column_indeces,
                     const mgcg_options *opt);
 int mgcg_solve_dist(mgcg_ctx *c, const double *d_b_local, double *d_x_local, mgcg_result *res);
+/* the same on HOST pointers (this rank's row block in host arrays, as the reference's multi-device class passes them to
+ * Initialize, ConjugateGradientParallelGpu.cs:358-379 -> Mgcg.cu:57-85): upload + setup + solve + download in one call.
+ * row_offsets may be the block's slice of the global offsets (row_offsets[0] != 0): it is rebased like Mgcg.cu:73. */
+int mgcg_solve_host_dist(mgcg_ctx *c, int global_count, int row_offset, int local_count, int local_elements_count,
+                         const double *elements, const int *row_offsets, const int *column_indeces,
+                         const double *b_local, double *x_local, const mgcg_options *opt, mgcg_result *res);
 /* collective micro-benchmark of the loop's exchanges after mgcg_setup_dist: microseconds per level-0 halo exchange,
  * per coarse all-gather and per scalar reduction (back to back, `reps` each) */
 int mgcg_dist_microbench(mgcg_ctx *c, int reps, double *out_us /* [3] */);
