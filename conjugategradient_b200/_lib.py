@@ -13,7 +13,7 @@ CSRC = os.path.join(_HERE, "csrc")
 OK, ERR_INVALID, ERR_CUDA, ERR_NOT_CONVERGED, ERR_BREAKDOWN, ERR_COMM, ERR_UNSUPPORTED = range(7)
 NORM_ABS_L2, NORM_ABS_LINF, NORM_REL_L2 = 0, 1, 2
 PRECOND_NONE, PRECOND_MG = 0, 1
-SPMV_AUTO, SPMV_STREAM, SPMV_VECTOR = 0, 1, 2
+SPMV_AUTO, SPMV_STREAM, SPMV_VECTOR, SPMV_ROWS = 0, 1, 2, 3
 TRANSPORT_AUTO, TRANSPORT_NCCL, TRANSPORT_PEER = 0, 1, 2
 AGG_AUTO, AGG_BLOCKS, AGG_MIS2 = 0, 1, 2
 

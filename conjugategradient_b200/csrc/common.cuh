@@ -25,8 +25,8 @@ const char *get_error();
 
 #define MGCG_CHECK(call)                                                                                 \
     do {                                                                                                 \
-        int s_ = (call);                                                                                 \
-        if (s_ != MGCG_OK) return s_;                                                                    \
+        int mgcg_chk_status_ = (call);                                                                   \
+        if (mgcg_chk_status_ != MGCG_OK) return mgcg_chk_status_;                                        \
     } while (0)
 
 #define MGCG_LAUNCH_CHECK() MGCG_CUDA(cudaGetLastError())

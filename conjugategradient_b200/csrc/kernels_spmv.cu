@@ -10,6 +10,7 @@
 // Both run as persistent grids (static tile->block map, so the fused reduction is deterministic).
 #include "common.cuh"
 #include "reduce.cuh"
+#include <stdlib.h>
 
 namespace mgcg {
 
@@ -246,6 +247,117 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// ROWS-TMA (medium and long rows: 8 .. ~300 entries — the reference's own 160-per-row band, particle matrices, restriction
+// operators, coarse Galerkin stencils; cf. the reference's ELL kernel with a local-memory window,
+// Mgcg/HandmadeCL/MgcgCL/Mgcg.cl:171-216).  A tile is 256/L consecutive rows, L lanes per row.  The tile's contiguous val/col
+// slice is brought into a ring of shared-memory stages by the TMA engine (cp.async.bulk on mbarriers) a tile or more ahead, so
+// the only global loads the lanes issue themselves are the x gathers (L2-resident for banded matrices); the lanes of a row walk
+// its segment from shared memory with stride L and finish with a fixed shuffle tree (deterministic; not the storage order of
+// the STREAM kernels).  The plain VECTOR kernel reads val/col through the same dependent chain rowptr -> (val,col) -> x[col]
+// and measured 0.69 of the HBM peak on the 79-per-row restriction operator.
+constexpr int kRowsCap = 2560;            // non-zeros per stage: (8 + 4) B x 2560 = 30 KB; L lanes serve rows up to ~10 L entries
+constexpr int kRowsStages = 2;
+constexpr int kRowsThreads = 256;
+constexpr size_t kRowsSmem = (size_t)kRowsStages * ((kRowsCap + 2) * 8 + (kRowsCap + 4) * 4 + 16 + 16) + 64;
+
+template <int EPI, int L>
+__global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_tiles, ReduceWs ws, Scalars *sc)
+{
+    if (a.gated && sc->done) return;
+    extern __shared__ __align__(16) unsigned char rows_smem[];
+    double *s_val = reinterpret_cast<double *>(rows_smem);                                            // [S][CAP + 2]
+    int *s_col = reinterpret_cast<int *>(rows_smem + (size_t)kRowsStages * (kRowsCap + 2) * 8);       // [S][CAP + 4]
+    unsigned long long *s_full = reinterpret_cast<unsigned long long *>(s_col + (size_t)kRowsStages * (kRowsCap + 4));
+    unsigned long long *s_empty = s_full + kRowsStages;
+    TmaMeta *s_meta = reinterpret_cast<TmaMeta *>(s_empty + kRowsStages);
+    constexpr int R = kRowsThreads / L;      // rows per tile
+    const int t = threadIdx.x, g = t / L, lane = t % L;
+    const double *__restrict__ val = a.A.val;
+    const int *__restrict__ col = a.A.col;
+    const int *__restrict__ rowptr = a.A.rowptr;
+    const double *__restrict__ x = a.x;
+    const int rows = a.A.rows;
+    const long long nnz_end = (long long)a.A.nnz;
+    double dsum = 0.0;
+
+    if (t == 0) {
+        for (int s = 0; s < kRowsStages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], kRowsThreads); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const int my_tiles = (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+    auto issue = [&](int j) {
+        const int s = j % kRowsStages;
+        const int tile = blockIdx.x + j * gridDim.x;
+        const int r0 = tile * R;
+        const int nr = min(R, rows - r0);
+        const int k0 = rowptr[r0], k1 = rowptr[r0 + nr];
+        const int ka = k0 & ~1, kc = k0 & ~3;
+        const unsigned vb = (unsigned)(((k1 - ka) * 8 + 15) & ~15), cb = (unsigned)(((k1 - kc) * 4 + 15) & ~15);
+        const bool fits = (k1 - ka) <= kRowsCap && (k1 - kc) <= kRowsCap && k1 > k0 &&
+                          ((long long)ka * 8 + vb <= nnz_end * 8) && ((long long)kc * 4 + cb <= nnz_end * 4);
+        s_meta[s].k0 = k0; s_meta[s].k1 = k1; s_meta[s].direct = fits ? 0 : 1;
+        if (fits) {
+            mbar_arrive_expect_tx(&s_full[s], vb + cb);
+            tma_load_1d(s_val + (size_t)s * (kRowsCap + 2), val + ka, vb, &s_full[s]);
+            tma_load_1d(s_col + (size_t)s * (kRowsCap + 4), col + kc, cb, &s_full[s]);
+        } else {
+            mbar_arrive(&s_full[s]);
+        }
+    };
+    if (t == 0)
+        for (int j = 0; j < kRowsStages && j < my_tiles; ++j) issue(j);
+
+    int rs_n = 0, re_n = 0;
+    {
+        const int r = blockIdx.x * R + g;
+        if (my_tiles > 0 && r < rows) { rs_n = rowptr[r]; re_n = rowptr[r + 1]; }
+    }
+    for (int j = 0; j < my_tiles; ++j) {
+        const int s = j % kRowsStages;
+        const unsigned parity = (unsigned)((j / kRowsStages) & 1);
+        const int tile = blockIdx.x + j * gridDim.x;
+        const int row = tile * R + g;
+        const int rs = rs_n, re = re_n;
+        rs_n = re_n = 0;
+        if (j + 1 < my_tiles) {
+            const int rn = (tile + gridDim.x) * R + g;
+            if (rn < rows) { rs_n = rowptr[rn]; re_n = rowptr[rn + 1]; }
+        }
+        EpiPre pre;
+        if (lane == 0 && row < rows) epi_prefetch<EPI>(row, a, pre);
+        mbar_wait(&s_full[s], parity);
+        double acc = 0.0;
+        if (row < rows) {
+            if (!s_meta[s].direct) {
+                const int k0 = s_meta[s].k0;
+                const double *sv = s_val + (size_t)s * (kRowsCap + 2) - (k0 & ~1);
+                const int *scl = s_col + (size_t)s * (kRowsCap + 4) - (k0 & ~3);
+#pragma unroll 4
+                for (int k = rs + lane; k < re; k += L) acc += sv[k] * x[scl[k]];
+            } else {
+#pragma unroll 4
+                for (int k = rs + lane; k < re; k += L) acc += __ldcs(val + k) * x[__ldcs(col + k)];
+            }
+        }
+        mbar_arrive(&s_empty[s]);
+        if (t == 0 && j + kRowsStages < my_tiles) {
+            mbar_wait(&s_empty[s], parity);
+            issue(j + kRowsStages);
+        }
+#pragma unroll
+        for (int o = L / 2; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, L);
+        if (lane == 0 && row < rows) epilogue_pre<EPI>(row, acc, a, dsum, pre);
+    }
+    if (EpiTraits<EPI>::reduces) {
+        double m = 0.0;
+        block_reduce<false>(dsum, m);
+        grid_reduce_finish<false>(dsum, m, ws, a.fin, sc, a.out);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 template <int EPI, int L>
 __global__ void __launch_bounds__(kSpmvThreads) k_spmv_vector(SpmvArgs a, ReduceWs ws, Scalars *sc)
 {
@@ -285,8 +397,26 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel)
     const double avg = rows > 0 ? (double)nnz / rows : 1.0;
     int cap = c->sm_count * 8;
     if (cap > kMaxPartials) cap = kMaxPartials;
-    if (kernel == MGCG_SPMV_AUTO) kernel = (avg <= 48.0) ? MGCG_SPMV_STREAM : MGCG_SPMV_VECTOR;
+    // AUTO: rows short enough for a 256-row tile to fit a TMA stage -> STREAM (TMA); up to ~300 per row -> ROWS (TMA-staged,
+    // L lanes per row); beyond -> VECTOR.  (MGCG_SPMV_NO_ROWS=1 restores the round-1 choice: STREAM up to 48 per row, else VECTOR.)
+    if (kernel == MGCG_SPMV_AUTO) {
+        static const bool no_rows = getenv("MGCG_SPMV_NO_ROWS") != nullptr;
+        if (avg * kTmaRows <= kTmaCap - 64) kernel = MGCG_SPMV_STREAM;
+        else if (no_rows) kernel = (avg <= 48.0) ? MGCG_SPMV_STREAM : MGCG_SPMV_VECTOR;
+        else kernel = (avg <= 300.0) ? MGCG_SPMV_ROWS : MGCG_SPMV_VECTOR;
+    }
     p.kernel = kernel;
+    if (kernel == MGCG_SPMV_ROWS) {
+        // smallest L (4..32) whose tile of 256/L rows fills at most ~5/6 of a stage on average
+        int L = 4;
+        while (L < 32 && (double)(kRowsThreads / L) * avg > kRowsCap * (5.0 / 6.0)) L <<= 1;
+        p.lanes = L;
+        const int tiles = div_up(rows > 0 ? rows : 1, kRowsThreads / L);
+        int gcap = c->sm_count * 3;
+        p.grid = tiles < gcap ? tiles : gcap;
+        if (p.grid < 1) p.grid = 1;
+        return p;
+    }
     // short rows (a 256-row tile fits a TMA stage): the TMA-staged variant of the stream kernel
     p.tma = (kernel == MGCG_SPMV_STREAM && avg * kTmaRows <= kTmaCap - 64);
     p.tma_short = p.tma && avg * kTmaRows <= kTmaCapShort - 64;
@@ -324,6 +454,26 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
     } else if (plan.kernel == MGCG_SPMV_STREAM) {
         int tiles = div_up(a.A.rows, plan.rows_per_tile);
         k_spmv_stream<EPI><<<plan.grid, kSpmvThreads, 0, c->stream>>>(a, plan.rows_per_tile, tiles, c->ws, c->d_scalars);
+    } else if (plan.kernel == MGCG_SPMV_ROWS && aligned) {
+        static unsigned long long attr_done = 0ull;      // per template instantiation, one bit per device (the attribute is per device)
+        const unsigned long long dev_bit = 1ull << (c->device & 63);
+        if (!(attr_done & dev_bit)) {
+            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmem));
+            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmem));
+            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmem));
+            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmem));
+            attr_done |= dev_bit;
+        }
+        const int L = plan.lanes;
+        const int tiles = div_up(a.A.rows, kRowsThreads / L);
+        int grid = c->sm_count * 3;
+        if (grid > tiles) grid = tiles;
+        switch (L) {
+        case 4: k_spmv_rows<EPI, 4><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, c->ws, c->d_scalars); break;
+        case 8: k_spmv_rows<EPI, 8><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, c->ws, c->d_scalars); break;
+        case 16: k_spmv_rows<EPI, 16><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, c->ws, c->d_scalars); break;
+        default: k_spmv_rows<EPI, 32><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, c->ws, c->d_scalars); break;
+        }
     } else {
         switch (plan.lanes) {
         case 4: k_spmv_vector<EPI, 4><<<plan.grid, kSpmvThreads, 0, c->stream>>>(a, c->ws, c->d_scalars); break;
@@ -337,11 +487,12 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
     return MGCG_OK;
 }
 
-// which kernel family spmv_launch picks for this plan / matrix: 0 stream, 1 TMA-staged stream, 2 lanes-per-row vector
+// which kernel family spmv_launch picks for this plan / matrix: 0 stream, 1 TMA-staged stream, 2 lanes-per-row vector, 3 TMA-staged rows
 int spmv_kernel_id(const SpmvPlan &plan, const Csr &A)
 {
     const bool aligned = ((((uintptr_t)A.val) | ((uintptr_t)A.col)) & 15u) == 0;
     if (plan.kernel == MGCG_SPMV_STREAM) return (plan.tma && aligned) ? 1 : 0;
+    if (plan.kernel == MGCG_SPMV_ROWS && aligned) return 3;
     return 2;
 }
 

@@ -506,7 +506,7 @@ static int psa_direct(mgcg_ctx *c, const Csr &A, int row_base, const int *agg, c
     {
         const int s_ = scan_counts_checked(c, cnt, n, P->rowptr, &nnz, "prolongator");
         tfree(cnt);
-        MGCG_CHECK(s_);
+        if (s_ != MGCG_OK) return s_;
     }
     P->nnz = nnz;
     MGCG_CHECK(dalloc(&P->val, (size_t)nnz)); MGCG_CHECK(dalloc(&P->col, (size_t)nnz));
@@ -661,7 +661,7 @@ int mg_build(mgcg_ctx *c)
             const int s_ = filtered ? build_prolongator(c, F.view(), 0, L.agg, dinvF, smooth_here, o.mg_prolong_omega, nc, &L.P)
                                     : build_prolongator(c, L.A, 0, L.agg, L.dinv, smooth_here, o.mg_prolong_omega, nc, &L.P);
             F.free_all(); pool_release(dinvF);
-            MGCG_CHECK(s_);
+            if (s_ != MGCG_OK) return s_;
         }
         tr.mark(l, "P");
         MGCG_CHECK(csr_transpose(c, L.P.view(), &L.R));

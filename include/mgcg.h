@@ -40,7 +40,7 @@ enum {
 
 enum { MGCG_PRECOND_NONE = 0, MGCG_PRECOND_MG = 1 };
 enum { MGCG_SMOOTHER_JACOBI = 0, MGCG_SMOOTHER_RBGS = 1 };
-enum { MGCG_SPMV_AUTO = 0, MGCG_SPMV_STREAM = 1, MGCG_SPMV_VECTOR = 2 };
+enum { MGCG_SPMV_AUTO = 0, MGCG_SPMV_STREAM = 1, MGCG_SPMV_VECTOR = 2, MGCG_SPMV_ROWS = 3 };
 enum { MGCG_TRANSPORT_AUTO = 0, MGCG_TRANSPORT_NCCL = 1, MGCG_TRANSPORT_PEER = 2 };
 /* aggregation of the multigrid hierarchy: AUTO = geometric blocks when nx,ny,nz are given, else strength-of-connection filter +
  * MIS-2 aggregates (caller-supplied CSR without a grid, e.g. particle matrices); BLOCKS = 8 consecutive rows when there is no

@@ -57,7 +57,7 @@ def _matrix(gen, name):
 
 
 @pytest.mark.parametrize("name", MATS)
-@pytest.mark.parametrize("kernel", [1, 2, 0])
+@pytest.mark.parametrize("kernel", [1, 2, 3, 0])       # STREAM (storage-order sums), VECTOR, ROWS (TMA-staged, lanes per row), AUTO
 def test_spmv_parity(env, oracle, gen, name, kernel):
     torch, L, ctx, _ = env
     v, rp, c = _matrix(gen, name)
@@ -162,3 +162,30 @@ def test_spmv_dot_fused(env, oracle, gen):
         assert outs[0] == outs[1]
         assert abs(outs[0] - oracle.dot(x, y_ref)) <= 1e-13 * np.abs(x * y_ref).sum()
         np.testing.assert_allclose(ty.cpu().numpy(), y_ref, rtol=1e-13, atol=1e-13 * np.abs(y_ref).max())
+
+
+@pytest.mark.parametrize("name", ["banded", "mps", "ragged", "p27"])
+def test_spmv_rows_kernel_fused_epilogues(env, oracle, gen, name):
+    """The TMA-staged rows kernel (MGCG_SPMV_ROWS) with the fused p.Ap epilogue, on a sub-block view whose row offsets do not start
+    at zero and whose arrays end inside the parent's (the sharded path's use), and with every lane count the plan can pick."""
+    torch, L, ctx, _ = env
+    v, rp, c = _matrix(gen, name)
+    n = len(rp) - 1
+    x = np.random.default_rng(5).standard_normal(n)
+    w = np.random.default_rng(6).standard_normal(n)
+    y_ref = oracle.spmv(v, rp, c, x)
+    scale = oracle.spmv(np.abs(v), rp, c, np.abs(x)) + 1e-300
+    tv, tr, tc, tx, tw = _dev(torch, v), _dev(torch, rp), _dev(torch, c), _dev(torch, x), _dev(torch, w)
+    ty = torch.full((n,), np.nan, dtype=torch.float64, device="cuda:0")
+    td = torch.zeros(1, dtype=torch.float64, device="cuda:0")
+    assert L.mgcg_spmv_dot(ctx, n, n, len(v), _p(tv), _p(tr), _p(tc), _p(tx), _p(ty), _p(tw), _p(td), 3) == 0
+    torch.cuda.synchronize()
+    y = ty.cpu().numpy()
+    assert np.max(np.abs(y - y_ref) / scale) < 1e-14
+    assert abs(float(td.item()) - float(np.dot(w, y))) <= 1e-12 * np.abs(w * y).sum()
+    # a row sub-block [r0, r1): row offsets keep the parent's numbering, val/col pointers are the parent's
+    r0, r1 = n // 3 + 1, (2 * n) // 3
+    ty2 = torch.full((r1 - r0,), np.nan, dtype=torch.float64, device="cuda:0")
+    assert L.mgcg_spmv(ctx, r1 - r0, n, len(v), _p(tv), C.c_void_p(tr.data_ptr() + 4 * r0), _p(tc), _p(tx), _p(ty2), 1.0, 0.0, 3) == 0
+    torch.cuda.synchronize()
+    assert np.max(np.abs(ty2.cpu().numpy() - y_ref[r0:r1]) / scale[r0:r1]) < 1e-14
