@@ -90,7 +90,9 @@ struct SpmvPlan {
     bool tma = false;               // STREAM: use the TMA-staged variant (short rows, 16-byte aligned val/col)
     bool tma_short = false;         // ... with twice the stages of half the size (very short rows)
     int rows_per_tile = 256;        // STREAM: rows handled per tile (<= 256)
-    int lanes = 8;                  // VECTOR: lanes per row
+    int lanes = 8;                  // VECTOR / ROWS: lanes per row
+    int rows_cap = 2552;            // ROWS: non-zeros a shared-memory stage holds (multiple of 4)
+    int rows_stages = 2;            // ROWS: stages in the ring (2..8)
     int grid = 0;
 };
 

@@ -250,26 +250,31 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
 // ROWS-TMA (medium and long rows: 8 .. ~300 entries — the reference's own 160-per-row band, particle matrices, restriction
 // operators, coarse Galerkin stencils; cf. the reference's ELL kernel with a local-memory window,
 // Mgcg/HandmadeCL/MgcgCL/Mgcg.cl:171-216).  A tile is 256/L consecutive rows, L lanes per row.  The tile's contiguous val/col
-// slice is brought into a ring of shared-memory stages by the TMA engine (cp.async.bulk on mbarriers) a tile or more ahead, so
+// slice is brought into a ring of shared-memory stages by the TMA engine (cp.async.bulk on mbarriers) several tiles ahead, so
 // the only global loads the lanes issue themselves are the x gathers (L2-resident for banded matrices); the lanes of a row walk
 // its segment from shared memory with stride L and finish with a fixed shuffle tree (deterministic; not the storage order of
 // the STREAM kernels).  The plain VECTOR kernel reads val/col through the same dependent chain rowptr -> (val,col) -> x[col]
 // and measured 0.69 of the HBM peak on the 79-per-row restriction operator.
-constexpr int kRowsCap = 2560;            // non-zeros per stage: (8 + 4) B x 2560 = 30 KB; L lanes serve rows up to ~10 L entries
-constexpr int kRowsStages = 2;
+// The stage capacity is a launch parameter: the ring always spans kRowsTotal entries (72 KB, 3 blocks per SM), cut into as many
+// stages as the matrix's tiles allow (cap ~ 1.25 x the average tile), because what sets the achieved bandwidth is the number
+// of bytes in flight per SM: the first version (2 stages of 2560) ran at 0.61 of peak on 38-per-row tiles that filled 47 % of a
+// stage and at 0.75 on 124-per-row tiles that filled 77 %.
+constexpr int kRowsTotal = 6144;          // non-zeros the ring holds: (8 + 4) B x 6144 = 72 KB; 3 blocks per SM
+constexpr int kRowsMaxStages = 8;
 constexpr int kRowsThreads = 256;
-constexpr size_t kRowsSmem = (size_t)kRowsStages * ((kRowsCap + 2) * 8 + (kRowsCap + 4) * 4 + 16 + 16) + 64;
+constexpr size_t kRowsSmem = (size_t)kRowsTotal * 12 + (size_t)kRowsMaxStages * (16 + 16 + 16 + 16) + 64;
 
 template <int EPI, int L>
-__global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_tiles, ReduceWs ws, Scalars *sc)
+__global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_tiles, int cap, int stages, ReduceWs ws, Scalars *sc)
 {
     if (a.gated && sc->done) return;
+    // cap is a multiple of 4: every stage's val slice (cap + 2 doubles) and col slice (cap + 4 ints) starts 16-byte aligned
     extern __shared__ __align__(16) unsigned char rows_smem[];
-    double *s_val = reinterpret_cast<double *>(rows_smem);                                            // [S][CAP + 2]
-    int *s_col = reinterpret_cast<int *>(rows_smem + (size_t)kRowsStages * (kRowsCap + 2) * 8);       // [S][CAP + 4]
-    unsigned long long *s_full = reinterpret_cast<unsigned long long *>(s_col + (size_t)kRowsStages * (kRowsCap + 4));
-    unsigned long long *s_empty = s_full + kRowsStages;
-    TmaMeta *s_meta = reinterpret_cast<TmaMeta *>(s_empty + kRowsStages);
+    double *s_val = reinterpret_cast<double *>(rows_smem);                                   // [stages][cap + 2]
+    int *s_col = reinterpret_cast<int *>(rows_smem + (size_t)stages * (cap + 2) * 8);        // [stages][cap + 4]
+    unsigned long long *s_full = reinterpret_cast<unsigned long long *>(rows_smem + (size_t)stages * ((cap + 2) * 8 + (cap + 4) * 4));
+    unsigned long long *s_empty = s_full + kRowsMaxStages;
+    TmaMeta *s_meta = reinterpret_cast<TmaMeta *>(s_empty + kRowsMaxStages);
     constexpr int R = kRowsThreads / L;      // rows per tile
     const int t = threadIdx.x, g = t / L, lane = t % L;
     const double *__restrict__ val = a.A.val;
@@ -281,42 +286,41 @@ __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_
     double dsum = 0.0;
 
     if (t == 0) {
-        for (int s = 0; s < kRowsStages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], kRowsThreads); }
+        for (int s = 0; s < stages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], kRowsThreads); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     const int my_tiles = (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
-    auto issue = [&](int j) {
-        const int s = j % kRowsStages;
+    auto issue = [&](int j, int s) {
         const int tile = blockIdx.x + j * gridDim.x;
         const int r0 = tile * R;
         const int nr = min(R, rows - r0);
         const int k0 = rowptr[r0], k1 = rowptr[r0 + nr];
         const int ka = k0 & ~1, kc = k0 & ~3;
         const unsigned vb = (unsigned)(((k1 - ka) * 8 + 15) & ~15), cb = (unsigned)(((k1 - kc) * 4 + 15) & ~15);
-        const bool fits = (k1 - ka) <= kRowsCap && (k1 - kc) <= kRowsCap && k1 > k0 &&
+        const bool fits = (k1 - ka) <= cap && (k1 - kc) <= cap && k1 > k0 &&
                           ((long long)ka * 8 + vb <= nnz_end * 8) && ((long long)kc * 4 + cb <= nnz_end * 4);
         s_meta[s].k0 = k0; s_meta[s].k1 = k1; s_meta[s].direct = fits ? 0 : 1;
         if (fits) {
             mbar_arrive_expect_tx(&s_full[s], vb + cb);
-            tma_load_1d(s_val + (size_t)s * (kRowsCap + 2), val + ka, vb, &s_full[s]);
-            tma_load_1d(s_col + (size_t)s * (kRowsCap + 4), col + kc, cb, &s_full[s]);
+            tma_load_1d(s_val + (size_t)s * (cap + 2), val + ka, vb, &s_full[s]);
+            tma_load_1d(s_col + (size_t)s * (cap + 4), col + kc, cb, &s_full[s]);
         } else {
             mbar_arrive(&s_full[s]);
         }
     };
     if (t == 0)
-        for (int j = 0; j < kRowsStages && j < my_tiles; ++j) issue(j);
+        for (int j = 0; j < stages && j < my_tiles; ++j) issue(j, j);
 
     int rs_n = 0, re_n = 0;
     {
         const int r = blockIdx.x * R + g;
         if (my_tiles > 0 && r < rows) { rs_n = rowptr[r]; re_n = rowptr[r + 1]; }
     }
+    int s = 0;
+    unsigned parity = 0;
     for (int j = 0; j < my_tiles; ++j) {
-        const int s = j % kRowsStages;
-        const unsigned parity = (unsigned)((j / kRowsStages) & 1);
         const int tile = blockIdx.x + j * gridDim.x;
         const int row = tile * R + g;
         const int rs = rs_n, re = re_n;
@@ -332,8 +336,8 @@ __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_
         if (row < rows) {
             if (!s_meta[s].direct) {
                 const int k0 = s_meta[s].k0;
-                const double *sv = s_val + (size_t)s * (kRowsCap + 2) - (k0 & ~1);
-                const int *scl = s_col + (size_t)s * (kRowsCap + 4) - (k0 & ~3);
+                const double *sv = s_val + (size_t)s * (cap + 2) - (k0 & ~1);
+                const int *scl = s_col + (size_t)s * (cap + 4) - (k0 & ~3);
 #pragma unroll 4
                 for (int k = rs + lane; k < re; k += L) acc += sv[k] * x[scl[k]];
             } else {
@@ -342,13 +346,14 @@ __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_
             }
         }
         mbar_arrive(&s_empty[s]);
-        if (t == 0 && j + kRowsStages < my_tiles) {
+        if (t == 0 && j + stages < my_tiles) {
             mbar_wait(&s_empty[s], parity);
-            issue(j + kRowsStages);
+            issue(j + stages, s);
         }
 #pragma unroll
         for (int o = L / 2; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, L);
         if (lane == 0 && row < rows) epilogue_pre<EPI>(row, acc, a, dsum, pre);
+        if (++s == stages) { s = 0; parity ^= 1u; }
     }
     if (EpiTraits<EPI>::reduces) {
         double m = 0.0;
@@ -407,11 +412,23 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel)
     }
     p.kernel = kernel;
     if (kernel == MGCG_SPMV_ROWS) {
-        // smallest L (4..32) whose tile of 256/L rows fills at most ~5/6 of a stage on average
-        int L = 4;
-        while (L < 32 && (double)(kRowsThreads / L) * avg > kRowsCap * (5.0 / 6.0)) L <<= 1;
-        p.lanes = L;
-        const int tiles = div_up(rows > 0 ? rows : 1, kRowsThreads / L);
+        // L lanes per row (4..32, at most ~8 entries per lane) and the cut of the ring into stages: the candidate with the most
+        // non-zeros in flight (stages x average tile) wins, the smaller L on ties.  A stage holds 1.1 x the average tile + 16.
+        int bestL = 0, best_st = 0;
+        double best_fly = -1.0;
+        for (int L = 4; L <= 32; L <<= 1) {
+            if (avg > 8.0 * L && L < 32) continue;
+            const double tile = (double)(kRowsThreads / L) * avg;
+            int st = (int)(kRowsTotal / (1.1 * tile + 16.0));
+            if (st > kRowsMaxStages) st = kRowsMaxStages;
+            if (st < 2) st = 2;
+            const double fly = st * (tile < kRowsTotal / 2 ? tile : kRowsTotal / 2);
+            if (fly > best_fly * 1.02) { best_fly = fly; bestL = L; best_st = st; }
+        }
+        p.lanes = bestL;
+        p.rows_stages = best_st;
+        p.rows_cap = ((kRowsTotal / best_st) & ~3) - 4;
+        const int tiles = div_up(rows > 0 ? rows : 1, kRowsThreads / bestL);
         int gcap = c->sm_count * 3;
         p.grid = tiles < gcap ? tiles : gcap;
         if (p.grid < 1) p.grid = 1;
@@ -469,10 +486,10 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
         int grid = c->sm_count * 3;
         if (grid > tiles) grid = tiles;
         switch (L) {
-        case 4: k_spmv_rows<EPI, 4><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, c->ws, c->d_scalars); break;
-        case 8: k_spmv_rows<EPI, 8><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, c->ws, c->d_scalars); break;
-        case 16: k_spmv_rows<EPI, 16><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, c->ws, c->d_scalars); break;
-        default: k_spmv_rows<EPI, 32><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, c->ws, c->d_scalars); break;
+        case 4: k_spmv_rows<EPI, 4><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
+        case 8: k_spmv_rows<EPI, 8><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
+        case 16: k_spmv_rows<EPI, 16><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
+        default: k_spmv_rows<EPI, 32><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
         }
     } else {
         switch (plan.lanes) {

@@ -425,25 +425,26 @@ static int run_merge(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, DevCsr 
 // into a per-warp shared-memory slot indexed by list number, and the sum is taken over the set bits of the four ballots in
 // list order — storage order of the A row, product by product, like the hash kernels and the CPU twin.
 // At 256^3 this product took 2.5 + 6.9 ms with the 8-lane hash kernels.
-constexpr int kWmSlots = 4;
+constexpr int kWmSlots = 4;       // 33..128 entries per A row
+constexpr int kWmSlotsLong = 8;   // 129..256 entries per A row (the reference's 160-per-row band, particle matrices at r_e = 3.1 l0)
 constexpr int kWmWarps = 8;
 
-template <bool NUMERIC>
+template <bool NUMERIC, int SLOTS>
 __global__ void __launch_bounds__(kWmWarps * 32) k_spgemm_wmerge(Csr A, Csr B, int shift, int *__restrict__ cnt, const int *__restrict__ c_rowptr,
                                                                 int *__restrict__ c_col, double *__restrict__ c_val)
 {
     constexpr unsigned kEnd = 0x7fffffffu;
-    __shared__ double s_prod[kWmWarps][32 * kWmSlots];
+    __shared__ double s_prod[kWmWarps][32 * SLOTS];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int nwarps = gridDim.x * kWmWarps;
     for (int row = blockIdx.x * kWmWarps + w; row < A.rows; row += nwarps) {
-        int q[kWmSlots], qe[kWmSlots];
-        unsigned hc[kWmSlots];
-        double a[kWmSlots];
+        int q[SLOTS], qe[SLOTS];
+        unsigned hc[SLOTS];
+        double a[SLOTS];
         const int ks = A.rowptr[row], m = A.rowptr[row + 1] - ks;
 #pragma unroll
-        for (int t = 0; t < kWmSlots; ++t) {
-            const int k = lane * kWmSlots + t;
+        for (int t = 0; t < SLOTS; ++t) {
+            const int k = lane * SLOTS + t;
             q[t] = 0; qe[t] = 0; hc[t] = kEnd; a[t] = 0.0;
             if (k < m) {
                 const int j = A.col[ks + k] - shift;
@@ -456,29 +457,30 @@ __global__ void __launch_bounds__(kWmWarps * 32) k_spgemm_wmerge(Csr A, Csr B, i
         while (true) {
             unsigned mine = kEnd;
 #pragma unroll
-            for (int t = 0; t < kWmSlots; ++t) mine = min(mine, hc[t]);
+            for (int t = 0; t < SLOTS; ++t) mine = min(mine, hc[t]);
             const unsigned cur = __reduce_min_sync(0xffffffffu, mine);
             if (cur == kEnd) break;
-            unsigned bal[kWmSlots];
+            unsigned bal[SLOTS];
+            unsigned any = 0u;
 #pragma unroll
-            for (int t = 0; t < kWmSlots; ++t) {
+            for (int t = 0; t < SLOTS; ++t) {
                 const bool hit = hc[t] == cur;
-                if (NUMERIC && hit) s_prod[w][lane * kWmSlots + t] = __dmul_rn(a[t], B.val[q[t]]);
+                if (NUMERIC && hit) s_prod[w][lane * SLOTS + t] = __dmul_rn(a[t], B.val[q[t]]);
                 bal[t] = __ballot_sync(0xffffffffu, hit);
+                any |= bal[t];
                 if (hit) { ++q[t]; hc[t] = q[t] < qe[t] ? (unsigned)B.col[q[t]] : kEnd; }
             }
             if (NUMERIC) {
                 __syncwarp();
-                unsigned any = bal[0] | bal[1] | bal[2] | bal[3];
                 double sum = 0.0;
                 bool have = false;
-                while (any) {
+                while (any) {          // lanes in ascending order, slots in ascending order == list number == storage order of the A row
                     const int l = __ffs(any) - 1;
                     any &= any - 1;
 #pragma unroll
-                    for (int t = 0; t < kWmSlots; ++t)
+                    for (int t = 0; t < SLOTS; ++t)
                         if ((bal[t] >> l) & 1u) {
-                            const double v = s_prod[w][l * kWmSlots + t];
+                            const double v = s_prod[w][l * SLOTS + t];
                             sum = have ? __dadd_rn(sum, v) : v;
                             have = true;
                         }
@@ -492,6 +494,7 @@ __global__ void __launch_bounds__(kWmWarps * 32) k_spgemm_wmerge(Csr A, Csr B, i
     }
 }
 
+template <int SLOTS>
 static int run_wmerge(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, DevCsr *C)
 {
     cudaStream_t st = c->stream;
@@ -500,7 +503,7 @@ static int run_wmerge(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, DevCsr
     MGCG_CUDA(cudaMemsetAsync(cnt + A.rows, 0, sizeof(int), st));
     int grid = (A.rows + kWmWarps - 1) / kWmWarps;
     if (grid > c->sm_count * 32) grid = c->sm_count * 32;
-    k_spgemm_wmerge<false><<<grid, kWmWarps * 32, 0, st>>>(A, B, shift, cnt, nullptr, nullptr, nullptr);
+    k_spgemm_wmerge<false, SLOTS><<<grid, kWmWarps * 32, 0, st>>>(A, B, shift, cnt, nullptr, nullptr, nullptr);
     MGCG_LAUNCH_CHECK();
     C->rows = A.rows; C->cols = B.cols;
     MGCG_CUDA(pool_alloc((void **)&C->rowptr, sizeof(int) * ((size_t)A.rows + 1), st));
@@ -513,8 +516,8 @@ static int run_wmerge(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, DevCsr
     C->nnz = nnz;
     MGCG_CUDA(pool_alloc((void **)&C->val, sizeof(double) * (size_t)(nnz > 0 ? nnz : 1), st));
     MGCG_CUDA(pool_alloc((void **)&C->col, sizeof(int) * (size_t)(nnz > 0 ? nnz : 1), st));
-    if (getenv("MGCG_TRACE")) fprintf(stderr, "[mgcg spgemm] rows %d warp-merge kernel nnz %d grid %d\n", A.rows, nnz, grid);
-    k_spgemm_wmerge<true><<<grid, kWmWarps * 32, 0, st>>>(A, B, shift, nullptr, C->rowptr, C->col, C->val);
+    if (getenv("MGCG_TRACE")) fprintf(stderr, "[mgcg spgemm] rows %d warp-merge kernel (%d lists per lane) nnz %d grid %d\n", A.rows, SLOTS, nnz, grid);
+    k_spgemm_wmerge<true, SLOTS><<<grid, kWmWarps * 32, 0, st>>>(A, B, shift, nullptr, C->rowptr, C->col, C->val);
     MGCG_LAUNCH_CHECK();
     return MGCG_OK;
 }
@@ -612,7 +615,8 @@ int spgemm(mgcg_ctx *c, const Csr &A, const Csr &B, DevCsr *C, int col_shift)
         if (maxlen <= 16) return run_merge<16>(c, A, B, col_shift, C);
         if (maxlen <= 32) return run_merge<32>(c, A, B, col_shift, C);
         const double avg_b0 = (double)B.nnz / (B.rows > 0 ? B.rows : 1);
-        if (maxlen <= 32 * kWmSlots && avg_b0 <= 16.0) return run_wmerge(c, A, B, col_shift, C);
+        if (maxlen <= 32 * kWmSlots && avg_b0 <= 16.0) return run_wmerge<kWmSlots>(c, A, B, col_shift, C);
+        if (maxlen <= 32 * kWmSlotsLong && avg_b0 <= 16.0) return run_wmerge<kWmSlotsLong>(c, A, B, col_shift, C);
     }
     const double avg_b = (double)B.nnz / (B.rows > 0 ? B.rows : 1);
     bool done = false;
