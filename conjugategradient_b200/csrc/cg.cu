@@ -34,7 +34,7 @@ static int enqueue_iteration(mgcg_ctx *c, const double *b, double *x, std::vecto
     } else {
         // same update, fused with the V-cycle's first pre-smoothing sweep from a zero guess: z0 = omega D^-1 r
         MGCG_CHECK(cg_update_xr(c, n, c->p, c->Ap, x, c->r, FIN_RR_PRECOND, false, 0.0, nullptr,
-                                mg_level0_first_x(c), mg_level0_dinv(c), c->opt.mg_omega));
+                                mg_level0_first_x(c), mg_level0_dinv(c), mg_level0_first_omega(c)));
         double *z = nullptr;
         MGCG_CHECK(mg_vcycle(c, c->r, &z, true, FIN_RZ));   // z = M r ; r.z ; beta = rz'/rz (fused into the last sweep)
         MGCG_CHECK(cg_update_p(c, n, z, c->p, false, 0.0)); // p = z + beta p

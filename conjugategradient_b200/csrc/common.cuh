@@ -93,6 +93,7 @@ struct SpmvPlan {
     int lanes = 8;                  // VECTOR / ROWS: lanes per row
     int rows_cap = 2552;            // ROWS: non-zeros a shared-memory stage holds (multiple of 4)
     int rows_stages = 2;            // ROWS: stages in the ring (2..8)
+    int rows_smem = 0;              // ROWS: dynamic shared memory of the launch
     int grid = 0;
 };
 
@@ -118,6 +119,10 @@ struct SpmvArgs {
     int fin = FIN_STORE;
     double *out = nullptr;         // FIN_STORE target
     bool gated = false;            // true: no-op once Scalars.done is set (kernels inside the CG loop)
+    // red-black Gauss-Seidel half sweep (JACOBI epilogues, STREAM kernels, in place: y == x): only the rows whose grid cell has
+    // parity (ix + iy + iz) & 1 == color are updated; the others keep x (and still enter the fused dot).  -1: every row.
+    int color = -1;
+    int cnx = 0, cny = 0;          // grid extents that decode a row index into (ix, iy, iz)
 };
 
 // ---------------------------------------------------------------------------------------------------------
@@ -200,6 +205,7 @@ void mg_free(mgcg_ctx *c);
 void formats_free(mgcg_ctx *c);
 int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done, int rz_fin);
 double *mg_level0_first_x(mgcg_ctx *c);   // buffer that receives the fused first pre-smoothing sweep
+double mg_level0_first_omega(mgcg_ctx *c); // its damping: mg_omega (weighted Jacobi) or 1 (level 0 smoothed by red-black Gauss-Seidel)
 const double *mg_level0_dinv(mgcg_ctx *c);
 
 // ---- dist.cu

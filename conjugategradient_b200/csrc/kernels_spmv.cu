@@ -60,6 +60,21 @@ __device__ __forceinline__ void epilogue_pre(int row, double s, const SpmvArgs &
     }
 }
 
+// red-black half sweeps: is `row` updated by this launch?
+__device__ __forceinline__ bool row_active(const SpmvArgs &a, int row)
+{
+    if (a.color < 0) return true;
+    const int ix = row % a.cnx, t = row / a.cnx;
+    const int iy = t % a.cny, iz = t / a.cny;
+    return ((ix + iy + iz) & 1) == a.color;
+}
+// epilogue of a row a half sweep leaves alone: x stays, the fused dot still takes b_i x_i
+template <int EPI>
+__device__ __forceinline__ void epilogue_inactive(const SpmvArgs &a, double &dsum, const EpiPre &p)
+{
+    if (EPI == EPI_JACOBI_DOT) dsum += p.e0 * p.e1;
+}
+
 template <int EPI> struct EpiTraits { static constexpr bool reduces = (EPI == EPI_DOT || EPI == EPI_JACOBI_DOT); };
 
 // ---------------------------------------------------------------------------------------------------------
@@ -96,7 +111,15 @@ __global__ void __launch_bounds__(kSpmvThreads) k_spmv_stream(SpmvArgs a, int ro
             const int s0 = max(ms, c0), s1 = min(me, c1);
             for (int k = s0; k < s1; ++k) acc += prod[k - c0];
         }
-        if (t < nr) epilogue<EPI>(r0 + t, acc, a, dsum);
+        if (t < nr) {
+            if ((EPI == EPI_JACOBI || EPI == EPI_JACOBI_DOT) && !row_active(a, r0 + t)) {
+                EpiPre pre;
+                epi_prefetch<EPI>(r0 + t, a, pre);
+                epilogue_inactive<EPI>(a, dsum, pre);
+            } else {
+                epilogue<EPI>(r0 + t, acc, a, dsum);
+            }
+        }
     }
     if (EpiTraits<EPI>::reduces) {
         double m = 0.0;
@@ -220,9 +243,10 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
         }
         EpiPre pre;
         if (row < rows) epi_prefetch<EPI>(row, a, pre);
+        const bool active = (EPI == EPI_JACOBI || EPI == EPI_JACOBI_DOT) ? (row < rows && row_active(a, row)) : (row < rows);
         mbar_wait(&s_full[s], parity);
         double acc = 0.0;
-        if (row < rows) {
+        if (active) {
             if (!s_meta[s].direct) {
                 const int k0 = s_meta[s].k0;
                 const double *sv = &s_val[s][0] - (k0 & ~1);
@@ -237,7 +261,8 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
             mbar_wait(&s_empty[s], parity);       // ... and once every thread is, refill it
             issue(j + kTmaStages);
         }
-        if (row < rows) epilogue_pre<EPI>(row, acc, a, dsum, pre);
+        if (active) epilogue_pre<EPI>(row, acc, a, dsum, pre);
+        else if (row < rows) epilogue_inactive<EPI>(a, dsum, pre);
     }
     if (EpiTraits<EPI>::reduces) {
         double m = 0.0;
@@ -259,10 +284,12 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
 // stages as the matrix's tiles allow (cap ~ 1.25 x the average tile), because what sets the achieved bandwidth is the number
 // of bytes in flight per SM: the first version (2 stages of 2560) ran at 0.61 of peak on 38-per-row tiles that filled 47 % of a
 // stage and at 0.75 on 124-per-row tiles that filled 77 %.
-constexpr int kRowsTotal = 6144;          // non-zeros the ring holds: (8 + 4) B x 6144 = 72 KB; 3 blocks per SM
+constexpr int kRowsTotalDefault = 5120;   // non-zeros the ring holds: (8 + 4) B x 5120 = 60 KB
+constexpr int kRowsTotalMax = 16384;
+constexpr int kRowsCtasDefault = 3;       // blocks per SM the grid is sized for
 constexpr int kRowsMaxStages = 8;
 constexpr int kRowsThreads = 256;
-constexpr size_t kRowsSmem = (size_t)kRowsTotal * 12 + (size_t)kRowsMaxStages * (16 + 16 + 16 + 16) + 64;
+constexpr size_t kRowsSmemMax = (size_t)kRowsTotalMax * 12 + (size_t)kRowsMaxStages * 64 + 64;
 
 template <int EPI, int L>
 __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_tiles, int cap, int stages, ReduceWs ws, Scalars *sc)
@@ -414,22 +441,32 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel)
     if (kernel == MGCG_SPMV_ROWS) {
         // L lanes per row (4..32, at most ~8 entries per lane) and the cut of the ring into stages: the candidate with the most
         // non-zeros in flight (stages x average tile) wins, the smaller L on ties.  A stage holds 1.1 x the average tile + 16.
+        // Tuning knobs (tools/spmv_sweep.py): MGCG_ROWS_TOTAL (ring entries), MGCG_ROWS_CTAS (blocks per SM), MGCG_ROWS_LANES.
+        int total = kRowsTotalDefault, ctas = kRowsCtasDefault, forceL = 0;
+        if (const char *e = getenv("MGCG_ROWS_TOTAL")) total = atoi(e);
+        if (const char *e = getenv("MGCG_ROWS_CTAS")) ctas = atoi(e);
+        if (const char *e = getenv("MGCG_ROWS_LANES")) forceL = atoi(e);
+        if (total < 512) total = 512;
+        if (total > kRowsTotalMax) total = kRowsTotalMax;
+        if (ctas < 1) ctas = 1;
         int bestL = 0, best_st = 0;
         double best_fly = -1.0;
         for (int L = 4; L <= 32; L <<= 1) {
-            if (avg > 8.0 * L && L < 32) continue;
+            if (forceL > 0 ? (L != forceL) : (avg > 8.0 * L && L < 32)) continue;
             const double tile = (double)(kRowsThreads / L) * avg;
-            int st = (int)(kRowsTotal / (1.1 * tile + 16.0));
+            int st = (int)(total / (1.1 * tile + 16.0));
             if (st > kRowsMaxStages) st = kRowsMaxStages;
             if (st < 2) st = 2;
-            const double fly = st * (tile < kRowsTotal / 2 ? tile : kRowsTotal / 2);
+            const double fly = st * (tile < total / 2 ? tile : total / 2);
             if (fly > best_fly * 1.02) { best_fly = fly; bestL = L; best_st = st; }
         }
+        if (bestL == 0) { bestL = 32; best_st = 2; }
         p.lanes = bestL;
         p.rows_stages = best_st;
-        p.rows_cap = ((kRowsTotal / best_st) & ~3) - 4;
+        p.rows_cap = ((total / best_st) & ~3) - 4;
+        p.rows_smem = (int)((size_t)total * 12 + (size_t)kRowsMaxStages * 64 + 64);
         const int tiles = div_up(rows > 0 ? rows : 1, kRowsThreads / bestL);
-        int gcap = c->sm_count * 3;
+        int gcap = c->sm_count * ctas;
         p.grid = tiles < gcap ? tiles : gcap;
         if (p.grid < 1) p.grid = 1;
         return p;
@@ -461,6 +498,10 @@ template <int EPI>
 static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
 {
     if (a.A.rows <= 0) return MGCG_OK;
+    if (a.color >= 0 && (plan.kernel != MGCG_SPMV_STREAM || (EPI != EPI_JACOBI && EPI != EPI_JACOBI_DOT) || a.cnx <= 0 || a.cny <= 0)) {
+        set_error("spmv_launch: a red-black half sweep needs a Jacobi epilogue, the STREAM kernels and the grid extents");
+        return MGCG_ERR_INVALID;
+    }
     const bool aligned = ((((uintptr_t)a.A.val) | ((uintptr_t)a.A.col)) & 15u) == 0;
     if (plan.kernel == MGCG_SPMV_STREAM && plan.tma && aligned) {
         const int tiles = div_up(a.A.rows, kTmaRows);
@@ -475,21 +516,28 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
         static unsigned long long attr_done = 0ull;      // per template instantiation, one bit per device (the attribute is per device)
         const unsigned long long dev_bit = 1ull << (c->device & 63);
         if (!(attr_done & dev_bit)) {
-            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmem));
-            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmem));
-            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmem));
-            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmem));
+            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmemMax));
+            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmemMax));
+            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmemMax));
+            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmemMax));
+            if (const char *e = getenv("MGCG_ROWS_CARVEOUT")) {     // tuning: percent of the unified L1/shared array given to shared memory
+                const int pc = atoi(e);
+                cudaFuncSetAttribute(k_spmv_rows<EPI, 4>, cudaFuncAttributePreferredSharedMemoryCarveout, pc);
+                cudaFuncSetAttribute(k_spmv_rows<EPI, 8>, cudaFuncAttributePreferredSharedMemoryCarveout, pc);
+                cudaFuncSetAttribute(k_spmv_rows<EPI, 16>, cudaFuncAttributePreferredSharedMemoryCarveout, pc);
+                cudaFuncSetAttribute(k_spmv_rows<EPI, 32>, cudaFuncAttributePreferredSharedMemoryCarveout, pc);
+            }
             attr_done |= dev_bit;
         }
         const int L = plan.lanes;
         const int tiles = div_up(a.A.rows, kRowsThreads / L);
-        int grid = c->sm_count * 3;
+        int grid = plan.grid;
         if (grid > tiles) grid = tiles;
         switch (L) {
-        case 4: k_spmv_rows<EPI, 4><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
-        case 8: k_spmv_rows<EPI, 8><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
-        case 16: k_spmv_rows<EPI, 16><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
-        default: k_spmv_rows<EPI, 32><<<grid, kRowsThreads, kRowsSmem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
+        case 4: k_spmv_rows<EPI, 4><<<grid, kRowsThreads, (size_t)plan.rows_smem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
+        case 8: k_spmv_rows<EPI, 8><<<grid, kRowsThreads, (size_t)plan.rows_smem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
+        case 16: k_spmv_rows<EPI, 16><<<grid, kRowsThreads, (size_t)plan.rows_smem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
+        default: k_spmv_rows<EPI, 32><<<grid, kRowsThreads, (size_t)plan.rows_smem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
         }
     } else {
         switch (plan.lanes) {

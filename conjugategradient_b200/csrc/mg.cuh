@@ -26,6 +26,7 @@ struct MgLevel {
     double *xcur = nullptr;
     SpmvPlan planA, planP, planR;
     int dims[3] = {0, 0, 0};
+    bool rb = false;       // smoothed by red-black Gauss-Seidel: grid known and every off-diagonal entry joins cells of opposite parity
 };
 
 // arguments of the persistent coarse-tail kernel (mg_tail.cu)
@@ -70,6 +71,8 @@ int scan_counts_checked(mgcg_ctx *c, const int *cnt, int rows, int *rowptr, int 
 // ---- mg_aggregate.cu: aggregation without a grid — strength filter (A -> A_F, 1/diag(A_F)) and MIS-2 aggregates on A_F
 int strength_filter(mgcg_ctx *c, const Csr &A, double theta, DevCsr *F, double **dinvF);
 int mis2_aggregate(mgcg_ctx *c, const Csr &F, int *agg, int *ncoarse, int *rounds_out);
+// 1 when every off-diagonal entry of A (rows = cells of an nx x ny x nz grid) joins cells of opposite parity (ix+iy+iz)&1
+int check_two_colourable(mgcg_ctx *c, const Csr &A, int nx, int ny, int *result);
 // ---- mg_tail.cu
 void mg_tail_plan(mgcg_ctx *c);
 int mg_tail_run(mgcg_ctx *c, int first, double **x_out);

@@ -255,4 +255,38 @@ int mis2_aggregate(mgcg_ctx *c, const Csr &F, int *agg, int *ncoarse, int *round
     return MGCG_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// red-black Gauss-Seidel needs a two-colouring: with rows = cells of a grid, parity (ix + iy + iz) & 1 is one exactly when no
+// off-diagonal entry joins two cells of the same parity (5-/7-point stencils and their plain-aggregation Galerkin products; not
+// the 27-point operator, not a smoothed-aggregation coarse level).
+__global__ void __launch_bounds__(256) k_check_two_colour(Csr A, int nx, int ny, int *bad)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x) {
+        const int pi = ((i % nx) + ((i / nx) % ny) + (i / nx / ny)) & 1;
+        for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k) {
+            const int j = A.col[k];
+            if (j == i) continue;
+            const int pj = ((j % nx) + ((j / nx) % ny) + (j / nx / ny)) & 1;
+            if (pj == pi) { *bad = 1; break; }
+        }
+    }
+}
+
+int check_two_colourable(mgcg_ctx *c, const Csr &A, int nx, int ny, int *result)
+{
+    cudaStream_t st = c->stream;
+    *result = 0;
+    if (nx <= 0 || ny <= 0) return MGCG_OK;
+    int *d_bad = nullptr, bad = 0;
+    MGCG_CUDA(pool_alloc((void **)&d_bad, sizeof(int), st));
+    MGCG_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), st));
+    k_check_two_colour<<<agrid(A.rows, c->sm_count), 256, 0, st>>>(A, nx, ny, d_bad);
+    MGCG_LAUNCH_CHECK();
+    MGCG_CUDA(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));
+    pool_free(d_bad, st);
+    *result = bad ? 0 : 1;
+    return MGCG_OK;
+}
+
 }  // namespace mgcg

@@ -18,6 +18,16 @@ static int jacobi_sweep(mgcg_ctx *c, MgLevel &L, double omega, bool with_dot, in
     return MGCG_OK;
 }
 
+// One red-black Gauss-Seidel half sweep, in place on L.xcur: rows of parity `color` get x_i += D_ii^-1 (b_i - (A x)_i), the others
+// keep x.  with_dot: sum_i b_i x_i over ALL rows goes through `fin` (r.z fused into the cycle's last half sweep).
+static int gs_half_sweep(mgcg_ctx *c, MgLevel &L, int color, bool with_dot, int fin)
+{
+    SpmvArgs a;
+    a.A = L.A; a.x = L.xcur; a.y = L.xcur; a.b = L.b; a.dinv = L.dinv; a.omega = 1.0; a.gated = true; a.fin = fin;
+    a.color = color; a.cnx = L.dims[0]; a.cny = L.dims[1];
+    return spmv_launch(c, L.planA, with_dot ? EPI_JACOBI_DOT : EPI_JACOBI, a);
+}
+
 // z_out receives the level-0 buffer holding z.  fuse_first_done: level 0's first sweep (xa = w D^-1 r) was already
 // produced by cg_update_xr.  rz_fin: FinOp applied to sum_i r_i z_i (fused into the last post-smoothing sweep).
 int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done, int rz_fin)
@@ -46,8 +56,15 @@ int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done
     for (int l = 0; l < down_end; ++l) {
         MgLevel &L = H->L[l];
         L.xcur = L.xa;
-        if (!(l == 0 && fuse_first_done)) MGCG_CHECK(mg_jacobi_first(c, L.A.rows, omega, L.dinv, L.b, L.xa));
-        for (int s = 1; s < pre; ++s) MGCG_CHECK(jacobi_sweep(c, L, omega, false, FIN_STORE));
+        if (!(l == 0 && fuse_first_done)) MGCG_CHECK(mg_jacobi_first(c, L.A.rows, L.rb ? 1.0 : omega, L.dinv, L.b, L.xa));
+        if (L.rb) {
+            // symmetric red-black Gauss-Seidel, red then black on the way down.  From a zero guess the red half sweep is
+            // x_R = D^-1 b_R; x = D^-1 b on every row followed by the black half sweep gives the same x_B = D^-1 (b_B - A_BR x_R)
+            MGCG_CHECK(gs_half_sweep(c, L, 1, false, FIN_STORE));
+            for (int s = 1; s < pre; ++s) { MGCG_CHECK(gs_half_sweep(c, L, 0, false, FIN_STORE)); MGCG_CHECK(gs_half_sweep(c, L, 1, false, FIN_STORE)); }
+        } else {
+            for (int s = 1; s < pre; ++s) MGCG_CHECK(jacobi_sweep(c, L, omega, false, FIN_STORE));
+        }
         SpmvArgs a;
         a.A = L.A; a.x = L.xcur; a.y = L.r; a.b = L.b; a.gated = true;
         MGCG_CHECK(spmv_launch(c, L.planA, EPI_RESID, a));
@@ -72,7 +89,12 @@ int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done
         MGCG_CHECK(spmv_launch(c, L.planP, EPI_AXPBY, a));
         for (int s = 0; s < post; ++s) {
             const bool last = (l == 0 && s == post - 1 && rz_fin >= 0);
-            MGCG_CHECK(jacobi_sweep(c, L, omega, last, last ? rz_fin : FIN_STORE));
+            if (L.rb) {      // black then red on the way up: the adjoint of the pre-smoother, so M stays symmetric
+                MGCG_CHECK(gs_half_sweep(c, L, 1, false, FIN_STORE));
+                MGCG_CHECK(gs_half_sweep(c, L, 0, last, last ? rz_fin : FIN_STORE));
+            } else {
+                MGCG_CHECK(jacobi_sweep(c, L, omega, last, last ? rz_fin : FIN_STORE));
+            }
         }
     }
     if (post == 0 && rz_fin >= 0) MGCG_CHECK(vec_dot(c, H->L[0].A.rows, r, H->L[0].xcur, rz_fin, nullptr));

@@ -598,7 +598,7 @@ int mg_build(mgcg_ctx *c)
     tr.mark(-1, "free-old");
     const mgcg_options &o = c->opt;
     if (o.mg_pre_sweeps < 1 || o.mg_post_sweeps < 0) { set_error("mg_build: mg_pre_sweeps must be >= 1, mg_post_sweeps >= 0"); return MGCG_ERR_INVALID; }
-    if (o.mg_smoother != MGCG_SMOOTHER_JACOBI) { set_error("mg_build: only the weighted-Jacobi smoother is implemented"); return MGCG_ERR_UNSUPPORTED; }
+    if (o.mg_smoother != MGCG_SMOOTHER_JACOBI && o.mg_smoother != MGCG_SMOOTHER_RBGS) { set_error("mg_build: unknown smoother %d", o.mg_smoother); return MGCG_ERR_INVALID; }
     cudaStream_t st = c->stream;
     Hierarchy *H = new Hierarchy();
     c->mg = H;
@@ -621,6 +621,13 @@ int mg_build(mgcg_ctx *c)
         MGCG_LAUNCH_CHECK();
         MGCG_CHECK(alloc_level_vectors(L, l == 0));
         if (n <= coarse_size || l + 1 >= max_levels) break;
+        if (o.mg_smoother == MGCG_SMOOTHER_RBGS && L.dims[0] > 0 && L.planA.kernel == MGCG_SPMV_STREAM) {
+            // red-black Gauss-Seidel where the level's operator is two-colourable by cell parity, weighted Jacobi elsewhere
+            int two = 0;
+            MGCG_CHECK(check_two_colourable(c, L.A, L.dims[0], L.dims[1], &two));
+            L.rb = two != 0;
+            if (tr.on) fprintf(stderr, "[mgcg setup] level %d smoother: %s\n", l, L.rb ? "red-black Gauss-Seidel" : "weighted Jacobi (not two-colourable)");
+        }
 
         // ---- aggregates
         int nc;
@@ -701,6 +708,7 @@ int mg_build(mgcg_ctx *c)
 }
 
 double *mg_level0_first_x(mgcg_ctx *c) { return c->mg ? c->mg->L[0].xa : nullptr; }
+double mg_level0_first_omega(mgcg_ctx *c) { return (c->mg && c->mg->L[0].rb) ? 1.0 : c->opt.mg_omega; }
 const double *mg_level0_dinv(mgcg_ctx *c) { return c->mg ? c->mg->L[0].dinv : nullptr; }
 
 }  // namespace mgcg

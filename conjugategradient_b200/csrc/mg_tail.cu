@@ -140,6 +140,7 @@ void mg_tail_plan(mgcg_ctx *c)
     H->tail_first = -1;
     const int nl = (int)H->L.size();
     if (nl < 2 || c->opt.mg_tail_rows <= 0) return;
+    if (c->opt.mg_smoother != MGCG_SMOOTHER_JACOBI) return;      // the persistent tail kernel knows weighted Jacobi only
     const int limit = c->opt.mg_tail_rows;
     int first = nl - 1;
     while (first > 0 && H->L[first - 1].A.rows <= limit) --first;
