@@ -25,6 +25,7 @@ typedef struct {
     double *dinv, *x, *x2, *b, *r;
     int dims[3];
     int ownA;
+    int rb;      /* smoothed by red-black Gauss-Seidel (mg_ref_set_smoother) */
 } level_t;
 typedef struct { int nl; level_t *L; double *coarse_inv; int coarse_n; } mg_ref_t;
 
@@ -367,6 +368,42 @@ void mg_ref_level_get(const mg_ref_t *H, int l, double *val, int *rowptr, int *c
 }
 void mg_ref_level_agg(const mg_ref_t *H, int l, int *agg) { memcpy(agg, H->L[l].agg, sizeof(int) * (size_t)H->L[l].A.rows); }
 
+/* smoother 0: weighted Jacobi on every level.  1: symmetric red-black Gauss-Seidel (red then black before the coarse correction,
+ * black then red after it) on every level whose rows are the cells of a known grid and whose off-diagonal entries all join cells
+ * of opposite parity (ix + iy + iz) & 1 — 5-/7-point operators; weighted Jacobi on the others (device: csrc/mg_cycle.cu,
+ * k_check_two_colour in csrc/mg_aggregate.cu). */
+static int cell_parity(const level_t *L, int i)
+{
+    int nx = L->dims[0], ny = L->dims[1];
+    return ((i % nx) + ((i / nx) % ny) + (i / nx / ny)) & 1;
+}
+void mg_ref_set_smoother(mg_ref_t *H, int smoother)
+{
+    for (int l = 0; l < H->nl; l++) {
+        level_t *L = &H->L[l];
+        L->rb = 0;
+        if (smoother != 1 || L->dims[0] <= 0 || l == H->nl - 1) continue;
+        int ok = 1;
+        for (int i = 0; i < L->A.rows && ok; i++)
+            for (int k = L->A.rowptr[i]; k < L->A.rowptr[i + 1]; k++)
+                if (L->A.col[k] != i && cell_parity(L, L->A.col[k]) == cell_parity(L, i)) { ok = 0; break; }
+        L->rb = ok;
+    }
+}
+int mg_ref_level_rb(const mg_ref_t *H, int l) { return H->L[l].rb; }
+
+/* in place: rows of parity `color` get x_i += D_ii^-1 (b_i - (A x)_i), row sums in storage order */
+static void gs_half_sweep(level_t *L, int color)
+{
+    const csr_t *A = &L->A;
+    for (int i = 0; i < A->rows; i++) {
+        if (cell_parity(L, i) != color) continue;
+        double s = 0.0;
+        for (int k = A->rowptr[i]; k < A->rowptr[i + 1]; k++) s = s + A->val[k] * L->x[A->col[k]];
+        L->x[i] = L->x[i] + 1.0 * L->dinv[i] * (L->b[i] - s);
+    }
+}
+
 static void jacobi_sweep(level_t *L, double omega)
 {
     const csr_t *A = &L->A;
@@ -383,8 +420,14 @@ void mg_ref_apply(mg_ref_t *H, int pre, int post, double omega, const double *r,
     for (int l = 0; l < nl - 1; l++) {
         level_t *L = &H->L[l];
         int m = L->A.rows;
-        for (int i = 0; i < m; i++) L->x[i] = omega * L->dinv[i] * L->b[i];
-        for (int s = 1; s < pre; s++) jacobi_sweep(L, omega);
+        if (L->rb) {
+            for (int i = 0; i < m; i++) L->x[i] = 1.0 * L->dinv[i] * L->b[i];     /* == the red half sweep from a zero guess, on every row */
+            gs_half_sweep(L, 1);
+            for (int s = 1; s < pre; s++) { gs_half_sweep(L, 0); gs_half_sweep(L, 1); }
+        } else {
+            for (int i = 0; i < m; i++) L->x[i] = omega * L->dinv[i] * L->b[i];
+            for (int s = 1; s < pre; s++) jacobi_sweep(L, omega);
+        }
         ref_spmv(m, L->A.val, L->A.rowptr, L->A.col, L->x, L->r);
         for (int i = 0; i < m; i++) L->r[i] = L->b[i] - L->r[i];
         ref_spmv(L->R.rows, L->R.val, L->R.rowptr, L->R.col, L->r, H->L[l + 1].b);
@@ -403,7 +446,10 @@ void mg_ref_apply(mg_ref_t *H, int pre, int post, double omega, const double *r,
         int m = L->A.rows;
         ref_spmv(m, L->P.val, L->P.rowptr, L->P.col, H->L[l + 1].x, L->x2);
         for (int i = 0; i < m; i++) L->x[i] = 1.0 * L->x2[i] + 1.0 * L->x[i];
-        for (int s = 0; s < post; s++) jacobi_sweep(L, omega);
+        for (int s = 0; s < post; s++) {
+            if (L->rb) { gs_half_sweep(L, 1); gs_half_sweep(L, 0); }
+            else jacobi_sweep(L, omega);
+        }
     }
     memcpy(z, H->L[0].x, sizeof(double) * (size_t)H->L[0].A.rows);
 }

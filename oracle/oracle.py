@@ -211,6 +211,14 @@ class MgRef:
     def levels(self):
         return lib().mg_ref_levels(self.h)
 
+    def set_smoother(self, smoother):
+        """0: weighted Jacobi everywhere; 1: red-black Gauss-Seidel on the two-colourable grid levels (returns their flags)."""
+        L = lib()
+        L.mg_ref_set_smoother.argtypes = [C.c_void_p, C.c_int]
+        L.mg_ref_level_rb.argtypes = [C.c_void_p, C.c_int]
+        L.mg_ref_set_smoother(self.h, smoother)
+        return [bool(L.mg_ref_level_rb(self.h, l)) for l in range(self.levels())]
+
     def level(self, l):
         rows, nnz = C.c_int(), C.c_int()
         lib().mg_ref_level_size(self.h, l, C.byref(rows), C.byref(nnz))

@@ -261,3 +261,65 @@ def test_level_size_overflow_is_refused():
     assert L.mgcg_test_scan_counts(ctx, 1 << 20, 4096, C.byref(nnz)) == _lib.ERR_UNSUPPORTED      # wraps to 0 in 32 bits
     assert b"int32" in L.mgcg_last_error()
     L.mgcg_destroy(ctx)
+
+
+@pytest.mark.parametrize("smoothed,pre,post", [(1, 1, 1), (0, 1, 1), (1, 2, 2), (0, 2, 1)])
+def test_vcycle_rbgs_matches_twin(oracle, gen, smoothed, pre, post):
+    """MGCG_SMOOTHER_RBGS: symmetric red-black Gauss-Seidel (colour-masked in-place half sweeps of the STREAM kernels) on the levels
+    whose operator is two-colourable by cell parity — level 0 of a 7-point grid; every level under plain aggregation — weighted
+    Jacobi on the others.  One V-cycle equals the CPU twin's, and M is symmetric (pre = red, black; post = black, red)."""
+    import torch
+    from conjugategradient_b200 import solver as S
+    n = 20
+    v, rp, c = gen.poisson3d7(n)
+    m = _setup(S, torch, v, rp, c, nx=n, ny=n, nz=n, mg_smoothed=smoothed, mg_pre_sweeps=pre, mg_post_sweeps=post, mg_coarse_size=100,
+               mg_smoother=1)
+    H = oracle.MgRef(v, rp, c, n, n, n, coarse_size=100, smoothed=smoothed)
+    flags = H.set_smoother(1)
+    assert flags[0] and (smoothed == 1 or all(flags[:-1]))
+    rng = np.random.default_rng(9)
+    u, w = rng.standard_normal(n ** 3), rng.standard_normal(n ** 3)
+    tz = torch.empty(n ** 3, dtype=torch.float64, device="cuda")
+    m.mg_apply(torch.as_tensor(u).cuda(), tz); zu = tz.cpu().numpy()
+    m.mg_apply(torch.as_tensor(w).cuda(), tz); zw = tz.cpu().numpy()
+    zt = H.apply(u, pre, post, 0.85)
+    assert np.abs(zu - zt).max() <= 1e-13 * np.abs(zt).max()
+    if pre == post:
+        assert abs(zu @ w - u @ zw) <= 1e-12 * abs(zu @ w)          # M = M^T
+    m.close(); H.close()
+
+
+@pytest.mark.parametrize("name", ["p3d32", "p3d_odd", "p2d128"])
+def test_mgcg_rbgs_matches_twin(oracle, gen, name):
+    import torch
+    from conjugategradient_b200 import solver as S
+    if name == "p3d32":
+        dims = (32, 32, 32); v, rp, c = gen.poisson3d7(32)
+    elif name == "p3d_odd":
+        dims = (37, 21, 18); v, rp, c = gen.poisson3d7(*dims)
+    else:
+        dims = (128, 128, 1); v, rp, c = gen.poisson2d5(128, 128)
+    n = len(rp) - 1
+    b = gen.rhs_uniform(n, 2)
+    out = []
+    for graph in (2, 0):
+        m = _setup(S, torch, v, rp, c, nx=dims[0], ny=dims[1], nz=dims[2], norm=2, tolerance=1e-8, max_iteration=1000, mg_smoother=1, use_graph=graph)
+        tb, tx = torch.as_tensor(b).cuda(), torch.zeros(n, dtype=torch.float64, device="cuda")
+        res = m.solve(tb, tx)
+        out.append((res.iteration, tx.cpu().numpy()))
+        m.close()
+    assert out[0][0] == out[1][0] and np.array_equal(out[0][1], out[1][1])       # graph replay == eager launches, bit for bit
+    H = oracle.MgRef(v, rp, c, *dims)
+    assert H.set_smoother(1)[0]
+    xt, itt, _, st = H.pcg(b, tol=1e-8, norm=oracle.NORM_REL_L2, max_iteration=1000)
+    Hj = oracle.MgRef(v, rp, c, *dims)
+    _, itj, _, _ = Hj.pcg(b, tol=1e-8, norm=oracle.NORM_REL_L2, max_iteration=1000)
+    it, x = out[0]
+    assert st == 0 and abs(it - itt) <= 1, (it, itt)
+    assert itt <= itj                                     # never worse than weighted Jacobi in iterations
+    if it == itt:
+        assert np.abs(x - xt).max() / np.abs(xt).max() <= 1e-10
+    import scipy.sparse as sp
+    A = sp.csr_matrix((v, c, rp))
+    assert np.linalg.norm(b - A @ x) / np.linalg.norm(b) < 2e-8
+    H.close(); Hj.close()

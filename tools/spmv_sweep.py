@@ -8,7 +8,9 @@ import bench
 
 n_side = int(sys.argv[1]) if len(sys.argv) > 1 else 160
 dev = torch.device("cuda:0")
-m = S.Mgcg(0)
+torch.cuda.set_device(dev)
+torch.cuda.set_stream(torch.cuda.Stream(dev))      # torch's events and the library's launches on one stream
+m = S.Mgcg(0, use_torch_stream=True)
 L = m.L
 peak = bench.measured_peak()[0]
 
