@@ -94,6 +94,7 @@ struct SpmvPlan {
     int rows_cap = 2552;            // ROWS: non-zeros a shared-memory stage holds (multiple of 4)
     int rows_stages = 2;            // ROWS: stages in the ring (2..8)
     int rows_smem = 0;              // ROWS: dynamic shared memory of the launch
+    int rows_carveout = 0;          // ROWS: shared-memory share (percent) asked of the unified L1 / shared array
     int grid = 0;
 };
 

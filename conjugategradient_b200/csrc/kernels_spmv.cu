@@ -280,16 +280,12 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
 // its segment from shared memory with stride L and finish with a fixed shuffle tree (deterministic; not the storage order of
 // the STREAM kernels).  The plain VECTOR kernel reads val/col through the same dependent chain rowptr -> (val,col) -> x[col]
 // and measured 0.69 of the HBM peak on the 79-per-row restriction operator.
-// The stage capacity is a launch parameter: the ring always spans kRowsTotal entries (72 KB, 3 blocks per SM), cut into as many
-// stages as the matrix's tiles allow (cap ~ 1.25 x the average tile), because what sets the achieved bandwidth is the number
-// of bytes in flight per SM: the first version (2 stages of 2560) ran at 0.61 of peak on 38-per-row tiles that filled 47 % of a
-// stage and at 0.75 on 124-per-row tiles that filled 77 %.
-constexpr int kRowsTotalDefault = 5120;   // non-zeros the ring holds: (8 + 4) B x 5120 = 60 KB
-constexpr int kRowsTotalMax = 16384;
-constexpr int kRowsCtasDefault = 3;       // blocks per SM the grid is sized for
+// Stage capacity, stage count and resident blocks per SM are launch parameters (spmv_make_plan): the sweep over them on the
+// particle matrices (profiles/r02_spmv_rows_sweep.txt) showed the kernel short of independent x gathers in flight rather than of
+// staged bytes — 2 -> 5 resident blocks per SM took the 35-per-row matrix from 0.42 to 0.81 of the HBM peak with the same ring.
+constexpr int kRowsTotalMax = 16384;      // non-zeros the ring may hold: (8 + 4) B x 16384 = 192 KB
 constexpr int kRowsMaxStages = 8;
 constexpr int kRowsThreads = 256;
-constexpr size_t kRowsSmemMax = (size_t)kRowsTotalMax * 12 + (size_t)kRowsMaxStages * 64 + 64;
 
 template <int EPI, int L>
 __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_tiles, int cap, int stages, ReduceWs ws, Scalars *sc)
@@ -439,33 +435,34 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel)
     }
     p.kernel = kernel;
     if (kernel == MGCG_SPMV_ROWS) {
-        // L lanes per row (4..32, at most ~8 entries per lane) and the cut of the ring into stages: the candidate with the most
-        // non-zeros in flight (stages x average tile) wins, the smaller L on ties.  A stage holds 1.1 x the average tile + 16.
-        // Tuning knobs (tools/spmv_sweep.py): MGCG_ROWS_TOTAL (ring entries), MGCG_ROWS_CTAS (blocks per SM), MGCG_ROWS_LANES.
-        int total = kRowsTotalDefault, ctas = kRowsCtasDefault, forceL = 0;
-        if (const char *e = getenv("MGCG_ROWS_TOTAL")) total = atoi(e);
+        // Shape chosen from the sweep in profiles/r02_spmv_rows_sweep.txt (tools/spmv_sweep.py): what the kernel is short of is
+        // independent gathers in flight, not staged bytes — so as many resident blocks as fit (up to 5 per SM), a small ring of 2
+        // stages, and L = the smallest power of two that leaves a lane at most ~8 entries of its row.
+        // Tuning knobs: MGCG_ROWS_LANES, MGCG_ROWS_STAGES, MGCG_ROWS_CAPF (stage capacity / average tile), MGCG_ROWS_CTAS.
+        int L = 4, stages = 2, ctas = 0;
+        double capf = 1.3;
+        while (L < 32 && avg > 8.0 * L) L <<= 1;
+        if (const char *e = getenv("MGCG_ROWS_LANES")) { const int v = atoi(e); if (v == 4 || v == 8 || v == 16 || v == 32) L = v; }
+        if (const char *e = getenv("MGCG_ROWS_STAGES")) { const int v = atoi(e); if (v >= 2 && v <= kRowsMaxStages) stages = v; }
+        if (const char *e = getenv("MGCG_ROWS_CAPF")) { const double v = atof(e); if (v >= 1.0 && v <= 4.0) capf = v; }
         if (const char *e = getenv("MGCG_ROWS_CTAS")) ctas = atoi(e);
-        if (const char *e = getenv("MGCG_ROWS_LANES")) forceL = atoi(e);
-        if (total < 512) total = 512;
-        if (total > kRowsTotalMax) total = kRowsTotalMax;
+        const double tile = (double)(kRowsThreads / L) * avg;
+        long long capn = (long long)(capf * tile) + 16;
+        capn = (capn + 3) & ~3LL;
+        if (capn < 256) capn = 256;
+        while (stages > 2 && capn * stages > kRowsTotalMax) --stages;
+        if (capn * stages > kRowsTotalMax) capn = (kRowsTotalMax / stages) & ~3;       // tiles that do not fit take the direct path
+        p.lanes = L;
+        p.rows_stages = stages;
+        p.rows_cap = (int)capn;
+        p.rows_smem = (int)((size_t)stages * ((capn + 2) * 8 + (capn + 4) * 4) + (size_t)kRowsMaxStages * 64 + 64);
+        const int fit = (int)((224 * 1024) / (p.rows_smem + 1536));
+        if (ctas <= 0) ctas = fit < 5 ? fit : 5;
+        if (ctas > fit) ctas = fit;
         if (ctas < 1) ctas = 1;
-        int bestL = 0, best_st = 0;
-        double best_fly = -1.0;
-        for (int L = 4; L <= 32; L <<= 1) {
-            if (forceL > 0 ? (L != forceL) : (avg > 8.0 * L && L < 32)) continue;
-            const double tile = (double)(kRowsThreads / L) * avg;
-            int st = (int)(total / (1.1 * tile + 16.0));
-            if (st > kRowsMaxStages) st = kRowsMaxStages;
-            if (st < 2) st = 2;
-            const double fly = st * (tile < total / 2 ? tile : total / 2);
-            if (fly > best_fly * 1.02) { best_fly = fly; bestL = L; best_st = st; }
-        }
-        if (bestL == 0) { bestL = 32; best_st = 2; }
-        p.lanes = bestL;
-        p.rows_stages = best_st;
-        p.rows_cap = ((total / best_st) & ~3) - 4;
-        p.rows_smem = (int)((size_t)total * 12 + (size_t)kRowsMaxStages * 64 + 64);
-        const int tiles = div_up(rows > 0 ? rows : 1, kRowsThreads / bestL);
+        p.rows_carveout = (int)(((long long)ctas * (p.rows_smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
+        if (p.rows_carveout > 100) p.rows_carveout = 100;
+        const int tiles = div_up(rows > 0 ? rows : 1, kRowsThreads / L);
         int gcap = c->sm_count * ctas;
         p.grid = tiles < gcap ? tiles : gcap;
         if (p.grid < 1) p.grid = 1;
@@ -494,6 +491,38 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel)
     return p;
 }
 
+// Dynamic shared memory of the rows kernel: the opt-in limit is raised only as far as a launch needs (per instantiation and
+// device), and the L1 / shared-memory split is asked for explicitly — blocks_per_sm x (ring + 1 KB) of shared memory, the rest
+// stays L1 for the x gathers.  (A limit set once to the largest ring made every launch run with the smallest L1.)
+template <int EPI, int L>
+static int rows_prepare_one(mgcg_ctx *c, const SpmvPlan &plan)
+{
+    static int set_bytes[64] = {0};
+    static int set_carve[64] = {0};
+    const int d = c->device & 63;
+    if (plan.rows_smem > set_bytes[d]) {
+        MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, L>, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.rows_smem));
+        set_bytes[d] = plan.rows_smem;
+    }
+    int carve = plan.rows_carveout;
+    if (const char *e = getenv("MGCG_ROWS_CARVEOUT")) carve = atoi(e);
+    if (carve != set_carve[d] && carve > 0) {
+        MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, L>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+        set_carve[d] = carve;
+    }
+    return MGCG_OK;
+}
+template <int EPI>
+static int rows_prepare(mgcg_ctx *c, const SpmvPlan &plan)
+{
+    switch (plan.lanes) {
+    case 4: return rows_prepare_one<EPI, 4>(c, plan);
+    case 8: return rows_prepare_one<EPI, 8>(c, plan);
+    case 16: return rows_prepare_one<EPI, 16>(c, plan);
+    default: return rows_prepare_one<EPI, 32>(c, plan);
+    }
+}
+
 template <int EPI>
 static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
 {
@@ -513,22 +542,7 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
         int tiles = div_up(a.A.rows, plan.rows_per_tile);
         k_spmv_stream<EPI><<<plan.grid, kSpmvThreads, 0, c->stream>>>(a, plan.rows_per_tile, tiles, c->ws, c->d_scalars);
     } else if (plan.kernel == MGCG_SPMV_ROWS && aligned) {
-        static unsigned long long attr_done = 0ull;      // per template instantiation, one bit per device (the attribute is per device)
-        const unsigned long long dev_bit = 1ull << (c->device & 63);
-        if (!(attr_done & dev_bit)) {
-            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmemMax));
-            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmemMax));
-            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmemMax));
-            MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRowsSmemMax));
-            if (const char *e = getenv("MGCG_ROWS_CARVEOUT")) {     // tuning: percent of the unified L1/shared array given to shared memory
-                const int pc = atoi(e);
-                cudaFuncSetAttribute(k_spmv_rows<EPI, 4>, cudaFuncAttributePreferredSharedMemoryCarveout, pc);
-                cudaFuncSetAttribute(k_spmv_rows<EPI, 8>, cudaFuncAttributePreferredSharedMemoryCarveout, pc);
-                cudaFuncSetAttribute(k_spmv_rows<EPI, 16>, cudaFuncAttributePreferredSharedMemoryCarveout, pc);
-                cudaFuncSetAttribute(k_spmv_rows<EPI, 32>, cudaFuncAttributePreferredSharedMemoryCarveout, pc);
-            }
-            attr_done |= dev_bit;
-        }
+        MGCG_CHECK(rows_prepare<EPI>(c, plan));
         const int L = plan.lanes;
         const int tiles = div_up(a.A.rows, kRowsThreads / L);
         int grid = plan.grid;

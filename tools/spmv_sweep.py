@@ -1,8 +1,9 @@
-"""Sweep of the rows SpMV kernel's launch shape (ring size, blocks per SM, lanes per row) on the C3 particle matrices, isolated
-SpMV+dot launches back to back.  One-off tuning tool: python tools/spmv_sweep.py [n_side] > gpurun_out/spmv_sweep.txt"""
-import ctypes as C, itertools, json, os, sys
+"""Sweep of the rows SpMV kernel's launch shape (lanes per row, stages, stage capacity, blocks per SM, L1 carve-out) on the C3
+particle matrices; isolated SpMV+dot launches back to back on the library's stream.
+One-off tuning tool: python tools/spmv_sweep.py [n_side] > gpurun_out/spmv_sweep.txt"""
+import itertools, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np, torch
+import torch
 from conjugategradient_b200 import solver as S, device_generators as dg
 import bench
 
@@ -13,6 +14,7 @@ torch.cuda.set_stream(torch.cuda.Stream(dev))      # torch's events and the libr
 m = S.Mgcg(0, use_torch_stream=True)
 L = m.L
 peak = bench.measured_peak()[0]
+KNOBS = ("MGCG_ROWS_LANES", "MGCG_ROWS_STAGES", "MGCG_ROWS_CAPF", "MGCG_ROWS_CTAS", "MGCG_ROWS_CARVEOUT")
 
 
 def timeit(tv, tr, tc, n, nnz, kernel, reps=10):
@@ -29,27 +31,38 @@ def timeit(tv, tr, tc, n, nnz, kernel, reps=10):
     return ms, (12.0 * nnz + 20.0 * n) / (ms * 1e-3) / 1e9
 
 
+def clear():
+    for v in KNOBS:
+        os.environ.pop(v, None)
+
+
 for re in (2.1, 3.1):
     pos = torch.from_numpy(bench.mps_positions(n_side)).to(dev)
     tv, tr, tc, order, _ = dg.mps_particles(m.ctx, pos, re, shift_abs=1.0, max_per_row=1 << 20)
     del pos, order
     n, nnz = tr.numel() - 1, tv.numel()
     print(f"== MPS {n_side}^3 re={re}: rows {n} nnz {nnz} avg {nnz / n:.1f}", flush=True)
-    for k, name in ((2, "vector"), (1, "stream")):
-        for v in ("MGCG_ROWS_TOTAL", "MGCG_ROWS_CTAS", "MGCG_ROWS_LANES", "MGCG_ROWS_CARVEOUT"):
-            os.environ.pop(v, None)
+    clear()
+    for k, name in ((2, "vector"), (1, "stream"), (3, "rows (library default shape)")):
         ms, gbs = timeit(tv, tr, tc, n, nnz, k)
-        print(f"  {name:28s} {ms:8.3f} ms {gbs:7.0f} GB/s  {gbs / peak:.3f}", flush=True)
+        print(f"  {name:34s} {ms:8.3f} ms {gbs:7.0f} GB/s  {gbs / peak:.3f}", flush=True)
     res = []
-    for total, ctas, lanes in itertools.product((2560, 3584, 4096, 5120, 6144, 8192), (2, 3, 4, 5), (8, 16, 32)):
-        if (total * 12 + 1600) * ctas > 226 * 1024:
-            continue
-        os.environ["MGCG_ROWS_TOTAL"] = str(total); os.environ["MGCG_ROWS_CTAS"] = str(ctas); os.environ["MGCG_ROWS_LANES"] = str(lanes)
-        ms, gbs = timeit(tv, tr, tc, n, nnz, 3)
-        res.append((gbs, total, ctas, lanes, ms))
-        print(f"  rows total={total:5d} ctas={ctas} L={lanes:2d}   {ms:8.3f} ms {gbs:7.0f} GB/s  {gbs / peak:.3f}", flush=True)
+    lanes_set = (4, 8, 16) if re < 3 else (8, 16, 32)
+    for lanes, stages, capf, ctas in itertools.product(lanes_set, (2, 3, 4), (1.15, 1.3, 1.6), (2, 3, 4, 5, 6)):
+        clear()
+        os.environ.update({"MGCG_ROWS_LANES": str(lanes), "MGCG_ROWS_STAGES": str(stages), "MGCG_ROWS_CAPF": str(capf), "MGCG_ROWS_CTAS": str(ctas)})
+        ms, gbs = timeit(tv, tr, tc, n, nnz, 3, reps=6)
+        res.append((gbs, lanes, stages, capf, ctas, ms))
+        print(f"  rows L={lanes:2d} stages={stages} capf={capf:4.2f} ctas={ctas}   {ms:8.3f} ms {gbs:7.0f} GB/s  {gbs / peak:.3f}", flush=True)
     res.sort(reverse=True)
-    print("  best:", res[:5], flush=True)
-    # carve-out preference on the best shape (attribute is set once per process and instantiation: last step of the loop)
+    print("  best:", [tuple(round(v, 3) if isinstance(v, float) else v for v in r) for r in res[:6]], flush=True)
+    gbs, lanes, stages, capf, ctas, _ = res[0]
+    for carve in (50, 65, 80, 100):
+        clear()
+        os.environ.update({"MGCG_ROWS_LANES": str(lanes), "MGCG_ROWS_STAGES": str(stages), "MGCG_ROWS_CAPF": str(capf), "MGCG_ROWS_CTAS": str(ctas),
+                           "MGCG_ROWS_CARVEOUT": str(carve)})
+        ms, gbs = timeit(tv, tr, tc, n, nnz, 3, reps=6)
+        print(f"  best shape, carve-out {carve:3d} %   {ms:8.3f} ms {gbs:7.0f} GB/s  {gbs / peak:.3f}", flush=True)
+    clear()
     del tv, tr, tc
     torch.cuda.empty_cache()
