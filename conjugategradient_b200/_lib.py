@@ -46,7 +46,7 @@ NATIVE_SYMBOLS = [
     "mgcg_setup", "mgcg_solve", "mgcg_solve_host", "mgcg_spmv", "mgcg_spmv_dot", "mgcg_dot", "mgcg_max_abs",
     "mgcg_axpy", "mgcg_scal", "mgcg_copy", "mgcg_update_xr", "mgcg_update_p", "mgcg_mg_levels", "mgcg_mg_level_size",
     "mgcg_mg_level_get", "mgcg_mg_level_aggregates", "mgcg_mg_apply", "mgcg_partition_offsets",
-    "mgcg_comm_unique_id", "mgcg_comm_init", "mgcg_setup_dist", "mgcg_solve_dist", "mgcg_solve_host_dist", "mgcg_dist_microbench",
+    "mgcg_comm_unique_id", "mgcg_comm_init", "mgcg_setup_dist", "mgcg_solve_dist", "mgcg_solve_host_dist", "mgcg_comm_finalize", "mgcg_dist_microbench",
     "mgcg_generate_poisson3d7_nnz", "mgcg_generate_poisson3d7", "mgcg_generate_poisson3d27_nnz", "mgcg_generate_poisson3d27",
     "mgcg_mps_order", "mgcg_mps_count", "mgcg_mps_fill", "mgcg_test_scan_counts",
 ]
@@ -117,6 +117,7 @@ def lib():
     L.mgcg_solve_dist.argtypes = [vp, vp, vp, C.POINTER(Result)]
     L.mgcg_solve_host_dist.argtypes = [vp, ci, ci, ci, ci, vp, vp, vp, vp, vp, C.POINTER(Options), C.POINTER(Result)]
     L.mgcg_dist_microbench.argtypes = [vp, ci, dp]
+    L.mgcg_comm_finalize.argtypes = [vp]
     L.mgcg_generate_poisson3d7_nnz.argtypes = [ci] * 5; L.mgcg_generate_poisson3d7_nnz.restype = C.c_longlong
     L.mgcg_generate_poisson3d7.argtypes = [vp] + [ci] * 5 + [vp, vp, vp]
     L.mgcg_generate_poisson3d27_nnz.argtypes = [ci] * 5; L.mgcg_generate_poisson3d27_nnz.restype = C.c_longlong

@@ -75,7 +75,7 @@ void dist_free(mgcg_ctx *c)
     DistState *D = c->dist;
     if (!D) return;
     dist_graph_free(D);
-    peer_close(c);
+    peer_close(c, false);
     dist_free_levels(D);
     if (D->coarse_spare) { mgcg_destroy(D->coarse_spare); D->coarse_spare = nullptr; }
     if (D->partial_send) cudaFree(D->partial_send);
@@ -469,7 +469,7 @@ static int dist_open_transport(mgcg_ctx *c)
         if (e && !strcmp(e, "nccl")) want = MGCG_TRANSPORT_NCCL;
         else if (e && !strcmp(e, "peer")) want = MGCG_TRANSPORT_PEER;
     }
-    if (D->world < 2 || want == MGCG_TRANSPORT_NCCL) { peer_close(c); return MGCG_OK; }
+    if (D->world < 2 || want == MGCG_TRANSPORT_NCCL) { peer_close(c, D->world >= 2); return MGCG_OK; }
     int halo_cap = 0;
     for (size_t l = 0; l < D->L.size(); ++l) if (D->L[l].halo > halo_cap && D->L[l].halo < 0x3fffffff) halo_cap = D->L[l].halo;
     MGCG_CHECK(peer_open(c, halo_cap, D->coarse ? D->coarse_n : 0));
@@ -813,6 +813,8 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     MGCG_CUDA(cudaMemcpyAsync(c->d_scalars, &c->h_scalars[0], sizeof(Scalars), cudaMemcpyHostToDevice, st));
     MGCG_CUDA(cudaEventRecord(ev0, st));
     double *p_own = D->p + L0.lo, *r_own = D->r + L0.lo;
+    // rendezvous: ranks enter a solve with arbitrary host skew; the first wait of the peer transport must not time a late rank out
+    if (D->peer.active) MGCG_CHECK(peer_reduce(c, -1, 1, false, 64));
     // init: Ap = A x0 (x0 staged through p's ghosts), r = b - Ap, p = r or M r, r.r [, r.z]   (Solve0, cs:436-463)
     MGCG_CUDA(cudaMemcpyAsync(p_own, x, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, st));
     MGCG_CHECK(dist_halo_exchange(c, D->p, n, L0.lo, L0.hi, L0.halo));
@@ -1067,4 +1069,18 @@ extern "C" int mgcg_solve_host_dist(mgcg_ctx *c, int global_count, int row_offse
     MGCG_CUDA(cudaMemcpyAsync(x_local, h->x, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
     MGCG_CUDA(cudaStreamSynchronize(st));
     return s;
+}
+
+// Collective teardown of the peer transport: every rank unmaps its peers' arenas, all ranks rendezvous, then each frees its own
+// arena (cudaFree of memory another process still has open is undefined).  Call on every rank before mgcg_destroy
+// when the ranks are separate processes; mgcg_destroy alone frees without a rendezvous.
+extern "C" int mgcg_comm_finalize(mgcg_ctx *c)
+{
+    if (!c) { set_error("mgcg_comm_finalize: null context"); return MGCG_ERR_INVALID; }
+    if (!c->dist) return MGCG_OK;
+    MGCG_CUDA(cudaSetDevice(c->device));
+    dist_graph_free(c->dist);
+    peer_close(c, true);
+    c->is_setup = false;
+    return MGCG_OK;
 }

@@ -163,10 +163,10 @@ __device__ __forceinline__ void dist_finalize(int mode, double s0, double s1, Sc
 
 // peer.cu
 int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap);   // collective; leaves peer.active = false if any rank cannot map
-void peer_close(mgcg_ctx *c);
+void peer_close(mgcg_ctx *c, bool collective);
 int peer_halo_exchange(mgcg_ctx *c, double *v_ext, int own, int lo, int hi, int halo);
 int peer_allgather(mgcg_ctx *c, double *full, const int *offs);
-int peer_reduce(mgcg_ctx *c, int mode, int k, bool gated);
+int peer_reduce(mgcg_ctx *c, int mode, int k, bool gated, int wait_scale = 1);
 
 // dist.cu
 int dist_halo_exchange(mgcg_ctx *c, double *v_ext, int own, int lo, int hi, int halo);

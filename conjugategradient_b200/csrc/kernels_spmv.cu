@@ -286,6 +286,7 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
 constexpr int kRowsTotalMax = 16384;      // non-zeros the ring may hold: (8 + 4) B x 16384 = 192 KB
 constexpr int kRowsMaxStages = 8;
 constexpr int kRowsThreads = 256;
+constexpr int kRowsUnroll = 8;             // entries a lane takes per chunk (gathers in flight per lane)
 
 template <int EPI, int L>
 __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_tiles, int cap, int stages, ReduceWs ws, Scalars *sc)
@@ -361,8 +362,25 @@ __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_
                 const int k0 = s_meta[s].k0;
                 const double *sv = s_val + (size_t)s * (cap + 2) - (k0 & ~1);
                 const int *scl = s_col + (size_t)s * (cap + 4) - (k0 & ~3);
-#pragma unroll 4
-                for (int k = rs + lane; k < re; k += L) acc += sv[k] * x[scl[k]];
+                // chunks of kRowsUnroll entries per lane: all the column indices first, then all the x gathers (independent loads in
+                // flight together — the ncu source page of the first version showed the lanes stalled on the gathers' long
+                // scoreboard, four at a time), then the products on two accumulators
+                double acc1 = 0.0;
+                for (int kb = rs + lane; kb < re; kb += kRowsUnroll * L) {
+                    int cc[kRowsUnroll];
+                    double xv[kRowsUnroll];
+#pragma unroll
+                    for (int u = 0; u < kRowsUnroll; ++u) { const int k = kb + u * L; cc[u] = scl[k < re ? k : kb]; }
+#pragma unroll
+                    for (int u = 0; u < kRowsUnroll; ++u) xv[u] = x[cc[u]];
+#pragma unroll
+                    for (int u = 0; u < kRowsUnroll; u += 2) {
+                        const int ka = kb + u * L, kc = ka + L;
+                        acc += (ka < re ? sv[ka] : 0.0) * xv[u];
+                        acc1 += (kc < re ? sv[kc] : 0.0) * xv[u + 1];
+                    }
+                }
+                acc += acc1;
             } else {
 #pragma unroll 4
                 for (int k = rs + lane; k < re; k += L) acc += __ldcs(val + k) * x[__ldcs(col + k)];

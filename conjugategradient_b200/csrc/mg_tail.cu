@@ -173,9 +173,17 @@ int mg_tail_run(mgcg_ctx *c, int first, double **x_out)
             T.xfinal = M.xa; M.xcur = M.xa;
         }
     }
-    k_mg_tail<<<c->sm_count, kTailThreads, 0, c->stream>>>(a, c->d_scalars);
+    // The blocks wait on one another at the hand-rolled grid barrier, so every one of them must be resident: size the grid from
+    // the occupancy the device reports and launch cooperatively (the driver then refuses a grid that cannot be co-resident
+    // instead of letting it hang behind another tenant of the device).
+    int per_sm = 0;
+    MGCG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_mg_tail, kTailThreads, 0));
+    if (per_sm < 1) { set_error("mg_tail_run: the persistent tail kernel does not fit on this device"); return MGCG_ERR_UNSUPPORTED; }
+    const int grid = c->sm_count;      // one block per SM (<= per_sm * sm_count by the check above)
+    const Scalars *scp = c->d_scalars;
+    void *args[] = {(void *)&a, (void *)&scp};
+    MGCG_CUDA(cudaLaunchCooperativeKernel((const void *)k_mg_tail, dim3(grid), dim3(kTailThreads), args, 0, c->stream));
     c->launches++;
-    MGCG_LAUNCH_CHECK();
     *x_out = a.L[0].xfinal;
     return MGCG_OK;
 }

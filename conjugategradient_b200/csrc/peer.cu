@@ -46,12 +46,19 @@ __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned lon
     return v;
 }
 
-// true when the flag reached `seq`; false after ~4 s (clock64 at <= 2 GHz)
-__device__ __forceinline__ bool wait_flag(const unsigned long long *flag, unsigned long long seq)
+// Clocks a wait may last before the solve is marked MGCG_ERR_COMM instead of hanging the device: ~4 s at 2 GHz by default,
+// MGCG_PEER_TIMEOUT_S overrides (peer_open).  The rendezvous at the start of every solve waits 64 x longer: ranks enter a
+// solve with whatever skew their hosts have (a first-call graph instantiation, a profiler, a debugger), and a rank that is
+// merely late must not fail its peers — inside the loop the ranks are already in step and a long wait means a dead peer.
+__device__ long long g_peer_wait_clocks = 8000000000ll;
+
+// true when the flag reached `seq`; false after the time limit
+__device__ __forceinline__ bool wait_flag(const unsigned long long *flag, unsigned long long seq, long long scale = 1)
 {
     const long long t0 = clock64();
+    const long long limit = g_peer_wait_clocks * scale;
     while (ld_acquire_sys(flag) < seq) {
-        if (clock64() - t0 > 8000000000ll) return false;
+        if (clock64() - t0 > limit) return false;
         __nanosleep(32);
     }
     return true;
@@ -115,7 +122,7 @@ __global__ void __launch_bounds__(256) k_peer_exchange(XchgDesc d, PeerCtl *ctl,
 
 // scalar all-reduction + the CG bookkeeping that follows it, one block.  `mine` holds this rank's k partial sums.
 __global__ void __launch_bounds__(64) k_peer_reduce(int mode, int k, int rank, int world, PeerPtrs pp, const double *__restrict__ mine,
-                                                   Scalars *sc, bool gated)
+                                                   Scalars *sc, bool gated, int wait_scale)
 {
     if (gated && sc->done) return;
     __shared__ double s_v[kPeerMax][2];
@@ -132,7 +139,7 @@ __global__ void __launch_bounds__(64) k_peer_reduce(int mode, int k, int rank, i
         q->rslot[par][rank][1] = k > 1 ? mine[1] : 0.0;
         __threadfence_system();
         st_release_sys(&q->rflag[rank], seq);
-        if (!wait_flag(&me->rflag[t], seq)) s_fail = 1;
+        if (!wait_flag(&me->rflag[t], seq, wait_scale)) s_fail = 1;
         s_v[t][0] = __ldcg(&me->rslot[par][t][0]);
         s_v[t][1] = __ldcg(&me->rslot[par][t][1]);
     }
@@ -215,12 +222,12 @@ int peer_allgather(mgcg_ctx *c, double *full, const int *offs)
     return peer_exchange_launch(c, d, true);
 }
 
-int peer_reduce(mgcg_ctx *c, int mode, int k, bool gated)
+int peer_reduce(mgcg_ctx *c, int mode, int k, bool gated, int wait_scale)
 {
     DistState *D = c->dist;
     PeerPtrs pp;
     for (int q = 0; q < kPeerMax; ++q) pp.ctl[q] = (PeerCtl *)(q < D->world ? D->peer.peer[q] : nullptr);
-    k_peer_reduce<<<1, 64, 0, c->stream>>>(mode, k, D->rank, D->world, pp, D->partial_send, c->d_scalars, gated);
+    k_peer_reduce<<<1, 64, 0, c->stream>>>(mode, k, D->rank, D->world, pp, D->partial_send, c->d_scalars, gated, wait_scale);
     c->launches++;
     MGCG_LAUNCH_CHECK();
     return MGCG_OK;
@@ -228,14 +235,29 @@ int peer_reduce(mgcg_ctx *c, int mode, int k, bool gated)
 
 // ---------------------------------------------------------------------------------------------------------
 // arena life cycle
-void peer_close(mgcg_ctx *c)
+// Unmap the peers' arenas, then free this rank's own.  CUDA leaves freeing memory that another process still has open through
+// cudaIpcOpenMemHandle undefined, and a peer may still be storing into it: `collective` = true (every rank is inside the same
+// call: a re-setup, mgcg_comm_finalize) puts an NCCL all-reduce between the two steps, so that nobody frees before everybody
+// has unmapped and drained.  Teardown through mgcg_destroy alone cannot assume the other ranks are there (one may have
+// failed): callers that share arenas across processes call mgcg_comm_finalize on every rank first (include/mgcg.h).
+void peer_close(mgcg_ctx *c, bool collective)
 {
     DistState *D = c->dist;
     if (!D) return;
     PeerState &P = D->peer;
+    if (c->stream) cudaStreamSynchronize(c->stream);
     for (int q = 0; q < kPeerMax; ++q) {
         if (P.peer[q] && P.mapped[q]) cudaIpcCloseMemHandle(P.peer[q]);
         P.peer[q] = nullptr; P.mapped[q] = false;
+    }
+    if (collective && P.arena && D->comm && D->api && D->world > 1) {
+        int *d_flag = nullptr;
+        if (cudaMalloc((void **)&d_flag, sizeof(int)) == cudaSuccess) {
+            cudaMemsetAsync(d_flag, 0, sizeof(int), c->stream);
+            D->api->AllReduce(d_flag, d_flag, 1, ncclInt, ncclSum, D->comm, c->stream);
+            cudaStreamSynchronize(c->stream);
+            cudaFree(d_flag);
+        }
     }
     if (P.arena) cudaFree(P.arena);
     P = PeerState();
@@ -258,7 +280,7 @@ int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
     cudaStream_t st = c->stream;
     const int W = D->world, rk = D->rank;
     P.active = false;
-    if (W < 2 || W > kPeerMax) { peer_close(c); return MGCG_OK; }
+    if (W < 2 || W > kPeerMax) { peer_close(c, false); return MGCG_OK; }
     halo_cap = (halo_cap + 1) & ~1;
     // A re-setup keeps the arena and its mappings when the new hierarchy fits (allocating and IPC-mapping with 7 peers costs
     // tens of milliseconds): every rank clears its own flags / sequence numbers, and the all-reduce that takes the decision
@@ -275,7 +297,17 @@ int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
         pool_release(d_flag);
         if (reuse) { P.active = true; return MGCG_OK; }
     }
-    peer_close(c);
+    peer_close(c, true);      // collective: every rank takes this branch together (the all-reduce above decided it)
+    {   // wait limit of the flag spins (seconds -> clocks at the device's clock rate)
+        long long clocks = 8000000000ll;
+        if (const char *e = getenv("MGCG_PEER_TIMEOUT_S")) {
+            const double sec = atof(e);
+            int khz = 0;
+            cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, c->device);
+            if (sec > 0 && khz > 0) clocks = (long long)(sec * 1e3 * (double)khz);
+        }
+        MGCG_CUDA(cudaMemcpyToSymbol(g_peer_wait_clocks, &clocks, sizeof(clocks)));
+    }
     // halo and gather staging are DISJOINT: a gather is pushed by every rank, also by ranks that are not this rank's
     // neighbours and have therefore not synchronised with it in the halo exchanges just before — their blocks must not land
     // where a slower rank may still be unpacking a halo of two exchanges ago (seen as a changed iteration count at 8 GPUs)
@@ -329,7 +361,7 @@ int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
     MGCG_CUDA(cudaMemcpyAsync(&ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost, st));
     MGCG_CUDA(cudaStreamSynchronize(st));
     cudaFree(d_all);
-    if (!ok) { peer_close(c); return MGCG_OK; }
+    if (!ok) { peer_close(c, true); return MGCG_OK; }      // every rank sees the same `ok`
     P.active = true; P.ready = true;
     return MGCG_OK;
 }
@@ -355,7 +387,7 @@ extern "C" int mgcg_dist_microbench(mgcg_ctx *c, int reps, double *out_us)
         MGCG_CUDA(cudaEventRecord(e[1], c->stream));
         if (D->coarse) for (int i = 0; i < reps; ++i) MGCG_CHECK(D->peer.active ? peer_allgather(c, D->coarse_b, D->coarse_offs) : MGCG_OK);
         MGCG_CUDA(cudaEventRecord(e[2], c->stream));
-        if (D->peer.active) for (int i = 0; i < reps; ++i) MGCG_CHECK(peer_reduce(c, -1, 2, false));
+        if (D->peer.active) for (int i = 0; i < reps; ++i) MGCG_CHECK(peer_reduce(c, -1, 2, false, 1));
         MGCG_CUDA(cudaEventRecord(e[3], c->stream));
         MGCG_CUDA(cudaStreamSynchronize(c->stream));
     }

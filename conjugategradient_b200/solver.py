@@ -368,6 +368,7 @@ class MgcgDist:
 
     def close(self):
         if self.ctx:
+            self.L.mgcg_comm_finalize(self.ctx)     # collective: unmap peers, rendezvous, free (every rank closes together)
             self.L.mgcg_destroy(self.ctx)
             self.ctx = None
 

@@ -206,6 +206,9 @@ int mgcg_solve_dist(mgcg_ctx *c, const double *d_b_local, double *d_x_local, mgc
 int mgcg_solve_host_dist(mgcg_ctx *c, int global_count, int row_offset, int local_count, int local_elements_count,
                          const double *elements, const int *row_offsets, const int *column_indeces,
                          const double *b_local, double *x_local, const mgcg_options *opt, mgcg_result *res);
+/* collective teardown of the peer-memory transport (unmap the peers' arenas, rendezvous, free the own arena): call on every rank
+ * before mgcg_destroy when the ranks are separate processes.  A later mgcg_setup_dist re-opens the transport. */
+int mgcg_comm_finalize(mgcg_ctx *c);
 /* collective micro-benchmark of the loop's exchanges after mgcg_setup_dist: microseconds per level-0 halo exchange,
  * per coarse all-gather and per scalar reduction (back to back, `reps` each) */
 int mgcg_dist_microbench(mgcg_ctx *c, int reps, double *out_us /* [3] */);

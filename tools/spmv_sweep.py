@@ -48,7 +48,8 @@ for re in (2.1, 3.1):
         print(f"  {name:34s} {ms:8.3f} ms {gbs:7.0f} GB/s  {gbs / peak:.3f}", flush=True)
     res = []
     lanes_set = (4, 8, 16) if re < 3 else (8, 16, 32)
-    for lanes, stages, capf, ctas in itertools.product(lanes_set, (2, 3, 4), (1.15, 1.3, 1.6), (2, 3, 4, 5, 6)):
+    quick = os.environ.get("SWEEP_QUICK") is not None
+    for lanes, stages, capf, ctas in itertools.product(lanes_set, (2,) if quick else (2, 3, 4), (1.3,) if quick else (1.15, 1.3, 1.6), (3, 4, 5, 6) if quick else (2, 3, 4, 5, 6)):
         clear()
         os.environ.update({"MGCG_ROWS_LANES": str(lanes), "MGCG_ROWS_STAGES": str(stages), "MGCG_ROWS_CAPF": str(capf), "MGCG_ROWS_CTAS": str(ctas)})
         ms, gbs = timeit(tv, tr, tc, n, nnz, 3, reps=6)
