@@ -93,6 +93,7 @@ struct SpmvPlan {
     int lanes = 8;                  // VECTOR / ROWS: lanes per row
     int rows_cap = 2552;            // ROWS: non-zeros a shared-memory stage holds (multiple of 4)
     int rows_stages = 2;            // ROWS: stages in the ring (2..8)
+    int rows_unroll = 4;            // ROWS: entries a lane takes per chunk (4 or 8)
     int rows_smem = 0;              // ROWS: dynamic shared memory of the launch
     int rows_carveout = 0;          // ROWS: shared-memory share (percent) asked of the unified L1 / shared array
     int grid = 0;

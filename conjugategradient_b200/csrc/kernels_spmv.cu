@@ -286,9 +286,11 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
 constexpr int kRowsTotalMax = 16384;      // non-zeros the ring may hold: (8 + 4) B x 16384 = 192 KB
 constexpr int kRowsMaxStages = 8;
 constexpr int kRowsThreads = 256;
-constexpr int kRowsUnroll = 8;             // entries a lane takes per chunk (gathers in flight per lane)
-
-template <int EPI, int L>
+// U = entries a lane takes per chunk (its gathers are issued together): 8 when a lane has more than ~6 entries of its row,
+// else the plain strided loop unrolled by 4 — the padding of a chunk is predicated off but still costs issue slots (sweep,
+// fraction of the HBM peak: 35 per row, L=8: 0.81 plain, 0.78 chunks of 8, 0.71 chunks of 4; 121 per row, L=16: 0.73 plain,
+// 0.88 chunks of 8).
+template <int EPI, int L, int kRowsUnroll>
 __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_tiles, int cap, int stages, ReduceWs ws, Scalars *sc)
 {
     if (a.gated && sc->done) return;
@@ -365,22 +367,28 @@ __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_
                 // chunks of kRowsUnroll entries per lane: all the column indices first, then all the x gathers (independent loads in
                 // flight together — the ncu source page of the first version showed the lanes stalled on the gathers' long
                 // scoreboard, four at a time), then the products on two accumulators
+                if (kRowsUnroll <= 4) {
+                    // few entries per lane: the plain strided loop (measured ahead of a padded chunk of 4 on the 35-per-row matrix)
+#pragma unroll 4
+                    for (int k = rs + lane; k < re; k += L) acc += sv[k] * x[scl[k]];
+                } else {
                 double acc1 = 0.0;
                 for (int kb = rs + lane; kb < re; kb += kRowsUnroll * L) {
                     int cc[kRowsUnroll];
                     double xv[kRowsUnroll];
 #pragma unroll
-                    for (int u = 0; u < kRowsUnroll; ++u) { const int k = kb + u * L; cc[u] = scl[k < re ? k : kb]; }
+                    for (int u = 0; u < kRowsUnroll; ++u) { const int k = kb + u * L; cc[u] = k < re ? scl[k] : -1; }
 #pragma unroll
-                    for (int u = 0; u < kRowsUnroll; ++u) xv[u] = x[cc[u]];
-#pragma unroll
+                    for (int u = 0; u < kRowsUnroll; ++u) xv[u] = cc[u] >= 0 ? x[cc[u]] : 0.0;   // predicated off past the row end:
+#pragma unroll                                                                                    // no L1 transaction for the padding
                     for (int u = 0; u < kRowsUnroll; u += 2) {
                         const int ka = kb + u * L, kc = ka + L;
-                        acc += (ka < re ? sv[ka] : 0.0) * xv[u];
-                        acc1 += (kc < re ? sv[kc] : 0.0) * xv[u + 1];
+                        acc += (cc[u] >= 0 ? sv[ka] : 0.0) * xv[u];
+                        acc1 += (cc[u + 1] >= 0 ? sv[kc] : 0.0) * xv[u + 1];
                     }
                 }
                 acc += acc1;
+                }
             } else {
 #pragma unroll 4
                 for (int k = rs + lane; k < re; k += L) acc += __ldcs(val + k) * x[__ldcs(col + k)];
@@ -471,6 +479,8 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel)
         while (stages > 2 && capn * stages > kRowsTotalMax) --stages;
         if (capn * stages > kRowsTotalMax) capn = (kRowsTotalMax / stages) & ~3;       // tiles that do not fit take the direct path
         p.lanes = L;
+        p.rows_unroll = avg > 6.0 * L ? 8 : 4;
+        if (const char *e = getenv("MGCG_ROWS_UNROLL")) { const int v = atoi(e); if (v == 4 || v == 8) p.rows_unroll = v; }
         p.rows_stages = stages;
         p.rows_cap = (int)capn;
         p.rows_smem = (int)((size_t)stages * ((capn + 2) * 8 + (capn + 4) * 4) + (size_t)kRowsMaxStages * 64 + 64);
@@ -512,20 +522,20 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel)
 // Dynamic shared memory of the rows kernel: the opt-in limit is raised only as far as a launch needs (per instantiation and
 // device), and the L1 / shared-memory split is asked for explicitly — blocks_per_sm x (ring + 1 KB) of shared memory, the rest
 // stays L1 for the x gathers.  (A limit set once to the largest ring made every launch run with the smallest L1.)
-template <int EPI, int L>
+template <int EPI, int L, int U>
 static int rows_prepare_one(mgcg_ctx *c, const SpmvPlan &plan)
 {
     static int set_bytes[64] = {0};
     static int set_carve[64] = {0};
     const int d = c->device & 63;
     if (plan.rows_smem > set_bytes[d]) {
-        MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, L>, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.rows_smem));
+        MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, L, U>, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.rows_smem));
         set_bytes[d] = plan.rows_smem;
     }
     int carve = plan.rows_carveout;
     if (const char *e = getenv("MGCG_ROWS_CARVEOUT")) carve = atoi(e);
     if (carve != set_carve[d] && carve > 0) {
-        MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, L>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+        MGCG_CUDA(cudaFuncSetAttribute(k_spmv_rows<EPI, L, U>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
         set_carve[d] = carve;
     }
     return MGCG_OK;
@@ -533,11 +543,12 @@ static int rows_prepare_one(mgcg_ctx *c, const SpmvPlan &plan)
 template <int EPI>
 static int rows_prepare(mgcg_ctx *c, const SpmvPlan &plan)
 {
+    const bool u8 = plan.rows_unroll >= 8;
     switch (plan.lanes) {
-    case 4: return rows_prepare_one<EPI, 4>(c, plan);
-    case 8: return rows_prepare_one<EPI, 8>(c, plan);
-    case 16: return rows_prepare_one<EPI, 16>(c, plan);
-    default: return rows_prepare_one<EPI, 32>(c, plan);
+    case 4: return u8 ? rows_prepare_one<EPI, 4, 8>(c, plan) : rows_prepare_one<EPI, 4, 4>(c, plan);
+    case 8: return u8 ? rows_prepare_one<EPI, 8, 8>(c, plan) : rows_prepare_one<EPI, 8, 4>(c, plan);
+    case 16: return u8 ? rows_prepare_one<EPI, 16, 8>(c, plan) : rows_prepare_one<EPI, 16, 4>(c, plan);
+    default: return u8 ? rows_prepare_one<EPI, 32, 8>(c, plan) : rows_prepare_one<EPI, 32, 4>(c, plan);
     }
 }
 
@@ -565,12 +576,16 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
         const int tiles = div_up(a.A.rows, kRowsThreads / L);
         int grid = plan.grid;
         if (grid > tiles) grid = tiles;
+#define MGCG_ROWS_LAUNCH(LL, UU) \
+    k_spmv_rows<EPI, LL, UU><<<grid, kRowsThreads, (size_t)plan.rows_smem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars)
+        const bool u8 = plan.rows_unroll >= 8;
         switch (L) {
-        case 4: k_spmv_rows<EPI, 4><<<grid, kRowsThreads, (size_t)plan.rows_smem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
-        case 8: k_spmv_rows<EPI, 8><<<grid, kRowsThreads, (size_t)plan.rows_smem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
-        case 16: k_spmv_rows<EPI, 16><<<grid, kRowsThreads, (size_t)plan.rows_smem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
-        default: k_spmv_rows<EPI, 32><<<grid, kRowsThreads, (size_t)plan.rows_smem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars); break;
+        case 4: if (u8) MGCG_ROWS_LAUNCH(4, 8); else MGCG_ROWS_LAUNCH(4, 4); break;
+        case 8: if (u8) MGCG_ROWS_LAUNCH(8, 8); else MGCG_ROWS_LAUNCH(8, 4); break;
+        case 16: if (u8) MGCG_ROWS_LAUNCH(16, 8); else MGCG_ROWS_LAUNCH(16, 4); break;
+        default: if (u8) MGCG_ROWS_LAUNCH(32, 8); else MGCG_ROWS_LAUNCH(32, 4); break;
         }
+#undef MGCG_ROWS_LAUNCH
     } else {
         switch (plan.lanes) {
         case 4: k_spmv_vector<EPI, 4><<<plan.grid, kSpmvThreads, 0, c->stream>>>(a, c->ws, c->d_scalars); break;

@@ -14,7 +14,7 @@ torch.cuda.set_stream(torch.cuda.Stream(dev))      # torch's events and the libr
 m = S.Mgcg(0, use_torch_stream=True)
 L = m.L
 peak = bench.measured_peak()[0]
-KNOBS = ("MGCG_ROWS_LANES", "MGCG_ROWS_STAGES", "MGCG_ROWS_CAPF", "MGCG_ROWS_CTAS", "MGCG_ROWS_CARVEOUT")
+KNOBS = ("MGCG_ROWS_UNROLL", "MGCG_ROWS_LANES", "MGCG_ROWS_STAGES", "MGCG_ROWS_CAPF", "MGCG_ROWS_CTAS", "MGCG_ROWS_CARVEOUT")
 
 
 def timeit(tv, tr, tc, n, nnz, kernel, reps=10):
@@ -49,18 +49,18 @@ for re in (2.1, 3.1):
     res = []
     lanes_set = (4, 8, 16) if re < 3 else (8, 16, 32)
     quick = os.environ.get("SWEEP_QUICK") is not None
-    for lanes, stages, capf, ctas in itertools.product(lanes_set, (2,) if quick else (2, 3, 4), (1.3,) if quick else (1.15, 1.3, 1.6), (3, 4, 5, 6) if quick else (2, 3, 4, 5, 6)):
+    for unroll, lanes, stages, capf, ctas in itertools.product((4, 8), lanes_set, (2,) if quick else (2, 3, 4), (1.3,) if quick else (1.15, 1.3, 1.6), (4, 5) if quick else (2, 3, 4, 5, 6)):
         clear()
-        os.environ.update({"MGCG_ROWS_LANES": str(lanes), "MGCG_ROWS_STAGES": str(stages), "MGCG_ROWS_CAPF": str(capf), "MGCG_ROWS_CTAS": str(ctas)})
+        os.environ.update({"MGCG_ROWS_UNROLL": str(unroll), "MGCG_ROWS_LANES": str(lanes), "MGCG_ROWS_STAGES": str(stages), "MGCG_ROWS_CAPF": str(capf), "MGCG_ROWS_CTAS": str(ctas)})
         ms, gbs = timeit(tv, tr, tc, n, nnz, 3, reps=6)
-        res.append((gbs, lanes, stages, capf, ctas, ms))
-        print(f"  rows L={lanes:2d} stages={stages} capf={capf:4.2f} ctas={ctas}   {ms:8.3f} ms {gbs:7.0f} GB/s  {gbs / peak:.3f}", flush=True)
+        res.append((gbs, lanes, stages, capf, ctas, ms, unroll))
+        print(f"  rows U={unroll} L={lanes:2d} stages={stages} capf={capf:4.2f} ctas={ctas}   {ms:8.3f} ms {gbs:7.0f} GB/s  {gbs / peak:.3f}", flush=True)
     res.sort(reverse=True)
     print("  best:", [tuple(round(v, 3) if isinstance(v, float) else v for v in r) for r in res[:6]], flush=True)
-    gbs, lanes, stages, capf, ctas, _ = res[0]
+    gbs, lanes, stages, capf, ctas, _, unroll = res[0]
     for carve in (50, 65, 80, 100):
         clear()
-        os.environ.update({"MGCG_ROWS_LANES": str(lanes), "MGCG_ROWS_STAGES": str(stages), "MGCG_ROWS_CAPF": str(capf), "MGCG_ROWS_CTAS": str(ctas),
+        os.environ.update({"MGCG_ROWS_UNROLL": str(unroll), "MGCG_ROWS_LANES": str(lanes), "MGCG_ROWS_STAGES": str(stages), "MGCG_ROWS_CAPF": str(capf), "MGCG_ROWS_CTAS": str(ctas),
                            "MGCG_ROWS_CARVEOUT": str(carve)})
         ms, gbs = timeit(tv, tr, tc, n, nnz, 3, reps=6)
         print(f"  best shape, carve-out {carve:3d} %   {ms:8.3f} ms {gbs:7.0f} GB/s  {gbs / peak:.3f}", flush=True)
