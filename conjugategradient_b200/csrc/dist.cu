@@ -27,6 +27,7 @@ int nccl_load(NcclApi **out)
         SYM_(Send, "ncclSend") SYM_(Recv, "ncclRecv") SYM_(GroupStart, "ncclGroupStart") SYM_(GroupEnd, "ncclGroupEnd")
         SYM_(GetErrorString, "ncclGetErrorString")
 #undef SYM_
+        *(void **)(&api.CommInitRankConfig) = dlsym(h, "ncclCommInitRankConfig");
         api.handle = h;
     }
     *out = &api;
@@ -80,6 +81,7 @@ void dist_free(mgcg_ctx *c)
     if (D->coarse_spare) { mgcg_destroy(D->coarse_spare); D->coarse_spare = nullptr; }
     if (D->partial_send) cudaFree(D->partial_send);
     if (D->partial_all) cudaFree(D->partial_all);
+    if (D->gather_ints) cudaFree(D->gather_ints);
     if (D->comm && D->api) D->api->CommDestroy(D->comm);
     delete D;
     c->dist = nullptr;
@@ -203,10 +205,16 @@ static int level_halfband(mgcg_ctx *c, const Csr &A, int row_base, int *out)
     MGCG_CUDA(pool_alloc((void **)&d, sizeof(int), c->stream));
     MGCG_CUDA(cudaMemsetAsync(d, 0, sizeof(int), c->stream));
     if (A.rows > 0) { k_halfband<<<gridn(A.rows), 256, 0, c->stream>>>(A, row_base, d); MGCG_LAUNCH_CHECK(); }
-    MGCG_NCCL(D->api, AllReduce(d, d, 1, ncclInt, ncclMax, D->comm, c->stream));
-    MGCG_CUDA(cudaMemcpyAsync(out, d, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    // max over ranks: all-gather + host max (the setup uses two NCCL connection classes only, the collective ring and
+    // point-to-point, both opened once in mgcg_comm_init; an all-reduce would open its own on first use)
+    MGCG_NCCL(D->api, AllGather(d, D->gather_ints, 1, ncclInt, D->comm, c->stream));
+    int all[kMaxRanks];
+    MGCG_CUDA(cudaMemcpyAsync(all, D->gather_ints, sizeof(int) * (size_t)D->world, cudaMemcpyDeviceToHost, c->stream));
     MGCG_CUDA(cudaStreamSynchronize(c->stream));
     pool_release(d);
+    int m = 0;
+    for (int r = 0; r < D->world; ++r) m = all[r] > m ? all[r] : m;
+    *out = m;
     return MGCG_OK;
 }
 
@@ -957,9 +965,36 @@ extern "C" int mgcg_comm_init(mgcg_ctx *c, const void *id128, int rank, int worl
     ncclUniqueId id;
     memcpy(&id, id128, 128);
     D->rank = rank; D->world = world;
-    MGCG_NCCL(D->api, CommInitRank(&D->comm, world, id, rank));
+    // NCCL carries the setup's exchanges only (a few MB of ghost rows and the replicated level); the loop runs on the
+    // library's own peer-memory kernels.  So the communicator is asked for few channels: connecting them is what the first
+    // collective / first send to a peer pays for, per channel and per peer.  MGCG_NCCL_MAX_CTAS=0 keeps NCCL's default.
+    int max_ctas = 4;
+    if (const char *e = getenv("MGCG_NCCL_MAX_CTAS")) max_ctas = atoi(e);
+    if (D->api->CommInitRankConfig && max_ctas > 0) {
+        ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
+        cfg.minCTAs = 1;
+        cfg.maxCTAs = max_ctas;
+        MGCG_NCCL(D->api, CommInitRankConfig(&D->comm, world, id, rank, &cfg));
+    } else {
+        MGCG_NCCL(D->api, CommInitRank(&D->comm, world, id, rank));
+    }
     MGCG_CUDA(cudaMalloc((void **)&D->partial_send, 4 * sizeof(double)));
     MGCG_CUDA(cudaMalloc((void **)&D->partial_all, 4 * sizeof(double) * (size_t)world));
+    MGCG_CUDA(cudaMalloc((void **)&D->gather_ints, sizeof(int) * (size_t)(2 * world + 2)));
+    MGCG_CUDA(cudaMemset(D->gather_ints, 0, sizeof(int) * (size_t)(2 * world + 2)));
+    // open both connection classes now (once per process) instead of inside the first setup
+    if (world > 1 && !getenv("MGCG_NCCL_LAZY")) {
+        int *g = D->gather_ints;
+        MGCG_NCCL(D->api, AllGather(g + world, g, 1, ncclInt, D->comm, c->stream));
+        MGCG_NCCL(D->api, GroupStart());
+        for (int q = 0; q < world; ++q) {
+            if (q == rank) continue;
+            MGCG_NCCL(D->api, Send(g + world, 1, ncclInt, q, D->comm, c->stream));
+            MGCG_NCCL(D->api, Recv(g + world + 1 + q, 1, ncclInt, q, D->comm, c->stream));
+        }
+        MGCG_NCCL(D->api, GroupEnd());
+        MGCG_CUDA(cudaStreamSynchronize(c->stream));
+    }
     return MGCG_OK;
 }
 

@@ -23,6 +23,7 @@ struct NcclApi {
     void *handle = nullptr;
     ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
     ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommInitRankConfig)(ncclComm_t *, int, ncclUniqueId, int, ncclConfig_t *) = nullptr;   // optional (NCCL >= 2.14)
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
@@ -125,6 +126,7 @@ struct DistState {
     // scalar reductions: per-rank partials -> all-gather -> fixed rank-order sum (cs:463 resultsDot.Sum())
     double *partial_send = nullptr;         // [2]
     double *partial_all = nullptr;          // [2 * world]
+    int *gather_ints = nullptr;             // [2 * world + 2] landing area of the setup's small all-gathers
     int halo_exchanges = 0, allgathers = 0; // per-solve accounting
     PeerState peer;                         // peer-memory transport of the loop (inactive: NCCL)
     // CUDA graph of one sharded iteration (peer transport only)
