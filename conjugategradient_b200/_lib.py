@@ -16,6 +16,8 @@ PRECOND_NONE, PRECOND_MG = 0, 1
 SPMV_AUTO, SPMV_STREAM, SPMV_VECTOR, SPMV_ROWS = 0, 1, 2, 3
 TRANSPORT_AUTO, TRANSPORT_NCCL, TRANSPORT_PEER = 0, 1, 2
 AGG_AUTO, AGG_BLOCKS, AGG_MIS2 = 0, 1, 2
+SMOOTHER_JACOBI, SMOOTHER_RBGS, SMOOTHER_CHEBYSHEV = 0, 1, 2
+CG_CLASSIC, CG_SINGLE_REDUCE = 0, 1
 
 
 class Options(C.Structure):
@@ -27,7 +29,8 @@ class Options(C.Structure):
         ("spmv_kernel", C.c_int), ("check_interval", C.c_int), ("use_graph", C.c_int), ("profile", C.c_int),
         ("mg_smoothed_levels", C.c_int), ("mg_aggregate_size", C.c_int), ("mg_aggregate_size_coarse", C.c_int),
         ("dist_replicate_below", C.c_int), ("dist_transport", C.c_int), ("mg_tail_rows", C.c_int), ("mg_aggregation", C.c_int),
-        ("reserved0", C.c_int), ("mg_strength_theta", C.c_double), ("reserved", C.c_int * 6),
+        ("mg_cheby_degree", C.c_int), ("mg_strength_theta", C.c_double), ("mg_cheby_ratio", C.c_double), ("cg_variant", C.c_int),
+        ("reserved", C.c_int * 3),
     ]
 
 

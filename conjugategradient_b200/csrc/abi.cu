@@ -24,7 +24,8 @@ int ctx_ensure_work(mgcg_ctx *c, int n)
     if (c->r) cudaFree(c->r);
     if (c->p) cudaFree(c->p);
     if (c->Ap) cudaFree(c->Ap);
-    c->r = c->p = c->Ap = nullptr;
+    if (c->s) cudaFree(c->s);
+    c->r = c->p = c->Ap = c->s = nullptr;
     size_t bytes = sizeof(double) * (size_t)(n > 0 ? n : 1);
     MGCG_CUDA(cudaMalloc((void **)&c->r, bytes));
     MGCG_CUDA(cudaMalloc((void **)&c->p, bytes));
@@ -38,10 +39,20 @@ int ctx_ensure_work(mgcg_ctx *c, int n)
 struct HostPath {   // device copies owned by mgcg_solve_host
     double *val = nullptr; int *rowptr = nullptr; int *col = nullptr; double *b = nullptr; double *x = nullptr;
     size_t cap_n = 0, cap_nnz = 0;
+    cudaStream_t copy = nullptr;          // b and x0 travel on this stream while the hierarchy is built on the solve stream
+    cudaEvent_t ev_matrix = nullptr, ev_vectors = nullptr;
     void release()
     {
         if (val) cudaFree(val); if (rowptr) cudaFree(rowptr); if (col) cudaFree(col); if (b) cudaFree(b); if (x) cudaFree(x);
         val = nullptr; rowptr = nullptr; col = nullptr; b = nullptr; x = nullptr; cap_n = cap_nnz = 0;
+    }
+    void release_all()
+    {
+        release();
+        if (copy) cudaStreamDestroy(copy);
+        if (ev_matrix) cudaEventDestroy(ev_matrix);
+        if (ev_vectors) cudaEventDestroy(ev_vectors);
+        copy = nullptr; ev_matrix = nullptr; ev_vectors = nullptr;
     }
 };
 
@@ -80,6 +91,9 @@ void mgcg_options_default(mgcg_options *o)
     o->profile = 0;
     o->mg_aggregation = MGCG_AGG_AUTO;
     o->mg_strength_theta = 0.5;
+    o->mg_cheby_degree = 2;
+    o->mg_cheby_ratio = 6.0;
+    o->cg_variant = MGCG_CG_CLASSIC;
 }
 
 mgcg_ctx *mgcg_create(int device)
@@ -130,12 +144,13 @@ void mgcg_destroy(mgcg_ctx *c)
     if (!c->child) pool_trim_stream(c->device, c->stream);
     if (c->graph_exec) cudaGraphExecDestroy(c->graph_exec);
     if (c->graph) cudaGraphDestroy(c->graph);
-    if (c->host_path) { ((HostPath *)c->host_path)->release(); delete (HostPath *)c->host_path; }
+    if (c->host_path) { ((HostPath *)c->host_path)->release_all(); delete (HostPath *)c->host_path; }
     formats_free(c);
     dist_host_path_free(c);
     if (c->r) cudaFree(c->r);
     if (c->p) cudaFree(c->p);
     if (c->Ap) cudaFree(c->Ap);
+    if (c->s) cudaFree(c->s);
     if (c->d_scalars) cudaFree(c->d_scalars);
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     if (c->ws.partial) cudaFree(c->ws.partial);
@@ -230,13 +245,26 @@ int mgcg_solve_host(mgcg_ctx *c, int count, int elements_count,
         h->cap_n = count; h->cap_nnz = elements_count;
     }
     cudaStream_t st = c->stream;
-    MGCG_CUDA(cudaMemcpyAsync(h->val, elements, sizeof(double) * (size_t)elements_count, cudaMemcpyHostToDevice, st));
-    MGCG_CUDA(cudaMemcpyAsync(h->col, column_indeces, sizeof(int) * (size_t)elements_count, cudaMemcpyHostToDevice, st));
+    if (!h->copy) {
+        MGCG_CUDA(cudaStreamCreateWithFlags(&h->copy, cudaStreamNonBlocking));
+        MGCG_CUDA(cudaEventCreateWithFlags(&h->ev_matrix, cudaEventDisableTiming));
+        MGCG_CUDA(cudaEventCreateWithFlags(&h->ev_vectors, cudaEventDisableTiming));
+    }
+    // the matrix first, on the solve stream (the hierarchy build needs all of it); b and x0 follow on a second stream once the
+    // matrix has left the host, so that their 16 N bytes cross PCIe while the hierarchy is being built
     MGCG_CUDA(cudaMemcpyAsync(h->rowptr, row_offsets, sizeof(int) * ((size_t)count + 1), cudaMemcpyHostToDevice, st));
-    MGCG_CUDA(cudaMemcpyAsync(h->b, b, sizeof(double) * (size_t)count, cudaMemcpyHostToDevice, st));
-    MGCG_CUDA(cudaMemcpyAsync(h->x, x, sizeof(double) * (size_t)count, cudaMemcpyHostToDevice, st));
-    MGCG_CHECK(mgcg_setup(c, count, elements_count, h->val, h->rowptr, h->col, opt));
-    int s = mgcg_solve(c, h->b, h->x, res);
+    MGCG_CUDA(cudaMemcpyAsync(h->col, column_indeces, sizeof(int) * (size_t)elements_count, cudaMemcpyHostToDevice, st));
+    MGCG_CUDA(cudaMemcpyAsync(h->val, elements, sizeof(double) * (size_t)elements_count, cudaMemcpyHostToDevice, st));
+    MGCG_CUDA(cudaEventRecord(h->ev_matrix, st));
+    MGCG_CUDA(cudaStreamWaitEvent(h->copy, h->ev_matrix, 0));
+    MGCG_CUDA(cudaMemcpyAsync(h->b, b, sizeof(double) * (size_t)count, cudaMemcpyHostToDevice, h->copy));
+    MGCG_CUDA(cudaMemcpyAsync(h->x, x, sizeof(double) * (size_t)count, cudaMemcpyHostToDevice, h->copy));
+    MGCG_CUDA(cudaEventRecord(h->ev_vectors, h->copy));
+    int s = mgcg_setup(c, count, elements_count, h->val, h->rowptr, h->col, opt);
+    // the solve (and any early return) must not overtake the vector upload
+    MGCG_CUDA(cudaStreamWaitEvent(st, h->ev_vectors, 0));
+    if (s != MGCG_OK) { cudaStreamSynchronize(h->copy); return s; }
+    s = mgcg_solve(c, h->b, h->x, res);
     MGCG_CUDA(cudaMemcpyAsync(x, h->x, sizeof(double) * (size_t)count, cudaMemcpyDeviceToHost, st));
     MGCG_CUDA(cudaStreamSynchronize(st));
     return s;

@@ -42,6 +42,28 @@ static int enqueue_iteration(mgcg_ctx *c, const double *b, double *x, std::vecto
     return MGCG_OK;
 }
 
+// One iteration of the single-reduce (Chronopoulos-Gear) recurrence, MGCG_CG_SINGLE_REDUCE: u = M r (or r), w = A u (kept in Ap),
+// s = A p by recurrence.  Same iterates as the classic loop in exact arithmetic; r.r, r.u and w.u are all finished in the last
+// block of the product kernel (FIN_CGCG_DELTA), where the stop rule on the residual updated at the top of the iteration is applied.
+static int enqueue_iteration_cgcg(mgcg_ctx *c, double *x)
+{
+    const int n = c->A.rows;
+    const bool pre = (c->opt.precond == MGCG_PRECOND_MG) && c->mg;
+    double *u = c->r;
+    if (!pre) {
+        // u == r is read (old r) and updated in the same pass: elementwise, so in place is safe
+        MGCG_CHECK(cgcg_update(c, n, c->r, c->Ap, c->p, c->s, x, c->r));
+    } else {
+        MGCG_CHECK(cgcg_update(c, n, c->cgcg_u, c->Ap, c->p, c->s, x, c->r, mg_level0_first_x(c), mg_level0_dinv(c), mg_level0_first_omega(c)));
+        MGCG_CHECK(mg_vcycle(c, c->r, &u, true, FIN_CGCG_GAMMA));
+        if (u != c->cgcg_u) { set_error("cg_solve: the V-cycle's output buffer moved between iterations"); return MGCG_ERR_INVALID; }
+    }
+    SpmvArgs a;
+    a.A = c->A; a.x = u; a.y = c->Ap; a.w = u; a.fin = pre ? FIN_CGCG_DELTA : FIN_CGCG_DELTA_PLAIN; a.gated = true;
+    MGCG_CHECK(spmv_launch(c, c->planA, EPI_DOT, a));
+    return MGCG_OK;
+}
+
 // "No limit" (the library default 1 << 30, or <= 0) is replaced by a finite bound: with the whole loop running as one
 // device-side WHILE graph the host cannot cancel a solve that stagnates above the tolerance (a tolerance below what fp64
 // can reach, a semi-definite system), so the device-side Iteration > MaxIteration test must be able to fire.  20 n + 1000
@@ -93,6 +115,7 @@ struct IterArgs { const double *b; double *x; };
 static int enqueue_iteration_thunk(mgcg_ctx *c, void *arg)
 {
     IterArgs *a = (IterArgs *)arg;
+    if (c->opt.cg_variant == MGCG_CG_SINGLE_REDUCE) return enqueue_iteration_cgcg(c, a->x);
     return enqueue_iteration(c, a->b, a->x);
 }
 
@@ -126,6 +149,30 @@ int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     MGCG_CUDA(cudaMemcpyAsync(c->d_scalars, &c->h_scalars[0], sizeof(Scalars), cudaMemcpyHostToDevice, st));
     MGCG_CUDA(cudaEventRecord(ev0, st));
 
+    const bool cgcg = c->opt.cg_variant == MGCG_CG_SINGLE_REDUCE;
+    if (c->opt.cg_variant != MGCG_CG_CLASSIC && !cgcg) { set_error("mgcg_solve: unknown cg_variant %d", c->opt.cg_variant); return MGCG_ERR_INVALID; }
+    if (cgcg && c->opt.profile) { set_error("mgcg_solve: profile=1 times the classic loop's product kernel; not available with MGCG_CG_SINGLE_REDUCE"); return MGCG_ERR_UNSUPPORTED; }
+    if (cgcg) {
+        // r = b - A x ; u = M r ; w = A u ; gamma = r.u ; delta = w.u ; alpha = gamma/delta ; beta = 0 ; p = s = 0
+        if (!c->s) MGCG_CUDA(cudaMalloc((void **)&c->s, sizeof(double) * (size_t)(c->work_n > 0 ? c->work_n : 1)));
+        SpmvArgs a;
+        a.A = c->A; a.x = x; a.y = c->Ap;
+        MGCG_CHECK(spmv_launch(c, c->planA, EPI_PLAIN, a));
+        double *u = c->r;
+        if (!pre) {
+            MGCG_CHECK(cg_init_residual(c, n, b, c->Ap, c->r, nullptr, FIN_INIT));          // rr = rr0 = rz = r.r
+            MGCG_CHECK(vec_dot(c, n, c->r, c->r, FIN_CGCG_GAMMA, nullptr));                  // gamma_new = r.r (FIN_CGCG_INIT reads it)
+        } else {
+            MGCG_CHECK(cg_init_residual(c, n, b, c->Ap, c->r, nullptr, FIN_INIT_RR));
+            MGCG_CHECK(mg_vcycle(c, c->r, &u, false, FIN_CGCG_GAMMA));
+            c->cgcg_u = u;
+        }
+        SpmvArgs q;
+        q.A = c->A; q.x = u; q.y = c->Ap; q.w = u; q.fin = FIN_CGCG_INIT;
+        MGCG_CHECK(spmv_launch(c, c->planA, EPI_DOT, q));
+        MGCG_CUDA(cudaMemsetAsync(c->p, 0, sizeof(double) * (size_t)n, st));
+        MGCG_CUDA(cudaMemsetAsync(c->s, 0, sizeof(double) * (size_t)n, st));
+    } else
     // init: Ap = A x ; r = b - Ap ; p = r (or z) ; rr                      (ConjugateGradientCpu.cs:54-57)
     {
         SpmvArgs a;
@@ -150,7 +197,8 @@ int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     int spmv_n = 0;
 
     const int want_mode = use_graph ? (c->opt.use_graph >= 2 ? 2 : 1) : 0;
-    if (use_graph && (!c->graph_exec || c->graph_b != b || c->graph_x != x || (c->graph_mode != want_mode && c->graph_mode != -want_mode))) {
+    if (use_graph && (!c->graph_exec || c->graph_b != b || c->graph_x != x || c->graph_variant != c->opt.cg_variant ||
+                      (c->graph_mode != want_mode && c->graph_mode != -want_mode))) {
         if (c->graph_exec) { cudaGraphExecDestroy(c->graph_exec); c->graph_exec = nullptr; }
         if (c->graph) { cudaGraphDestroy(c->graph); c->graph = nullptr; }
         int saved = c->launches;
@@ -163,7 +211,8 @@ int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
         }
         if (c->graph_mode == 0) {
             MGCG_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-            int s = enqueue_iteration(c, b, x);
+            IterArgs ia{b, x};
+            int s = enqueue_iteration_thunk(c, &ia);
             cudaError_t e = cudaStreamEndCapture(st, &c->graph);
             if (s != MGCG_OK) return s;
             MGCG_CUDA(e);
@@ -173,7 +222,7 @@ int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
             c->graph_body_nodes = (int)nodes;
             c->graph_mode = want_mode == 2 ? -2 : 1;   // -2: asked for the while loop, the driver cannot; do not retry every solve
         }
-        c->graph_b = b; c->graph_x = x;
+        c->graph_b = b; c->graph_x = x; c->graph_variant = c->opt.cg_variant;
         c->launches = saved;
     }
     const bool while_loop = use_graph && c->graph_mode == 2;
@@ -192,7 +241,8 @@ int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
             if (use_graph) {
                 MGCG_CUDA(cudaGraphLaunch(c->graph_exec, st));
             } else {
-                MGCG_CHECK(enqueue_iteration(c, b, x, profile ? &pev : nullptr));
+                if (cgcg) MGCG_CHECK(enqueue_iteration_cgcg(c, x));
+                else MGCG_CHECK(enqueue_iteration(c, b, x, profile ? &pev : nullptr));
             }
             ++enq;
         }

@@ -52,6 +52,8 @@ struct Scalars {
     int done;         // set by the device when converged / failed: every later kernel of the loop is a no-op
     int status;       // MGCG_OK / MGCG_ERR_*
     int pad;
+    double rr_pend;   // single-reduce CG: r.r of the residual just updated (its stop rule is applied at the iteration's one reduction point)
+    double gamma_new; // single-reduce CG: r.u of the new residual
 };
 
 // what the LAST block of a reducing kernel does with the finished sum (runs in one thread)
@@ -64,7 +66,13 @@ enum FinOp {
     FIN_RR,         // rr_new = sum; stop rule; (no precond) beta = rr_new/rr, rz = rr = rr_new
     FIN_RR_PRECOND, // rr = sum; stop rule only
     FIN_RZ,         // beta = sum / rz; rz = sum
-    FIN_STORE_MAX   // out[0] = max
+    FIN_STORE_MAX,  // out[0] = max
+    // single-reduce (Chronopoulos-Gear) CG: the three sums of an iteration are finished where the last one lands
+    FIN_CGCG_RR,        // rr_pend = sum; rmax = max
+    FIN_CGCG_GAMMA,     // gamma_new = sum
+    FIN_CGCG_INIT,      // delta = sum: rz = gamma_new; alpha = rz / delta; beta = 0
+    FIN_CGCG_DELTA,     // delta = sum: stop rule on rr_pend; beta = gamma_new / rz; alpha = gamma_new / (delta - beta gamma_new / alpha); rz = gamma_new
+    FIN_CGCG_DELTA_PLAIN // as FIN_CGCG_DELTA without preconditioner (gamma_new == rr_pend)
 };
 
 constexpr int kMaxPartials = 4096;   // upper bound on the grid of any reducing kernel
@@ -106,7 +114,9 @@ enum SpmvEpi {
     EPI_DOT,         // y = s; partial += w_i * s                (p.Ap fused)
     EPI_RESID,       // y = b_i - s
     EPI_JACOBI,      // y = x_i + omega*dinv_i*(b_i - s)         (x is the SpMV input vector)
-    EPI_JACOBI_DOT   // as EPI_JACOBI; partial += b_i * y_i      (r.z fused into the last post-smoothing sweep)
+    EPI_JACOBI_DOT,  // as EPI_JACOBI; partial += b_i * y_i      (r.z fused into the last post-smoothing sweep)
+    EPI_CHEBY,       // d = alpha*d_in_i + omega*dinv_i*(b_i - s); d_out_i = d; y = x_i + d     (one Chebyshev smoothing step)
+    EPI_CHEBY_DOT    // as EPI_CHEBY; partial += b_i * y_i
 };
 
 struct SpmvArgs {
@@ -117,6 +127,8 @@ struct SpmvArgs {
     const double *b = nullptr;     // RESID / JACOBI
     const double *dinv = nullptr;  // JACOBI
     const double *w = nullptr;     // DOT
+    const double *d_in = nullptr;  // CHEBY: previous direction (not read when alpha == 0)
+    double *d_out = nullptr;       // CHEBY: new direction (may alias d_in: row-local)
     double alpha = 1.0, beta = 0.0, omega = 1.0;
     int fin = FIN_STORE;
     double *out = nullptr;         // FIN_STORE target
@@ -154,6 +166,9 @@ struct mgcg_ctx {
     bool is_setup = false;
     // work vectors (owned)
     double *r = nullptr, *p = nullptr, *Ap = nullptr;
+    double *s = nullptr;           // single-reduce CG: s = A p by recurrence (allocated on first use)
+    double *cgcg_u = nullptr;      // single-reduce CG: the V-cycle's output buffer (u = M r), fixed across iterations
+    int graph_variant = 0;         // cg_variant the captured graph was built for
     int work_n = 0;
     mgcg::Hierarchy *mg = nullptr;
     mgcg::DistState *dist = nullptr;
@@ -189,6 +204,9 @@ int cg_init_residual(mgcg_ctx *c, int n, const double *b, const double *Ap, doub
 int cg_update_xr(mgcg_ctx *c, int n, const double *p, const double *Ap, double *x, double *r, int fin,
                  bool use_host_alpha, double host_alpha, double *out,
                  double *z0 = nullptr, const double *dinv = nullptr, double omega = 0.0);
+// single-reduce CG: p = u + beta p ; s = w + beta s ; x += alpha p ; r -= alpha s ; r.r, max|r| -> FIN_CGCG_RR  [; z0 = omega dinv r]
+int cgcg_update(mgcg_ctx *c, int n, const double *u, const double *w, double *p, double *s, double *x, double *r,
+                double *z0 = nullptr, const double *dinv = nullptr, double omega = 0.0, double *out = nullptr);
 // p = z + beta p   (z == r without preconditioner)
 int cg_update_p(mgcg_ctx *c, int n, const double *z, double *p, bool use_host_beta, double host_beta);
 // x = omega * dinv .* b

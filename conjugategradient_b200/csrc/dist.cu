@@ -35,6 +35,7 @@ int nccl_load(NcclApi **out)
 }
 
 static void dist_graph_free(DistState *D);
+static int dist_level_chebyshev(mgcg_ctx *c, DistLevel &L);
 
 // one int from device memory, ordered after the work queued on the context's (non-blocking) stream
 static int fetch_int(mgcg_ctx *c, int *h, const int *d)
@@ -54,6 +55,7 @@ void dist_free_levels(DistState *D)
         if (L.xa) pool_release(L.xa);
         if (L.xb) pool_release(L.xb);
         if (L.r) pool_release(L.r);
+        if (L.d) pool_release(L.d);
         if (l > 0 && L.b) pool_release(L.b);
     }
     D->L.clear();
@@ -69,6 +71,7 @@ void dist_free_levels(DistState *D)
     if (D->p) { pool_release(D->p); D->p = nullptr; }
     if (D->r) { pool_release(D->r); D->r = nullptr; }
     if (D->Ap) { pool_release(D->Ap); D->Ap = nullptr; }
+    if (D->s) { pool_release(D->s); D->s = nullptr; }
 }
 
 void dist_free(mgcg_ctx *c)
@@ -544,6 +547,7 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
         L.lo = rk > 0 ? L.halo : 0; L.hi = rk < W - 1 ? L.halo : 0;
         MGCG_CHECK(alloc_level_vectors_dist(L, true, st));
         MGCG_CHECK(extract_dinv(c, L.A, L.off, L.dinv));
+        if (o.precond == MGCG_PRECOND_MG) MGCG_CHECK(dist_level_chebyshev(c, L));
         const size_t e = (size_t)L.lo + L.own + L.hi + 1;
         MGCG_CUDA(pool_alloc((void **)&D->p, sizeof(double) * e, c->stream));
         MGCG_CUDA(pool_alloc((void **)&D->r, sizeof(double) * e, c->stream));
@@ -583,6 +587,7 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
                 if (D->L[l].xa) pool_release(D->L[l].xa);
                 if (D->L[l].xb) pool_release(D->L[l].xb);
                 if (D->L[l].r) pool_release(D->L[l].r);
+                if (D->L[l].d) pool_release(D->L[l].d);
                 if (D->L[l].b) pool_release(D->L[l].b);
                 D->L.pop_back();
             }
@@ -604,6 +609,7 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
         if (!halo_fits) N.halo = 0x3fffffff;   // forces replication of this level on the next pass
         MGCG_CHECK(alloc_level_vectors_dist(N, false, st));
         MGCG_CHECK(extract_dinv(c, N.A, N.off, N.dinv));
+        MGCG_CHECK(dist_level_chebyshev(c, N));
         memcpy(cur_offs, g.coff, sizeof(int) * (size_t)(W + 1));
         if (g.structured) { cur_nx = g.cx; cur_ny = g.cy; } else { cur_nx = cur_ny = 0; }
     }
@@ -624,9 +630,9 @@ __global__ void k_dist_finalize(int mode, int k, int world, const double *__rest
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     if (gated && sc->done) return;
-    double s0 = 0.0, s1 = 0.0;
-    for (int r = 0; r < world; ++r) { s0 += all[r * k]; if (k > 1) s1 += all[r * k + 1]; }
-    dist_finalize(mode, s0, s1, sc);
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+    for (int r = 0; r < world; ++r) { s0 += all[r * k]; if (k > 1) s1 += all[r * k + 1]; if (k > 2) s2 += all[r * k + 2]; }
+    dist_finalize(mode, s0, s1, s2, sc);
 }
 
 static int dist_reduce(mgcg_ctx *c, int mode, int k, bool gated)
@@ -641,6 +647,8 @@ static int dist_reduce(mgcg_ctx *c, int mode, int k, bool gated)
     return MGCG_OK;
 }
 
+static inline const double *shifted(const double *ext, int off, int lo) { return ext - ((ptrdiff_t)off - lo); }
+
 static int dist_gather_coarse_b(mgcg_ctx *c)
 {
     DistState *D = c->dist;
@@ -648,7 +656,50 @@ static int dist_gather_coarse_b(mgcg_ctx *c)
     return allgather_v(c, D->coarse_b, D->coarse_offs, ncclDouble, sizeof(double));
 }
 
-static inline const double *shifted(const double *ext, int off, int lo) { return ext - ((ptrdiff_t)off - lo); }
+// Chebyshev smoother on a distributed level: the eigenvalue bound is the maximum over every rank's rows
+static int dist_level_chebyshev(mgcg_ctx *c, DistLevel &L)
+{
+    DistState *D = c->dist;
+    if (c->opt.mg_smoother != MGCG_SMOOTHER_CHEBYSHEV) return MGCG_OK;
+    L.cheb = c->opt.mg_cheby_degree;
+    double mine = 0.0;
+    MGCG_CHECK(gershgorin_lmax(c, L.A, L.dinv, &mine));
+    double *d = nullptr;
+    MGCG_CUDA(pool_alloc((void **)&d, 2 * sizeof(double), c->stream));
+    MGCG_CUDA(cudaMemcpyAsync(d, &mine, sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    MGCG_NCCL(D->api, AllReduce(d, d + 1, 1, ncclDouble, ncclMax, D->comm, c->stream));
+    MGCG_CUDA(cudaMemcpyAsync(&L.lmax, d + 1, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    MGCG_CUDA(cudaStreamSynchronize(c->stream));
+    pool_release(d);
+    MGCG_CUDA(pool_alloc((void **)&L.d, sizeof(double) * ((size_t)L.own + 1), c->stream));
+    return MGCG_OK;
+}
+static double dist_first_omega(mgcg_ctx *c, const DistLevel &L)
+{
+    if (!L.cheb) return c->opt.mg_omega;
+    double c1, c2;
+    cheby_coeffs(L.lmax, c->opt.mg_cheby_ratio, 0, &c1, &c2);
+    return c2;
+}
+
+// one Chebyshev smoothing step (L.cheb products, a halo exchange before each); see mg_cycle.cu cheby_smooth
+static int dist_cheby_smooth(mgcg_ctx *c, DistLevel &L, bool skip_first, double *dot_out)
+{
+    for (int k = skip_first ? 1 : 0; k < L.cheb; ++k) {
+        double c1, c2;
+        cheby_coeffs(L.lmax, c->opt.mg_cheby_ratio, k, &c1, &c2);
+        double *other = (L.xcur == L.xa) ? L.xb : L.xa;
+        const bool last = dot_out && k == L.cheb - 1;
+        MGCG_CHECK(dist_halo_exchange(c, L.xcur, L.own, L.lo, L.hi, L.halo));
+        SpmvArgs a;
+        a.A = L.A; a.x = shifted(L.xcur, L.off, L.lo); a.xrow = L.xcur + L.lo; a.y = other + L.lo; a.b = L.b; a.dinv = L.dinv;
+        a.alpha = c1; a.omega = c2; a.d_in = (skip_first && k == 1) ? L.xcur + L.lo : L.d; a.d_out = L.d;
+        a.gated = true; a.fin = FIN_STORE; a.out = dot_out;
+        MGCG_CHECK(spmv_launch(c, L.planA, last ? EPI_CHEBY_DOT : EPI_CHEBY, a));
+        L.xcur = other;
+    }
+    return MGCG_OK;
+}
 
 static int dist_jacobi_sweep(mgcg_ctx *c, DistLevel &L, double omega, double *dot_out)
 {
@@ -685,8 +736,13 @@ static int dist_vcycle(mgcg_ctx *c, double *r_ext, double **z_own, bool fuse_fir
     for (int l = 0; l < Ld; ++l) {
         DistLevel &L = D->L[l];
         L.xcur = L.xa;
-        if (!(l == 0 && fuse_first_done)) MGCG_CHECK(mg_jacobi_first(c, L.own, omega, L.dinv, L.b, L.xa + L.lo));
-        for (int s = 1; s < pre; ++s) MGCG_CHECK(dist_jacobi_sweep(c, L, omega, nullptr));
+        if (!(l == 0 && fuse_first_done)) MGCG_CHECK(mg_jacobi_first(c, L.own, dist_first_omega(c, L), L.dinv, L.b, L.xa + L.lo));
+        if (L.cheb) {
+            MGCG_CHECK(dist_cheby_smooth(c, L, true, nullptr));
+            for (int s = 1; s < pre; ++s) MGCG_CHECK(dist_cheby_smooth(c, L, false, nullptr));
+        } else {
+            for (int s = 1; s < pre; ++s) MGCG_CHECK(dist_jacobi_sweep(c, L, omega, nullptr));
+        }
         dist_trace(c, l == 0 ? "L0 pre-smooth" : "L1+ pre-smooth");
         MGCG_CHECK(dist_halo_exchange(c, L.xcur, L.own, L.lo, L.hi, L.halo));
         dist_trace(c, l == 0 ? "L0 halo(z)" : "L1+ halo(z)");
@@ -723,7 +779,8 @@ static int dist_vcycle(mgcg_ctx *c, double *r_ext, double **z_own, bool fuse_fir
         dist_trace(c, l == 0 ? "L0 prolong" : "L1+ prolong");
         for (int s = 0; s < post; ++s) {
             const bool last = (l == 0 && s == post - 1 && rz_out);
-            MGCG_CHECK(dist_jacobi_sweep(c, L, omega, last ? rz_out : nullptr));
+            if (L.cheb) MGCG_CHECK(dist_cheby_smooth(c, L, false, last ? rz_out : nullptr));
+            else MGCG_CHECK(dist_jacobi_sweep(c, L, omega, last ? rz_out : nullptr));
             dist_trace(c, l == 0 ? "L0 post-smooth (halo + sweep)" : "L1+ post-smooth (halo + sweep)");
         }
     }
@@ -759,7 +816,7 @@ static int dist_enqueue_iteration(mgcg_ctx *c, double *x)
     } else {
         const bool fuse = D->first_replicated > 0;
         MGCG_CHECK(cg_update_xr(c, n, p_own, D->Ap, x, r_own, FIN_STORE, false, 0.0, D->partial_send,
-                                fuse ? L0.xa + L0.lo : nullptr, fuse ? L0.dinv : nullptr, c->opt.mg_omega));
+                                fuse ? L0.xa + L0.lo : nullptr, fuse ? L0.dinv : nullptr, dist_first_omega(c, L0)));
         dist_trace(c, "update x,r (+z0)");
         double *z = nullptr;
         MGCG_CHECK(dist_vcycle(c, D->r, &z, fuse, D->partial_send + 1));
@@ -767,6 +824,42 @@ static int dist_enqueue_iteration(mgcg_ctx *c, double *x)
         dist_trace(c, "reduce r.r, r.z");
         MGCG_CHECK(cg_update_p(c, n, z, p_own, false, 0.0));
     }
+    return MGCG_OK;
+}
+
+// One iteration of the single-reduce recurrence on the shards (cg.cu enqueue_iteration_cgcg): ONE scalar exchange carrying w.u, r.u
+// and r.r instead of the classic loop's two.
+static int dist_enqueue_iteration_cgcg(mgcg_ctx *c, double *x)
+{
+    DistState *D = c->dist;
+    DistLevel &L0 = D->L[0];
+    const int n = L0.own;
+    const bool pre = (c->opt.precond == MGCG_PRECOND_MG);
+    double *p_own = D->p + L0.lo, *r_own = D->r + L0.lo;
+    double *u_ext = D->r;
+    if (!pre) {
+        MGCG_CHECK(cgcg_update(c, n, r_own, D->Ap, p_own, D->s, x, r_own, nullptr, nullptr, 0.0, D->partial_send + 2));
+    } else {
+        const bool fuse = D->first_replicated > 0;
+        MGCG_CHECK(cgcg_update(c, n, D->cgcg_u, D->Ap, p_own, D->s, x, r_own, fuse ? L0.xa + L0.lo : nullptr, fuse ? L0.dinv : nullptr,
+                               dist_first_omega(c, L0), D->partial_send + 2));
+        dist_trace(c, "update p,s,x,r (+z0)");
+        double *z = nullptr;
+        MGCG_CHECK(dist_vcycle(c, D->r, &z, fuse, D->partial_send + 1));
+        if (z != D->cgcg_u) { set_error("mgcg_solve_dist: the V-cycle's output buffer moved between iterations"); return MGCG_ERR_INVALID; }
+        u_ext = z - L0.lo;
+    }
+    if (!(pre && D->first_replicated == 0)) {    // (a fully replicated preconditioner returns a slice of a global-length vector)
+        MGCG_CHECK(dist_halo_exchange(c, u_ext, n, L0.lo, L0.hi, L0.halo));
+        dist_trace(c, "halo(u)");
+    }
+    SpmvArgs a;
+    a.A = c->A; a.y = D->Ap; a.w = u_ext + L0.lo; a.fin = FIN_STORE; a.out = D->partial_send; a.gated = true;
+    a.x = (pre && D->first_replicated == 0) ? (u_ext + L0.lo) - L0.off : shifted(u_ext, L0.off, L0.lo);
+    MGCG_CHECK(spmv_launch(c, c->planA, EPI_DOT, a));
+    dist_trace(c, "A u + u.Au");
+    MGCG_CHECK(dist_reduce(c, pre ? DF_CGCG : DF_CGCG_PLAIN, 3, true));
+    dist_trace(c, "reduce w.u, r.u, r.r");
     return MGCG_OK;
 }
 
@@ -793,7 +886,11 @@ static void dist_trace_dump(mgcg_ctx *c, int iterations, float solve_ms)
     ev.clear();
 }
 
-static int dist_enqueue_thunk(mgcg_ctx *c, void *x) { return dist_enqueue_iteration(c, (double *)x); }
+static int dist_enqueue_thunk(mgcg_ctx *c, void *x)
+{
+    if (c->opt.cg_variant == MGCG_CG_SINGLE_REDUCE) return dist_enqueue_iteration_cgcg(c, (double *)x);
+    return dist_enqueue_iteration(c, (double *)x);
+}
 
 static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
 {
@@ -831,15 +928,30 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
         a.A = c->A; a.x = shifted(D->p, L0.off, L0.lo); a.y = D->Ap;
         MGCG_CHECK(spmv_launch(c, c->planA, EPI_PLAIN, a));
     }
+    const bool cgcg = c->opt.cg_variant == MGCG_CG_SINGLE_REDUCE;
     if (!pre) {
-        MGCG_CHECK(cg_init_residual(c, n, b, D->Ap, r_own, p_own, FIN_STORE, D->partial_send));
+        MGCG_CHECK(cg_init_residual(c, n, b, D->Ap, r_own, cgcg ? nullptr : p_own, FIN_STORE, D->partial_send));
         MGCG_CHECK(dist_reduce(c, DF_INIT_PLAIN, 1, false));
     } else {
         MGCG_CHECK(cg_init_residual(c, n, b, D->Ap, r_own, nullptr, FIN_STORE, D->partial_send));
         double *z = nullptr;
         MGCG_CHECK(dist_vcycle(c, D->r, &z, false, D->partial_send + 1));
         MGCG_CHECK(dist_reduce(c, DF_INIT_PRE, 2, false));
-        MGCG_CHECK(vec_copy(c, n, z, p_own));
+        if (cgcg) D->cgcg_u = z;
+        else MGCG_CHECK(vec_copy(c, n, z, p_own));
+    }
+    if (cgcg) {   // w = A u ; delta = w.u ; alpha = gamma / delta ; beta = 0 ; p = s = 0
+        if (!D->s) MGCG_CUDA(pool_alloc((void **)&D->s, sizeof(double) * ((size_t)n + 1), st));
+        const bool repl = pre && D->first_replicated == 0;
+        double *u_ext = pre ? D->cgcg_u - L0.lo : D->r;
+        if (!repl) MGCG_CHECK(dist_halo_exchange(c, u_ext, n, L0.lo, L0.hi, L0.halo));
+        SpmvArgs a;
+        a.A = c->A; a.y = D->Ap; a.w = u_ext + L0.lo; a.fin = FIN_STORE; a.out = D->partial_send;
+        a.x = repl ? (u_ext + L0.lo) - L0.off : shifted(u_ext, L0.off, L0.lo);
+        MGCG_CHECK(spmv_launch(c, c->planA, EPI_DOT, a));
+        MGCG_CHECK(dist_reduce(c, DF_CGCG_INIT, 1, false));
+        MGCG_CUDA(cudaMemsetAsync(p_own, 0, sizeof(double) * (size_t)n, st));
+        MGCG_CUDA(cudaMemsetAsync(D->s, 0, sizeof(double) * (size_t)n, st));
     }
     const int interval = c->opt.check_interval > 0 ? c->opt.check_interval : 8;
     long long enq = 0;
@@ -853,8 +965,10 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     }
     const bool use_graph = D->peer.active && c->opt.use_graph && !c->opt.profile && !D->trace;
     const int want_mode = use_graph ? (c->opt.use_graph >= 2 ? 2 : 1) : 0;
-    if (use_graph && (!D->graph_exec || D->graph_b != b || D->graph_x != x || (D->graph_mode != want_mode && D->graph_mode != -want_mode))) {
+    if (use_graph && (!D->graph_exec || D->graph_b != b || D->graph_x != x || D->graph_variant != c->opt.cg_variant ||
+                      (D->graph_mode != want_mode && D->graph_mode != -want_mode))) {
         dist_graph_free(D);
+        D->graph_variant = c->opt.cg_variant;
         const int l0 = c->launches, lc0 = D->coarse ? D->coarse->launches : 0, h0 = D->halo_exchanges, g0 = D->allgathers;
         D->graph_mode = 0;
         if (want_mode == 2) {   // WHILE(!done) { iteration } on the device: every rank leaves the loop at the same iteration
@@ -866,7 +980,7 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
             c->launches = l0; D->halo_exchanges = h0; D->allgathers = g0;
             if (D->coarse) D->coarse->launches = lc0;
             MGCG_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-            int s = dist_enqueue_iteration(c, x);
+            int s = dist_enqueue_thunk(c, x);
             cudaError_t e = cudaStreamEndCapture(st, &D->graph);
             if (s != MGCG_OK) return s;
             MGCG_CUDA(e);
@@ -892,7 +1006,7 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
                 MGCG_CUDA(cudaGraphLaunch(D->graph_exec, st));
                 c->launches += D->graph_nodes; D->halo_exchanges += D->graph_halo; D->allgathers += D->graph_gather;
             } else {
-                MGCG_CHECK(dist_enqueue_iteration(c, x));
+                MGCG_CHECK(dist_enqueue_thunk(c, x));
             }
             ++enq;
         }
@@ -1010,7 +1124,9 @@ extern "C" int mgcg_setup_dist(mgcg_ctx *c, int global_count, int row_offset, in
     MGCG_CUDA(cudaSetDevice(c->device));
     if (opt) c->opt = *opt;
     if (c->opt.norm == MGCG_NORM_ABS_LINF) { set_error("mgcg_setup_dist: the max-norm stop rule is not available on the sharded path"); return MGCG_ERR_UNSUPPORTED; }
-    if (c->opt.mg_smoother != MGCG_SMOOTHER_JACOBI) { set_error("mgcg_setup_dist: only the weighted-Jacobi smoother is implemented"); return MGCG_ERR_UNSUPPORTED; }
+    if (c->opt.mg_smoother != MGCG_SMOOTHER_JACOBI && c->opt.mg_smoother != MGCG_SMOOTHER_CHEBYSHEV) {
+        set_error("mgcg_setup_dist: the sharded levels are smoothed by weighted Jacobi or Chebyshev (red-black Gauss-Seidel is single-GPU)"); return MGCG_ERR_UNSUPPORTED;
+    }
     if (c->opt.precond == MGCG_PRECOND_MG && c->opt.mg_aggregation == MGCG_AGG_MIS2) {
         set_error("mgcg_setup_dist: MIS-2 aggregation is single-GPU only (sharded levels aggregate by grid blocks or blocks of 8 rows)");
         return MGCG_ERR_UNSUPPORTED;

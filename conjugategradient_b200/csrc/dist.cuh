@@ -54,7 +54,7 @@ constexpr int kPeerMax = 16;            // ranks of one NVSwitch domain served b
 struct PeerCtl {                        // head of every rank's arena; remote ranks write xflag / rflag / rslot
     unsigned long long xflag[kPeerMax]; // xflag[q]: sequence number of the last exchange whose data from rank q has landed
     unsigned long long rflag[kPeerMax]; // the same for the scalar reductions
-    double rslot[2][kPeerMax][2];       // [parity][sender][value]
+    double rslot[2][kPeerMax][4];       // [parity][sender][value] (up to 3 sums per reduction)
     unsigned long long xseq, rseq;      // local: exchanges / reductions completed (device-resident so graphs replay)
     unsigned int ticket1, ticket2, pad[2];
 };
@@ -98,6 +98,9 @@ struct DistLevel {
     double *b = nullptr;                    // own (levels >= 1; level 0 uses the CG residual, which is [lo|own|hi] too)
     double *xcur = nullptr;
     SpmvPlan planA, planP, planR;
+    int cheb = 0;                           // Chebyshev smoother: degree (0: weighted Jacobi)
+    double lmax = 0.0;                      // ... Gershgorin bound of D^-1 A over ALL ranks' rows
+    double *d = nullptr;                    // ... direction vector (own rows)
     LevelGeom geom;                         // rule that maps this level's rows to the next level's aggregates
     int dims_z = 0;                         // structured: z-planes owned
     bool next_replicated = false;
@@ -123,6 +126,9 @@ struct DistState {
     double *p = nullptr;                    // [lo|own|hi]
     double *r = nullptr;                    // [lo|own|hi] (ghosts used by the restriction)
     double *Ap = nullptr;                   // own
+    double *s = nullptr;                    // own; single-reduce CG: s = A p by recurrence (allocated on first use)
+    double *cgcg_u = nullptr;               // single-reduce CG: own-rows pointer of the V-cycle's output (fixed across iterations)
+    int graph_variant = 0;                  // cg_variant the captured graph was built for
     // scalar reductions: per-rank partials -> all-gather -> fixed rank-order sum (cs:463 resultsDot.Sum())
     double *partial_send = nullptr;         // [2]
     double *partial_all = nullptr;          // [2 * world]
@@ -151,10 +157,14 @@ inline void dist_trace(mgcg_ctx *c, const char *label)
 }
 
 // solve: per-rank partial sums -> exchange -> every rank adds them in rank order, then the CG bookkeeping
-enum DistFin { DF_INIT_PLAIN = 0, DF_INIT_PRE, DF_PAP, DF_RR, DF_RR_RZ };
-__device__ __forceinline__ void dist_finalize(int mode, double s0, double s1, Scalars *sc)
+enum DistFin { DF_INIT_PLAIN = 0, DF_INIT_PRE, DF_PAP, DF_RR, DF_RR_RZ, DF_CGCG_INIT, DF_CGCG, DF_CGCG_PLAIN };
+__device__ __forceinline__ void dist_finalize(int mode, double s0, double s1, double s2, Scalars *sc)
 {
     switch (mode) {
+    // single-reduce CG: s0 = w.u, s1 = r.u, s2 = r.r — the iteration's only scalar exchange
+    case DF_CGCG_INIT: sc->gamma_new = sc->rz; finalize(FIN_CGCG_INIT, s0, 0.0, sc, nullptr); break;
+    case DF_CGCG: sc->rr_pend = s2; sc->rmax = 0.0; sc->gamma_new = s1; finalize(FIN_CGCG_DELTA, s0, 0.0, sc, nullptr); break;
+    case DF_CGCG_PLAIN: sc->rr_pend = s2; sc->rmax = 0.0; finalize(FIN_CGCG_DELTA_PLAIN, s0, 0.0, sc, nullptr); break;
     case DF_INIT_PLAIN: finalize(FIN_INIT, s0, 0.0, sc, nullptr); break;
     case DF_INIT_PRE: finalize(FIN_INIT_RR, s0, 0.0, sc, nullptr); finalize(FIN_INIT_RZ, s1, 0.0, sc, nullptr); break;
     case DF_PAP: finalize(FIN_PAP, s0, 0.0, sc, nullptr); break;

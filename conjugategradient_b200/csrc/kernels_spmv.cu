@@ -30,20 +30,32 @@ __device__ __forceinline__ void epilogue(int row, double s, const SpmvArgs &a, d
         a.y[row] = yi;
         if (EPI == EPI_JACOBI_DOT) dsum += bi * yi;
     }
+    else if (EPI == EPI_CHEBY || EPI == EPI_CHEBY_DOT) {
+        const double bi = a.b[row];
+        const double dn = (a.alpha == 0.0 ? 0.0 : a.alpha * a.d_in[row]) + a.omega * a.dinv[row] * (bi - s);
+        const double yi = (a.xrow ? a.xrow : a.x)[row] + dn;
+        a.d_out[row] = dn;
+        a.y[row] = yi;
+        if (EPI == EPI_CHEBY_DOT) dsum += bi * yi;
+    }
 }
 
 // The epilogue's operands that do not depend on the row sum, loaded BEFORE the wait for the tile's matrix slice so that their
 // latency overlaps it (the prolongator's 3-entry rows leave nothing else to hide a y[row] round trip behind).  Same
 // expressions as epilogue<EPI>, operand for operand.
-struct EpiPre { double e0, e1, e2; };
+struct EpiPre { double e0, e1, e2, e3; };
 template <int EPI>
 __device__ __forceinline__ void epi_prefetch(int row, const SpmvArgs &a, EpiPre &p)
 {
-    p.e0 = 0.0; p.e1 = 0.0; p.e2 = 0.0;
+    p.e0 = 0.0; p.e1 = 0.0; p.e2 = 0.0; p.e3 = 0.0;
     if (EPI == EPI_AXPBY) { if (a.beta != 0.0) p.e0 = a.y[row]; }
     else if (EPI == EPI_DOT) p.e0 = a.w[row];
     else if (EPI == EPI_RESID) p.e0 = a.b[row];
     else if (EPI == EPI_JACOBI || EPI == EPI_JACOBI_DOT) { p.e0 = a.b[row]; p.e1 = (a.xrow ? a.xrow : a.x)[row]; p.e2 = a.dinv[row]; }
+    else if (EPI == EPI_CHEBY || EPI == EPI_CHEBY_DOT) {
+        p.e0 = a.b[row]; p.e1 = (a.xrow ? a.xrow : a.x)[row]; p.e2 = a.dinv[row];
+        if (a.alpha != 0.0) p.e3 = a.d_in[row];
+    }
 }
 template <int EPI>
 __device__ __forceinline__ void epilogue_pre(int row, double s, const SpmvArgs &a, double &dsum, const EpiPre &p)
@@ -57,6 +69,14 @@ __device__ __forceinline__ void epilogue_pre(int row, double s, const SpmvArgs &
         const double yi = p.e1 + a.omega * p.e2 * (bi - s);
         a.y[row] = yi;
         if (EPI == EPI_JACOBI_DOT) dsum += bi * yi;
+    }
+    else if (EPI == EPI_CHEBY || EPI == EPI_CHEBY_DOT) {
+        const double bi = p.e0;
+        const double dn = (a.alpha == 0.0 ? 0.0 : a.alpha * p.e3) + a.omega * p.e2 * (bi - s);
+        const double yi = p.e1 + dn;
+        a.d_out[row] = dn;
+        a.y[row] = yi;
+        if (EPI == EPI_CHEBY_DOT) dsum += bi * yi;
     }
 }
 
@@ -75,7 +95,7 @@ __device__ __forceinline__ void epilogue_inactive(const SpmvArgs &a, double &dsu
     if (EPI == EPI_JACOBI_DOT) dsum += p.e0 * p.e1;
 }
 
-template <int EPI> struct EpiTraits { static constexpr bool reduces = (EPI == EPI_DOT || EPI == EPI_JACOBI_DOT); };
+template <int EPI> struct EpiTraits { static constexpr bool reduces = (EPI == EPI_DOT || EPI == EPI_JACOBI_DOT || EPI == EPI_CHEBY_DOT); };
 
 // ---------------------------------------------------------------------------------------------------------
 template <int EPI>
@@ -617,6 +637,8 @@ int spmv_launch(mgcg_ctx *c, const SpmvPlan &plan, int epi, const SpmvArgs &a)
     case EPI_RESID: return launch_epi<EPI_RESID>(c, plan, a);
     case EPI_JACOBI: return launch_epi<EPI_JACOBI>(c, plan, a);
     case EPI_JACOBI_DOT: return launch_epi<EPI_JACOBI_DOT>(c, plan, a);
+    case EPI_CHEBY: return launch_epi<EPI_CHEBY>(c, plan, a);
+    case EPI_CHEBY_DOT: return launch_epi<EPI_CHEBY_DOT>(c, plan, a);
     }
     set_error("spmv_launch: unknown epilogue %d", epi);
     return MGCG_ERR_INVALID;

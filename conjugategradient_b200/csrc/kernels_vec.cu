@@ -219,6 +219,45 @@ int cg_update_xr(mgcg_ctx *c, int n, const double *p, const double *Ap, double *
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// single-reduce (Chronopoulos-Gear) CG, one pass over 6 (8) vectors:
+//   p = u + beta p ; s = w + beta s ; x += alpha p ; r -= alpha s ; r.r, max|r| [; z0 = omega dinv r]
+// s tracks A p by recurrence, so the iteration's only product is w = A u and its three sums land at one point.
+template <bool Z0>
+__global__ void __launch_bounds__(kVecThreads) k_cgcg_update(int n, const double *__restrict__ u, const double *__restrict__ w,
+                                                             double *__restrict__ p, double *__restrict__ s, double *__restrict__ x,
+                                                             double *__restrict__ r, ReduceWs ws, Scalars *sc, double *out,
+                                                             double *__restrict__ z0, const double *__restrict__ dinv, double omega)
+{
+    if (sc->done) return;
+    const double alpha = sc->alpha, beta = sc->beta, nalpha = -alpha;
+    double sum = 0.0, m = 0.0;
+    const int stride = gridDim.x * blockDim.x;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const double pi = u[i] + beta * p[i];
+        const double si = w[i] + beta * s[i];
+        const double xi = x[i] + alpha * pi;
+        const double ri = r[i] + nalpha * si;
+        p[i] = pi; s[i] = si; x[i] = xi; r[i] = ri;
+        sum += ri * ri;
+        m = fmax(m, fabs(ri));
+        if (Z0) z0[i] = omega * dinv[i] * ri;
+    }
+    block_reduce<true>(sum, m);
+    grid_reduce_finish<true>(sum, m, ws, out ? FIN_STORE : FIN_CGCG_RR, sc, out);
+}
+
+int cgcg_update(mgcg_ctx *c, int n, const double *u, const double *w, double *p, double *s, double *x, double *r,
+                double *z0, const double *dinv, double omega, double *out)
+{
+    const int grid = vec_grid(c, n, 2);
+    if (z0) k_cgcg_update<true><<<grid, kVecThreads, 0, c->stream>>>(n, u, w, p, s, x, r, c->ws, c->d_scalars, out, z0, dinv, omega);
+    else k_cgcg_update<false><<<grid, kVecThreads, 0, c->stream>>>(n, u, w, p, s, x, r, c->ws, c->d_scalars, out, z0, dinv, omega);
+    c->launches++;
+    MGCG_LAUNCH_CHECK();
+    return MGCG_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // p = z + beta p   (ConjugateGradientCpu.cs:94; Solve3 Mgcg.cu:197 does it as scal+axpy = 2 passes)
 template <int V>
 __global__ void __launch_bounds__(kVecThreads) k_update_p(int n, const double *__restrict__ z, double *__restrict__ p,

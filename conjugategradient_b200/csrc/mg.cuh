@@ -27,7 +27,25 @@ struct MgLevel {
     SpmvPlan planA, planP, planR;
     int dims[3] = {0, 0, 0};
     bool rb = false;       // smoothed by red-black Gauss-Seidel: grid known and every off-diagonal entry joins cells of opposite parity
+    int cheb = 0;          // smoothed by a Chebyshev polynomial of this degree in D^-1 A (0: no)
+    double lmax = 0.0;     // ... on [lmax / ratio, lmax], lmax = max_i sum_j |a_ij| / |a_ii|
+    double *d = nullptr;   // ... its direction vector
 };
+// coefficients of step k (0-based) of the Chebyshev iteration on [lmax/ratio, lmax] (Saad, alg. 12.1): d_k = c1 d_{k-1} + c2 D^-1 r
+inline void cheby_coeffs(double lmax, double ratio, int k, double *c1, double *c2)
+{
+    const double lmin = lmax / ratio;
+    const double theta = 0.5 * (lmax + lmin), delta = 0.5 * (lmax - lmin), sigma = theta / delta;
+    double rho = 1.0 / sigma;
+    *c1 = 0.0; *c2 = 1.0 / theta;
+    for (int j = 1; j <= k; ++j) {
+        const double rho_new = 1.0 / (2.0 * sigma - rho);
+        *c1 = rho_new * rho; *c2 = 2.0 * rho_new / delta;
+        rho = rho_new;
+    }
+}
+// max_i sum_j |a_ij| * |dinv_i| (device scalar -> host; synchronises)                                      (mg_setup.cu)
+int gershgorin_lmax(mgcg_ctx *c, const Csr &A, const double *dinv, double *out);
 
 // arguments of the persistent coarse-tail kernel (mg_tail.cu)
 constexpr int kTailMaxLevels = 8;

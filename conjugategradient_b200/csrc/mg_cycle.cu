@@ -28,6 +28,26 @@ static int gs_half_sweep(mgcg_ctx *c, MgLevel &L, int color, bool with_dot, int 
     return spmv_launch(c, L.planA, with_dot ? EPI_JACOBI_DOT : EPI_JACOBI, a);
 }
 
+// One Chebyshev smoothing step = L.cheb products (CPU twin: oracle/mg_ref.c cheby_smooth).  skip_first: step 0 from a zero guess was
+// already done by the caller (x = d = c2_0 D^-1 b sits in L.xcur; its direction is read from there by step 1).
+// with_dot: sum_i b_i x_i of the final x goes through `fin`.
+static int cheby_smooth(mgcg_ctx *c, MgLevel &L, bool skip_first, bool with_dot, int fin)
+{
+    const double ratio = c->opt.mg_cheby_ratio;
+    for (int k = skip_first ? 1 : 0; k < L.cheb; ++k) {
+        double c1, c2;
+        cheby_coeffs(L.lmax, ratio, k, &c1, &c2);
+        double *other = (L.xcur == L.xa) ? L.xb : L.xa;
+        const bool last = with_dot && k == L.cheb - 1;
+        SpmvArgs a;
+        a.A = L.A; a.x = L.xcur; a.y = other; a.b = L.b; a.dinv = L.dinv; a.gated = true; a.fin = last ? fin : FIN_STORE;
+        a.alpha = c1; a.omega = c2; a.d_in = (skip_first && k == 1) ? L.xcur : L.d; a.d_out = L.d;
+        MGCG_CHECK(spmv_launch(c, L.planA, last ? EPI_CHEBY_DOT : EPI_CHEBY, a));
+        L.xcur = other;
+    }
+    return MGCG_OK;
+}
+
 // z_out receives the level-0 buffer holding z.  fuse_first_done: level 0's first sweep (xa = w D^-1 r) was already
 // produced by cg_update_xr.  rz_fin: FinOp applied to sum_i r_i z_i (fused into the last post-smoothing sweep).
 int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done, int rz_fin)
@@ -56,6 +76,13 @@ int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done
     for (int l = 0; l < down_end; ++l) {
         MgLevel &L = H->L[l];
         L.xcur = L.xa;
+        if (L.cheb) {
+            double c1, c2;
+            cheby_coeffs(L.lmax, c->opt.mg_cheby_ratio, 0, &c1, &c2);
+            if (!(l == 0 && fuse_first_done)) MGCG_CHECK(mg_jacobi_first(c, L.A.rows, c2, L.dinv, L.b, L.xa));
+            MGCG_CHECK(cheby_smooth(c, L, true, false, FIN_STORE));
+            for (int s = 1; s < pre; ++s) MGCG_CHECK(cheby_smooth(c, L, false, false, FIN_STORE));
+        } else {
         if (!(l == 0 && fuse_first_done)) MGCG_CHECK(mg_jacobi_first(c, L.A.rows, L.rb ? 1.0 : omega, L.dinv, L.b, L.xa));
         if (L.rb) {
             // symmetric red-black Gauss-Seidel, red then black on the way down.  From a zero guess the red half sweep is
@@ -64,6 +91,7 @@ int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done
             for (int s = 1; s < pre; ++s) { MGCG_CHECK(gs_half_sweep(c, L, 0, false, FIN_STORE)); MGCG_CHECK(gs_half_sweep(c, L, 1, false, FIN_STORE)); }
         } else {
             for (int s = 1; s < pre; ++s) MGCG_CHECK(jacobi_sweep(c, L, omega, false, FIN_STORE));
+        }
         }
         SpmvArgs a;
         a.A = L.A; a.x = L.xcur; a.y = L.r; a.b = L.b; a.gated = true;
@@ -89,7 +117,9 @@ int mg_vcycle(mgcg_ctx *c, const double *r, double **z_out, bool fuse_first_done
         MGCG_CHECK(spmv_launch(c, L.planP, EPI_AXPBY, a));
         for (int s = 0; s < post; ++s) {
             const bool last = (l == 0 && s == post - 1 && rz_fin >= 0);
-            if (L.rb) {      // black then red on the way up: the adjoint of the pre-smoother, so M stays symmetric
+            if (L.cheb) {
+                MGCG_CHECK(cheby_smooth(c, L, false, last, last ? rz_fin : FIN_STORE));
+            } else if (L.rb) {      // black then red on the way up: the adjoint of the pre-smoother, so M stays symmetric
                 MGCG_CHECK(gs_half_sweep(c, L, 1, false, FIN_STORE));
                 MGCG_CHECK(gs_half_sweep(c, L, 0, last, last ? rz_fin : FIN_STORE));
             } else {

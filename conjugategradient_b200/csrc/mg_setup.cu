@@ -12,6 +12,7 @@
 //   coarsest   : dense inverse by in-place Gauss-Jordan (SPD, no pivoting)
 // cub::DeviceRadixSort / DeviceScan are used for the sort and the scans of the SETUP only (not the solve path).
 #include "mg.cuh"
+#include <string.h>
 #include <cub/cub.cuh>
 #include <chrono>
 #include <stdlib.h>
@@ -560,6 +561,35 @@ int extract_dinv(mgcg_ctx *c, const Csr &A, int row_base, double *dinv)
     return MGCG_OK;
 }
 
+// Gershgorin bound of the spectrum of D^-1 A: max over rows of sum_j |a_ij| |dinv_i|.  Row sums in storage order like the
+// CPU twin (oracle/mg_ref.c mg_ref_set_chebyshev); the maximum is order-independent, so the result is bit-identical.
+__global__ void k_gershgorin(Csr A, const double *__restrict__ dinv, unsigned long long *out)
+{
+    double m = 0.0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < A.rows; i += gridDim.x * blockDim.x) {
+        double s = 0.0;
+        for (int k = A.rowptr[i]; k < A.rowptr[i + 1]; ++k) s = __dadd_rn(s, fabs(A.val[k]));
+        s = __dmul_rn(s, fabs(dinv[i]));
+        m = fmax(m, s);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_down_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(out, (unsigned long long)__double_as_longlong(m));   // non-negative doubles order like their bits
+}
+int gershgorin_lmax(mgcg_ctx *c, const Csr &A, const double *dinv, double *out)
+{
+    unsigned long long *d = nullptr, h = 0;
+    MGCG_CUDA(pool_alloc((void **)&d, sizeof(unsigned long long), c->stream));
+    MGCG_CUDA(cudaMemsetAsync(d, 0, sizeof(unsigned long long), c->stream));
+    k_gershgorin<<<grid_for(A.rows), 256, 0, c->stream>>>(A, dinv, d);
+    MGCG_LAUNCH_CHECK();
+    MGCG_CUDA(cudaMemcpyAsync(&h, d, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+    MGCG_CUDA(cudaStreamSynchronize(c->stream));
+    pool_release(d);
+    memcpy(out, &h, sizeof(double));
+    return MGCG_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 static int alloc_level_vectors(MgLevel &L, bool level0)
 {
@@ -581,6 +611,7 @@ void mg_free(mgcg_ctx *c)
         pool_release(L.xa);
         pool_release(L.xb);
         pool_release(L.r);
+        pool_release(L.d);
         if (l > 0) pool_release(L.b);
     }
     pool_release(H->coarse_inv);
@@ -598,7 +629,10 @@ int mg_build(mgcg_ctx *c)
     tr.mark(-1, "free-old");
     const mgcg_options &o = c->opt;
     if (o.mg_pre_sweeps < 1 || o.mg_post_sweeps < 0) { set_error("mg_build: mg_pre_sweeps must be >= 1, mg_post_sweeps >= 0"); return MGCG_ERR_INVALID; }
-    if (o.mg_smoother != MGCG_SMOOTHER_JACOBI && o.mg_smoother != MGCG_SMOOTHER_RBGS) { set_error("mg_build: unknown smoother %d", o.mg_smoother); return MGCG_ERR_INVALID; }
+    if (o.mg_smoother != MGCG_SMOOTHER_JACOBI && o.mg_smoother != MGCG_SMOOTHER_RBGS && o.mg_smoother != MGCG_SMOOTHER_CHEBYSHEV) { set_error("mg_build: unknown smoother %d", o.mg_smoother); return MGCG_ERR_INVALID; }
+    if (o.mg_smoother == MGCG_SMOOTHER_CHEBYSHEV && (o.mg_cheby_degree < 1 || o.mg_cheby_degree > 16 || !(o.mg_cheby_ratio > 1.0))) {
+        set_error("mg_build: Chebyshev smoother needs 1 <= mg_cheby_degree <= 16 and mg_cheby_ratio > 1"); return MGCG_ERR_INVALID;
+    }
     cudaStream_t st = c->stream;
     Hierarchy *H = new Hierarchy();
     c->mg = H;
@@ -621,6 +655,12 @@ int mg_build(mgcg_ctx *c)
         MGCG_LAUNCH_CHECK();
         MGCG_CHECK(alloc_level_vectors(L, l == 0));
         if (n <= coarse_size || l + 1 >= max_levels) break;
+        if (o.mg_smoother == MGCG_SMOOTHER_CHEBYSHEV) {
+            L.cheb = o.mg_cheby_degree;
+            MGCG_CHECK(gershgorin_lmax(c, L.A, L.dinv, &L.lmax));
+            MGCG_CHECK(dalloc(&L.d, (size_t)n));
+            if (tr.on) fprintf(stderr, "[mgcg setup] level %d smoother: Chebyshev degree %d on [%.4f, %.4f]\n", l, L.cheb, L.lmax / o.mg_cheby_ratio, L.lmax);
+        }
         if (o.mg_smoother == MGCG_SMOOTHER_RBGS && L.dims[0] > 0 && L.planA.kernel == MGCG_SPMV_STREAM) {
             // red-black Gauss-Seidel where the level's operator is two-colourable by cell parity, weighted Jacobi elsewhere
             int two = 0;
@@ -708,7 +748,11 @@ int mg_build(mgcg_ctx *c)
 }
 
 double *mg_level0_first_x(mgcg_ctx *c) { return c->mg ? c->mg->L[0].xa : nullptr; }
-double mg_level0_first_omega(mgcg_ctx *c) { return (c->mg && c->mg->L[0].rb) ? 1.0 : c->opt.mg_omega; }
+double mg_level0_first_omega(mgcg_ctx *c)
+{
+    if (c->mg && c->mg->L[0].cheb) { double c1, c2; cheby_coeffs(c->mg->L[0].lmax, c->opt.mg_cheby_ratio, 0, &c1, &c2); return c2; }
+    return (c->mg && c->mg->L[0].rb) ? 1.0 : c->opt.mg_omega;
+}
 const double *mg_level0_dinv(mgcg_ctx *c) { return c->mg ? c->mg->L[0].dinv : nullptr; }
 
 }  // namespace mgcg

@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(64) k_peer_reduce(int mode, int k, int rank, i
                                                    Scalars *sc, bool gated, int wait_scale)
 {
     if (gated && sc->done) return;
-    __shared__ double s_v[kPeerMax][2];
+    __shared__ double s_v[kPeerMax][3];
     __shared__ int s_fail;
     const int t = threadIdx.x;
     PeerCtl *me = pp.ctl[rank];
@@ -137,18 +137,20 @@ __global__ void __launch_bounds__(64) k_peer_reduce(int mode, int k, int rank, i
         PeerCtl *q = pp.ctl[t];
         q->rslot[par][rank][0] = mine[0];
         q->rslot[par][rank][1] = k > 1 ? mine[1] : 0.0;
+        q->rslot[par][rank][2] = k > 2 ? mine[2] : 0.0;
         __threadfence_system();
         st_release_sys(&q->rflag[rank], seq);
         if (!wait_flag(&me->rflag[t], seq, wait_scale)) s_fail = 1;
         s_v[t][0] = __ldcg(&me->rslot[par][t][0]);
         s_v[t][1] = __ldcg(&me->rslot[par][t][1]);
+        s_v[t][2] = __ldcg(&me->rslot[par][t][2]);
     }
     __syncthreads();
     if (t != 0) return;
     if (s_fail) { sc->status = MGCG_ERR_COMM; sc->done = 1; me->rseq = seq; return; }
-    double s0 = 0.0, s1 = 0.0;
-    for (int r = 0; r < world; ++r) { s0 += s_v[r][0]; s1 += s_v[r][1]; }   // rank order (cs:463 resultsDot.Sum())
-    if (mode >= 0) dist_finalize(mode, s0, s1, sc);
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+    for (int r = 0; r < world; ++r) { s0 += s_v[r][0]; s1 += s_v[r][1]; s2 += s_v[r][2]; }   // rank order (cs:463 resultsDot.Sum())
+    if (mode >= 0) dist_finalize(mode, s0, s1, s2, sc);
     me->rseq = seq;
 }
 

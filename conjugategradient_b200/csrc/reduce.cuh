@@ -41,6 +41,35 @@ __device__ __forceinline__ void block_reduce(double &s, double &m)
     }
 }
 
+// The reference's stop rule on the residual just updated (rr_new = r.r, mx = max|r|): sets residual / rmax / rr, and either
+// done (+ status) or iteration + 1.  Returns true when the loop ends here.
+__device__ __forceinline__ bool stop_rule(double rr_new, double mx, Scalars *sc)
+{
+    double res;
+    bool below;
+    if (sc->norm == MGCG_NORM_ABS_L2) { res = sqrt(rr_new); below = res < sc->tolerance; }
+    else if (sc->norm == MGCG_NORM_ABS_LINF) { res = mx; below = res < sc->tolerance; }
+    else if (sc->rr0 == 0.0) { res = 0.0; below = true; }
+    else { res = sqrt(rr_new / sc->rr0); below = (rr_new / sc->rr0) < sc->tolerance * sc->tolerance; }
+    sc->residual = res;
+    sc->rmax = mx;
+    const int it = sc->iteration;
+    bool conv;
+    if (sc->min_strict) {                       // SimpleConjugateGradient.cu:107
+        if (it > sc->max_iteration) { sc->status = MGCG_ERR_NOT_CONVERGED; sc->done = 1; conv = true; }
+        else conv = (sc->min_iteration < it) && below;
+    } else {                                    // ConjugateGradient.cs:64-77
+        if (it < sc->min_iteration) conv = false;
+        else if (it > sc->max_iteration) { sc->status = MGCG_ERR_NOT_CONVERGED; sc->done = 1; conv = true; }
+        else conv = below;
+    }
+    if (!(rr_new == rr_new)) { sc->status = MGCG_ERR_BREAKDOWN; sc->done = 1; conv = true; }   // NaN
+    sc->rr = rr_new;
+    if (conv) sc->done = 1;
+    else sc->iteration = it + 1;
+    return conv;
+}
+
 // what the last block does with the finished sums
 __device__ __forceinline__ void finalize(int fin, double sum, double mx, Scalars *sc, double *out)
 {
@@ -58,32 +87,31 @@ __device__ __forceinline__ void finalize(int fin, double sum, double mx, Scalars
     }
     case FIN_RR:
     case FIN_RR_PRECOND: {
-        const double rr_new = sum;
-        double res;
-        bool below;
-        if (sc->norm == MGCG_NORM_ABS_L2) { res = sqrt(rr_new); below = res < sc->tolerance; }
-        else if (sc->norm == MGCG_NORM_ABS_LINF) { res = mx; below = res < sc->tolerance; }
-        else if (sc->rr0 == 0.0) { res = 0.0; below = true; }
-        else { res = sqrt(rr_new / sc->rr0); below = (rr_new / sc->rr0) < sc->tolerance * sc->tolerance; }
-        sc->residual = res;
-        sc->rmax = mx;
-        const int it = sc->iteration;
-        bool conv;
-        if (sc->min_strict) {                       // SimpleConjugateGradient.cu:107
-            if (it > sc->max_iteration) { sc->status = MGCG_ERR_NOT_CONVERGED; sc->done = 1; conv = true; }
-            else conv = (sc->min_iteration < it) && below;
-        } else {                                    // ConjugateGradient.cs:64-77
-            if (it < sc->min_iteration) conv = false;
-            else if (it > sc->max_iteration) { sc->status = MGCG_ERR_NOT_CONVERGED; sc->done = 1; conv = true; }
-            else conv = below;
-        }
-        if (!(rr_new == rr_new)) { sc->status = MGCG_ERR_BREAKDOWN; sc->done = 1; conv = true; }   // NaN
-        if (conv) { sc->done = 1; sc->rr = rr_new; }
-        else {
-            if (fin == FIN_RR) { sc->beta = (sc->rr == 0.0) ? 0.0 : rr_new / sc->rr; sc->rz = rr_new; }   // ConjugateGradientCpu.cs:93
-            sc->rr = rr_new;
-            sc->iteration = it + 1;
-        }
+        const double rr_old = sc->rr;
+        if (!stop_rule(sum, mx, sc) && fin == FIN_RR) { sc->beta = (rr_old == 0.0) ? 0.0 : sum / rr_old; sc->rz = sum; }   // ConjugateGradientCpu.cs:93
+        break;
+    }
+    case FIN_CGCG_RR: sc->rr_pend = sum; sc->rmax = mx; break;
+    case FIN_CGCG_GAMMA: sc->gamma_new = sum; break;
+    case FIN_CGCG_INIT: {
+        sc->rz = sc->gamma_new;
+        sc->pAp = sum;
+        sc->alpha = (sc->rz == 0.0) ? 0.0 : sc->rz / sum;
+        sc->beta = 0.0;
+        if (!(sum > 0.0) && sc->rz != 0.0) { sc->status = MGCG_ERR_BREAKDOWN; sc->done = 1; }
+        break;
+    }
+    case FIN_CGCG_DELTA:
+    case FIN_CGCG_DELTA_PLAIN: {
+        if (stop_rule(sc->rr_pend, sc->rmax, sc)) break;
+        const double g = (fin == FIN_CGCG_DELTA) ? sc->gamma_new : sc->rr_pend;
+        const double beta = (sc->rz == 0.0) ? 0.0 : g / sc->rz;
+        const double den = sum - beta * g / sc->alpha;      // == p'.A p' of the next direction (Chronopoulos & Gear 1989)
+        sc->beta = beta;
+        sc->pAp = den;
+        sc->alpha = (g == 0.0) ? 0.0 : g / den;
+        sc->rz = g;
+        if (!(den > 0.0) && g != 0.0) { sc->status = MGCG_ERR_BREAKDOWN; sc->done = 1; }
         break;
     }
     case FIN_RZ: sc->beta = (sc->rz == 0.0) ? 0.0 : sum / sc->rz; sc->rz = sum; break;

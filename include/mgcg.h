@@ -39,7 +39,14 @@ enum {
 };
 
 enum { MGCG_PRECOND_NONE = 0, MGCG_PRECOND_MG = 1 };
-enum { MGCG_SMOOTHER_JACOBI = 0, MGCG_SMOOTHER_RBGS = 1 };
+/* smoothers: weighted Jacobi; symmetric red-black Gauss-Seidel (two-colourable grid levels, Jacobi elsewhere); Chebyshev polynomial
+ * of degree mg_cheby_degree in D^-1 A on [lmax/mg_cheby_ratio, lmax], lmax = the Gershgorin bound max_i sum_j|a_ij|/|a_ii|
+ * (opt-in, SURVEY 8(f)4: fewer iterations on the 27-point variable-coefficient operator, more products per cycle) */
+enum { MGCG_SMOOTHER_JACOBI = 0, MGCG_SMOOTHER_RBGS = 1, MGCG_SMOOTHER_CHEBYSHEV = 2 };
+/* CG recurrence: CLASSIC = the reference's (ConjugateGradientCpu.cs:45-98: two reduction points per iteration, p.Ap then r.r / r.z);
+ * SINGLE_REDUCE = Chronopoulos-Gear: the iteration's three sums (r.u, w.u, r.r) are finished at ONE point, so the sharded loop
+ * has one scalar exchange per iteration instead of two.  Same iterates in exact arithmetic; opt-in, outside the parity contract */
+enum { MGCG_CG_CLASSIC = 0, MGCG_CG_SINGLE_REDUCE = 1 };
 enum { MGCG_SPMV_AUTO = 0, MGCG_SPMV_STREAM = 1, MGCG_SPMV_VECTOR = 2, MGCG_SPMV_ROWS = 3 };
 enum { MGCG_TRANSPORT_AUTO = 0, MGCG_TRANSPORT_NCCL = 1, MGCG_TRANSPORT_PEER = 2 };
 /* aggregation of the multigrid hierarchy: AUTO = geometric blocks when nx,ny,nz are given, else strength-of-connection filter +
@@ -85,9 +92,11 @@ typedef struct mgcg_options {
                                         ONE persistent kernel with grid barriers between the steps.  Default 0 = off: measured
                                         no faster than graph-replayed launches on B200 (mg_tail.cu) */
     int    mg_aggregation;           /* MGCG_AGG_* */
-    int    reserved0;
+    int    mg_cheby_degree;          /* MGCG_SMOOTHER_CHEBYSHEV: products per smoothing step (default 2; 1 == Jacobi with w = 2/(lmax+lmin)) */
     double mg_strength_theta;        /* MIS-2: a_ij is a strong connection when |a_ij| >= theta * min(max_k|a_ik|, max_k|a_jk|); default 0.5 */
-    int    reserved[6];
+    double mg_cheby_ratio;           /* MGCG_SMOOTHER_CHEBYSHEV: lmax / lmin of the damped window (default 6) */
+    int    cg_variant;               /* MGCG_CG_* */
+    int    reserved[3];
 } mgcg_options;
 
 typedef struct mgcg_result {

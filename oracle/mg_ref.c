@@ -26,6 +26,9 @@ typedef struct {
     int dims[3];
     int ownA;
     int rb;      /* smoothed by red-black Gauss-Seidel (mg_ref_set_smoother) */
+    int cheb;    /* Chebyshev polynomial smoother of this degree in D^-1 A (0: off; mg_ref_set_chebyshev) */
+    double lmax, lmin;   /* its eigenvalue window: lmax = max_i sum_j |a_ij| / |a_ii| (Gershgorin), lmin = lmax / ratio */
+    double *d;   /* its direction vector */
 } level_t;
 typedef struct { int nl; level_t *L; double *coarse_inv; int coarse_n; } mg_ref_t;
 
@@ -352,7 +355,7 @@ void mg_ref_free(mg_ref_t *H)
         level_t *L = &H->L[l];
         if (L->ownA) csr_free(&L->A);
         csr_free(&L->P); csr_free(&L->R);
-        free(L->agg); free(L->dinv); free(L->x); free(L->x2); free(L->b); free(L->r);
+        free(L->agg); free(L->dinv); free(L->x); free(L->x2); free(L->b); free(L->r); free(L->d);
     }
     free(H->L); free(H->coarse_inv); free(H);
 }
@@ -404,6 +407,55 @@ static void gs_half_sweep(level_t *L, int color)
     }
 }
 
+/* Chebyshev smoothing (opt-in mode outside the reference-parity contract; device: csrc/mg_cycle.cu cheby_smooth).
+ * degree steps of the Chebyshev iteration for D^-1 A on [lmin, lmax] (Saad, Iterative Methods, alg. 12.1):
+ *   theta = (lmax+lmin)/2, delta = (lmax-lmin)/2, sigma = theta/delta, rho_0 = 1/sigma
+ *   d_0 = (1/theta) D^-1 (b - A x) ; x += d_0
+ *   rho_k = 1/(2 sigma - rho_{k-1}) ; d_k = rho_k rho_{k-1} d_{k-1} + (2 rho_k/delta) D^-1 (b - A x) ; x += d_k          */
+void mg_ref_set_chebyshev(mg_ref_t *H, int degree, double ratio)
+{
+    for (int l = 0; l < H->nl; l++) {
+        level_t *L = &H->L[l];
+        L->cheb = (l == H->nl - 1) ? 0 : degree;
+        if (!L->cheb) continue;
+        double g = 0.0;
+        for (int i = 0; i < L->A.rows; i++) {
+            double s = 0.0;
+            for (int k = L->A.rowptr[i]; k < L->A.rowptr[i + 1]; k++) s = s + fabs(L->A.val[k]);
+            s = s * fabs(L->dinv[i]);
+            if (s > g) g = s;
+        }
+        L->lmax = g; L->lmin = g / ratio;
+        if (!L->d) L->d = (double *)calloc((size_t)(L->A.rows > 0 ? L->A.rows : 1), sizeof(double));
+    }
+}
+double mg_ref_level_lmax(const mg_ref_t *H, int l) { return H->L[l].lmax; }
+
+/* zero_guess: x = 0 on entry (the first step needs no product) */
+static void cheby_smooth(level_t *L, int zero_guess)
+{
+    const csr_t *A = &L->A;
+    const int m = A->rows;
+    const double theta = 0.5 * (L->lmax + L->lmin), delta = 0.5 * (L->lmax - L->lmin), sigma = theta / delta;
+    double rho = 1.0 / sigma;
+    const double c0 = 1.0 / theta;
+    if (zero_guess) {
+        for (int i = 0; i < m; i++) { L->d[i] = c0 * L->dinv[i] * L->b[i]; L->x[i] = L->d[i]; }
+    } else {
+        ref_spmv(m, A->val, A->rowptr, A->col, L->x, L->x2);
+        for (int i = 0; i < m; i++) { L->d[i] = c0 * L->dinv[i] * (L->b[i] - L->x2[i]); L->x2[i] = L->x[i] + L->d[i]; }
+        double *t = L->x; L->x = L->x2; L->x2 = t;
+    }
+    for (int k = 1; k < L->cheb; k++) {
+        const double rho_new = 1.0 / (2.0 * sigma - rho);
+        const double c1 = rho_new * rho, c2 = 2.0 * rho_new / delta;
+        ref_spmv(m, A->val, A->rowptr, A->col, L->x, L->x2);
+        for (int i = 0; i < m; i++) { L->d[i] = c1 * L->d[i] + c2 * L->dinv[i] * (L->b[i] - L->x2[i]); L->x2[i] = L->x[i] + L->d[i]; }
+        double *t = L->x; L->x = L->x2; L->x2 = t;
+        rho = rho_new;
+    }
+}
+
 static void jacobi_sweep(level_t *L, double omega)
 {
     const csr_t *A = &L->A;
@@ -420,7 +472,10 @@ void mg_ref_apply(mg_ref_t *H, int pre, int post, double omega, const double *r,
     for (int l = 0; l < nl - 1; l++) {
         level_t *L = &H->L[l];
         int m = L->A.rows;
-        if (L->rb) {
+        if (L->cheb) {
+            cheby_smooth(L, 1);
+            for (int s = 1; s < pre; s++) cheby_smooth(L, 0);
+        } else if (L->rb) {
             for (int i = 0; i < m; i++) L->x[i] = 1.0 * L->dinv[i] * L->b[i];     /* == the red half sweep from a zero guess, on every row */
             gs_half_sweep(L, 1);
             for (int s = 1; s < pre; s++) { gs_half_sweep(L, 0); gs_half_sweep(L, 1); }
@@ -447,7 +502,8 @@ void mg_ref_apply(mg_ref_t *H, int pre, int post, double omega, const double *r,
         ref_spmv(m, L->P.val, L->P.rowptr, L->P.col, H->L[l + 1].x, L->x2);
         for (int i = 0; i < m; i++) L->x[i] = 1.0 * L->x2[i] + 1.0 * L->x[i];
         for (int s = 0; s < post; s++) {
-            if (L->rb) { gs_half_sweep(L, 1); gs_half_sweep(L, 0); }
+            if (L->cheb) cheby_smooth(L, 0);
+            else if (L->rb) { gs_half_sweep(L, 1); gs_half_sweep(L, 0); }
             else jacobi_sweep(L, omega);
         }
     }

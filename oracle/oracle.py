@@ -219,6 +219,15 @@ class MgRef:
         L.mg_ref_set_smoother(self.h, smoother)
         return [bool(L.mg_ref_level_rb(self.h, l)) for l in range(self.levels())]
 
+    def set_chebyshev(self, degree, ratio=4.0):
+        """Chebyshev polynomial smoother of `degree` in D^-1 A on [lmax/ratio, lmax], lmax = Gershgorin bound (0: off).  Returns lmax per level."""
+        L = lib()
+        L.mg_ref_set_chebyshev.argtypes = [C.c_void_p, C.c_int, C.c_double]
+        L.mg_ref_level_lmax.argtypes = [C.c_void_p, C.c_int]
+        L.mg_ref_level_lmax.restype = C.c_double
+        L.mg_ref_set_chebyshev(self.h, degree, ratio)
+        return [L.mg_ref_level_lmax(self.h, l) for l in range(self.levels())]
+
     def level(self, l):
         rows, nnz = C.c_int(), C.c_int()
         lib().mg_ref_level_size(self.h, l, C.byref(rows), C.byref(nnz))

@@ -200,3 +200,29 @@ def test_solve_host_end_to_end(oracle, gen):
     xo, ito, _, _ = oracle.cg_solve(v, rp, c, b, x0, tol=1e-8)
     assert abs(res.iteration - ito) <= IT_TOL and _relerr(x, xo) <= REL_ERR
     m.close()
+
+
+@pytest.mark.parametrize("name", ["banded2000", "p2d_rand", "p3d"])
+@pytest.mark.parametrize("graph", [2, 0])
+def test_single_reduce_cg_matches_oracle(oracle, gen, name, graph):
+    """MGCG_CG_SINGLE_REDUCE (Chronopoulos-Gear; opt-in): the recurrence that finishes an iteration's sums at one
+    point reaches the reference's tolerance at the reference's iteration (+-1) with the same solution to 1e-10 — the iterates are
+    the classic ones in exact arithmetic."""
+    import torch
+    from conjugategradient_b200 import solver as S, _lib
+    v, rp, c, b, x0, min_it = _case(gen, name)
+    n = len(b)
+    m = S.Mgcg(0)
+    tv, tr, tc = (torch.as_tensor(a).cuda() for a in (v, rp, c))
+    m.setup(tv, tr, tc, S.default_options(tolerance=1e-8, min_iteration=min_it, max_iteration=n, cg_variant=_lib.CG_SINGLE_REDUCE, use_graph=graph))
+    tb, tx = torch.as_tensor(b).cuda(), torch.as_tensor(x0).cuda().clone()
+    res = m.solve(tb, tx)
+    xo, ito, reso, st = oracle.cg_solve(v, rp, c, b, x0, tol=1e-8, min_iteration=min_it, max_iteration=n)
+    assert st == 0 and res.status == 0
+    assert abs(res.iteration - ito) <= IT_TOL, (res.iteration, ito)
+    if res.iteration == ito:
+        assert _relerr(tx.cpu().numpy(), xo) <= 1e-9
+    import scipy.sparse as sp
+    A = sp.csr_matrix((v, c, rp))
+    assert np.linalg.norm(b - A @ tx.cpu().numpy()) < 2e-8 * max(1.0, np.linalg.norm(b))
+    m.close()

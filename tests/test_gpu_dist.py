@@ -37,6 +37,17 @@ CASES = [
                                       "solves": 3, "setups": 2}),
     ("mg_27pt_peer_eager", {"n": 24, "matrix": "p27", "options": {"precond": 1, "dist_replicate_below": 500, "dist_transport": 2, "use_graph": 0},
                             "transport": 2, "tight": 1e-12}),    # high-contrast coefficients (1e6): judged against a 1e-12 solve
+    # opt-in modes, compared with the single-GPU solve run in the SAME mode: Chebyshev smoother on the sharded levels
+    # (global eigenvalue bound), single-reduce CG (one scalar exchange per iteration), and both
+    ("mg_chebyshev_peer", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "mg_smoother": 2}, "transport": 2}),
+    ("mg_27pt_chebyshev_nccl", {"n": 24, "matrix": "p27", "options": {"precond": 1, "dist_replicate_below": 500, "dist_transport": 1, "mg_smoother": 2},
+                                "tight": 1e-12}),
+    ("plain_cg_single_reduce_peer", {"n": 32, "options": {"precond": 0, "dist_transport": 2, "cg_variant": 1}, "transport": 2}),
+    ("mg_single_reduce_peer", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "cg_variant": 1}, "transport": 2,
+                               "solves": 2}),
+    ("mg_single_reduce_replicated_nccl", {"n": 32, "options": {"precond": 1, "dist_transport": 1, "cg_variant": 1}}),
+    ("mg_chebyshev_single_reduce_w4", {"n": 48, "world": 4, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "mg_smoother": 2,
+                                                                        "cg_variant": 1}, "transport": 2}),
 ]
 
 

@@ -323,3 +323,90 @@ def test_mgcg_rbgs_matches_twin(oracle, gen, name):
     A = sp.csr_matrix((v, c, rp))
     assert np.linalg.norm(b - A @ x) / np.linalg.norm(b) < 2e-8
     H.close(); Hj.close()
+
+
+@pytest.mark.parametrize("degree,pre,post", [(1, 1, 1), (2, 1, 1), (3, 1, 1), (2, 2, 2), (2, 2, 1)])
+def test_vcycle_chebyshev_matches_twin(oracle, gen, degree, pre, post):
+    """MGCG_SMOOTHER_CHEBYSHEV (opt-in): degree-k Chebyshev polynomial in D^-1 A on [lmax/ratio, lmax] with the Gershgorin
+    lmax — one V-cycle equals the CPU twin's, the eigenvalue bounds are bit-identical, and M stays symmetric for pre == post."""
+    import torch
+    from conjugategradient_b200 import solver as S
+    nx, ny, nz = 20, 17, 12
+    v, rp, c = gen.poisson3d27_varcoef(nx, ny, nz)[:3]
+    n = nx * ny * nz
+    m = _setup(S, torch, v, rp, c, nx=nx, ny=ny, nz=nz, mg_pre_sweeps=pre, mg_post_sweeps=post, mg_coarse_size=100,
+               mg_smoother=2, mg_cheby_degree=degree, mg_cheby_ratio=5.0)
+    H = oracle.MgRef(v, rp, c, nx, ny, nz, coarse_size=100)
+    lmax = H.set_chebyshev(degree, 5.0)
+    assert m.levels() == H.levels() >= 3 and lmax[0] > 1.0
+    rng = np.random.default_rng(9)
+    u, w = rng.standard_normal(n), rng.standard_normal(n)
+    tz = torch.empty(n, dtype=torch.float64, device="cuda")
+    m.mg_apply(torch.as_tensor(u).cuda(), tz); zu = tz.cpu().numpy()
+    m.mg_apply(torch.as_tensor(w).cuda(), tz); zw = tz.cpu().numpy()
+    zt = H.apply(u, pre, post, 0.85)
+    assert np.abs(zu - zt).max() <= 1e-12 * np.abs(zt).max()
+    if pre == post:
+        assert abs(zu @ w - u @ zw) <= 1e-11 * abs(zu @ w)          # M = M^T
+    m.close(); H.close()
+
+
+@pytest.mark.parametrize("name", ["p3d32", "v27_24"])
+def test_mgcg_chebyshev_matches_twin(oracle, gen, name):
+    """PCG with the Chebyshev-smoothed V-cycle: same iteration count (+-1) and solution as the twin, graph replay == eager launches
+    bit for bit, and fewer iterations than weighted Jacobi (what the mode is for)."""
+    import torch
+    from conjugategradient_b200 import solver as S
+    if name == "p3d32":
+        dims = (32, 32, 32); v, rp, c = gen.poisson3d7(32)
+    else:
+        dims = (24, 24, 24); v, rp, c = gen.poisson3d27_varcoef(24)[:3]
+    n = len(rp) - 1
+    b = gen.rhs_uniform(n, 2)
+    out = []
+    for graph in (2, 0):
+        m = _setup(S, torch, v, rp, c, nx=dims[0], ny=dims[1], nz=dims[2], norm=2, tolerance=1e-8, max_iteration=1000, mg_smoother=2, use_graph=graph)
+        tb, tx = torch.as_tensor(b).cuda(), torch.zeros(n, dtype=torch.float64, device="cuda")
+        res = m.solve(tb, tx)
+        out.append((res.iteration, tx.cpu().numpy()))
+        m.close()
+    assert out[0][0] == out[1][0] and np.array_equal(out[0][1], out[1][1])
+    H = oracle.MgRef(v, rp, c, *dims)
+    H.set_chebyshev(2, 6.0)                                # the library defaults
+    xt, itt, _, st = H.pcg(b, tol=1e-8, norm=oracle.NORM_REL_L2, max_iteration=1000)
+    Hj = oracle.MgRef(v, rp, c, *dims)
+    _, itj, _, _ = Hj.pcg(b, tol=1e-8, norm=oracle.NORM_REL_L2, max_iteration=1000)
+    it, x = out[0]
+    assert st == 0 and abs(it - itt) <= 1, (it, itt)
+    assert itt < itj
+    if it == itt:
+        assert np.abs(x - xt).max() / np.abs(xt).max() <= 1e-10
+    import scipy.sparse as sp
+    A = sp.csr_matrix((v, c, rp))
+    assert np.linalg.norm(b - A @ x) / np.linalg.norm(b) < 2e-8
+    H.close(); Hj.close()
+
+
+@pytest.mark.parametrize("name", ["p3d32", "v27_24"])
+def test_mgcg_single_reduce_matches_classic(oracle, gen, name):
+    """MGCG with the single-reduce recurrence: same iteration count (+-1) as the classic loop and the CPU twin, same solution to
+    1e-9, while-graph == eager bit for bit."""
+    import torch
+    from conjugategradient_b200 import solver as S, _lib
+    if name == "p3d32":
+        dims = (32, 32, 32); v, rp, c = gen.poisson3d7(32)
+    else:
+        dims = (24, 24, 24); v, rp, c = gen.poisson3d27_varcoef(24)[:3]
+    n = len(rp) - 1
+    b = gen.rhs_uniform(n, 2)
+    out = {}
+    for variant, graph in ((0, 2), (1, 2), (1, 0)):
+        m = _setup(S, torch, v, rp, c, nx=dims[0], ny=dims[1], nz=dims[2], norm=2, tolerance=1e-10, max_iteration=1000, cg_variant=variant, use_graph=graph)
+        tb, tx = torch.as_tensor(b).cuda(), torch.zeros(n, dtype=torch.float64, device="cuda")
+        res = m.solve(tb, tx)
+        assert res.status == 0
+        out[(variant, graph)] = (res.iteration, tx.cpu().numpy())
+        m.close()
+    assert out[(1, 2)][0] == out[(1, 0)][0] and np.array_equal(out[(1, 2)][1], out[(1, 0)][1])
+    assert abs(out[(1, 2)][0] - out[(0, 2)][0]) <= 1
+    assert np.abs(out[(1, 2)][1] - out[(0, 2)][1]).max() / np.abs(out[(0, 2)][1]).max() <= 1e-9
