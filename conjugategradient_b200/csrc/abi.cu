@@ -1,6 +1,7 @@
 // abi.cu — the mgcg_* C ABI (include/mgcg.h): context lifetime, setup/solve on device and host pointers,
 // individually exported kernels, the reference partition rule.
 #include "mg.cuh"
+#include <chrono>
 #include <math.h>
 #include <stdarg.h>
 #include <string.h>
@@ -252,6 +253,10 @@ int mgcg_solve_host(mgcg_ctx *c, int count, int elements_count,
     }
     // the matrix first, on the solve stream (the hierarchy build needs all of it); b and x0 follow on a second stream once the
     // matrix has left the host, so that their 16 N bytes cross PCIe while the hierarchy is being built
+    const bool trace = getenv("MGCG_TRACE") != nullptr;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto ms_since = [](std::chrono::steady_clock::time_point a) { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - a).count(); };
+    auto t0 = now();
     MGCG_CUDA(cudaMemcpyAsync(h->rowptr, row_offsets, sizeof(int) * ((size_t)count + 1), cudaMemcpyHostToDevice, st));
     MGCG_CUDA(cudaMemcpyAsync(h->col, column_indeces, sizeof(int) * (size_t)elements_count, cudaMemcpyHostToDevice, st));
     MGCG_CUDA(cudaMemcpyAsync(h->val, elements, sizeof(double) * (size_t)elements_count, cudaMemcpyHostToDevice, st));
@@ -260,13 +265,17 @@ int mgcg_solve_host(mgcg_ctx *c, int count, int elements_count,
     MGCG_CUDA(cudaMemcpyAsync(h->b, b, sizeof(double) * (size_t)count, cudaMemcpyHostToDevice, h->copy));
     MGCG_CUDA(cudaMemcpyAsync(h->x, x, sizeof(double) * (size_t)count, cudaMemcpyHostToDevice, h->copy));
     MGCG_CUDA(cudaEventRecord(h->ev_vectors, h->copy));
+    if (trace) { cudaEventSynchronize(h->ev_matrix); fprintf(stderr, "[mgcg host] matrix on the device   %8.3f ms\n", ms_since(t0)); }
     int s = mgcg_setup(c, count, elements_count, h->val, h->rowptr, h->col, opt);
+    if (trace) fprintf(stderr, "[mgcg host] hierarchy built        %8.3f ms (vectors %s)\n", ms_since(t0), cudaEventQuery(h->ev_vectors) == cudaSuccess ? "arrived meanwhile" : "still in flight");
     // the solve (and any early return) must not overtake the vector upload
     MGCG_CUDA(cudaStreamWaitEvent(st, h->ev_vectors, 0));
     if (s != MGCG_OK) { cudaStreamSynchronize(h->copy); return s; }
     s = mgcg_solve(c, h->b, h->x, res);
+    if (trace) fprintf(stderr, "[mgcg host] solved                 %8.3f ms\n", ms_since(t0));
     MGCG_CUDA(cudaMemcpyAsync(x, h->x, sizeof(double) * (size_t)count, cudaMemcpyDeviceToHost, st));
     MGCG_CUDA(cudaStreamSynchronize(st));
+    if (trace) fprintf(stderr, "[mgcg host] x on the host          %8.3f ms\n", ms_since(t0));
     return s;
 }
 

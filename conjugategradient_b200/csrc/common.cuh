@@ -119,6 +119,23 @@ enum SpmvEpi {
     EPI_CHEBY_DOT    // as EPI_CHEBY; partial += b_i * y_i
 };
 
+// ---- fused halo exchange of the sharded solve (device side: halo.cuh; host side: dist.cu / peer.cu)
+struct PeerCtl;
+// producer side: where the boundary rows of the vector a kernel writes also go
+struct Mirror {
+    double *lo = nullptr;                 // lower neighbour's HIGH ghost rows: receive my rows [0, halo)
+    double *hi = nullptr;                 // upper neighbour's LOW ghost rows: receive my rows [own - halo, own)
+    int halo = 0, own = 0;
+    unsigned long long *flag_lo = nullptr, *flag_hi = nullptr;   // xflag[me] in the neighbours' arenas
+    PeerCtl *ctl = nullptr;               // my control block (null: no mirroring)
+};
+// consumer side: whose flags to wait for before ghost rows are read
+struct GhostWait {
+    PeerCtl *ctl = nullptr;               // null: no wait
+    const unsigned long long *flag_lo = nullptr, *flag_hi = nullptr;   // xflag[neighbour] in MY arena
+    long long clocks = 0;
+};
+
 struct SpmvArgs {
     Csr A;
     const double *x = nullptr;
@@ -137,6 +154,8 @@ struct SpmvArgs {
     // parity (ix + iy + iz) & 1 == color are updated; the others keep x (and still enter the fused dot).  -1: every row.
     int color = -1;
     int cnx = 0, cny = 0;          // grid extents that decode a row index into (ix, iy, iz)
+    Mirror mir;                    // sharded solve: y's boundary rows also go to the neighbours' ghost rows
+    GhostWait gw;                  // sharded solve: x's ghost rows are valid once the neighbours' flags say so
 };
 
 // ---------------------------------------------------------------------------------------------------------
@@ -203,14 +222,14 @@ int cg_init_residual(mgcg_ctx *c, int n, const double *b, const double *Ap, doub
 // z0/dinv != nullptr: also z0 = omega*dinv*r (first pre-smoothing sweep of the V-cycle from a zero guess, fused)
 int cg_update_xr(mgcg_ctx *c, int n, const double *p, const double *Ap, double *x, double *r, int fin,
                  bool use_host_alpha, double host_alpha, double *out,
-                 double *z0 = nullptr, const double *dinv = nullptr, double omega = 0.0);
+                 double *z0 = nullptr, const double *dinv = nullptr, double omega = 0.0, const Mirror *mir = nullptr);
 // single-reduce CG: p = u + beta p ; s = w + beta s ; x += alpha p ; r -= alpha s ; r.r, max|r| -> FIN_CGCG_RR  [; z0 = omega dinv r]
 int cgcg_update(mgcg_ctx *c, int n, const double *u, const double *w, double *p, double *s, double *x, double *r,
-                double *z0 = nullptr, const double *dinv = nullptr, double omega = 0.0, double *out = nullptr);
+                double *z0 = nullptr, const double *dinv = nullptr, double omega = 0.0, double *out = nullptr, const Mirror *mir = nullptr);
 // p = z + beta p   (z == r without preconditioner)
-int cg_update_p(mgcg_ctx *c, int n, const double *z, double *p, bool use_host_beta, double host_beta);
+int cg_update_p(mgcg_ctx *c, int n, const double *z, double *p, bool use_host_beta, double host_beta, const Mirror *mir = nullptr);
 // x = omega * dinv .* b
-int mg_jacobi_first(mgcg_ctx *c, int n, double omega, const double *dinv, const double *b, double *x);
+int mg_jacobi_first(mgcg_ctx *c, int n, double omega, const double *dinv, const double *b, double *x, const Mirror *mir = nullptr);
 // y = Minv * b for the dense coarsest level (n x n row-major)
 int mg_dense_apply(mgcg_ctx *c, int n, const double *Minv, const double *b, double *y);
 

@@ -52,9 +52,11 @@ void dist_free_levels(DistState *D)
         DistLevel &L = D->L[l];
         L.Aown.free_all(); L.Pext.free_all(); L.R.free_all();
         if (L.dinv) pool_release(L.dinv);
-        if (L.xa) pool_release(L.xa);
-        if (L.xb) pool_release(L.xb);
-        if (L.r) pool_release(L.r);
+        if (!D->vec_in_arena) {     // (arena vectors belong to the peer transport)
+            if (L.xa) pool_release(L.xa);
+            if (L.xb) pool_release(L.xb);
+            if (L.r) pool_release(L.r);
+        }
         if (L.d) pool_release(L.d);
         if (l > 0 && L.b) pool_release(L.b);
     }
@@ -68,8 +70,10 @@ void dist_free_levels(DistState *D)
     }
     D->coarse_A.free_all();
     if (D->coarse_b) { pool_release(D->coarse_b); D->coarse_b = nullptr; }
-    if (D->p) { pool_release(D->p); D->p = nullptr; }
-    if (D->r) { pool_release(D->r); D->r = nullptr; }
+    if (D->p && !D->vec_in_arena) pool_release(D->p);
+    if (D->r && !D->vec_in_arena) pool_release(D->r);
+    D->p = D->r = nullptr;
+    D->vec_in_arena = false;
     if (D->Ap) { pool_release(D->Ap); D->Ap = nullptr; }
     if (D->s) { pool_release(D->s); D->s = nullptr; }
 }
@@ -483,10 +487,38 @@ static int dist_open_transport(mgcg_ctx *c)
     if (D->world < 2 || want == MGCG_TRANSPORT_NCCL) { peer_close(c, D->world >= 2); return MGCG_OK; }
     int halo_cap = 0;
     for (size_t l = 0; l < D->L.size(); ++l) if (D->L[l].halo > halo_cap && D->L[l].halo < 0x3fffffff) halo_cap = D->L[l].halo;
-    MGCG_CHECK(peer_open(c, halo_cap, D->coarse ? D->coarse_n : 0));
+    // fused halo exchange (default; MGCG_DIST_FUSED=0 keeps the separate exchange kernels): the [lo|own|hi] vectors move into the arena
+    const char *ef = getenv("MGCG_DIST_FUSED");
+    const bool want_fused = !(ef && ef[0] == '0');
+    size_t vec_doubles = 0;
+    auto ext_doubles = [](const DistLevel &L) { return (((size_t)L.lo + L.own + L.hi + 2) * sizeof(double) + 255) / 256 * 32; };
+    if (want_fused) {
+        vec_doubles += 2 * ext_doubles(D->L[0]);
+        for (size_t l = 0; l < D->L.size(); ++l) vec_doubles += 3 * ext_doubles(D->L[l]);
+    }
+    MGCG_CHECK(peer_open(c, halo_cap, D->coarse ? D->coarse_n : 0, vec_doubles));
     if (!D->peer.active && want == MGCG_TRANSPORT_PEER) {
         set_error("mgcg_setup_dist: dist_transport = peer, but the ranks cannot map each other's memory (world %d, limit %d)", D->world, kPeerMax);
         return MGCG_ERR_UNSUPPORTED;
+    }
+    if (D->peer.active && D->peer.fused) {
+        // same order on every rank: p, r, then xa / xb / r of every distributed level
+        auto rehome = [&](double **v, const DistLevel &L) -> int {
+            double *a = peer_vec_alloc(c, L.lo, L.own, L.hi, L.halo);
+            if (!a) { set_error("mgcg_setup_dist: the peer arena's vector region is full"); return MGCG_ERR_INVALID; }
+            if (*v) pool_release(*v);
+            *v = a;
+            return MGCG_OK;
+        };
+        DistLevel &L0 = D->L[0];
+        MGCG_CHECK(rehome(&D->p, L0));
+        MGCG_CHECK(rehome(&D->r, L0));
+        for (size_t l = 0; l < D->L.size(); ++l) {
+            DistLevel &L = D->L[l];
+            MGCG_CHECK(rehome(&L.xa, L)); MGCG_CHECK(rehome(&L.xb, L)); MGCG_CHECK(rehome(&L.r, L));
+        }
+        D->vec_in_arena = true;
+        MGCG_CHECK(peer_vec_publish(c));
     }
     return MGCG_OK;
 }
@@ -649,6 +681,30 @@ static int dist_reduce(mgcg_ctx *c, int mode, int k, bool gated)
 
 static inline const double *shifted(const double *ext, int off, int lo) { return ext - ((ptrdiff_t)off - lo); }
 
+// ---- fused halo exchange (halo.cuh): with the level vectors in the peer arena, the kernel that WRITES a [lo|own|hi] vector stores
+// its boundary rows into the neighbours' ghost rows and publishes the exchange, and the kernel that READS ghost rows waits for
+// the neighbours' flags — dist_halo_exchange's separate launch disappears from the loop.  Why the direct ghost stores cannot
+// overwrite rows a neighbour is still reading: between two stores into the same buffer there is always either a scalar reduction
+// or the coarse all-gather (every rank waits for every rank, after its readers in stream order), or the storing kernel has itself
+// waited for a flag the neighbour published at the END of a kernel that follows its last reader of that buffer (the sweeps of a
+// level alternate xa / xb, and every sweep both waits and publishes).
+static inline bool dist_fused(const mgcg_ctx *c) { return c->dist->peer.active && c->dist->peer.fused; }
+// producer descriptor of ext vector v (counts as one exchange); mir.ctl stays null when the exchange is not fused
+static inline Mirror mirror_for(mgcg_ctx *c, const double *v_ext)
+{
+    Mirror m;
+    if (dist_fused(c) && peer_mirror_of(c, v_ext, &m)) c->dist->halo_exchanges++;
+    return m;
+}
+static inline void wait_for_ghosts(mgcg_ctx *c, SpmvArgs &a) { if (dist_fused(c)) peer_wait_of(c, &a.gw); }
+// explicit exchange of v unless its producer mirrored it
+static inline int halo_unless_fused(mgcg_ctx *c, double *v, int own, int lo, int hi, int halo)
+{
+    Mirror m;
+    if (dist_fused(c) && peer_mirror_of(c, v, &m)) return MGCG_OK;
+    return dist_halo_exchange(c, v, own, lo, hi, halo);
+}
+
 static int dist_gather_coarse_b(mgcg_ctx *c)
 {
     DistState *D = c->dist;
@@ -683,16 +739,18 @@ static double dist_first_omega(mgcg_ctx *c, const DistLevel &L)
 }
 
 // one Chebyshev smoothing step (L.cheb products, a halo exchange before each); see mg_cycle.cu cheby_smooth
-static int dist_cheby_smooth(mgcg_ctx *c, DistLevel &L, bool skip_first, double *dot_out)
+static int dist_cheby_smooth(mgcg_ctx *c, DistLevel &L, bool skip_first, double *dot_out, bool ghosts_needed = true)
 {
     for (int k = skip_first ? 1 : 0; k < L.cheb; ++k) {
         double c1, c2;
         cheby_coeffs(L.lmax, c->opt.mg_cheby_ratio, k, &c1, &c2);
         double *other = (L.xcur == L.xa) ? L.xb : L.xa;
         const bool last = dot_out && k == L.cheb - 1;
-        MGCG_CHECK(dist_halo_exchange(c, L.xcur, L.own, L.lo, L.hi, L.halo));
+        MGCG_CHECK(halo_unless_fused(c, L.xcur, L.own, L.lo, L.hi, L.halo));
         SpmvArgs a;
         a.A = L.A; a.x = shifted(L.xcur, L.off, L.lo); a.xrow = L.xcur + L.lo; a.y = other + L.lo; a.b = L.b; a.dinv = L.dinv;
+        wait_for_ghosts(c, a);
+        if (ghosts_needed || k + 1 < L.cheb) a.mir = mirror_for(c, other);
         a.alpha = c1; a.omega = c2; a.d_in = (skip_first && k == 1) ? L.xcur + L.lo : L.d; a.d_out = L.d;
         a.gated = true; a.fin = FIN_STORE; a.out = dot_out;
         MGCG_CHECK(spmv_launch(c, L.planA, last ? EPI_CHEBY_DOT : EPI_CHEBY, a));
@@ -701,12 +759,14 @@ static int dist_cheby_smooth(mgcg_ctx *c, DistLevel &L, bool skip_first, double 
     return MGCG_OK;
 }
 
-static int dist_jacobi_sweep(mgcg_ctx *c, DistLevel &L, double omega, double *dot_out)
+static int dist_jacobi_sweep(mgcg_ctx *c, DistLevel &L, double omega, double *dot_out, bool ghosts_needed = true)
 {
     double *other = (L.xcur == L.xa) ? L.xb : L.xa;
-    MGCG_CHECK(dist_halo_exchange(c, L.xcur, L.own, L.lo, L.hi, L.halo));
+    MGCG_CHECK(halo_unless_fused(c, L.xcur, L.own, L.lo, L.hi, L.halo));
     SpmvArgs a;
     a.A = L.A; a.x = shifted(L.xcur, L.off, L.lo); a.xrow = L.xcur + L.lo; a.y = other + L.lo; a.b = L.b; a.dinv = L.dinv;
+    wait_for_ghosts(c, a);
+    if (ghosts_needed) a.mir = mirror_for(c, other);
     a.omega = omega; a.gated = true; a.fin = FIN_STORE; a.out = dot_out;
     MGCG_CHECK(spmv_launch(c, L.planA, dot_out ? EPI_JACOBI_DOT : EPI_JACOBI, a));
     L.xcur = other;
@@ -736,7 +796,10 @@ static int dist_vcycle(mgcg_ctx *c, double *r_ext, double **z_own, bool fuse_fir
     for (int l = 0; l < Ld; ++l) {
         DistLevel &L = D->L[l];
         L.xcur = L.xa;
-        if (!(l == 0 && fuse_first_done)) MGCG_CHECK(mg_jacobi_first(c, L.own, dist_first_omega(c, L), L.dinv, L.b, L.xa + L.lo));
+        if (!(l == 0 && fuse_first_done)) {
+            const Mirror m1 = mirror_for(c, L.xa);
+            MGCG_CHECK(mg_jacobi_first(c, L.own, dist_first_omega(c, L), L.dinv, L.b, L.xa + L.lo, &m1));
+        }
         if (L.cheb) {
             MGCG_CHECK(dist_cheby_smooth(c, L, true, nullptr));
             for (int s = 1; s < pre; ++s) MGCG_CHECK(dist_cheby_smooth(c, L, false, nullptr));
@@ -744,16 +807,18 @@ static int dist_vcycle(mgcg_ctx *c, double *r_ext, double **z_own, bool fuse_fir
             for (int s = 1; s < pre; ++s) MGCG_CHECK(dist_jacobi_sweep(c, L, omega, nullptr));
         }
         dist_trace(c, l == 0 ? "L0 pre-smooth" : "L1+ pre-smooth");
-        MGCG_CHECK(dist_halo_exchange(c, L.xcur, L.own, L.lo, L.hi, L.halo));
+        MGCG_CHECK(halo_unless_fused(c, L.xcur, L.own, L.lo, L.hi, L.halo));
         dist_trace(c, l == 0 ? "L0 halo(z)" : "L1+ halo(z)");
         SpmvArgs a;
         a.A = L.A; a.x = shifted(L.xcur, L.off, L.lo); a.y = L.r + L.lo; a.b = L.b; a.gated = true;
+        wait_for_ghosts(c, a); a.mir = mirror_for(c, L.r);
         MGCG_CHECK(spmv_launch(c, L.planA, EPI_RESID, a));
         dist_trace(c, l == 0 ? "L0 residual" : "L1+ residual");
-        MGCG_CHECK(dist_halo_exchange(c, L.r, L.own, L.lo, L.hi, L.halo));
+        MGCG_CHECK(halo_unless_fused(c, L.r, L.own, L.lo, L.hi, L.halo));
         dist_trace(c, l == 0 ? "L0 halo(r)" : "L1+ halo(r)");
         SpmvArgs q;
         q.A = L.R.view(); q.x = L.r; q.gated = true;
+        wait_for_ghosts(c, q);
         q.y = (l + 1 < Ld) ? D->L[l + 1].b : D->coarse_b + D->coarse_offs[D->rank];
         MGCG_CHECK(spmv_launch(c, L.planR, EPI_PLAIN, q));
         dist_trace(c, l == 0 ? "L0 restrict" : "L1+ restrict");
@@ -769,18 +834,22 @@ static int dist_vcycle(mgcg_ctx *c, double *r_ext, double **z_own, bool fuse_fir
         if (l + 1 == Ld) xn = zc;
         else {
             DistLevel &N = D->L[l + 1];
-            MGCG_CHECK(dist_halo_exchange(c, N.xcur, N.own, N.lo, N.hi, N.halo));
+            MGCG_CHECK(halo_unless_fused(c, N.xcur, N.own, N.lo, N.hi, N.halo));
             dist_trace(c, "L1+ halo(xc)");
             xn = shifted(N.xcur, N.off, N.lo);
         }
         SpmvArgs a;
         a.A = L.P; a.x = xn; a.y = L.xcur + L.lo; a.alpha = 1.0; a.beta = 1.0; a.gated = true;
+        if (l + 1 < Ld) wait_for_ghosts(c, a);
+        if (post > 0 || l > 0) a.mir = mirror_for(c, L.xcur);
         MGCG_CHECK(spmv_launch(c, L.planP, EPI_AXPBY, a));
         dist_trace(c, l == 0 ? "L0 prolong" : "L1+ prolong");
         for (int s = 0; s < post; ++s) {
             const bool last = (l == 0 && s == post - 1 && rz_out);
-            if (L.cheb) MGCG_CHECK(dist_cheby_smooth(c, L, false, last ? rz_out : nullptr));
-            else MGCG_CHECK(dist_jacobi_sweep(c, L, omega, last ? rz_out : nullptr));
+            // the ghost rows of the cycle's result z are read only by the single-reduce recurrence (w = A z)
+            const bool ghosts = !(l == 0 && s == post - 1) || c->opt.cg_variant == MGCG_CG_SINGLE_REDUCE;
+            if (L.cheb) MGCG_CHECK(dist_cheby_smooth(c, L, false, last ? rz_out : nullptr, ghosts));
+            else MGCG_CHECK(dist_jacobi_sweep(c, L, omega, last ? rz_out : nullptr, ghosts));
             dist_trace(c, l == 0 ? "L0 post-smooth (halo + sweep)" : "L1+ post-smooth (halo + sweep)");
         }
     }
@@ -801,10 +870,11 @@ static int dist_enqueue_iteration(mgcg_ctx *c, double *x)
     double *p_own = D->p + L0.lo, *r_own = D->r + L0.lo;
     // halo of p, Ap = A p, local p.Ap                                    (SyncP + Solve1, cs:470-499)
     dist_trace(c, "update p");
-    MGCG_CHECK(dist_halo_exchange(c, D->p, n, L0.lo, L0.hi, L0.halo));
+    MGCG_CHECK(halo_unless_fused(c, D->p, n, L0.lo, L0.hi, L0.halo));    // fused: pushed by the update of p (by dist_solve before the first iteration)
     dist_trace(c, "halo(p)");
     SpmvArgs a;
     a.A = c->A; a.x = shifted(D->p, L0.off, L0.lo); a.y = D->Ap; a.w = p_own; a.fin = FIN_STORE; a.out = D->partial_send; a.gated = true;
+    wait_for_ghosts(c, a);
     MGCG_CHECK(spmv_launch(c, c->planA, EPI_DOT, a));
     dist_trace(c, "A p + p.Ap");
     MGCG_CHECK(dist_reduce(c, DF_PAP, 1, true));
@@ -812,17 +882,20 @@ static int dist_enqueue_iteration(mgcg_ctx *c, double *x)
     if (!pre) {
         MGCG_CHECK(cg_update_xr(c, n, p_own, D->Ap, x, r_own, FIN_STORE, false, 0.0, D->partial_send));   // Solve2, cs:505-525
         MGCG_CHECK(dist_reduce(c, DF_RR, 1, true));
-        MGCG_CHECK(cg_update_p(c, n, r_own, p_own, false, 0.0));                                          // Solve3, cs:548-556
+        const Mirror mp = mirror_for(c, D->p);
+        MGCG_CHECK(cg_update_p(c, n, r_own, p_own, false, 0.0, &mp));                                     // Solve3, cs:548-556
     } else {
         const bool fuse = D->first_replicated > 0;
+        const Mirror mz = fuse ? mirror_for(c, L0.xa) : Mirror();
         MGCG_CHECK(cg_update_xr(c, n, p_own, D->Ap, x, r_own, FIN_STORE, false, 0.0, D->partial_send,
-                                fuse ? L0.xa + L0.lo : nullptr, fuse ? L0.dinv : nullptr, dist_first_omega(c, L0)));
+                                fuse ? L0.xa + L0.lo : nullptr, fuse ? L0.dinv : nullptr, dist_first_omega(c, L0), &mz));
         dist_trace(c, "update x,r (+z0)");
         double *z = nullptr;
         MGCG_CHECK(dist_vcycle(c, D->r, &z, fuse, D->partial_send + 1));
         MGCG_CHECK(dist_reduce(c, DF_RR_RZ, 2, true));   // stop rule on r.r, beta from r.z: one exchange for both
         dist_trace(c, "reduce r.r, r.z");
-        MGCG_CHECK(cg_update_p(c, n, z, p_own, false, 0.0));
+        const Mirror mp = mirror_for(c, D->p);
+        MGCG_CHECK(cg_update_p(c, n, z, p_own, false, 0.0, &mp));
     }
     return MGCG_OK;
 }
@@ -841,8 +914,9 @@ static int dist_enqueue_iteration_cgcg(mgcg_ctx *c, double *x)
         MGCG_CHECK(cgcg_update(c, n, r_own, D->Ap, p_own, D->s, x, r_own, nullptr, nullptr, 0.0, D->partial_send + 2));
     } else {
         const bool fuse = D->first_replicated > 0;
+        const Mirror mz = fuse ? mirror_for(c, L0.xa) : Mirror();
         MGCG_CHECK(cgcg_update(c, n, D->cgcg_u, D->Ap, p_own, D->s, x, r_own, fuse ? L0.xa + L0.lo : nullptr, fuse ? L0.dinv : nullptr,
-                               dist_first_omega(c, L0), D->partial_send + 2));
+                               dist_first_omega(c, L0), D->partial_send + 2, &mz));
         dist_trace(c, "update p,s,x,r (+z0)");
         double *z = nullptr;
         MGCG_CHECK(dist_vcycle(c, D->r, &z, fuse, D->partial_send + 1));
@@ -850,11 +924,14 @@ static int dist_enqueue_iteration_cgcg(mgcg_ctx *c, double *x)
         u_ext = z - L0.lo;
     }
     if (!(pre && D->first_replicated == 0)) {    // (a fully replicated preconditioner returns a slice of a global-length vector)
-        MGCG_CHECK(dist_halo_exchange(c, u_ext, n, L0.lo, L0.hi, L0.halo));
+        // fused: u = the V-cycle's last post-smoothing output was pushed by that sweep; the plain recurrence's u = r was not
+        if (pre && D->first_replicated > 0 && c->opt.mg_post_sweeps > 0) MGCG_CHECK(halo_unless_fused(c, u_ext, n, L0.lo, L0.hi, L0.halo));
+        else MGCG_CHECK(dist_halo_exchange(c, u_ext, n, L0.lo, L0.hi, L0.halo));
         dist_trace(c, "halo(u)");
     }
     SpmvArgs a;
     a.A = c->A; a.y = D->Ap; a.w = u_ext + L0.lo; a.fin = FIN_STORE; a.out = D->partial_send; a.gated = true;
+    if (!(pre && D->first_replicated == 0)) wait_for_ghosts(c, a);
     a.x = (pre && D->first_replicated == 0) ? (u_ext + L0.lo) - L0.off : shifted(u_ext, L0.off, L0.lo);
     MGCG_CHECK(spmv_launch(c, c->planA, EPI_DOT, a));
     dist_trace(c, "A u + u.Au");
@@ -940,6 +1017,8 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
         if (cgcg) D->cgcg_u = z;
         else MGCG_CHECK(vec_copy(c, n, z, p_own));
     }
+    // fused halo exchange: inside the loop p's ghost rows are pushed by the kernel that updates p; the first iteration's come from here
+    if (!cgcg && dist_fused(c)) MGCG_CHECK(dist_halo_exchange(c, D->p, n, L0.lo, L0.hi, L0.halo));
     if (cgcg) {   // w = A u ; delta = w.u ; alpha = gamma / delta ; beta = 0 ; p = s = 0
         if (!D->s) MGCG_CUDA(pool_alloc((void **)&D->s, sizeof(double) * ((size_t)n + 1), st));
         const bool repl = pre && D->first_replicated == 0;

@@ -15,6 +15,7 @@
 #pragma once
 #include "mg.cuh"
 #include "reduce.cuh"
+#include "halo.cuh"
 #include <nccl.h>
 
 namespace mgcg {
@@ -49,21 +50,23 @@ constexpr int kMaxRanks = 64;
 
 // ---------------------------------------------------------------------------------------------------------
 // peer-memory transport (peer.cu): the loop's exchanges as this library's own kernels over NVLink peer stores
-constexpr int kPeerMax = 16;            // ranks of one NVSwitch domain served by the peer transport (NCCL beyond that)
-
-struct PeerCtl {                        // head of every rank's arena; remote ranks write xflag / rflag / rslot
-    unsigned long long xflag[kPeerMax]; // xflag[q]: sequence number of the last exchange whose data from rank q has landed
-    unsigned long long rflag[kPeerMax]; // the same for the scalar reductions
-    double rslot[2][kPeerMax][4];       // [parity][sender][value] (up to 3 sums per reduction)
-    unsigned long long xseq, rseq;      // local: exchanges / reductions completed (device-resident so graphs replay)
-    unsigned int ticket1, ticket2, pad[2];
-};
 struct PeerPtrs { PeerCtl *ctl[kPeerMax]; };
 struct XchgSend { const double *src; double *dst; unsigned long long *flag; int count; int pad; };
 struct XchgRecv { const double *stage; double *dst; const unsigned long long *flag; int count; int pad; };
 struct XchgDesc { int ns, nr; size_t stage_stride; XchgSend s[kPeerMax]; XchgRecv r[kPeerMax]; };
 
+constexpr int kPeerVecMax = 40;         // sharded vectors that can live in the arena: p, r and three per distributed level
+struct PeerVecSlot { size_t lo_off, hi_off; };   // byte offsets (in the owner's arena) of a vector's low- and high-ghost rows
+
 struct PeerState {
+    bool fused = false;                 // the level vectors live in the arena: producers store ghost rows directly (halo.cuh)
+    int nvec = 0;                       // vectors placed in the arena by the current setup
+    size_t vec_off = 0, vec_cap = 0;    // byte offset / capacity of the vector region
+    size_t vec_used = 0;
+    double *vbase[kPeerVecMax] = {};    // my vectors ([lo|own|hi]) ...
+    int vlo[kPeerVecMax] = {}, vown[kPeerVecMax] = {}, vhi[kPeerVecMax] = {}, vhalo[kPeerVecMax] = {};
+    PeerVecSlot nb_lo[kPeerVecMax] = {}, nb_hi[kPeerVecMax] = {};   // ... and the ghost slots of the same vector on rank-1 / rank+1
+    long long wait_clocks = 8000000000ll;
     bool active = false;                // the loop of the CURRENT setup runs over peer memory
     bool ready = false;                 // arena allocated and every peer mapped (survives a re-setup that fits)
     void *arena = nullptr;              // this rank's arena (cudaMalloc)
@@ -126,6 +129,7 @@ struct DistState {
     double *p = nullptr;                    // [lo|own|hi]
     double *r = nullptr;                    // [lo|own|hi] (ghosts used by the restriction)
     double *Ap = nullptr;                   // own
+    bool vec_in_arena = false;              // p, r and the levels' xa / xb / r live in the peer arena (fused halo exchange)
     double *s = nullptr;                    // own; single-reduce CG: s = A p by recurrence (allocated on first use)
     double *cgcg_u = nullptr;               // single-reduce CG: own-rows pointer of the V-cycle's output (fixed across iterations)
     int graph_variant = 0;                  // cg_variant the captured graph was built for
@@ -174,7 +178,16 @@ __device__ __forceinline__ void dist_finalize(int mode, double s0, double s1, do
 }
 
 // peer.cu
-int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap);   // collective; leaves peer.active = false if any rank cannot map
+// collective; leaves peer.active = false if any rank cannot map.  vec_doubles > 0: also reserve that many doubles for the
+// sharded vectors (fused halo exchange)
+int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap, size_t vec_doubles = 0);
+// place a [lo|own|hi] vector in the arena's vector region (zeroed); null when the region is full
+double *peer_vec_alloc(mgcg_ctx *c, int lo, int own, int hi, int halo);
+// collective: exchange the ghost-slot offsets of the vectors placed so far with the neighbouring ranks
+int peer_vec_publish(mgcg_ctx *c);
+// producer / consumer descriptors of a vector placed by peer_vec_alloc (ext = its [lo|own|hi] base); false if it is not one
+bool peer_mirror_of(mgcg_ctx *c, const double *ext, Mirror *m);
+bool peer_wait_of(mgcg_ctx *c, GhostWait *g);
 void peer_close(mgcg_ctx *c, bool collective);
 int peer_halo_exchange(mgcg_ctx *c, double *v_ext, int own, int lo, int hi, int halo);
 int peer_allgather(mgcg_ctx *c, double *full, const int *offs);

@@ -10,6 +10,7 @@
 // Both run as persistent grids (static tile->block map, so the fused reduction is deterministic).
 #include "common.cuh"
 #include "reduce.cuh"
+#include "halo.cuh"
 #include <stdlib.h>
 
 namespace mgcg {
@@ -17,27 +18,29 @@ namespace mgcg {
 constexpr int kSpmvThreads = 256;
 constexpr int kChunk = 2048;   // products staged per pass: 16 KB of shared memory
 
+// `wrote` is set when the row's result was also stored into a neighbouring rank's ghost rows (a.mir, sharded solve)
 template <int EPI>
-__device__ __forceinline__ void epilogue(int row, double s, const SpmvArgs &a, double &dsum)
+__device__ __forceinline__ void epilogue(int row, double s, const SpmvArgs &a, double &dsum, bool &wrote)
 {
-    if (EPI == EPI_PLAIN) a.y[row] = s;
-    else if (EPI == EPI_AXPBY) a.y[row] = (a.beta == 0.0) ? a.alpha * s : a.alpha * s + a.beta * a.y[row];
-    else if (EPI == EPI_DOT) { a.y[row] = s; dsum += a.w[row] * s; }
-    else if (EPI == EPI_RESID) a.y[row] = a.b[row] - s;
+    double yi;
+    if (EPI == EPI_PLAIN) yi = s;
+    else if (EPI == EPI_AXPBY) yi = (a.beta == 0.0) ? a.alpha * s : a.alpha * s + a.beta * a.y[row];
+    else if (EPI == EPI_DOT) { yi = s; dsum += a.w[row] * s; }
+    else if (EPI == EPI_RESID) yi = a.b[row] - s;
     else if (EPI == EPI_JACOBI || EPI == EPI_JACOBI_DOT) {
         const double bi = a.b[row];
-        const double yi = (a.xrow ? a.xrow : a.x)[row] + a.omega * a.dinv[row] * (bi - s);
-        a.y[row] = yi;
+        yi = (a.xrow ? a.xrow : a.x)[row] + a.omega * a.dinv[row] * (bi - s);
         if (EPI == EPI_JACOBI_DOT) dsum += bi * yi;
     }
-    else if (EPI == EPI_CHEBY || EPI == EPI_CHEBY_DOT) {
+    else {   // EPI_CHEBY, EPI_CHEBY_DOT
         const double bi = a.b[row];
         const double dn = (a.alpha == 0.0 ? 0.0 : a.alpha * a.d_in[row]) + a.omega * a.dinv[row] * (bi - s);
-        const double yi = (a.xrow ? a.xrow : a.x)[row] + dn;
+        yi = (a.xrow ? a.xrow : a.x)[row] + dn;
         a.d_out[row] = dn;
-        a.y[row] = yi;
         if (EPI == EPI_CHEBY_DOT) dsum += bi * yi;
     }
+    a.y[row] = yi;
+    if (a.mir.ctl) wrote |= mirror_store(a.mir, row, yi);
 }
 
 // The epilogue's operands that do not depend on the row sum, loaded BEFORE the wait for the tile's matrix slice so that their
@@ -58,26 +61,27 @@ __device__ __forceinline__ void epi_prefetch(int row, const SpmvArgs &a, EpiPre 
     }
 }
 template <int EPI>
-__device__ __forceinline__ void epilogue_pre(int row, double s, const SpmvArgs &a, double &dsum, const EpiPre &p)
+__device__ __forceinline__ void epilogue_pre(int row, double s, const SpmvArgs &a, double &dsum, const EpiPre &p, bool &wrote)
 {
-    if (EPI == EPI_PLAIN) a.y[row] = s;
-    else if (EPI == EPI_AXPBY) a.y[row] = (a.beta == 0.0) ? a.alpha * s : a.alpha * s + a.beta * p.e0;
-    else if (EPI == EPI_DOT) { a.y[row] = s; dsum += p.e0 * s; }
-    else if (EPI == EPI_RESID) a.y[row] = p.e0 - s;
+    double yi;
+    if (EPI == EPI_PLAIN) yi = s;
+    else if (EPI == EPI_AXPBY) yi = (a.beta == 0.0) ? a.alpha * s : a.alpha * s + a.beta * p.e0;
+    else if (EPI == EPI_DOT) { yi = s; dsum += p.e0 * s; }
+    else if (EPI == EPI_RESID) yi = p.e0 - s;
     else if (EPI == EPI_JACOBI || EPI == EPI_JACOBI_DOT) {
         const double bi = p.e0;
-        const double yi = p.e1 + a.omega * p.e2 * (bi - s);
-        a.y[row] = yi;
+        yi = p.e1 + a.omega * p.e2 * (bi - s);
         if (EPI == EPI_JACOBI_DOT) dsum += bi * yi;
     }
-    else if (EPI == EPI_CHEBY || EPI == EPI_CHEBY_DOT) {
+    else {   // EPI_CHEBY, EPI_CHEBY_DOT
         const double bi = p.e0;
         const double dn = (a.alpha == 0.0 ? 0.0 : a.alpha * p.e3) + a.omega * p.e2 * (bi - s);
-        const double yi = p.e1 + dn;
+        yi = p.e1 + dn;
         a.d_out[row] = dn;
-        a.y[row] = yi;
         if (EPI == EPI_CHEBY_DOT) dsum += bi * yi;
     }
+    a.y[row] = yi;
+    if (a.mir.ctl) wrote |= mirror_store(a.mir, row, yi);
 }
 
 // red-black half sweeps: is `row` updated by this launch?
@@ -110,6 +114,8 @@ __global__ void __launch_bounds__(kSpmvThreads) k_spmv_stream(SpmvArgs a, int ro
     const int *__restrict__ col = a.A.col;
     const double *__restrict__ x = a.x;
     double dsum = 0.0;
+    bool wrote = false;
+    halo_wait(a.gw, sc);
 
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int r0 = tile * rows_per_tile;
@@ -137,7 +143,7 @@ __global__ void __launch_bounds__(kSpmvThreads) k_spmv_stream(SpmvArgs a, int ro
                 epi_prefetch<EPI>(r0 + t, a, pre);
                 epilogue_inactive<EPI>(a, dsum, pre);
             } else {
-                epilogue<EPI>(r0 + t, acc, a, dsum);
+                epilogue<EPI>(r0 + t, acc, a, dsum, wrote);
             }
         }
     }
@@ -146,6 +152,7 @@ __global__ void __launch_bounds__(kSpmvThreads) k_spmv_stream(SpmvArgs a, int ro
         block_reduce<false>(dsum, m);
         grid_reduce_finish<false>(dsum, m, ws, a.fin, sc, a.out);
     }
+    halo_signal(a.mir, wrote);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -249,6 +256,8 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
         const int r = blockIdx.x * kTmaRows + t;
         if (my_tiles > 0 && r < rows) { rs_n = rowptr[r]; re_n = rowptr[r + 1]; }
     }
+    bool wrote = false;
+    halo_wait(a.gw, sc);      // the first tiles' matrix slices are already on their way
     for (int j = 0; j < my_tiles; ++j) {
         const int s = j % kTmaStages;
         const unsigned parity = (unsigned)((j / kTmaStages) & 1);
@@ -281,7 +290,7 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
             mbar_wait(&s_empty[s], parity);       // ... and once every thread is, refill it
             issue(j + kTmaStages);
         }
-        if (active) epilogue_pre<EPI>(row, acc, a, dsum, pre);
+        if (active) epilogue_pre<EPI>(row, acc, a, dsum, pre, wrote);
         else if (row < rows) epilogue_inactive<EPI>(a, dsum, pre);
     }
     if (EpiTraits<EPI>::reduces) {
@@ -289,6 +298,7 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
         block_reduce<false>(dsum, m);
         grid_reduce_finish<false>(dsum, m, ws, a.fin, sc, a.out);
     }
+    halo_signal(a.mir, wrote);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -364,6 +374,8 @@ __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_
         const int r = blockIdx.x * R + g;
         if (my_tiles > 0 && r < rows) { rs_n = rowptr[r]; re_n = rowptr[r + 1]; }
     }
+    bool wrote = false;
+    halo_wait(a.gw, sc);
     int s = 0;
     unsigned parity = 0;
     for (int j = 0; j < my_tiles; ++j) {
@@ -421,7 +433,7 @@ __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_
         }
 #pragma unroll
         for (int o = L / 2; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, L);
-        if (lane == 0 && row < rows) epilogue_pre<EPI>(row, acc, a, dsum, pre);
+        if (lane == 0 && row < rows) epilogue_pre<EPI>(row, acc, a, dsum, pre, wrote);
         if (++s == stages) { s = 0; parity ^= 1u; }
     }
     if (EpiTraits<EPI>::reduces) {
@@ -429,6 +441,7 @@ __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_
         block_reduce<false>(dsum, m);
         grid_reduce_finish<false>(dsum, m, ws, a.fin, sc, a.out);
     }
+    halo_signal(a.mir, wrote);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -446,6 +459,8 @@ __global__ void __launch_bounds__(kSpmvThreads) k_spmv_vector(SpmvArgs a, Reduce
     const int rows = a.A.rows;
     const int rows_padded = ((rows + ngroups - 1) / ngroups) * ngroups;   // uniform trip count for the shuffles
     double dsum = 0.0;
+    bool wrote = false;
+    halo_wait(a.gw, sc);
     for (int row = g; row < rows_padded; row += ngroups) {
         double s = 0.0;
         if (row < rows) {
@@ -455,13 +470,14 @@ __global__ void __launch_bounds__(kSpmvThreads) k_spmv_vector(SpmvArgs a, Reduce
         }
 #pragma unroll
         for (int o = L / 2; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o, L);
-        if (lane == 0 && row < rows) epilogue<EPI>(row, s, a, dsum);
+        if (lane == 0 && row < rows) epilogue<EPI>(row, s, a, dsum, wrote);
     }
     if (EpiTraits<EPI>::reduces) {
         double m = 0.0;
         block_reduce<false>(dsum, m);
         grid_reduce_finish<false>(dsum, m, ws, a.fin, sc, a.out);
     }
+    halo_signal(a.mir, wrote);
 }
 
 // ---------------------------------------------------------------------------------------------------------

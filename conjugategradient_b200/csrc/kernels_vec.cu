@@ -3,6 +3,7 @@
 // Replaces the 7-launch cuBLAS sequence of the reference loop (Mgcg.cu:244-266; SimpleConjugateGradient.cu:96-121).
 #include "common.cuh"
 #include "reduce.cuh"
+#include "halo.cuh"
 
 namespace mgcg {
 
@@ -160,9 +161,10 @@ __global__ void __launch_bounds__(kVecThreads) k_update_xr(int n, const double *
                                                            double *__restrict__ x, double *__restrict__ r,
                                                            ReduceWs ws, int fin, Scalars *sc, bool host_alpha, double alpha_h,
                                                            double *out, double *__restrict__ z0, const double *__restrict__ dinv,
-                                                           double omega)
+                                                           double omega, Mirror mir)
 {
     if (!host_alpha && sc->done) return;
+    bool wrote = false;
     const double alpha = host_alpha ? alpha_h : sc->alpha;
     const double nalpha = -alpha;
     double s = 0.0, m = 0.0;
@@ -184,32 +186,35 @@ __global__ void __launch_bounds__(kVecThreads) k_update_xr(int n, const double *
                 double2 dv = reinterpret_cast<const double2 *>(dinv)[i];
                 double2 zv; zv.x = omega * dv.x * rv.x; zv.y = omega * dv.y * rv.y;
                 reinterpret_cast<double2 *>(z0)[i] = zv;
+                if (mir.ctl) { wrote |= mirror_store(mir, 2 * i, zv.x); wrote |= mirror_store(mir, 2 * i + 1, zv.y); }
             }
         }
         if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
             int i = n - 1;
             double xi = x[i] + alpha * p[i], ri = r[i] + nalpha * Ap[i];
             x[i] = xi; r[i] = ri; s += ri * ri; m = fmax(m, fabs(ri));
-            if (Z0) z0[i] = omega * dinv[i] * ri;
+            if (Z0) { const double zi = omega * dinv[i] * ri; z0[i] = zi; if (mir.ctl) wrote |= mirror_store(mir, i, zi); }
         }
     } else {
         for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
             double xi = x[i] + alpha * p[i], ri = r[i] + nalpha * Ap[i];
             x[i] = xi; r[i] = ri; s += ri * ri; m = fmax(m, fabs(ri));
-            if (Z0) z0[i] = omega * dinv[i] * ri;
+            if (Z0) { const double zi = omega * dinv[i] * ri; z0[i] = zi; if (mir.ctl) wrote |= mirror_store(mir, i, zi); }
         }
     }
     block_reduce<true>(s, m);
     grid_reduce_finish<true>(s, m, ws, fin, sc, out);
+    if (Z0) halo_signal(mir, wrote);
 }
 
 int cg_update_xr(mgcg_ctx *c, int n, const double *p, const double *Ap, double *x, double *r, int fin,
-                 bool use_host_alpha, double host_alpha, double *out, double *z0, const double *dinv, double omega)
+                 bool use_host_alpha, double host_alpha, double *out, double *z0, const double *dinv, double omega, const Mirror *mir)
 {
+    const Mirror mm = (mir && z0) ? *mir : Mirror();
     int grid = vec_grid(c, n, 2);
     bool al = aligned16(p) && aligned16(Ap) && aligned16(x) && aligned16(r) && (!z0 || (aligned16(z0) && aligned16(dinv)));
 #define LAUNCH_(V, Z) k_update_xr<V, Z><<<grid, kVecThreads, 0, c->stream>>>(n, p, Ap, x, r, c->ws, fin, c->d_scalars, \
-                                                                             use_host_alpha, host_alpha, out, z0, dinv, omega)
+                                                                             use_host_alpha, host_alpha, out, z0, dinv, omega, mm)
     if (al) { if (z0) LAUNCH_(2, true); else LAUNCH_(2, false); }
     else    { if (z0) LAUNCH_(1, true); else LAUNCH_(1, false); }
 #undef LAUNCH_
@@ -226,9 +231,10 @@ template <bool Z0>
 __global__ void __launch_bounds__(kVecThreads) k_cgcg_update(int n, const double *__restrict__ u, const double *__restrict__ w,
                                                              double *__restrict__ p, double *__restrict__ s, double *__restrict__ x,
                                                              double *__restrict__ r, ReduceWs ws, Scalars *sc, double *out,
-                                                             double *__restrict__ z0, const double *__restrict__ dinv, double omega)
+                                                             double *__restrict__ z0, const double *__restrict__ dinv, double omega, Mirror mir)
 {
     if (sc->done) return;
+    bool wrote = false;
     const double alpha = sc->alpha, beta = sc->beta, nalpha = -alpha;
     double sum = 0.0, m = 0.0;
     const int stride = gridDim.x * blockDim.x;
@@ -240,18 +246,20 @@ __global__ void __launch_bounds__(kVecThreads) k_cgcg_update(int n, const double
         p[i] = pi; s[i] = si; x[i] = xi; r[i] = ri;
         sum += ri * ri;
         m = fmax(m, fabs(ri));
-        if (Z0) z0[i] = omega * dinv[i] * ri;
+        if (Z0) { const double zi = omega * dinv[i] * ri; z0[i] = zi; if (mir.ctl) wrote |= mirror_store(mir, i, zi); }
     }
     block_reduce<true>(sum, m);
     grid_reduce_finish<true>(sum, m, ws, out ? FIN_STORE : FIN_CGCG_RR, sc, out);
+    if (Z0) halo_signal(mir, wrote);
 }
 
 int cgcg_update(mgcg_ctx *c, int n, const double *u, const double *w, double *p, double *s, double *x, double *r,
-                double *z0, const double *dinv, double omega, double *out)
+                double *z0, const double *dinv, double omega, double *out, const Mirror *mir)
 {
     const int grid = vec_grid(c, n, 2);
-    if (z0) k_cgcg_update<true><<<grid, kVecThreads, 0, c->stream>>>(n, u, w, p, s, x, r, c->ws, c->d_scalars, out, z0, dinv, omega);
-    else k_cgcg_update<false><<<grid, kVecThreads, 0, c->stream>>>(n, u, w, p, s, x, r, c->ws, c->d_scalars, out, z0, dinv, omega);
+    const Mirror mm = (mir && z0) ? *mir : Mirror();
+    if (z0) k_cgcg_update<true><<<grid, kVecThreads, 0, c->stream>>>(n, u, w, p, s, x, r, c->ws, c->d_scalars, out, z0, dinv, omega, mm);
+    else k_cgcg_update<false><<<grid, kVecThreads, 0, c->stream>>>(n, u, w, p, s, x, r, c->ws, c->d_scalars, out, z0, dinv, omega, mm);
     c->launches++;
     MGCG_LAUNCH_CHECK();
     return MGCG_OK;
@@ -261,9 +269,10 @@ int cgcg_update(mgcg_ctx *c, int n, const double *u, const double *w, double *p,
 // p = z + beta p   (ConjugateGradientCpu.cs:94; Solve3 Mgcg.cu:197 does it as scal+axpy = 2 passes)
 template <int V>
 __global__ void __launch_bounds__(kVecThreads) k_update_p(int n, const double *__restrict__ z, double *__restrict__ p,
-                                                          Scalars *sc, bool host_beta, double beta_h)
+                                                          Scalars *sc, bool host_beta, double beta_h, Mirror mir)
 {
     if (!host_beta && sc->done) return;
+    bool wrote = false;
     const double beta = host_beta ? beta_h : sc->beta;
     const int stride = gridDim.x * blockDim.x;
     if (V == 2) {
@@ -274,18 +283,29 @@ __global__ void __launch_bounds__(kVecThreads) k_update_p(int n, const double *_
             double2 zv = z2[i], pv = p2[i];
             pv.x = zv.x + beta * pv.x; pv.y = zv.y + beta * pv.y;
             p2[i] = pv;
+            if (mir.ctl) { wrote |= mirror_store(mir, 2 * i, pv.x); wrote |= mirror_store(mir, 2 * i + 1, pv.y); }
         }
-        if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) p[n - 1] = z[n - 1] + beta * p[n - 1];
+        if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+            const double pi = z[n - 1] + beta * p[n - 1];
+            p[n - 1] = pi;
+            if (mir.ctl) wrote |= mirror_store(mir, n - 1, pi);
+        }
     } else {
-        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) p[i] = z[i] + beta * p[i];
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+            const double pi = z[i] + beta * p[i];
+            p[i] = pi;
+            if (mir.ctl) wrote |= mirror_store(mir, i, pi);
+        }
     }
+    halo_signal(mir, wrote);
 }
 
-int cg_update_p(mgcg_ctx *c, int n, const double *z, double *p, bool use_host_beta, double host_beta)
+int cg_update_p(mgcg_ctx *c, int n, const double *z, double *p, bool use_host_beta, double host_beta, const Mirror *mir)
 {
     int grid = vec_grid(c, n, 2);
-    if (aligned16(z) && aligned16(p)) k_update_p<2><<<grid, kVecThreads, 0, c->stream>>>(n, z, p, c->d_scalars, use_host_beta, host_beta);
-    else k_update_p<1><<<grid, kVecThreads, 0, c->stream>>>(n, z, p, c->d_scalars, use_host_beta, host_beta);
+    const Mirror mm = mir ? *mir : Mirror();
+    if (aligned16(z) && aligned16(p)) k_update_p<2><<<grid, kVecThreads, 0, c->stream>>>(n, z, p, c->d_scalars, use_host_beta, host_beta, mm);
+    else k_update_p<1><<<grid, kVecThreads, 0, c->stream>>>(n, z, p, c->d_scalars, use_host_beta, host_beta, mm);
     c->launches++;
     MGCG_LAUNCH_CHECK();
     return MGCG_OK;
@@ -294,16 +314,22 @@ int cg_update_p(mgcg_ctx *c, int n, const double *z, double *p, bool use_host_be
 // ---------------------------------------------------------------------------------------------------------
 // multigrid vector pieces
 __global__ void __launch_bounds__(kVecThreads) k_jacobi_first(int n, double omega, const double *__restrict__ dinv,
-                                                              const double *__restrict__ b, double *__restrict__ x, const Scalars *sc)
+                                                              const double *__restrict__ b, double *__restrict__ x, const Scalars *sc, Mirror mir)
 {
     if (sc->done) return;
+    bool wrote = false;
     const int stride = gridDim.x * blockDim.x;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) x[i] = omega * dinv[i] * b[i];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const double xi = omega * dinv[i] * b[i];
+        x[i] = xi;
+        if (mir.ctl) wrote |= mirror_store(mir, i, xi);
+    }
+    halo_signal(mir, wrote);
 }
 
-int mg_jacobi_first(mgcg_ctx *c, int n, double omega, const double *dinv, const double *b, double *x)
+int mg_jacobi_first(mgcg_ctx *c, int n, double omega, const double *dinv, const double *b, double *x, const Mirror *mir)
 {
-    k_jacobi_first<<<vec_grid(c, n, 2), kVecThreads, 0, c->stream>>>(n, omega, dinv, b, x, c->d_scalars);
+    k_jacobi_first<<<vec_grid(c, n, 2), kVecThreads, 0, c->stream>>>(n, omega, dinv, b, x, c->d_scalars, mir ? *mir : Mirror());
     c->launches++;
     MGCG_LAUNCH_CHECK();
     return MGCG_OK;

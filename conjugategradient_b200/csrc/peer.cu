@@ -29,23 +29,6 @@
 
 namespace mgcg {
 
-__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v)
-{
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p)
-{
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p)
-{
-    unsigned long long v;
-    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-
 // Clocks a wait may last before the solve is marked MGCG_ERR_COMM instead of hanging the device: ~4 s at 2 GHz by default,
 // MGCG_PEER_TIMEOUT_S overrides (peer_open).  The rendezvous at the start of every solve waits 64 x longer: ranks enter a
 // solve with whatever skew their hosts have (a first-call graph instantiation, a profiler, a debugger), and a rank that is
@@ -275,7 +258,7 @@ struct PeerHello {
 
 // Collective: allocate the arena for `halo_cap` ghost rows per side and `gather_cap` gathered rows, exchange the handles
 // (over NCCL: this is setup, not the loop) and map every peer.  Leaves P.active = true only if EVERY rank succeeded.
-int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
+int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap, size_t vec_doubles)
 {
     DistState *D = c->dist;
     PeerState &P = D->peer;
@@ -288,7 +271,8 @@ int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
     // tens of milliseconds): every rank clears its own flags / sequence numbers, and the all-reduce that takes the decision
     // is also the barrier that orders those memsets before anybody's first push.
     {
-        int reuse = (P.ready && P.arena && halo_cap <= P.halo_cap && (size_t)2 * P.halo_cap + (size_t)gather_cap <= P.stage_cap) ? 1 : 0;
+        int reuse = (P.ready && P.arena && halo_cap <= P.halo_cap && (size_t)2 * P.halo_cap + (size_t)gather_cap <= P.stage_cap &&
+                     vec_doubles * sizeof(double) <= P.vec_cap) ? 1 : 0;
         int *d_flag = nullptr;
         MGCG_CUDA(pool_alloc((void **)&d_flag, sizeof(int), st));
         if (reuse) MGCG_CUDA(cudaMemsetAsync(P.arena, 0, P.stage_off, st));
@@ -297,7 +281,7 @@ int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
         MGCG_CUDA(cudaMemcpyAsync(&reuse, d_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
         MGCG_CUDA(cudaStreamSynchronize(st));
         pool_release(d_flag);
-        if (reuse) { P.active = true; return MGCG_OK; }
+        if (reuse) { P.active = true; P.fused = vec_doubles > 0; P.nvec = 0; P.vec_used = 0; return MGCG_OK; }
     }
     peer_close(c, true);      // collective: every rank takes this branch together (the all-reduce above decided it)
     {   // wait limit of the flag spins (seconds -> clocks at the device's clock rate)
@@ -309,6 +293,7 @@ int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
             if (sec > 0 && khz > 0) clocks = (long long)(sec * 1e3 * (double)khz);
         }
         MGCG_CUDA(cudaMemcpyToSymbol(g_peer_wait_clocks, &clocks, sizeof(clocks)));
+        P.wait_clocks = clocks;
     }
     // halo and gather staging are DISJOINT: a gather is pushed by every rank, also by ranks that are not this rank's
     // neighbours and have therefore not synchronised with it in the halo exchanges just before — their blocks must not land
@@ -317,7 +302,10 @@ int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
     cap = (cap + 1) & ~(size_t)1;
     P.halo_cap = halo_cap; P.stage_cap = cap;
     P.stage_off = (sizeof(PeerCtl) + 255) & ~(size_t)255;
-    const size_t bytes = P.stage_off + sizeof(double) * 2 * cap;
+    P.vec_off = (P.stage_off + sizeof(double) * 2 * cap + 255) & ~(size_t)255;
+    P.vec_cap = vec_doubles * sizeof(double);
+    P.fused = vec_doubles > 0; P.nvec = 0; P.vec_used = 0;
+    const size_t bytes = P.vec_off + P.vec_cap;
     PeerHello me;
     memset(&me, 0, sizeof(me));
     me.ok = 1;
@@ -366,6 +354,88 @@ int peer_open(mgcg_ctx *c, int halo_cap, int gather_cap)
     if (!ok) { peer_close(c, true); return MGCG_OK; }      // every rank sees the same `ok`
     P.active = true; P.ready = true;
     return MGCG_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// sharded vectors inside the arena (fused halo exchange, halo.cuh)
+static inline size_t round256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+double *peer_vec_alloc(mgcg_ctx *c, int lo, int own, int hi, int halo)
+{
+    PeerState &P = c->dist->peer;
+    if (!P.active || !P.fused || P.nvec >= kPeerVecMax) return nullptr;
+    const size_t bytes = round256(sizeof(double) * ((size_t)lo + own + hi + 2));
+    if (P.vec_used + bytes > P.vec_cap) return nullptr;
+    double *v = (double *)((char *)P.arena + P.vec_off + P.vec_used);
+    if (cudaMemsetAsync(v, 0, bytes, c->stream) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    const int i = P.nvec++;
+    P.vbase[i] = v; P.vlo[i] = lo; P.vown[i] = own; P.vhi[i] = hi; P.vhalo[i] = halo;
+    P.vec_used += bytes;
+    return v;
+}
+
+struct PeerVecTable { int nvec, pad; PeerVecSlot slot[kPeerVecMax]; };
+
+int peer_vec_publish(mgcg_ctx *c)
+{
+    DistState *D = c->dist;
+    PeerState &P = D->peer;
+    cudaStream_t st = c->stream;
+    const int W = D->world, rk = D->rank;
+    PeerVecTable me;
+    memset(&me, 0, sizeof(me));
+    me.nvec = P.nvec;
+    for (int i = 0; i < P.nvec; ++i) {
+        me.slot[i].lo_off = (size_t)((char *)P.vbase[i] - (char *)P.arena);
+        me.slot[i].hi_off = me.slot[i].lo_off + sizeof(double) * ((size_t)P.vlo[i] + P.vown[i]);
+    }
+    PeerVecTable *d_all = nullptr;
+    MGCG_CUDA(pool_alloc((void **)&d_all, sizeof(PeerVecTable) * (size_t)(W + 1), st));
+    MGCG_CUDA(cudaMemcpyAsync(d_all + W, &me, sizeof(me), cudaMemcpyHostToDevice, st));
+    MGCG_NCCL(D->api, AllGather(d_all + W, d_all, sizeof(PeerVecTable), ncclChar, D->comm, st));
+    std::vector<PeerVecTable> all((size_t)W);
+    MGCG_CUDA(cudaMemcpyAsync(all.data(), d_all, sizeof(PeerVecTable) * (size_t)W, cudaMemcpyDeviceToHost, st));
+    MGCG_CUDA(cudaStreamSynchronize(st));     // (also: every rank's vectors are zeroed before anybody's first push)
+    pool_release(d_all);
+    for (int q = 0; q < W; ++q)
+        if (all[q].nvec != P.nvec) { set_error("peer_vec_publish: rank %d placed %d vectors, rank %d placed %d", q, all[q].nvec, rk, P.nvec); return MGCG_ERR_COMM; }
+    for (int i = 0; i < P.nvec; ++i) {
+        if (rk > 0) P.nb_lo[i] = all[rk - 1].slot[i];
+        if (rk < W - 1) P.nb_hi[i] = all[rk + 1].slot[i];
+    }
+    return MGCG_OK;
+}
+
+bool peer_mirror_of(mgcg_ctx *c, const double *ext, Mirror *m)
+{
+    DistState *D = c->dist;
+    PeerState &P = D->peer;
+    *m = Mirror();
+    if (!P.active || !P.fused) return false;
+    const int W = D->world, rk = D->rank;
+    for (int i = 0; i < P.nvec; ++i) {
+        if (P.vbase[i] != ext) continue;
+        m->halo = P.vhalo[i]; m->own = P.vown[i];
+        m->ctl = (PeerCtl *)P.arena;
+        if (rk > 0) { m->lo = (double *)((char *)P.peer[rk - 1] + P.nb_lo[i].hi_off); m->flag_lo = &((PeerCtl *)P.peer[rk - 1])->xflag[rk]; }
+        if (rk < W - 1) { m->hi = (double *)((char *)P.peer[rk + 1] + P.nb_hi[i].lo_off); m->flag_hi = &((PeerCtl *)P.peer[rk + 1])->xflag[rk]; }
+        return true;
+    }
+    return false;
+}
+
+bool peer_wait_of(mgcg_ctx *c, GhostWait *g)
+{
+    DistState *D = c->dist;
+    PeerState &P = D->peer;
+    *g = GhostWait();
+    if (!P.active || !P.fused) return false;
+    PeerCtl *me = (PeerCtl *)P.arena;
+    g->ctl = me;
+    if (D->rank > 0) g->flag_lo = &me->xflag[D->rank - 1];
+    if (D->rank < D->world - 1) g->flag_hi = &me->xflag[D->rank + 1];
+    g->clocks = P.wait_clocks;
+    return true;
 }
 
 }  // namespace mgcg
