@@ -669,17 +669,25 @@ def run_ours_dist(args):
     dist.all_reduce(nnz_global)
     nnz_global = int(nnz_global.item())
     if not args.no_parity and nnz_global < 2 ** 31:
-        parts = [torch.empty(int(zo[q + 1] - zo[q]) * n_side * n_side, dtype=torch.float64, device=dev) for q in range(world)] if rank == 0 else None
+        def gather_to_rank0(x_local):
+            parts = [torch.empty(int(zo[q + 1] - zo[q]) * n_side * n_side, dtype=torch.float64, device=dev) for q in range(world)] if rank == 0 else None
+            if rank == 0:
+                parts[0].copy_(x_local)
+                reqs = [dist.irecv(parts[q], src=q) for q in range(1, world)]
+                for r_ in reqs:
+                    r_.wait()
+                return torch.cat(parts)
+            dist.send(x_local, dst=0)
+            return None
+        xd = gather_to_rank0(x_timed)
+        # the sharded and the single-GPU hierarchies differ where aggregates meet a shard boundary, so two solves stopped at 1e-8
+        # differ by O(1e-8); the sharded PATH is judged on solves of the same system taken to 1e-12 on both sides
+        m.setup(n, r0, tv, tr, tc, solver_options(args, S, tolerance=1e-12, **extra))
+        tx.zero_()
+        rt_d = m.solve(tb, tx)
+        xdt = gather_to_rank0(tx)
+        m.setup(n, r0, tv, tr, tc, opts)
         if rank == 0:
-            parts[0].copy_(x_timed)
-            reqs = [dist.irecv(parts[q], src=q) for q in range(1, world)]
-            for r_ in reqs:
-                r_.wait()
-        else:
-            dist.send(x_timed, dst=0)
-        if rank == 0:
-            xd = torch.cat(parts)
-            del parts
             ms1 = S.Mgcg(lr, use_torch_stream=True)
             fv, fr, fc, fb = device_problem(args, ms1, dev)
             fx = torch.zeros(n, dtype=torch.float64, device=dev)
@@ -691,12 +699,15 @@ def run_ours_dist(args):
             ms1.setup(fv, fr, fc, solver_options(args, S, tolerance=1e-12))
             ft = torch.zeros(n, dtype=torch.float64, device=dev)
             ms1.solve(fb, ft)
-            parity = {"dist_x_rel_err": err, "single_gpu_iterations": r1g.iterations_done, "single_gpu_solve_ms": r1g.solve_ms,
+            parity = {"dist_x_rel_err": float((xdt - ft).abs().max()) / scale,
+                      "dist_x_rel_err_note": "sharded vs single-GPU solution of the same system, both solved to 1e-12 relative residual "
+                                             f"(sharded: {rt_d.iterations_done} iterations, residual {rt_d.residual:.2e})",
+                      "dist_x_rel_err_at_1e-8": err, "single_gpu_iterations": r1g.iterations_done, "single_gpu_solve_ms": r1g.solve_ms,
                       "dist_x_rel_err_vs_tight_solve": float((xd - ft).abs().max()) / scale,
                       "single_x_rel_err_vs_tight_solve": float((fx - ft).abs().max()) / scale,
                       "norm": "max|dx| / max|x|; single-GPU solves of the same device-assembled system on rank 0's GPU, outside the timed region"}
             ms1.close()
-            del xd, fx, ft, fv, fr, fc, fb
+            del xd, xdt, fx, ft, fv, fr, fc, fb
         dist.barrier()
 
     # e2e: ONE C-ABI call per rank on pinned host shards (mgcg_solve_host_dist): upload + hierarchy + solve + download timed

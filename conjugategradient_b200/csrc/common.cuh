@@ -97,6 +97,8 @@ struct SpmvPlan {
     int kernel = MGCG_SPMV_STREAM;  // STREAM or VECTOR
     bool tma = false;               // STREAM: use the TMA-staged variant (short rows, 16-byte aligned val/col)
     bool tma_short = false;         // ... with twice the stages of half the size (very short rows)
+    int tma_wide_cap = 0;           // > 0: the WIDE variant (rows of 8..32 entries): stage capacity, ring in dynamic shared memory
+    int tma_wide_smem = 0;
     int rows_per_tile = 256;        // STREAM: rows handled per tile (<= 256)
     int lanes = 8;                  // VECTOR / ROWS: lanes per row
     int rows_cap = 2552;            // ROWS: non-zeros a shared-memory stage holds (multiple of 4)

@@ -171,6 +171,7 @@ constexpr int kTmaStagesLong = 2;
 // of DRAM peak against 73-75 % on the 7-per-row operator)
 constexpr int kTmaCapShort = 960;
 constexpr int kTmaStagesShort = 4;
+constexpr double kTmaWideMaxAvg = 32.0;       // WIDE variant: 256 rows x 32 x 1.06 x 12 B x 2 stages = 208 KB of dynamic shared memory
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
@@ -201,12 +202,22 @@ __device__ __forceinline__ void tma_load_1d(void *dst, const void *src, unsigned
 
 struct TmaMeta { int k0, k1, direct, pad; };
 
+// kTmaCap == 0: WIDE variant — the stage capacity is a launch parameter and the ring lives in dynamic shared memory (rows of
+// 8..32 entries: a 256-row tile is up to ~100 KB, one block per SM).  One thread per row keeps consecutive rows in consecutive
+// threads, so on stencil-like matrices (the 27-point operator of C5, the level-1 Galerkin operators) the k-th gathers of a warp fall
+// into one 256-byte run of x; the lanes-per-row ROWS kernel spreads a warp's gathers over L runs of 256/L bytes and measured 0.56
+// of the HBM peak on the 512^3 27-point shard against 0.96 for this layout on the 7-point operator.
 template <int EPI, int kTmaCap, int kTmaStages>
-__global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles, ReduceWs ws, Scalars *sc)
+__global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles, int dyn_cap, ReduceWs ws, Scalars *sc)
 {
     if (a.gated && sc->done) return;
-    __shared__ __align__(16) double s_val[kTmaStages][kTmaCap + 2];
-    __shared__ __align__(16) int s_col[kTmaStages][kTmaCap + 4];
+    constexpr bool kDyn = (kTmaCap == 0);
+    __shared__ __align__(16) double s_val_st[kDyn ? 1 : kTmaStages][kDyn ? 2 : kTmaCap + 2];
+    __shared__ __align__(16) int s_col_st[kDyn ? 1 : kTmaStages][kDyn ? 4 : kTmaCap + 4];
+    extern __shared__ __align__(16) unsigned char tma_dyn[];
+    const int cap = kDyn ? dyn_cap : kTmaCap;                 // multiple of 4: every stage starts 16-byte aligned
+    double *const s_val_b = kDyn ? reinterpret_cast<double *>(tma_dyn) : &s_val_st[0][0];                                   // [stages][cap + 2]
+    int *const s_col_b = kDyn ? reinterpret_cast<int *>(tma_dyn + (size_t)kTmaStages * (cap + 2) * 8) : &s_col_st[0][0];    // [stages][cap + 4]
     __shared__ __align__(8) unsigned long long s_full[kTmaStages], s_empty[kTmaStages];
     __shared__ TmaMeta s_meta[kTmaStages];
     const int t = threadIdx.x;
@@ -236,13 +247,13 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
         const int k0 = rowptr[r0], k1 = rowptr[r0 + nr];
         const int ka = k0 & ~1, kc = k0 & ~3;
         const unsigned vb = (unsigned)(((k1 - ka) * 8 + 15) & ~15), cb = (unsigned)(((k1 - kc) * 4 + 15) & ~15);
-        const bool fits = (k1 - ka) <= kTmaCap && (k1 - kc) <= kTmaCap && k1 > k0 &&
+        const bool fits = (k1 - ka) <= cap && (k1 - kc) <= cap && k1 > k0 &&
                           ((long long)ka * 8 + vb <= nnz_end * 8) && ((long long)kc * 4 + cb <= nnz_end * 4);
         s_meta[s].k0 = k0; s_meta[s].k1 = k1; s_meta[s].direct = fits ? 0 : 1;
         if (fits) {
             mbar_arrive_expect_tx(&s_full[s], vb + cb);
-            tma_load_1d(&s_val[s][0], val + ka, vb, &s_full[s]);
-            tma_load_1d(&s_col[s][0], col + kc, cb, &s_full[s]);
+            tma_load_1d(s_val_b + (size_t)s * (cap + 2), val + ka, vb, &s_full[s]);
+            tma_load_1d(s_col_b + (size_t)s * (cap + 4), col + kc, cb, &s_full[s]);
         } else {
             mbar_arrive(&s_full[s]);
         }
@@ -278,9 +289,23 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
         if (active) {
             if (!s_meta[s].direct) {
                 const int k0 = s_meta[s].k0;
-                const double *sv = &s_val[s][0] - (k0 & ~1);
-                const int *scl = &s_col[s][0] - (k0 & ~3);
-                for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(sv[k], x[scl[k]]));
+                const double *sv = s_val_b + (size_t)s * (cap + 2) - (k0 & ~1);
+                const int *scl = s_col_b + (size_t)s * (cap + 4) - (k0 & ~3);
+                if (kDyn) {
+                    // medium rows: the gathers of four entries are issued together; the sum keeps the storage order
+                    int k = rs;
+                    for (; k + 4 <= re; k += 4) {
+                        const int c0 = scl[k], c1 = scl[k + 1], c2 = scl[k + 2], c3 = scl[k + 3];
+                        const double x0 = x[c0], x1 = x[c1], x2 = x[c2], x3 = x[c3];
+                        acc = __dadd_rn(acc, __dmul_rn(sv[k], x0));
+                        acc = __dadd_rn(acc, __dmul_rn(sv[k + 1], x1));
+                        acc = __dadd_rn(acc, __dmul_rn(sv[k + 2], x2));
+                        acc = __dadd_rn(acc, __dmul_rn(sv[k + 3], x3));
+                    }
+                    for (; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(sv[k], x[scl[k]]));
+                } else {
+                    for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(sv[k], x[scl[k]]));
+                }
             } else {
                 for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(__ldcs(val + k), x[__ldcs(col + k)]));
             }
@@ -489,9 +514,11 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel)
     if (cap > kMaxPartials) cap = kMaxPartials;
     // AUTO: rows short enough for a 256-row tile to fit a TMA stage -> STREAM (TMA); up to ~300 per row -> ROWS (TMA-staged,
     // L lanes per row); beyond -> VECTOR.  (MGCG_SPMV_NO_ROWS=1 restores the round-1 choice: STREAM up to 48 per row, else VECTOR.)
+    static const bool no_wide = getenv("MGCG_SPMV_NO_WIDE") != nullptr;
+    const bool wide_ok = !no_wide && avg > (double)(kTmaCap - 64) / kTmaRows && avg <= kTmaWideMaxAvg;
     if (kernel == MGCG_SPMV_AUTO) {
         static const bool no_rows = getenv("MGCG_SPMV_NO_ROWS") != nullptr;
-        if (avg * kTmaRows <= kTmaCap - 64) kernel = MGCG_SPMV_STREAM;
+        if (avg * kTmaRows <= kTmaCap - 64 || wide_ok) kernel = MGCG_SPMV_STREAM;
         else if (no_rows) kernel = (avg <= 48.0) ? MGCG_SPMV_STREAM : MGCG_SPMV_VECTOR;
         else kernel = (avg <= 300.0) ? MGCG_SPMV_ROWS : MGCG_SPMV_VECTOR;
     }
@@ -533,8 +560,14 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel)
         return p;
     }
     // short rows (a 256-row tile fits a TMA stage): the TMA-staged variant of the stream kernel
-    p.tma = (kernel == MGCG_SPMV_STREAM && avg * kTmaRows <= kTmaCap - 64);
+    p.tma = (kernel == MGCG_SPMV_STREAM && (avg * kTmaRows <= kTmaCap - 64 || wide_ok));
     p.tma_short = p.tma && avg * kTmaRows <= kTmaCapShort - 64;
+    if (p.tma && avg * kTmaRows > kTmaCap - 64) {     // WIDE: stage capacity from the average tile, 2 stages in dynamic shared memory
+        long long capn = (long long)(avg * kTmaRows * 1.06) + 96;
+        capn = (capn + 3) & ~3LL;
+        p.tma_wide_cap = (int)capn;
+        p.tma_wide_smem = (int)((size_t)kTmaStagesLong * ((capn + 2) * 8 + (capn + 4) * 4));
+    }
     if (kernel == MGCG_SPMV_STREAM) {
         int per = (int)(avg + 0.999);
         if (per < 1) per = 1;
@@ -601,8 +634,22 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
         const int tiles = div_up(a.A.rows, kTmaRows);
         int grid = c->sm_count * 4;
         if (grid > tiles) grid = tiles;
-        if (plan.tma_short) k_spmv_tma<EPI, kTmaCapShort, kTmaStagesShort><<<grid, kTmaRows, 0, c->stream>>>(a, tiles, c->ws, c->d_scalars);
-        else k_spmv_tma<EPI, kTmaCap, kTmaStagesLong><<<grid, kTmaRows, 0, c->stream>>>(a, tiles, c->ws, c->d_scalars);
+        if (plan.tma_wide_cap > 0) {
+            static int set_bytes[64] = {0};
+            const int d = c->device & 63;
+            if (plan.tma_wide_smem > set_bytes[d]) {
+                MGCG_CUDA(cudaFuncSetAttribute(k_spmv_tma<EPI, 0, kTmaStagesLong>, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.tma_wide_smem));
+                set_bytes[d] = plan.tma_wide_smem;
+            }
+            int per_sm = (int)((224 * 1024) / (plan.tma_wide_smem + 2048));
+            if (per_sm < 1) per_sm = 1;
+            if (per_sm > 4) per_sm = 4;
+            grid = c->sm_count * per_sm;
+            if (grid > tiles) grid = tiles;
+            k_spmv_tma<EPI, 0, kTmaStagesLong><<<grid, kTmaRows, (size_t)plan.tma_wide_smem, c->stream>>>(a, tiles, plan.tma_wide_cap, c->ws, c->d_scalars);
+        }
+        else if (plan.tma_short) k_spmv_tma<EPI, kTmaCapShort, kTmaStagesShort><<<grid, kTmaRows, 0, c->stream>>>(a, tiles, 0, c->ws, c->d_scalars);
+        else k_spmv_tma<EPI, kTmaCap, kTmaStagesLong><<<grid, kTmaRows, 0, c->stream>>>(a, tiles, 0, c->ws, c->d_scalars);
     } else if (plan.kernel == MGCG_SPMV_STREAM) {
         int tiles = div_up(a.A.rows, plan.rows_per_tile);
         k_spmv_stream<EPI><<<plan.grid, kSpmvThreads, 0, c->stream>>>(a, plan.rows_per_tile, tiles, c->ws, c->d_scalars);

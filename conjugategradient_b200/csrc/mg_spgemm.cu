@@ -494,6 +494,94 @@ __global__ void __launch_bounds__(kWmWarps * 32) k_spgemm_wmerge(Csr A, Csr B, i
     }
 }
 
+
+// Numeric pass for output rows of at most 32 entries (the fine-level Galerkin product: 27 per row): OWNER lanes.
+// Phase 1 repeats the symbolic merge and leaves the row's sorted distinct columns one per lane.  Phase 2 walks the A row in storage
+// order, 32 entries at a time; every lane reads the B row of the current entry (uniform addresses: one L1 transaction per load) and
+// the lane that owns the entry's column adds the product — so c_ij is still summed in the storage order of the A row, product by
+// product, bit-identical to the merge kernels and the CPU twin, but the ordered sums of the row's 27 outputs advance in parallel
+// instead of one after the other (the warp-merge numeric pass spent ~85 % of its issue slots walking ballots: 7.8 ms at 256^3).
+template <int SLOTS>
+__global__ void __launch_bounds__(kWmWarps * 32) k_spgemm_owner(Csr A, Csr B, int shift, const int *__restrict__ c_rowptr,
+                                                               int *__restrict__ c_col, double *__restrict__ c_val)
+{
+    constexpr unsigned kEnd = 0x7fffffffu;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int nwarps = gridDim.x * kWmWarps;
+    for (int row = blockIdx.x * kWmWarps + w; row < A.rows; row += nwarps) {
+        const int ks = A.rowptr[row], m = A.rowptr[row + 1] - ks;
+        // ---- phase 1: sorted distinct columns, lane o keeps the o-th
+        unsigned mycol = kEnd;
+        {
+            int q[SLOTS], qe[SLOTS];
+            unsigned hc[SLOTS];
+#pragma unroll
+            for (int t = 0; t < SLOTS; ++t) {
+                const int k = lane * SLOTS + t;
+                q[t] = 0; qe[t] = 0; hc[t] = kEnd;
+                if (k < m) {
+                    const int j = A.col[ks + k] - shift;
+                    q[t] = B.rowptr[j]; qe[t] = B.rowptr[j + 1];
+                    if (q[t] < qe[t]) hc[t] = (unsigned)B.col[q[t]];
+                }
+            }
+            int o = 0;
+            while (true) {
+                unsigned mine = kEnd;
+#pragma unroll
+                for (int t = 0; t < SLOTS; ++t) mine = min(mine, hc[t]);
+                const unsigned cur = __reduce_min_sync(0xffffffffu, mine);
+                if (cur == kEnd) break;
+                if (lane == o) mycol = cur;
+                ++o;
+#pragma unroll
+                for (int t = 0; t < SLOTS; ++t)
+                    if (hc[t] == cur) { ++q[t]; hc[t] = q[t] < qe[t] ? (unsigned)B.col[q[t]] : kEnd; }
+            }
+        }
+        // ---- phase 2: ordered accumulation by the owner lanes
+        double sum = 0.0;
+        bool have = false;
+        for (int k0 = 0; k0 < m; k0 += 32) {
+            const int kk = k0 + lane;
+            int bq = 0, bqe = 0;
+            double av = 0.0;
+            if (kk < m) {
+                const int j = A.col[ks + kk] - shift;
+                bq = B.rowptr[j]; bqe = B.rowptr[j + 1];
+                av = A.val[ks + kk];
+            }
+            const int cnt = min(32, m - k0);
+            for (int t = 0; t < cnt; ++t) {
+                const int e0 = __shfl_sync(0xffffffffu, bq, t), e1 = __shfl_sync(0xffffffffu, bqe, t);
+                const double a = __shfl_sync(0xffffffffu, av, t);
+                for (int e = e0; e < e1; e += 4) {
+                    unsigned cc[4];
+                    double vv[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const bool in = e + u < e1;
+                        cc[u] = in ? (unsigned)B.col[e + u] : kEnd;
+                        vv[u] = in ? B.val[e + u] : 0.0;
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (cc[u] == mycol && cc[u] != kEnd) {
+                            const double pr = __dmul_rn(a, vv[u]);
+                            sum = have ? __dadd_rn(sum, pr) : pr;
+                            have = true;
+                        }
+                }
+            }
+        }
+        if (mycol != kEnd) {
+            const int o = c_rowptr[row] + lane;
+            c_col[o] = (int)mycol;
+            c_val[o] = sum;
+        }
+    }
+}
+
 template <int SLOTS>
 static int run_wmerge(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, DevCsr *C)
 {
@@ -507,17 +595,30 @@ static int run_wmerge(mgcg_ctx *c, const Csr &A, const Csr &B, int shift, DevCsr
     MGCG_LAUNCH_CHECK();
     C->rows = A.rows; C->cols = B.cols;
     MGCG_CUDA(pool_alloc((void **)&C->rowptr, sizeof(int) * ((size_t)A.rows + 1), st));
-    int nnz = 0;
+    int nnz = 0, maxcnt = 0;
     {
-        const int s_ = scan_counts_checked(c, cnt, A.rows, C->rowptr, &nnz, "spgemm");
+        // longest output row: at most 32 entries -> the owner-lane numeric pass
+        size_t tb = 0;
+        int *d_maxc = nullptr;
+        void *tmp = nullptr;
+        MGCG_CUDA(pool_alloc((void **)&d_maxc, sizeof(int), st));
+        MGCG_CUDA(cub::DeviceReduce::Max(nullptr, tb, cnt, d_maxc, A.rows, st));
+        MGCG_CUDA(pool_alloc(&tmp, tb > 0 ? tb : 1, st));
+        MGCG_CUDA(cub::DeviceReduce::Max(tmp, tb, cnt, d_maxc, A.rows, st));
+        MGCG_CUDA(cudaMemcpyAsync(&maxcnt, d_maxc, sizeof(int), cudaMemcpyDeviceToHost, st));
+        const int s_ = scan_counts_checked(c, cnt, A.rows, C->rowptr, &nnz, "spgemm");     // synchronises
+        pool_free(tmp, st); pool_free(d_maxc, st);
         pool_free(cnt, st);
         if (s_ != MGCG_OK) { pool_free(C->rowptr, st); C->rowptr = nullptr; return s_; }
     }
     C->nnz = nnz;
     MGCG_CUDA(pool_alloc((void **)&C->val, sizeof(double) * (size_t)(nnz > 0 ? nnz : 1), st));
     MGCG_CUDA(pool_alloc((void **)&C->col, sizeof(int) * (size_t)(nnz > 0 ? nnz : 1), st));
-    if (getenv("MGCG_TRACE")) fprintf(stderr, "[mgcg spgemm] rows %d warp-merge kernel (%d lists per lane) nnz %d grid %d\n", A.rows, SLOTS, nnz, grid);
-    k_spgemm_wmerge<true, SLOTS><<<grid, kWmWarps * 32, 0, st>>>(A, B, shift, nullptr, C->rowptr, C->col, C->val);
+    const bool owner = maxcnt <= 32 && !getenv("MGCG_SPGEMM_NO_OWNER");
+    if (getenv("MGCG_TRACE")) fprintf(stderr, "[mgcg spgemm] rows %d warp-merge kernel (%d lists per lane, %s numeric pass, longest output row %d) nnz %d grid %d\n",
+                                      A.rows, SLOTS, owner ? "owner-lane" : "merge", maxcnt, nnz, grid);
+    if (owner) k_spgemm_owner<SLOTS><<<grid, kWmWarps * 32, 0, st>>>(A, B, shift, C->rowptr, C->col, C->val);
+    else k_spgemm_wmerge<true, SLOTS><<<grid, kWmWarps * 32, 0, st>>>(A, B, shift, nullptr, C->rowptr, C->col, C->val);
     MGCG_LAUNCH_CHECK();
     return MGCG_OK;
 }

@@ -46,7 +46,7 @@ def main():
         kw.update(nx=n, ny=n, nz=n)
     elif kw.get("precond", 0) == 1:
         kw.update(mg_aggregation=1)     # without a grid the sharded hierarchy aggregates by blocks of 8 rows (csrc/dist.cu agg_of)
-    o = S.default_options(norm=2, tolerance=1e-8, max_iteration=2000, **kw)
+    o = S.default_options(norm=2, tolerance=cfg.get("tolerance", 1e-8), max_iteration=2000, **kw)
     m.setup(N, r0, tv, tr, tc, o)
     res = m.solve(tb, tx)
     for _ in range(cfg.get("setups", 1) - 1):     # a re-setup reuses the peer arena, the private coarse context and cached blocks

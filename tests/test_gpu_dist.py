@@ -40,8 +40,9 @@ CASES = [
     # opt-in modes, compared with the single-GPU solve run in the SAME mode: Chebyshev smoother on the sharded levels
     # (global eigenvalue bound), single-reduce CG (one scalar exchange per iteration), and both
     ("mg_chebyshev_peer", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "mg_smoother": 2}, "transport": 2}),
+    # (ill-conditioned: both solves are taken to 1e-10 so that each is within the north_star's 1e-10 of the far-converged solution)
     ("mg_27pt_chebyshev_nccl", {"n": 24, "matrix": "p27", "options": {"precond": 1, "dist_replicate_below": 500, "dist_transport": 1, "mg_smoother": 2},
-                                "tight": 1e-12}),
+                                "tight": 1e-13, "tolerance": 1e-10}),
     ("plain_cg_single_reduce_peer", {"n": 32, "options": {"precond": 0, "dist_transport": 2, "cg_variant": 1}, "transport": 2}),
     ("mg_single_reduce_peer", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "cg_variant": 1}, "transport": 2,
                                "solves": 2}),
@@ -66,10 +67,13 @@ def test_sharded_matches_single_gpu(name, cfg):
         assert abs(r["it_dist"] - r["it_single"]) <= 1, r      # iteration count within +-1
         if "tight" in cfg:
             # the sharded x is as close to the far-converged solution as the single-GPU x is, to 1e-10 of max|x|
-            assert r["tight_residual"] <= 1e-12 and r["err_tight_dist"] <= r["err_tight_single"] + 1e-10, r
+            if cfg.get("tolerance", 1e-8) < 1e-8:
+                assert r["tight_residual"] <= 2e-13 and r["err_tight_dist"] <= 1e-10 and r["err_tight_single"] <= 1e-10, r
+            else:
+                assert r["tight_residual"] <= 1e-12 and r["err_tight_dist"] <= r["err_tight_single"] + 1e-10, r
         else:
             assert r["err"] <= 1e-10 if r["it_dist"] == r["it_single"] else r["err"] <= 1e-6, r
-        assert r["residual"] < 1e-8
+        assert r["residual"] < cfg.get("tolerance", 1e-8)
     if "transport" in cfg:
         assert all(r["transport"] == cfg["transport"] for r in res), res
     assert len({r["it_dist"] for r in res}) == 1 and len({r["residual"] for r in res}) == 1   # identical scalars on all ranks
