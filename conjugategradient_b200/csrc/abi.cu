@@ -5,6 +5,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <string.h>
+#include <stdlib.h>
 
 namespace mgcg {
 
@@ -18,6 +19,12 @@ void set_error(const char *fmt, ...)
     va_end(ap);
 }
 const char *get_error() { return g_err; }
+
+bool pdl_enabled()
+{
+    static const bool on = [] { const char *e = getenv("MGCG_PDL"); return !(e && e[0] == '0'); }();
+    return on;
+}
 
 int ctx_ensure_work(mgcg_ctx *c, int n)
 {
@@ -195,6 +202,8 @@ int mgcg_setup(mgcg_ctx *c, int count, int elements_count,
     c->setup_ms = 0.f;
     MGCG_CHECK(ctx_ensure_work(c, count));
     if (c->opt.precond == MGCG_PRECOND_MG) {
+        // the block cache's next slab: what a hierarchy build of this size takes (operators, transients, sort buffers, level vectors)
+        pool_reserve((size_t)(2.2 * 12.0 * (double)elements_count + 200.0 * (double)count) + ((size_t)64 << 20));
         cudaEvent_t e0, e1;
         MGCG_CUDA(cudaEventCreate(&e0)); MGCG_CUDA(cudaEventCreate(&e1));
         MGCG_CUDA(cudaEventRecord(e0, c->stream));

@@ -5,12 +5,18 @@
 // 90-700 ms stalls inside `R = P^T` / `A*P` of an otherwise 46 ms build (profiles/r01_setup_trace_256.txt).  Here freed
 // blocks are kept in per-(device, stream, rounded size) free lists and handed back to the next request of that bucket:
 // from the second setup of a given problem on, the build makes no driver allocation at all.
+// A bucket miss is served from a SLAB: one large driver allocation per device that blocks are carved from with a bump pointer
+// (pool_reserve sizes the next slab from the problem; 512 MiB otherwise).  A driver allocation costs ~0.33 ms whatever its size on
+// this box (tools/malloc_cost.py: 100 x 64 MiB = 37 ms) and, once peer access is enabled, is mapped into every peer; a cold
+// hierarchy build made ~100-300 of them.  Carved blocks go through the same free lists; a slab returns to the driver when nothing
+// carved from it is live and the cache is trimmed.
 // Reuse is stream-ordered: a block is only re-issued to work on the stream it was allocated for (the build runs on one
 // stream, and a free in host order is a free in stream order).  Sizes are rounded up to 1/8 of their power of two (<= 12.5 %).
 #include "common.cuh"
 #include <map>
 #include <mutex>
 #include <tuple>
+#include <stdlib.h>
 
 namespace mgcg {
 
@@ -21,6 +27,53 @@ std::mutex g_mu;
 std::map<void *, Block> g_live;                  // blocks handed out
 std::map<Key, std::vector<void *>> g_free;       // blocks waiting for the next request of their bucket
 size_t g_cached_bytes = 0;
+struct Slab { char *base; size_t size, used; int device; long live; };
+std::vector<Slab> g_slabs;
+size_t g_slab_hint = 0;                          // size of the next slab (pool_reserve)
+constexpr size_t kSlabDefault = (size_t)512 << 20;
+
+int slab_of(const void *p)
+{
+    for (size_t i = 0; i < g_slabs.size(); ++i)
+        if ((const char *)p >= g_slabs[i].base && (const char *)p < g_slabs[i].base + g_slabs[i].size) return (int)i;
+    return -1;
+}
+
+// carve rb bytes (256-byte aligned) for `dev`; nullptr when no slab has room and a new one cannot be made
+void *slab_carve(int dev, size_t rb)
+{
+    static const bool off = getenv("MGCG_POOL_NO_SLAB") != nullptr;
+    if (off) return nullptr;
+    const size_t need = (rb + 255) & ~(size_t)255;
+    for (Slab &s : g_slabs)
+        if (s.device == dev && s.used + need <= s.size) { void *p = s.base + s.used; s.used += need; s.live++; return p; }
+    size_t want = g_slab_hint > kSlabDefault ? g_slab_hint : kSlabDefault;
+    if (need > want / 2) return nullptr;         // very large blocks get their own driver allocation
+    void *base = nullptr;
+    if (cudaMalloc(&base, want) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    g_slabs.push_back(Slab{(char *)base, want, need, dev, 1});
+    return base;
+}
+
+// give slabs without live blocks back to the driver (their cached blocks are dropped from the free lists first)
+void free_dead_slabs_locked(int device)
+{
+    for (size_t i = 0; i < g_slabs.size();) {
+        Slab &s = g_slabs[i];
+        if ((device >= 0 && s.device != device) || s.live > 0) { ++i; continue; }
+        for (auto it = g_free.begin(); it != g_free.end();) {
+            std::vector<void *> &v = it->second;
+            for (size_t k = 0; k < v.size();) {
+                if ((char *)v[k] >= s.base && (char *)v[k] < s.base + s.size) { g_cached_bytes -= std::get<2>(it->first); v[k] = v.back(); v.pop_back(); }
+                else ++k;
+            }
+            if (v.empty()) it = g_free.erase(it); else ++it;
+        }
+        cudaFree(s.base);
+        g_slabs[i] = g_slabs.back();
+        g_slabs.pop_back();
+    }
+}
 
 size_t round_up(size_t bytes)
 {
@@ -35,7 +88,7 @@ void drop_cached_locked(int device, bool any_stream = true, cudaStream_t stream 
 {
     for (auto it = g_free.begin(); it != g_free.end();) {
         if ((device < 0 || std::get<0>(it->first) == device) && (any_stream || std::get<1>(it->first) == stream)) {
-            for (void *p : it->second) { cudaFree(p); g_cached_bytes -= std::get<2>(it->first); }
+            for (void *p : it->second) { if (slab_of(p) < 0) cudaFree(p); g_cached_bytes -= std::get<2>(it->first); }   // (carved blocks stay in their slab)
             it = g_free.erase(it);
         } else ++it;
     }
@@ -55,17 +108,27 @@ cudaError_t pool_alloc(void **p, size_t bytes, cudaStream_t st)
         *p = it->second.back();
         it->second.pop_back();
         g_cached_bytes -= rb;
-    } else {
+        const int si = slab_of(*p);
+        if (si >= 0) g_slabs[si].live++;
+    } else if ((*p = slab_carve(dev, rb)) == nullptr) {
         e = cudaMalloc(p, rb);
         if (e != cudaSuccess) {          // out of memory: give the cached blocks back and try once more
             cudaGetLastError();
             drop_cached_locked(dev);
+            free_dead_slabs_locked(dev);
             e = cudaMalloc(p, rb);
             if (e != cudaSuccess) return e;
         }
     }
     g_live[*p] = Block{rb, dev, st};
     return cudaSuccess;
+}
+
+// the next slab of this process is at least `bytes` large (mgcg_setup: a multiple of the matrix size)
+void pool_reserve(size_t bytes)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_slab_hint = bytes;
 }
 
 // Free a block obtained from pool_alloc (kept for reuse), or anything else (cudaFree).  Safe for work still queued on the
@@ -79,6 +142,8 @@ void pool_release(void *p)
         if (it != g_live.end()) {
             const Block b = it->second;
             g_live.erase(it);
+            const int si = slab_of(p);
+            if (si >= 0) g_slabs[si].live--;
             g_free[Key(b.device, b.stream, b.bytes)].push_back(p);
             g_cached_bytes += b.bytes;
             return;
@@ -93,6 +158,7 @@ void pool_trim(int device)
 {
     std::lock_guard<std::mutex> lk(g_mu);
     drop_cached_locked(device);
+    free_dead_slabs_locked(device);
 }
 
 // a context is going away: blocks cached for its stream can never be re-issued
@@ -100,6 +166,7 @@ void pool_trim_stream(int device, cudaStream_t st)
 {
     std::lock_guard<std::mutex> lk(g_mu);
     drop_cached_locked(device, false, st);
+    free_dead_slabs_locked(device);
 }
 
 size_t pool_cached_bytes()

@@ -261,12 +261,35 @@ int effective_max_iteration(int requested, int n);   // the option's "no limit" 
 // has no conditional nodes (callers fall back to one iteration per launch).
 int graph_build_while(mgcg_ctx *c, int (*enqueue)(mgcg_ctx *, void *), void *arg, cudaGraph_t *graph, cudaGraphExec_t *exec, int *body_nodes);
 
+// ---- programmatic dependent launch (PDL) of the kernels inside the CG loop: a kernel launched with the attribute may be scheduled
+// while its predecessor on the stream is still draining; it does everything that reads only the (never rewritten) matrix first —
+// mbarrier setup, row pointers, the TMA requests for its first tiles — and blocks in pdl_wait() before it touches anything the
+// predecessor wrote (vectors, the device scalars, tickets).  Every loop kernel calls pdl_wait, so completion is transitive.
+// MGCG_PDL=0 launches everything fully serialised.
+bool pdl_enabled();
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <typename... P, typename... A>
+inline cudaError_t launch_k(bool pdl, void (*kernel)(P...), int grid, int block, size_t smem, cudaStream_t st, A... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)block); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = (pdl && pdl_enabled()) ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, P(args)...);
+}
+#endif
+
 // ---- helpers
 // Allocation for the hierarchy build (alloc.cu): a size-bucketed block cache — freed blocks are re-issued to the next
 // request of the same rounded size on the same stream, so a repeated build makes no driver allocation.
 cudaError_t pool_alloc(void **p, size_t bytes, cudaStream_t st);
 void pool_free(void *p, cudaStream_t st);
 void pool_release(void *p);          // block of pool_alloc -> cache; any other device pointer -> cudaFree
+void pool_reserve(size_t bytes);     // size of the next slab the block cache carves from
 void pool_trim_stream(int device, cudaStream_t st);
 void pool_trim(int device);          // give the cached blocks of a device (-1: all) back to the driver
 size_t pool_cached_bytes();

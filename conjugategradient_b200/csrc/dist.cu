@@ -536,6 +536,7 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
     D->peer.active = false;          // setup traffic goes over NCCL; the arena is kept for dist_open_transport to reuse
     dist_free_levels(D);
     set_alloc_stream(st);
+    pool_reserve((size_t)(2.6 * 12.0 * (double)local_nnz + 240.0 * (double)local_count) + ((size_t)96 << 20));
     tr.mark(-1, "d:free old");
     // ---- the partition: all-gather of the local row counts (ConjugateGradientParallelGpu.cs:271-277 is the caller's rule)
     int offs[kMaxRanks + 1];

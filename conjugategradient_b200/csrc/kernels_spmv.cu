@@ -106,6 +106,7 @@ template <int EPI>
 __global__ void __launch_bounds__(kSpmvThreads) k_spmv_stream(SpmvArgs a, int rows_per_tile, int num_tiles,
                                                               ReduceWs ws, Scalars *sc)
 {
+    pdl_wait(); pdl_launch_dependents();
     if (a.gated && sc->done) return;
     __shared__ double prod[kChunk];
     __shared__ int rp[kSpmvThreads + 1];
@@ -205,12 +206,11 @@ struct TmaMeta { int k0, k1, direct, pad; };
 // kTmaCap == 0: WIDE variant — the stage capacity is a launch parameter and the ring lives in dynamic shared memory (rows of
 // 8..32 entries: a 256-row tile is up to ~100 KB, one block per SM).  One thread per row keeps consecutive rows in consecutive
 // threads, so on stencil-like matrices (the 27-point operator of C5, the level-1 Galerkin operators) the k-th gathers of a warp fall
-// into one 256-byte run of x; the lanes-per-row ROWS kernel spreads a warp's gathers over L runs of 256/L bytes and measured 0.56
-// of the HBM peak on the 512^3 27-point shard against 0.96 for this layout on the 7-point operator.
+// into one 256-byte run of x (the lanes-per-row ROWS kernel spreads a warp's gathers over L runs of 256/L bytes).  Measured, it is
+// still behind ROWS there (0.60 against 0.74 of the HBM peak at 256^3): opt-in, see spmv_make_plan.
 template <int EPI, int kTmaCap, int kTmaStages>
 __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles, int dyn_cap, ReduceWs ws, Scalars *sc)
 {
-    if (a.gated && sc->done) return;
     constexpr bool kDyn = (kTmaCap == 0);
     __shared__ __align__(16) double s_val_st[kDyn ? 1 : kTmaStages][kDyn ? 2 : kTmaCap + 2];
     __shared__ __align__(16) int s_col_st[kDyn ? 1 : kTmaStages][kDyn ? 4 : kTmaCap + 4];
@@ -266,6 +266,13 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
     {
         const int r = blockIdx.x * kTmaRows + t;
         if (my_tiles > 0 && r < rows) { rs_n = rowptr[r]; re_n = rowptr[r + 1]; }
+    }
+    // Everything above read only the matrix, which nothing inside the loop writes: under programmatic dependent launch it overlaps the
+    // previous kernel's tail.  From here on the vectors and the device scalars of the predecessors are read.
+    pdl_wait(); pdl_launch_dependents();
+    if (a.gated && sc->done) {       // loop already over: let the requested slices land, then leave
+        if (t == 0) for (int j = 0; j < kTmaStages && j < my_tiles; ++j) mbar_wait(&s_full[j], 0u);
+        return;
     }
     bool wrote = false;
     halo_wait(a.gw, sc);      // the first tiles' matrix slices are already on their way
@@ -348,7 +355,6 @@ constexpr int kRowsThreads = 256;
 template <int EPI, int L, int kRowsUnroll>
 __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_tiles, int cap, int stages, ReduceWs ws, Scalars *sc)
 {
-    if (a.gated && sc->done) return;
     // cap is a multiple of 4: every stage's val slice (cap + 2 doubles) and col slice (cap + 4 ints) starts 16-byte aligned
     extern __shared__ __align__(16) unsigned char rows_smem[];
     double *s_val = reinterpret_cast<double *>(rows_smem);                                   // [stages][cap + 2]
@@ -398,6 +404,11 @@ __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_
     {
         const int r = blockIdx.x * R + g;
         if (my_tiles > 0 && r < rows) { rs_n = rowptr[r]; re_n = rowptr[r + 1]; }
+    }
+    pdl_wait(); pdl_launch_dependents();     // (see k_spmv_tma)
+    if (a.gated && sc->done) {
+        if (t == 0) for (int j = 0; j < stages && j < my_tiles; ++j) mbar_wait(&s_full[j], 0u);
+        return;
     }
     bool wrote = false;
     halo_wait(a.gw, sc);
@@ -473,6 +484,7 @@ __global__ void __launch_bounds__(kRowsThreads) k_spmv_rows(SpmvArgs a, int num_
 template <int EPI, int L>
 __global__ void __launch_bounds__(kSpmvThreads) k_spmv_vector(SpmvArgs a, ReduceWs ws, Scalars *sc)
 {
+    pdl_wait(); pdl_launch_dependents();
     if (a.gated && sc->done) return;
     const int lane = threadIdx.x & (L - 1);
     const int groups_per_block = kSpmvThreads / L;
@@ -514,8 +526,11 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel)
     if (cap > kMaxPartials) cap = kMaxPartials;
     // AUTO: rows short enough for a 256-row tile to fit a TMA stage -> STREAM (TMA); up to ~300 per row -> ROWS (TMA-staged,
     // L lanes per row); beyond -> VECTOR.  (MGCG_SPMV_NO_ROWS=1 restores the round-1 choice: STREAM up to 48 per row, else VECTOR.)
-    static const bool no_wide = getenv("MGCG_SPMV_NO_WIDE") != nullptr;
-    const bool wide_ok = !no_wide && avg > (double)(kTmaCap - 64) / kTmaRows && avg <= kTmaWideMaxAvg;
+    // WIDE is opt-in (MGCG_SPMV_WIDE=1): measured BEHIND the ROWS kernel on the 27-point operator (256^3: 3 849 against 4 773 GB/s,
+    // tools/spmv_27pt.py) — one resident block of 256 threads per SM keeps too few gathers in flight; it remains for callers that
+    // want the storage-order (bit-exact) row sums of the STREAM kernels on medium rows.
+    static const bool want_wide = getenv("MGCG_SPMV_WIDE") != nullptr && getenv("MGCG_SPMV_WIDE")[0] == '1';
+    const bool wide_ok = want_wide && avg > (double)(kTmaCap - 64) / kTmaRows && avg <= kTmaWideMaxAvg;
     if (kernel == MGCG_SPMV_AUTO) {
         static const bool no_rows = getenv("MGCG_SPMV_NO_ROWS") != nullptr;
         if (avg * kTmaRows <= kTmaCap - 64 || wide_ok) kernel = MGCG_SPMV_STREAM;
@@ -646,13 +661,13 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
             if (per_sm > 4) per_sm = 4;
             grid = c->sm_count * per_sm;
             if (grid > tiles) grid = tiles;
-            k_spmv_tma<EPI, 0, kTmaStagesLong><<<grid, kTmaRows, (size_t)plan.tma_wide_smem, c->stream>>>(a, tiles, plan.tma_wide_cap, c->ws, c->d_scalars);
+            launch_k(a.gated, k_spmv_tma<EPI, 0, kTmaStagesLong>, grid, kTmaRows, (size_t)plan.tma_wide_smem, c->stream, a, tiles, plan.tma_wide_cap, c->ws, c->d_scalars);
         }
-        else if (plan.tma_short) k_spmv_tma<EPI, kTmaCapShort, kTmaStagesShort><<<grid, kTmaRows, 0, c->stream>>>(a, tiles, 0, c->ws, c->d_scalars);
-        else k_spmv_tma<EPI, kTmaCap, kTmaStagesLong><<<grid, kTmaRows, 0, c->stream>>>(a, tiles, 0, c->ws, c->d_scalars);
+        else if (plan.tma_short) launch_k(a.gated, k_spmv_tma<EPI, kTmaCapShort, kTmaStagesShort>, grid, kTmaRows, 0, c->stream, a, tiles, 0, c->ws, c->d_scalars);
+        else launch_k(a.gated, k_spmv_tma<EPI, kTmaCap, kTmaStagesLong>, grid, kTmaRows, 0, c->stream, a, tiles, 0, c->ws, c->d_scalars);
     } else if (plan.kernel == MGCG_SPMV_STREAM) {
         int tiles = div_up(a.A.rows, plan.rows_per_tile);
-        k_spmv_stream<EPI><<<plan.grid, kSpmvThreads, 0, c->stream>>>(a, plan.rows_per_tile, tiles, c->ws, c->d_scalars);
+        launch_k(a.gated, k_spmv_stream<EPI>, plan.grid, kSpmvThreads, 0, c->stream, a, plan.rows_per_tile, tiles, c->ws, c->d_scalars);
     } else if (plan.kernel == MGCG_SPMV_ROWS && aligned) {
         MGCG_CHECK(rows_prepare<EPI>(c, plan));
         const int L = plan.lanes;
@@ -660,7 +675,7 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
         int grid = plan.grid;
         if (grid > tiles) grid = tiles;
 #define MGCG_ROWS_LAUNCH(LL, UU) \
-    k_spmv_rows<EPI, LL, UU><<<grid, kRowsThreads, (size_t)plan.rows_smem, c->stream>>>(a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars)
+    launch_k(a.gated, k_spmv_rows<EPI, LL, UU>, grid, kRowsThreads, (size_t)plan.rows_smem, c->stream, a, tiles, plan.rows_cap, plan.rows_stages, c->ws, c->d_scalars)
         const bool u8 = plan.rows_unroll >= 8;
         switch (L) {
         case 4: if (u8) MGCG_ROWS_LAUNCH(4, 8); else MGCG_ROWS_LAUNCH(4, 4); break;
@@ -671,10 +686,10 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
 #undef MGCG_ROWS_LAUNCH
     } else {
         switch (plan.lanes) {
-        case 4: k_spmv_vector<EPI, 4><<<plan.grid, kSpmvThreads, 0, c->stream>>>(a, c->ws, c->d_scalars); break;
-        case 8: k_spmv_vector<EPI, 8><<<plan.grid, kSpmvThreads, 0, c->stream>>>(a, c->ws, c->d_scalars); break;
-        case 16: k_spmv_vector<EPI, 16><<<plan.grid, kSpmvThreads, 0, c->stream>>>(a, c->ws, c->d_scalars); break;
-        default: k_spmv_vector<EPI, 32><<<plan.grid, kSpmvThreads, 0, c->stream>>>(a, c->ws, c->d_scalars); break;
+        case 4: launch_k(a.gated, k_spmv_vector<EPI, 4>, plan.grid, kSpmvThreads, 0, c->stream, a, c->ws, c->d_scalars); break;
+        case 8: launch_k(a.gated, k_spmv_vector<EPI, 8>, plan.grid, kSpmvThreads, 0, c->stream, a, c->ws, c->d_scalars); break;
+        case 16: launch_k(a.gated, k_spmv_vector<EPI, 16>, plan.grid, kSpmvThreads, 0, c->stream, a, c->ws, c->d_scalars); break;
+        default: launch_k(a.gated, k_spmv_vector<EPI, 32>, plan.grid, kSpmvThreads, 0, c->stream, a, c->ws, c->d_scalars); break;
         }
     }
     c->launches++;

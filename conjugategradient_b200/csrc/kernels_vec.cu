@@ -26,6 +26,7 @@ template <int V>
 __global__ void __launch_bounds__(kVecThreads) k_dot(int n, const double *__restrict__ a, const double *__restrict__ b,
                                                      ReduceWs ws, int fin, Scalars *sc, double *out, bool loop_gated)
 {
+    pdl_wait(); pdl_launch_dependents();
     if (loop_gated && sc->done) return;
     double s = 0.0, m = 0.0;
     const int stride = gridDim.x * blockDim.x;
@@ -60,9 +61,9 @@ int vec_dot(mgcg_ctx *c, int n, const double *a, const double *b, int fin, doubl
     int grid = vec_grid(c, n, 4);
     bool gated = (fin == FIN_PAP || fin == FIN_RR || fin == FIN_RR_PRECOND || fin == FIN_RZ);
     if (aligned16(a) && aligned16(b))
-        k_dot<2><<<grid, kVecThreads, 0, c->stream>>>(n, a, b, c->ws, fin, c->d_scalars, out, gated);
+        launch_k(gated, k_dot<2>, grid, kVecThreads, 0, c->stream, n, a, b, c->ws, fin, c->d_scalars, out, gated);
     else
-        k_dot<1><<<grid, kVecThreads, 0, c->stream>>>(n, a, b, c->ws, fin, c->d_scalars, out, gated);
+        launch_k(gated, k_dot<1>, grid, kVecThreads, 0, c->stream, n, a, b, c->ws, fin, c->d_scalars, out, gated);
     c->launches++;
     MGCG_LAUNCH_CHECK();
     return MGCG_OK;
@@ -163,6 +164,7 @@ __global__ void __launch_bounds__(kVecThreads) k_update_xr(int n, const double *
                                                            double *out, double *__restrict__ z0, const double *__restrict__ dinv,
                                                            double omega, Mirror mir)
 {
+    pdl_wait(); pdl_launch_dependents();
     if (!host_alpha && sc->done) return;
     bool wrote = false;
     const double alpha = host_alpha ? alpha_h : sc->alpha;
@@ -213,8 +215,8 @@ int cg_update_xr(mgcg_ctx *c, int n, const double *p, const double *Ap, double *
     const Mirror mm = (mir && z0) ? *mir : Mirror();
     int grid = vec_grid(c, n, 2);
     bool al = aligned16(p) && aligned16(Ap) && aligned16(x) && aligned16(r) && (!z0 || (aligned16(z0) && aligned16(dinv)));
-#define LAUNCH_(V, Z) k_update_xr<V, Z><<<grid, kVecThreads, 0, c->stream>>>(n, p, Ap, x, r, c->ws, fin, c->d_scalars, \
-                                                                             use_host_alpha, host_alpha, out, z0, dinv, omega, mm)
+#define LAUNCH_(V, Z) launch_k(!use_host_alpha, k_update_xr<V, Z>, grid, kVecThreads, 0, c->stream, n, p, Ap, x, r, c->ws, fin, c->d_scalars, \
+                               use_host_alpha, host_alpha, out, z0, dinv, omega, mm)
     if (al) { if (z0) LAUNCH_(2, true); else LAUNCH_(2, false); }
     else    { if (z0) LAUNCH_(1, true); else LAUNCH_(1, false); }
 #undef LAUNCH_
@@ -233,6 +235,7 @@ __global__ void __launch_bounds__(kVecThreads) k_cgcg_update(int n, const double
                                                              double *__restrict__ r, ReduceWs ws, Scalars *sc, double *out,
                                                              double *__restrict__ z0, const double *__restrict__ dinv, double omega, Mirror mir)
 {
+    pdl_wait(); pdl_launch_dependents();
     if (sc->done) return;
     bool wrote = false;
     const double alpha = sc->alpha, beta = sc->beta, nalpha = -alpha;
@@ -258,8 +261,8 @@ int cgcg_update(mgcg_ctx *c, int n, const double *u, const double *w, double *p,
 {
     const int grid = vec_grid(c, n, 2);
     const Mirror mm = (mir && z0) ? *mir : Mirror();
-    if (z0) k_cgcg_update<true><<<grid, kVecThreads, 0, c->stream>>>(n, u, w, p, s, x, r, c->ws, c->d_scalars, out, z0, dinv, omega, mm);
-    else k_cgcg_update<false><<<grid, kVecThreads, 0, c->stream>>>(n, u, w, p, s, x, r, c->ws, c->d_scalars, out, z0, dinv, omega, mm);
+    if (z0) launch_k(true, k_cgcg_update<true>, grid, kVecThreads, 0, c->stream, n, u, w, p, s, x, r, c->ws, c->d_scalars, out, z0, dinv, omega, mm);
+    else launch_k(true, k_cgcg_update<false>, grid, kVecThreads, 0, c->stream, n, u, w, p, s, x, r, c->ws, c->d_scalars, out, z0, dinv, omega, mm);
     c->launches++;
     MGCG_LAUNCH_CHECK();
     return MGCG_OK;
@@ -271,6 +274,7 @@ template <int V>
 __global__ void __launch_bounds__(kVecThreads) k_update_p(int n, const double *__restrict__ z, double *__restrict__ p,
                                                           Scalars *sc, bool host_beta, double beta_h, Mirror mir)
 {
+    pdl_wait(); pdl_launch_dependents();
     if (!host_beta && sc->done) return;
     bool wrote = false;
     const double beta = host_beta ? beta_h : sc->beta;
@@ -304,8 +308,8 @@ int cg_update_p(mgcg_ctx *c, int n, const double *z, double *p, bool use_host_be
 {
     int grid = vec_grid(c, n, 2);
     const Mirror mm = mir ? *mir : Mirror();
-    if (aligned16(z) && aligned16(p)) k_update_p<2><<<grid, kVecThreads, 0, c->stream>>>(n, z, p, c->d_scalars, use_host_beta, host_beta, mm);
-    else k_update_p<1><<<grid, kVecThreads, 0, c->stream>>>(n, z, p, c->d_scalars, use_host_beta, host_beta, mm);
+    if (aligned16(z) && aligned16(p)) launch_k(!use_host_beta, k_update_p<2>, grid, kVecThreads, 0, c->stream, n, z, p, c->d_scalars, use_host_beta, host_beta, mm);
+    else launch_k(!use_host_beta, k_update_p<1>, grid, kVecThreads, 0, c->stream, n, z, p, c->d_scalars, use_host_beta, host_beta, mm);
     c->launches++;
     MGCG_LAUNCH_CHECK();
     return MGCG_OK;
@@ -316,6 +320,7 @@ int cg_update_p(mgcg_ctx *c, int n, const double *z, double *p, bool use_host_be
 __global__ void __launch_bounds__(kVecThreads) k_jacobi_first(int n, double omega, const double *__restrict__ dinv,
                                                               const double *__restrict__ b, double *__restrict__ x, const Scalars *sc, Mirror mir)
 {
+    pdl_wait(); pdl_launch_dependents();
     if (sc->done) return;
     bool wrote = false;
     const int stride = gridDim.x * blockDim.x;
@@ -329,7 +334,7 @@ __global__ void __launch_bounds__(kVecThreads) k_jacobi_first(int n, double omeg
 
 int mg_jacobi_first(mgcg_ctx *c, int n, double omega, const double *dinv, const double *b, double *x, const Mirror *mir)
 {
-    k_jacobi_first<<<vec_grid(c, n, 2), kVecThreads, 0, c->stream>>>(n, omega, dinv, b, x, c->d_scalars, mir ? *mir : Mirror());
+    launch_k(true, k_jacobi_first, vec_grid(c, n, 2), kVecThreads, 0, c->stream, n, omega, dinv, b, x, (const Scalars *)c->d_scalars, mir ? *mir : Mirror());
     c->launches++;
     MGCG_LAUNCH_CHECK();
     return MGCG_OK;
@@ -339,6 +344,7 @@ int mg_jacobi_first(mgcg_ctx *c, int n, double omega, const double *dinv, const 
 __global__ void __launch_bounds__(256) k_dense_apply(int n, const double *__restrict__ Minv, const double *__restrict__ b,
                                                      double *__restrict__ y, const Scalars *sc)
 {
+    pdl_wait(); pdl_launch_dependents();
     if (sc->done) return;
     const int lane = threadIdx.x & 31;
     const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -353,7 +359,7 @@ __global__ void __launch_bounds__(256) k_dense_apply(int n, const double *__rest
 int mg_dense_apply(mgcg_ctx *c, int n, const double *Minv, const double *b, double *y)
 {
     int grid = div_up(n * 32, 256);
-    k_dense_apply<<<grid, 256, 0, c->stream>>>(n, Minv, b, y, c->d_scalars);
+    launch_k(true, k_dense_apply, grid, 256, 0, c->stream, n, Minv, b, y, (const Scalars *)c->d_scalars);
     c->launches++;
     MGCG_LAUNCH_CHECK();
     return MGCG_OK;

@@ -501,11 +501,14 @@ __global__ void __launch_bounds__(kWmWarps * 32) k_spgemm_wmerge(Csr A, Csr B, i
 // the lane that owns the entry's column adds the product — so c_ij is still summed in the storage order of the A row, product by
 // product, bit-identical to the merge kernels and the CPU twin, but the ordered sums of the row's 27 outputs advance in parallel
 // instead of one after the other (the warp-merge numeric pass spent ~85 % of its issue slots walking ballots: 7.8 ms at 256^3).
+constexpr int kOwnStage = 12;      // entries of a B row staged per lane: 8 warps x 32 rows x 12 x 12 B = 36 KB per block
 template <int SLOTS>
 __global__ void __launch_bounds__(kWmWarps * 32) k_spgemm_owner(Csr A, Csr B, int shift, const int *__restrict__ c_rowptr,
                                                                int *__restrict__ c_col, double *__restrict__ c_val)
 {
     constexpr unsigned kEnd = 0x7fffffffu;
+    __shared__ unsigned s_bcol[kWmWarps][32 * kOwnStage];
+    __shared__ double s_bval[kWmWarps][32 * kOwnStage];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int nwarps = gridDim.x * kWmWarps;
     for (int row = blockIdx.x * kWmWarps + w; row < A.rows; row += nwarps) {
@@ -539,9 +542,13 @@ __global__ void __launch_bounds__(kWmWarps * 32) k_spgemm_owner(Csr A, Csr B, in
                     if (hc[t] == cur) { ++q[t]; hc[t] = q[t] < qe[t] ? (unsigned)B.col[q[t]] : kEnd; }
             }
         }
-        // ---- phase 2: ordered accumulation by the owner lanes
+        // ---- phase 2: ordered accumulation by the owner lanes.  32 entries of the A row at a time: lane t first stages B row t
+        // (up to kOwnStage entries) in the warp's shared-memory slab — 32 rows fetched in parallel, instead of one L2 round trip
+        // per entry of the A row — then the warp walks the staged rows in order with broadcast reads.
         double sum = 0.0;
         bool have = false;
+        unsigned *scol = s_bcol[w];
+        double *sval = s_bval[w];
         for (int k0 = 0; k0 < m; k0 += 32) {
             const int kk = k0 + lane;
             int bq = 0, bqe = 0;
@@ -551,26 +558,30 @@ __global__ void __launch_bounds__(kWmWarps * 32) k_spgemm_owner(Csr A, Csr B, in
                 bq = B.rowptr[j]; bqe = B.rowptr[j + 1];
                 av = A.val[ks + kk];
             }
+            __syncwarp();                        // the previous chunk's readers are done with the slab
+            {
+                const int len = min(bqe - bq, kOwnStage);
+                for (int e = 0; e < len; ++e) { scol[lane * kOwnStage + e] = (unsigned)B.col[bq + e]; sval[lane * kOwnStage + e] = B.val[bq + e]; }
+            }
+            __syncwarp();
             const int cnt = min(32, m - k0);
             for (int t = 0; t < cnt; ++t) {
                 const int e0 = __shfl_sync(0xffffffffu, bq, t), e1 = __shfl_sync(0xffffffffu, bqe, t);
                 const double a = __shfl_sync(0xffffffffu, av, t);
-                for (int e = e0; e < e1; e += 4) {
-                    unsigned cc[4];
-                    double vv[4];
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const bool in = e + u < e1;
-                        cc[u] = in ? (unsigned)B.col[e + u] : kEnd;
-                        vv[u] = in ? B.val[e + u] : 0.0;
+                const int staged = min(e1 - e0, kOwnStage);
+                for (int e = 0; e < staged; ++e) {
+                    if (scol[t * kOwnStage + e] == mycol) {
+                        const double pr = __dmul_rn(a, sval[t * kOwnStage + e]);
+                        sum = have ? __dadd_rn(sum, pr) : pr;
+                        have = true;
                     }
-#pragma unroll
-                    for (int u = 0; u < 4; ++u)
-                        if (cc[u] == mycol && cc[u] != kEnd) {
-                            const double pr = __dmul_rn(a, vv[u]);
-                            sum = have ? __dadd_rn(sum, pr) : pr;
-                            have = true;
-                        }
+                }
+                for (int e = e0 + staged; e < e1; ++e) {       // rows longer than the stage: the rest from global memory
+                    if ((unsigned)B.col[e] == mycol) {
+                        const double pr = __dmul_rn(a, B.val[e]);
+                        sum = have ? __dadd_rn(sum, pr) : pr;
+                        have = true;
+                    }
                 }
             }
         }
