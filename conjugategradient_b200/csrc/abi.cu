@@ -22,7 +22,9 @@ const char *get_error() { return g_err; }
 
 bool pdl_enabled()
 {
-    static const bool on = [] { const char *e = getenv("MGCG_PDL"); return !(e && e[0] == '0'); }();
+    // opt-in: measured SLOWER inside the loop's WHILE graph (256^3: 34.0 against 28.6 ms, 128^3: 5.86 against 5.38 ms,
+    // profiles/r02_pdl_slab_owner.txt) — programmatic edges cost the graph ~7 us per kernel node, more than the overlapped prologue saves
+    static const bool on = [] { const char *e = getenv("MGCG_PDL"); return e && e[0] == '1'; }();
     return on;
 }
 

@@ -265,7 +265,7 @@ int graph_build_while(mgcg_ctx *c, int (*enqueue)(mgcg_ctx *, void *), void *arg
 // while its predecessor on the stream is still draining; it does everything that reads only the (never rewritten) matrix first —
 // mbarrier setup, row pointers, the TMA requests for its first tiles — and blocks in pdl_wait() before it touches anything the
 // predecessor wrote (vectors, the device scalars, tickets).  Every loop kernel calls pdl_wait, so completion is transitive.
-// MGCG_PDL=0 launches everything fully serialised.
+// Opt-in (MGCG_PDL=1): inside the WHILE graph the programmatic edges measured slower than plain kernel nodes (abi.cu pdl_enabled).
 bool pdl_enabled();
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
