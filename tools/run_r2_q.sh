@@ -4,7 +4,7 @@
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 nvidia-smi -L | wc -l; nproc
-timeout 900 python -m pytest tests/test_gpu_dist.py -m gpu -q --timeout 600 -p no:cacheprovider -rf -k "w4 or chebyshev or single_reduce" > gpurun_out/q_pytest_dist.log 2>&1; echo "pytest rc=$?"
+timeout 900 python -m pytest tests/test_gpu_dist.py -m gpu -q --timeout 600 -p no:cacheprovider -rf -k "w4 or 27pt_chebyshev" > gpurun_out/q_pytest_dist.log 2>&1; echo "pytest rc=$?"
 tail -n 12 gpurun_out/q_pytest_dist.log | cut -c 1-400
 summ() { python - "$1" <<'PY'
 import json,sys
@@ -16,15 +16,15 @@ try:
 except Exception as ex: print('   parse failed', ex)
 PY
 }
-timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu > gpurun_out/q_bench_c4_n1.json 2> gpurun_out/q_bench_c4_n1.err; echo "c4 n1 rc=$?"; summ gpurun_out/q_bench_c4_n1.json
-for n in 2 4 8; do
+timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu --no-e2e --no-parity > gpurun_out/q_bench_c4_n1.json 2> gpurun_out/q_bench_c4_n1.err; echo "c4 n1 rc=$?"; summ gpurun_out/q_bench_c4_n1.json
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port 29554 bench.py --gpus 4 --steps 5 --warmup 3 --no-e2e > gpurun_out/q_bench_c4_n4.json 2> gpurun_out/q_bench_c4_n4.err; echo "c4 n4 rc=$?"; summ gpurun_out/q_bench_c4_n4.json
+for n in 8; do
   timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2955$n bench.py --gpus $n --steps 5 --warmup 3 > gpurun_out/q_bench_c4_n$n.json 2> gpurun_out/q_bench_c4_n$n.err; echo "c4 n$n rc=$?"; summ gpurun_out/q_bench_c4_n$n.json
 done
 MGCG_DIST_FUSED=0 timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29561 bench.py --gpus 8 --steps 5 --warmup 3 --no-e2e --no-parity > gpurun_out/q_bench_c4_n8_unfused.json 2> gpurun_out/q_bench_c4_n8_unfused.err; echo "c4 n8 unfused rc=$?"; summ gpurun_out/q_bench_c4_n8_unfused.json
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29562 bench.py --gpus 8 --steps 5 --warmup 3 --no-e2e --no-parity --replicate-below 65536 > gpurun_out/q_bench_c4_n8_rb65k.json 2> gpurun_out/q_bench_c4_n8_rb65k.err; echo "c4 n8 rb65k rc=$?"; summ gpurun_out/q_bench_c4_n8_rb65k.json
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29563 bench.py --gpus 8 --steps 5 --warmup 3 --no-e2e --no-parity --opt mg_smoother=2 > gpurun_out/q_bench_c4_n8_cheby.json 2> gpurun_out/q_bench_c4_n8_cheby.err; echo "c4 n8 cheby rc=$?"; summ gpurun_out/q_bench_c4_n8_cheby.json
 MGCG_DIST_TRACE=1 timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29564 bench.py --gpus 8 --steps 2 --warmup 1 --no-e2e --no-parity > gpurun_out/q_trace_n8.json 2> gpurun_out/q_trace_n8.err; echo "trace rc=$?"
 grep -A 34 "dist trace" gpurun_out/q_trace_n8.err | tail -35
 timeout 500 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29565 bench.py --gpus 8 --config c5 --steps 3 --warmup 2 --no-e2e > gpurun_out/q_bench_c5_n8.json 2> gpurun_out/q_bench_c5_n8.err; echo "c5 n8 rc=$?"; summ gpurun_out/q_bench_c5_n8.json
 tail -n 2 gpurun_out/q_bench_c5_n8.err | cut -c 1-300
-timeout 500 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29566 bench.py --gpus 8 --size 512 --steps 3 --warmup 2 --no-e2e --no-parity > gpurun_out/q_bench_512_n8.json 2> gpurun_out/q_bench_512_n8.err; echo "512 n8 rc=$?"; summ gpurun_out/q_bench_512_n8.json
+timeout 500 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29566 bench.py --gpus 8 --size 512 --steps 2 --warmup 1 --no-e2e --no-parity > gpurun_out/q_bench_512_n8.json 2> gpurun_out/q_bench_512_n8.err; echo "512 n8 rc=$?"; summ gpurun_out/q_bench_512_n8.json
+timeout 300 python bench.py --size 512 --steps 2 --warmup 1 --no-cpu --no-e2e --no-parity > gpurun_out/q_bench_512_n1.json 2> gpurun_out/q_bench_512_n1.err; echo "512 n1 rc=$?"; summ gpurun_out/q_bench_512_n1.json
