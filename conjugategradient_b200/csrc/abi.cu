@@ -85,7 +85,7 @@ void mgcg_options_default(mgcg_options *o)
     o->min_strict = 0;
     o->precond = MGCG_PRECOND_NONE;
     o->mg_max_levels = 12;
-    o->mg_coarse_size = 512;
+    o->mg_coarse_size = 1400;         /* 11^3 = 1331 rows are still solved densely (blocked Gauss-Jordan inverse): one level fewer in the cycle than with 512 */
     o->mg_pre_sweeps = 1;
     o->mg_post_sweeps = 1;
     o->mg_omega = 0.85;   /* ~6/7, the optimal Jacobi damping of the 3-D 7-point stencil: one iteration fewer than 0.8 at 256^3 */

@@ -65,7 +65,7 @@ typedef struct mgcg_options {
     int    precond;          /* MGCG_PRECOND_* */
     int    nx, ny, nz;       /* optional structured-grid hint (0 = none): rows are idx = x + nx*(y + ny*z) */
     int    mg_max_levels;    /* default 12 */
-    int    mg_coarse_size;   /* stop coarsening at <= this many rows; dense inverse there (default 512) */
+    int    mg_coarse_size;   /* stop coarsening at <= this many rows; dense inverse there (default 1400) */
     int    mg_pre_sweeps;    /* default 1 */
     int    mg_post_sweeps;   /* default 1 (keep == pre for an SPD preconditioner) */
     double mg_omega;         /* Jacobi damping, default 0.85 */

@@ -190,7 +190,7 @@ def gen_banded_sin(n, max_nonzero=160):
 
 # ---- multigrid CPU twin (oracle/mg_ref.c; parity unpinned: the reference has no multigrid) ------------------
 class MgRef:
-    def __init__(self, val, rowptr, col, nx=0, ny=0, nz=0, max_levels=12, coarse_size=512, smoothed=1, prolong_omega=2.0 / 3.0,
+    def __init__(self, val, rowptr, col, nx=0, ny=0, nz=0, max_levels=12, coarse_size=1400, smoothed=1, prolong_omega=2.0 / 3.0,
                  smoothed_levels=0, agg_size=3, agg_size_coarse=2, aggregation=0, theta=0.5):
         L = lib()
         L.mg_ref_build.restype = C.c_void_p

@@ -410,3 +410,35 @@ def test_mgcg_single_reduce_matches_classic(oracle, gen, name):
     assert out[(1, 2)][0] == out[(1, 0)][0] and np.array_equal(out[(1, 2)][1], out[(1, 0)][1])
     assert abs(out[(1, 2)][0] - out[(0, 2)][0]) <= 1
     assert np.abs(out[(1, 2)][1] - out[(0, 2)][1]).max() / np.abs(out[(0, 2)][1]).max() <= 1e-9
+
+
+@pytest.mark.parametrize("dims,coarse", [((20, 17, 12), 300), ((24, 24, 24), 600), ((33, 33, 33), 1400)])
+def test_blocked_dense_inverse_bitwise(oracle, gen, monkeypatch, dims, coarse):
+    """The coarsest level's dense inverse by BLOCKED Gauss-Jordan (16 pivots per pair of launches) is bit-identical to the
+    one-launch-per-pivot elimination it replaces (and hence to the CPU twin's): same V-cycle output bit for bit, for coarsest levels
+    that are / are not multiples of the block (90, 216, 1331 rows)."""
+    import torch
+    from conjugategradient_b200 import solver as S
+    nx, ny, nz = dims
+    n = nx * ny * nz
+    v, rp, c = gen.poisson3d7(nx, ny, nz)
+    r = gen.rhs_uniform(n, 4)
+    out = []
+    for unblocked in (False, True):
+        if unblocked:
+            monkeypatch.setenv("MGCG_GJ_UNBLOCKED", "1")
+        else:
+            monkeypatch.delenv("MGCG_GJ_UNBLOCKED", raising=False)
+        m = _setup(S, torch, v, rp, c, nx=nx, ny=ny, nz=nz, mg_coarse_size=coarse)
+        sizes = [m.level(l)[1].shape[0] - 1 for l in range(m.levels())]
+        tz = torch.empty(n, dtype=torch.float64, device="cuda")
+        m.mg_apply(torch.as_tensor(r).cuda(), tz)
+        out.append((sizes, tz.cpu().numpy()))
+        m.close()
+    assert out[0][0] == out[1][0] and out[0][0][-1] <= coarse
+    assert np.array_equal(out[0][1], out[1][1])
+    if n <= 20000:
+        H = oracle.MgRef(v, rp, c, nx, ny, nz, coarse_size=coarse)
+        zt = H.apply(r, 1, 1, 0.85)
+        assert np.abs(out[0][1] - zt).max() <= 1e-13 * np.abs(zt).max()
+        H.close()
