@@ -478,16 +478,23 @@ def run_ours_single(args):
     s1.record()
     torch.cuda.synchronize()
     spmv_iso_ms = s0.elapsed_time(s1) / reps
-    spmv_bytes = 12.0 * nnz + 20.0 * n
+    kname = pres.reserved[5]
+    coded = (kname == 4)        # coded columns (csrc/spmv_code.cu, --opt spmv_coding=1): 8 + 1 instead of 8 + 4 bytes per entry
+    csr_bytes = 12.0 * nnz + 20.0 * n
+    spmv_bytes = (9.0 if coded else 12.0) * nnz + 20.0 * n
     peak, peak_how = measured_peak()
     achieved = spmv_bytes / (spmv_ms * 1e-3) / 1e9
-    kname = pres.reserved[5]
     kernel_text = {1: "k_spmv_tma<EPI_DOT> (fine-level A*p with fused p.Ap, TMA-staged stream kernel)",
+                   4: "k_spmv_tma<EPI_DOT, coded> (fine-level A*p with fused p.Ap, TMA-staged stream kernel on coded columns: "
+                      "9 B per entry instead of CSR's 12)",
                    2: "k_spmv_vector<EPI_DOT> (fine-level A*p with fused p.Ap, lanes-per-row kernel)",
                    3: "k_spmv_rowblock<EPI_DOT> (fine-level A*p with fused p.Ap, TMA-staged long-row kernel)",
                    0: "k_spmv_stream<EPI_DOT>"}.get(kname, "fine-level SpMV + p.Ap")
-    traffic, traffic_src = ncu_traffic("k_spmv_tma<2", args)
+    traffic, traffic_src = (None, None) if coded else ncu_traffic("k_spmv_tma<2", args)
     roofline = {"bound": "hbm", "kernel": kernel_text, "achieved": achieved,
+                "layout": "coded columns (1 B) + fp64 values" if coded else "CSR (int32 columns + fp64 values)",
+                "bytes_rule": ("9 nnz + 20 N (the layout the kernel reads)" if coded else "12 nnz + 20 N (SURVEY 8d)"),
+                "csr_bytes_per_launch": csr_bytes, "csr_equivalent_gbs": csr_bytes / (spmv_ms * 1e-3) / 1e9,
                 "peak": peak, "unit": "GB/s", "frac": achieved / peak, "frac_of_8TBs_nominal": achieved / 8000.0,
                 "traffic": traffic,
                 "traffic_source": f"dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full ({traffic_src})" if traffic else None,
@@ -658,7 +665,9 @@ def run_ours_dist(args):
     s1.record()
     torch.cuda.synchronize()
     spmv_ms = s0.elapsed_time(s1) / reps
-    spmv_bytes = 12.0 * nnz_local + 20.0 * (r1 - r0)
+    ndict = C.c_int(0)
+    L.mgcg_matrix_codes(m.ctx, C.byref(ndict), None, None)
+    spmv_bytes = (9.0 if ndict.value > 0 else 12.0) * nnz_local + 20.0 * (r1 - r0)
     peak, peak_how = measured_peak()
     achieved = spmv_bytes / (spmv_ms * 1e-3) / 1e9
     del tp, ty

@@ -18,6 +18,7 @@ TRANSPORT_AUTO, TRANSPORT_NCCL, TRANSPORT_PEER = 0, 1, 2
 AGG_AUTO, AGG_BLOCKS, AGG_MIS2 = 0, 1, 2
 SMOOTHER_JACOBI, SMOOTHER_RBGS, SMOOTHER_CHEBYSHEV = 0, 1, 2
 CG_CLASSIC, CG_SINGLE_REDUCE = 0, 1
+CODING_OFF, CODING_ON = 0, 1
 
 
 class Options(C.Structure):
@@ -30,7 +31,7 @@ class Options(C.Structure):
         ("mg_smoothed_levels", C.c_int), ("mg_aggregate_size", C.c_int), ("mg_aggregate_size_coarse", C.c_int),
         ("dist_replicate_below", C.c_int), ("dist_transport", C.c_int), ("mg_tail_rows", C.c_int), ("mg_aggregation", C.c_int),
         ("mg_cheby_degree", C.c_int), ("mg_strength_theta", C.c_double), ("mg_cheby_ratio", C.c_double), ("cg_variant", C.c_int),
-        ("reserved", C.c_int * 3),
+        ("spmv_coding", C.c_int), ("reserved", C.c_int * 2),
     ]
 
 
@@ -51,7 +52,7 @@ NATIVE_SYMBOLS = [
     "mgcg_mg_level_get", "mgcg_mg_level_aggregates", "mgcg_mg_apply", "mgcg_partition_offsets",
     "mgcg_comm_unique_id", "mgcg_comm_init", "mgcg_setup_dist", "mgcg_solve_dist", "mgcg_solve_host_dist", "mgcg_comm_finalize", "mgcg_dist_microbench",
     "mgcg_generate_poisson3d7_nnz", "mgcg_generate_poisson3d7", "mgcg_generate_poisson3d27_nnz", "mgcg_generate_poisson3d27",
-    "mgcg_mps_order", "mgcg_mps_count", "mgcg_mps_fill", "mgcg_test_scan_counts",
+    "mgcg_mps_order", "mgcg_mps_count", "mgcg_mps_fill", "mgcg_test_scan_counts", "mgcg_matrix_codes",
 ]
 # every symbol include/mgcg_formats.h declares (ELL input, Write/Solve/Read/Iteration object)
 FORMAT_SYMBOLS = [
@@ -100,6 +101,7 @@ def lib():
     L.mgcg_solve.argtypes = [vp, vp, vp, C.POINTER(Result)]
     L.mgcg_solve_host.argtypes = [vp, ci, ci, vp, vp, vp, vp, vp, C.POINTER(Options), C.POINTER(Result)]
     L.mgcg_spmv.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, vp, cd, cd, ci]
+    L.mgcg_matrix_codes.argtypes = [vp, C.POINTER(ci), vp, vp]
     L.mgcg_spmv_dot.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, vp, vp, vp, ci]
     L.mgcg_dot.argtypes = [vp, ci, vp, vp, vp, dp]
     L.mgcg_max_abs.argtypes = [vp, ci, vp, vp, dp]

@@ -151,6 +151,7 @@ void mgcg_destroy(mgcg_ctx *c)
     if (c->stream) cudaStreamSynchronize(c->stream);
     dist_free(c);
     mg_free(c);
+    spmv_code_free(c);
     if (!c->child) pool_trim_stream(c->device, c->stream);
     if (c->graph_exec) cudaGraphExecDestroy(c->graph_exec);
     if (c->graph) cudaGraphDestroy(c->graph);
@@ -209,7 +210,8 @@ int mgcg_setup(mgcg_ctx *c, int count, int elements_count,
         cudaEvent_t e0, e1;
         MGCG_CUDA(cudaEventCreate(&e0)); MGCG_CUDA(cudaEventCreate(&e1));
         MGCG_CUDA(cudaEventRecord(e0, c->stream));
-        int s = mg_build(c);
+        int s = spmv_code_build(c, &c->A, c->planA);       // coded columns of the fine operator (opt-in; timed with the set-up)
+        if (s == MGCG_OK) s = mg_build(c);
         if (s != MGCG_OK) { mg_free(c); cudaEventDestroy(e0); cudaEventDestroy(e1); return s; }
         MGCG_CUDA(cudaEventRecord(e1, c->stream));
         MGCG_CUDA(cudaEventSynchronize(e1));
@@ -217,6 +219,7 @@ int mgcg_setup(mgcg_ctx *c, int count, int elements_count,
         cudaEventDestroy(e0); cudaEventDestroy(e1);
     } else {
         mg_free(c);
+        MGCG_CHECK(spmv_code_build(c, &c->A, c->planA));
     }
     c->is_setup = true;
     return MGCG_OK;
@@ -300,6 +303,26 @@ static int fetch_scalar(mgcg_ctx *c, const double *d, double *host_out)
     return MGCG_OK;
 }
 
+// the arrays of the matrix the context was set up with (then the launch may use what the set-up derived from them)
+static bool same_as_setup(const mgcg_ctx *c, const Csr &A)
+{
+    return c->is_setup && A.rows == c->A.rows && A.cols == c->A.cols && A.nnz == c->A.nnz &&
+           A.val == c->A.val && A.rowptr == c->A.rowptr && A.col == c->A.col;
+}
+
+int mgcg_matrix_codes(mgcg_ctx *c, int *ndict, int *dict, unsigned char *codes)
+{
+    if (!c || !c->is_setup) { set_error("mgcg_matrix_codes: context not set up"); return MGCG_ERR_INVALID; }
+    MGCG_CUDA(cudaSetDevice(c->device));
+    const bool coded = c->A.code && c->A.dict;
+    if (ndict) *ndict = coded ? c->code_ndict : 0;
+    if (!coded) return MGCG_OK;
+    MGCG_CUDA(cudaStreamSynchronize(c->stream));
+    if (dict) MGCG_CUDA(cudaMemcpy(dict, c->A.dict, sizeof(int) * 256, cudaMemcpyDeviceToHost));
+    if (codes) MGCG_CUDA(cudaMemcpy(codes, c->A.code, (size_t)c->A.nnz, cudaMemcpyDeviceToHost));
+    return MGCG_OK;
+}
+
 int mgcg_spmv(mgcg_ctx *c, int rows, int cols, int elements_count,
               const double *d_elements, const int *d_row_offsets, const int *d_column_indeces,
               const double *d_x, double *d_y, double alpha, double beta, int kernel)
@@ -310,6 +333,7 @@ int mgcg_spmv(mgcg_ctx *c, int rows, int cols, int elements_count,
     a.A.rows = rows; a.A.cols = cols; a.A.nnz = elements_count; a.A.val = d_elements; a.A.rowptr = d_row_offsets; a.A.col = d_column_indeces;
     a.x = d_x; a.y = d_y; a.alpha = alpha; a.beta = beta;
     SpmvPlan p = spmv_make_plan(c, rows, elements_count, kernel);
+    if (same_as_setup(c, a.A) && kernel == c->opt.spmv_kernel) { a.A = c->A; p = c->planA; }   // the set-up matrix: its coded columns
     const bool plain = (alpha == 1.0 && beta == 0.0);
     return spmv_launch(c, p, plain ? EPI_PLAIN : EPI_AXPBY, a);
 }
@@ -324,6 +348,7 @@ int mgcg_spmv_dot(mgcg_ctx *c, int rows, int cols, int elements_count,
     a.A.rows = rows; a.A.cols = cols; a.A.nnz = elements_count; a.A.val = d_elements; a.A.rowptr = d_row_offsets; a.A.col = d_column_indeces;
     a.x = d_x; a.y = d_y; a.w = d_w; a.fin = FIN_STORE; a.out = d_dot;
     SpmvPlan p = spmv_make_plan(c, rows, elements_count, kernel);
+    if (same_as_setup(c, a.A) && kernel == c->opt.spmv_kernel) { a.A = c->A; p = c->planA; }
     return spmv_launch(c, p, EPI_DOT, a);
 }
 

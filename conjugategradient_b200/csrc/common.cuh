@@ -90,6 +90,9 @@ struct Csr {
     const double *val = nullptr;
     const int *rowptr = nullptr;
     const int *col = nullptr;
+    // coded columns (spmv_code.cu), optional: col[k] == row + dict[code[k]]; kernels that cannot read them use `col`
+    const unsigned char *code = nullptr;
+    const int *dict = nullptr;       // 256 ints
 };
 
 // SpMV plan: kernel choice and launch geometry for one matrix
@@ -207,6 +210,11 @@ struct mgcg_ctx {
     void *host_path = nullptr;
     void *ell_path = nullptr;        // device system owned by mgcg_solve_host_ell (formats.cu)
     void *host_path_dist = nullptr;  // device copies owned by mgcg_solve_host_dist (dist.cu)
+    // coded columns of the fine-level operator (spmv_code.cu)
+    unsigned char *code_buf = nullptr;
+    void *code_state = nullptr;
+    size_t code_cap = 0;
+    int code_ndict = 0;
 };
 
 namespace mgcg {
@@ -239,6 +247,11 @@ int mg_dense_apply(mgcg_ctx *c, int n, const double *Minv, const double *b, doub
 SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel);
 int spmv_launch(mgcg_ctx *c, const SpmvPlan &plan, int epi, const SpmvArgs &a);
 int spmv_kernel_id(const SpmvPlan &plan, const Csr &A);
+bool spmv_plan_reads_code(const SpmvPlan &plan);   // the kernel this plan selects understands coded columns
+
+// ---- spmv_code.cu
+int spmv_code_build(mgcg_ctx *c, Csr *A, const SpmvPlan &plan);
+void spmv_code_free(mgcg_ctx *c);
 
 // ---- mg_setup.cu / mg_cycle.cu
 int mg_build(mgcg_ctx *c);

@@ -208,16 +208,25 @@ struct TmaMeta { int k0, k1, direct, pad; };
 // threads, so on stencil-like matrices (the 27-point operator of C5, the level-1 Galerkin operators) the k-th gathers of a warp fall
 // into one 256-byte run of x (the lanes-per-row ROWS kernel spreads a warp's gathers over L runs of 256/L bytes).  Measured, it is
 // still behind ROWS there (0.60 against 0.74 of the HBM peak at 256^3): opt-in, see spmv_make_plan.
-template <int EPI, int kTmaCap, int kTmaStages>
+// kCoded: the matrix carries coded columns (spmv_code.cu) — a stage holds one BYTE per entry instead of an int32 column, and
+// col = row + dict[code] is rebuilt from a 256-entry table in shared memory: 9 instead of 12 bytes per entry cross HBM, the entries,
+// their order and the x operands are the same, so are the bits of every row sum.  The coded instantiations use the dynamic ring
+// (kTmaCap == 0) so that it can hold more stages than the 48 KB of static shared memory allow.
+template <int EPI, int kTmaCap, int kTmaStages, bool kCoded>
 __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles, int dyn_cap, ReduceWs ws, Scalars *sc)
 {
     constexpr bool kDyn = (kTmaCap == 0);
+    static_assert(kDyn || !kCoded, "coded columns use the dynamic ring");
+    constexpr int kIdxBytes = kCoded ? 1 : 4;            // bytes of a staged column entry
+    constexpr int kIdxPad = 16 / kIdxBytes;              // slack entries: a slice starts at a 16-byte boundary of its array
     __shared__ __align__(16) double s_val_st[kDyn ? 1 : kTmaStages][kDyn ? 2 : kTmaCap + 2];
-    __shared__ __align__(16) int s_col_st[kDyn ? 1 : kTmaStages][kDyn ? 4 : kTmaCap + 4];
+    __shared__ __align__(16) unsigned char s_idx_st[kDyn ? 16 : kTmaStages * (kTmaCap + kIdxPad) * kIdxBytes];
+    __shared__ int s_dict[kCoded ? 256 : 1];
     extern __shared__ __align__(16) unsigned char tma_dyn[];
-    const int cap = kDyn ? dyn_cap : kTmaCap;                 // multiple of 4: every stage starts 16-byte aligned
+    const int cap = kDyn ? dyn_cap : kTmaCap;                 // multiple of 4 (16 when coded): every stage starts 16-byte aligned
     double *const s_val_b = kDyn ? reinterpret_cast<double *>(tma_dyn) : &s_val_st[0][0];                                   // [stages][cap + 2]
-    int *const s_col_b = kDyn ? reinterpret_cast<int *>(tma_dyn + (size_t)kTmaStages * (cap + 2) * 8) : &s_col_st[0][0];    // [stages][cap + 4]
+    unsigned char *const s_idx_b = kDyn ? tma_dyn + (size_t)kTmaStages * (cap + 2) * 8 : &s_idx_st[0];                      // [stages][cap + pad]
+    const size_t idx_stride = (size_t)(cap + kIdxPad) * kIdxBytes;
     __shared__ __align__(8) unsigned long long s_full[kTmaStages], s_empty[kTmaStages];
     __shared__ TmaMeta s_meta[kTmaStages];
     const int t = threadIdx.x;
@@ -225,6 +234,7 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
     const int *__restrict__ col = a.A.col;
     const int *__restrict__ rowptr = a.A.rowptr;
     const double *__restrict__ x = a.x;
+    const unsigned char *__restrict__ code = a.A.code;
     const int rows = a.A.rows;
     const long long nnz_end = (long long)a.A.nnz;     // entries val/col are known to hold (sub-block views pass the parent's)
     double dsum = 0.0;
@@ -233,6 +243,7 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
         for (int s = 0; s < kTmaStages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], kTmaRows); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    if (kCoded) s_dict[t] = a.A.dict[t];              // kTmaRows == 256 threads
     __syncthreads();
 
     // the block's tiles: blockIdx.x, blockIdx.x + gridDim.x, ...
@@ -245,15 +256,17 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
         const int r0 = tile * kTmaRows;
         const int nr = min(kTmaRows, rows - r0);
         const int k0 = rowptr[r0], k1 = rowptr[r0 + nr];
-        const int ka = k0 & ~1, kc = k0 & ~3;
-        const unsigned vb = (unsigned)(((k1 - ka) * 8 + 15) & ~15), cb = (unsigned)(((k1 - kc) * 4 + 15) & ~15);
+        const int ka = k0 & ~1, kc = k0 & ~(kIdxPad - 1);
+        const unsigned vb = (unsigned)(((k1 - ka) * 8 + 15) & ~15), cb = (unsigned)(((k1 - kc) * kIdxBytes + 15) & ~15);
+        // (the code array is allocated in whole 16-byte pieces with one to spare: its slices never run out of it)
         const bool fits = (k1 - ka) <= cap && (k1 - kc) <= cap && k1 > k0 &&
-                          ((long long)ka * 8 + vb <= nnz_end * 8) && ((long long)kc * 4 + cb <= nnz_end * 4);
+                          ((long long)ka * 8 + vb <= nnz_end * 8) && (kCoded || (long long)kc * 4 + cb <= nnz_end * 4);
         s_meta[s].k0 = k0; s_meta[s].k1 = k1; s_meta[s].direct = fits ? 0 : 1;
         if (fits) {
             mbar_arrive_expect_tx(&s_full[s], vb + cb);
             tma_load_1d(s_val_b + (size_t)s * (cap + 2), val + ka, vb, &s_full[s]);
-            tma_load_1d(s_col_b + (size_t)s * (cap + 4), col + kc, cb, &s_full[s]);
+            if (kCoded) tma_load_1d(s_idx_b + s * idx_stride, code + kc, cb, &s_full[s]);
+            else tma_load_1d(s_idx_b + s * idx_stride, col + kc, cb, &s_full[s]);
         } else {
             mbar_arrive(&s_full[s]);
         }
@@ -297,8 +310,11 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
             if (!s_meta[s].direct) {
                 const int k0 = s_meta[s].k0;
                 const double *sv = s_val_b + (size_t)s * (cap + 2) - (k0 & ~1);
-                const int *scl = s_col_b + (size_t)s * (cap + 4) - (k0 & ~3);
-                if (kDyn) {
+                const int *scl = reinterpret_cast<const int *>(s_idx_b + s * idx_stride) - (k0 & ~3);
+                if (kCoded) {
+                    const unsigned char *scd = s_idx_b + s * idx_stride - (k0 & ~15);
+                    for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(sv[k], x[row + s_dict[scd[k]]]));
+                } else if (kDyn) {
                     // medium rows: the gathers of four entries are issued together; the sum keeps the storage order
                     int k = rs;
                     for (; k + 4 <= re; k += 4) {
@@ -313,6 +329,8 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
                 } else {
                     for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(sv[k], x[scl[k]]));
                 }
+            } else if (kCoded) {
+                for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(__ldcs(val + k), x[row + s_dict[__ldcs(code + k)]]));
             } else {
                 for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(__ldcs(val + k), x[__ldcs(col + k)]));
             }
@@ -636,6 +654,38 @@ static int rows_prepare(mgcg_ctx *c, const SpmvPlan &plan)
     }
 }
 
+// Coded columns: the ring lives in dynamic shared memory so that it can be deeper than the int32 kernel's.  A stage is 9 instead of
+// 12 bytes per entry; with the int32 kernel's two stages and four resident blocks per SM too few bytes were in flight per SM to
+// cover the HBM latency (0.303 ms per fine-level product inside a 256^3 solve against 0.273 ms on int32 columns); three stages x four
+// blocks: 0.281 ms.  Stages and resident blocks are tuning knobs (MGCG_CODED_STAGES 2..4, MGCG_CODED_CTAS).
+template <int EPI, int STAGES>
+static int launch_coded_one(mgcg_ctx *c, const SpmvArgs &a, int tiles, int ctas)
+{
+    static bool set[64] = {false};
+    const int smem = STAGES * ((kTmaCap + 2) * 8 + (kTmaCap + 16));
+    const int d = c->device & 63;
+    if (!set[d]) {
+        MGCG_CUDA(cudaFuncSetAttribute(k_spmv_tma<EPI, 0, STAGES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        set[d] = true;
+    }
+    int grid = c->sm_count * ctas;
+    if (grid > tiles) grid = tiles;
+    launch_k(a.gated, k_spmv_tma<EPI, 0, STAGES, true>, grid, kTmaRows, (size_t)smem, c->stream, a, tiles, kTmaCap, c->ws, c->d_scalars);
+    return MGCG_OK;
+}
+template <int EPI>
+static int launch_coded(mgcg_ctx *c, const SpmvArgs &a, int tiles)
+{
+    static const int stages = [] { const char *e = getenv("MGCG_CODED_STAGES"); const int v = e ? atoi(e) : 0; return (v >= 2 && v <= 4) ? v : 3; }();
+    static const int ctas_env = [] { const char *e = getenv("MGCG_CODED_CTAS"); const int v = e ? atoi(e) : 0; return (v >= 1 && v <= 8) ? v : 0; }();
+    const int fit = (224 * 1024) / (stages * ((kTmaCap + 2) * 8 + (kTmaCap + 16)) + 3 * 1024);
+    int ctas = ctas_env > 0 ? ctas_env : fit;
+    if (ctas > 6) ctas = 6;
+    if (stages == 2) return launch_coded_one<EPI, 2>(c, a, tiles, ctas);
+    if (stages == 3) return launch_coded_one<EPI, 3>(c, a, tiles, ctas);
+    return launch_coded_one<EPI, 4>(c, a, tiles, ctas);
+}
+
 template <int EPI>
 static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
 {
@@ -647,13 +697,19 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
     const bool aligned = ((((uintptr_t)a.A.val) | ((uintptr_t)a.A.col)) & 15u) == 0;
     if (plan.kernel == MGCG_SPMV_STREAM && plan.tma && aligned) {
         const int tiles = div_up(a.A.rows, kTmaRows);
+        if (a.A.code && a.A.dict && spmv_plan_reads_code(plan)) {
+            MGCG_CHECK(launch_coded<EPI>(c, a, tiles));
+            c->launches++;
+            MGCG_LAUNCH_CHECK();
+            return MGCG_OK;
+        }
         int grid = c->sm_count * 4;
         if (grid > tiles) grid = tiles;
         if (plan.tma_wide_cap > 0) {
             static int set_bytes[64] = {0};
             const int d = c->device & 63;
             if (plan.tma_wide_smem > set_bytes[d]) {
-                MGCG_CUDA(cudaFuncSetAttribute(k_spmv_tma<EPI, 0, kTmaStagesLong>, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.tma_wide_smem));
+                MGCG_CUDA(cudaFuncSetAttribute(k_spmv_tma<EPI, 0, kTmaStagesLong, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.tma_wide_smem));
                 set_bytes[d] = plan.tma_wide_smem;
             }
             int per_sm = (int)((224 * 1024) / (plan.tma_wide_smem + 2048));
@@ -661,10 +717,10 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
             if (per_sm > 4) per_sm = 4;
             grid = c->sm_count * per_sm;
             if (grid > tiles) grid = tiles;
-            launch_k(a.gated, k_spmv_tma<EPI, 0, kTmaStagesLong>, grid, kTmaRows, (size_t)plan.tma_wide_smem, c->stream, a, tiles, plan.tma_wide_cap, c->ws, c->d_scalars);
+            launch_k(a.gated, k_spmv_tma<EPI, 0, kTmaStagesLong, false>, grid, kTmaRows, (size_t)plan.tma_wide_smem, c->stream, a, tiles, plan.tma_wide_cap, c->ws, c->d_scalars);
         }
-        else if (plan.tma_short) launch_k(a.gated, k_spmv_tma<EPI, kTmaCapShort, kTmaStagesShort>, grid, kTmaRows, 0, c->stream, a, tiles, 0, c->ws, c->d_scalars);
-        else launch_k(a.gated, k_spmv_tma<EPI, kTmaCap, kTmaStagesLong>, grid, kTmaRows, 0, c->stream, a, tiles, 0, c->ws, c->d_scalars);
+        else if (plan.tma_short) launch_k(a.gated, k_spmv_tma<EPI, kTmaCapShort, kTmaStagesShort, false>, grid, kTmaRows, 0, c->stream, a, tiles, 0, c->ws, c->d_scalars);
+        else launch_k(a.gated, k_spmv_tma<EPI, kTmaCap, kTmaStagesLong, false>, grid, kTmaRows, 0, c->stream, a, tiles, 0, c->ws, c->d_scalars);
     } else if (plan.kernel == MGCG_SPMV_STREAM) {
         int tiles = div_up(a.A.rows, plan.rows_per_tile);
         launch_k(a.gated, k_spmv_stream<EPI>, plan.grid, kSpmvThreads, 0, c->stream, a, plan.rows_per_tile, tiles, c->ws, c->d_scalars);
@@ -697,10 +753,17 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
     return MGCG_OK;
 }
 
-// which kernel family spmv_launch picks for this plan / matrix: 0 stream, 1 TMA-staged stream, 2 lanes-per-row vector, 3 TMA-staged rows
+bool spmv_plan_reads_code(const SpmvPlan &plan)
+{
+    return plan.kernel == MGCG_SPMV_STREAM && plan.tma && !plan.tma_short && plan.tma_wide_cap == 0;
+}
+
+// which kernel family spmv_launch picks for this plan / matrix: 0 stream, 1 TMA-staged stream, 2 lanes-per-row vector, 3 TMA-staged rows,
+// 4 TMA-staged stream on coded columns
 int spmv_kernel_id(const SpmvPlan &plan, const Csr &A)
 {
     const bool aligned = ((((uintptr_t)A.val) | ((uintptr_t)A.col)) & 15u) == 0;
+    if (aligned && A.code && A.dict && spmv_plan_reads_code(plan)) return 4;
     if (plan.kernel == MGCG_SPMV_STREAM) return (plan.tma && aligned) ? 1 : 0;
     if (plan.kernel == MGCG_SPMV_ROWS && aligned) return 3;
     return 2;

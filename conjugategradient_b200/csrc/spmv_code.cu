@@ -1,0 +1,174 @@
+// spmv_code.cu — coded column indices: an internal layout behind the unchanged CSR interface (north_star subsystem 1: "an
+// optional ... internal layout behind the unchanged CSR API"; the reference hands cusparseDcsrmv plain int32 column indices,
+// Mgcg.cu:10-19).  Opt-in (mgcg_options.spmv_coding = MGCG_CODING_ON).
+//
+// On a stencil matrix the DISTANCE col - row of an entry takes only a handful of values (7 for the 7-point operator, 27 for the
+// 27-point one, whatever the grid size; a row-block shard adds a constant).  When a matrix has at most 256 distinct distances,
+// its int32 column array (4 B per entry) is restated as one byte per entry — the rank of the entry's distance in the SORTED list
+// of distinct distances — plus that list (<= 1 KB).  The SpMV kernel that understands the code (kernels_spmv.cu, k_spmv_tma with
+// kCoded) stages 9 instead of 12 bytes per entry and rebuilds col = row + dict[code]: the same entries in the same storage order
+// with the same x operands, so every row sum keeps its bits.  The CSR arrays the caller gave are not touched and stay the
+// operands of everything else (hierarchy build, the uncoded kernels).
+//
+// Build: one pass collects the distinct distances (block-local hash set in shared memory, merged into a global one), one block
+// sorts them, one pass writes the codes.  A matrix with more than 256 distinct distances (particle systems, aggregation
+// operators) is simply left uncoded.
+#include "common.cuh"
+#include <limits.h>
+#include <stdlib.h>
+
+namespace mgcg {
+
+constexpr int kCodeSlots = 1024;        // open-addressing slots of the distance sets (power of two, 4x the 256 codes)
+constexpr int kCodeMax = 256;
+constexpr int kCodeEmpty = INT_MIN;
+constexpr int kCodeThreads = 256;
+
+struct CodeState {
+    int keys[kCodeSlots];
+    int count, overflow;
+    int dict[kCodeMax];
+    int ndict, pad;
+};
+
+__device__ __forceinline__ unsigned code_hash(int d) { return ((unsigned)d * 2654435761u) >> 22; }   // 10 bits
+
+// insert d into an open-addressing set; *count counts distinct keys; *overflow is raised beyond kCodeMax keys
+__device__ __forceinline__ void code_insert(int *keys, int *count, int *overflow, int d)
+{
+    unsigned h = code_hash(d);
+    for (int probe = 0; probe < kCodeSlots; ++probe) {
+        const int cur = *(volatile int *)&keys[h];
+        if (cur == d) return;
+        if (cur == kCodeEmpty) {
+            const int old = atomicCAS(&keys[h], kCodeEmpty, d);
+            if (old == kCodeEmpty) {
+                if (atomicAdd(count, 1) >= kCodeMax) *(volatile int *)overflow = 1;
+                return;
+            }
+            if (old == d) return;
+        }
+        h = (h + 1) & (kCodeSlots - 1);
+    }
+    *(volatile int *)overflow = 1;
+}
+
+__global__ void __launch_bounds__(kCodeThreads) k_code_clear(CodeState *st)
+{
+    for (int i = threadIdx.x; i < kCodeSlots; i += kCodeThreads) st->keys[i] = kCodeEmpty;
+    if (threadIdx.x < kCodeMax) st->dict[threadIdx.x] = 0;
+    if (threadIdx.x == 0) { st->count = 0; st->overflow = 0; st->ndict = 0; }
+}
+
+__global__ void __launch_bounds__(kCodeThreads) k_code_collect(Csr A, CodeState *st)
+{
+    __shared__ int s_keys[kCodeSlots];
+    __shared__ int s_count, s_over;
+    const int t = threadIdx.x;
+    for (int i = t; i < kCodeSlots; i += kCodeThreads) s_keys[i] = kCodeEmpty;
+    if (t == 0) { s_count = 0; s_over = *(volatile int *)&st->overflow; }
+    __syncthreads();
+    const int *__restrict__ rowptr = A.rowptr;
+    const int *__restrict__ col = A.col;
+    for (int row = blockIdx.x * kCodeThreads + t; row < A.rows; row += gridDim.x * kCodeThreads) {
+        if (*(volatile int *)&s_over) break;
+        const int ks = rowptr[row], ke = rowptr[row + 1];
+        for (int k = ks; k < ke; ++k) code_insert(s_keys, &s_count, &s_over, __ldcs(col + k) - row);
+    }
+    __syncthreads();
+    if (s_over) { if (t == 0) st->overflow = 1; return; }
+    for (int i = t; i < kCodeSlots; i += kCodeThreads)
+        if (s_keys[i] != kCodeEmpty) code_insert(st->keys, &st->count, &st->overflow, s_keys[i]);
+}
+
+// one block of kCodeSlots threads: sort the set ascending (bitonic, empties last) -> dict
+__global__ void __launch_bounds__(kCodeSlots) k_code_sort(CodeState *st)
+{
+    __shared__ int s[kCodeSlots];
+    const int t = threadIdx.x;
+    const int v = st->keys[t];
+    s[t] = (v == kCodeEmpty) ? INT_MAX : v;
+    __syncthreads();
+    for (int k = 2; k <= kCodeSlots; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const int o = t ^ j;
+            if (o > t) {
+                const int a = s[t], b = s[o];
+                const bool up = (t & k) == 0;
+                if ((a > b) == up) { s[t] = b; s[o] = a; }
+            }
+            __syncthreads();
+        }
+    const int n = st->count < kCodeMax ? st->count : kCodeMax;
+    if (t < kCodeMax) st->dict[t] = t < n ? s[t] : 0;
+    if (t == 0) st->ndict = n;
+}
+
+__global__ void __launch_bounds__(kCodeThreads) k_code_encode(Csr A, const CodeState *st, unsigned char *code)
+{
+    __shared__ int s_dict[kCodeMax];
+    const int t = threadIdx.x;
+    s_dict[t] = st->dict[t];
+    const int n = st->ndict;
+    __syncthreads();
+    const int *__restrict__ rowptr = A.rowptr;
+    const int *__restrict__ col = A.col;
+    for (int row = blockIdx.x * kCodeThreads + t; row < A.rows; row += gridDim.x * kCodeThreads) {
+        const int ks = rowptr[row], ke = rowptr[row + 1];
+        for (int k = ks; k < ke; ++k) {
+            const int d = __ldcs(col + k) - row;
+            int lo = 0, hi = n - 1;            // d is in the list: plain bisection
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (s_dict[mid] < d) lo = mid + 1; else hi = mid;
+            }
+            code[k] = (unsigned char)lo;
+        }
+    }
+}
+
+// Restate A's columns as codes when the option asks for it, the kernel `plan` selects can read them and the matrix has few enough
+// distinct distances.  On success A->code / A->dict point into the context's code store (kept across set-ups, grown on demand);
+// otherwise they stay null and the plain CSR kernels run.  One host synchronisation (the verdict of the collect pass).
+int spmv_code_build(mgcg_ctx *c, Csr *A, const SpmvPlan &plan)
+{
+    A->code = nullptr; A->dict = nullptr;
+    c->code_ndict = 0;
+    const int min_rows = 1 << 15;          // below this the SpMV is launch-bound and the build would not pay
+    static const bool env_on = [] { const char *e = getenv("MGCG_SPMV_CODED"); return e && e[0] == '1'; }();
+    if (!(c->opt.spmv_coding == MGCG_CODING_ON || env_on) || !spmv_plan_reads_code(plan) || A->rows < min_rows || A->nnz <= 0) return MGCG_OK;
+    if (!c->code_state) MGCG_CUDA(pool_alloc(&c->code_state, sizeof(CodeState), c->stream));
+    const size_t need = (((size_t)A->nnz + 15) & ~(size_t)15) + 16;     // whole 16-byte pieces: the TMA slices may run past the end
+    if (c->code_cap < need) {
+        if (c->code_buf) { pool_free(c->code_buf, c->stream); c->code_buf = nullptr; c->code_cap = 0; }
+        MGCG_CUDA(pool_alloc((void **)&c->code_buf, need, c->stream));
+        c->code_cap = need;
+    }
+    CodeState *st = (CodeState *)c->code_state;
+    int grid = div_up(A->rows, kCodeThreads);
+    if (grid > c->sm_count * 8) grid = c->sm_count * 8;
+    k_code_clear<<<1, kCodeThreads, 0, c->stream>>>(st);
+    k_code_collect<<<grid, kCodeThreads, 0, c->stream>>>(*A, st);
+    MGCG_LAUNCH_CHECK();
+    int verdict[2] = {0, 1};
+    MGCG_CUDA(cudaMemcpyAsync(verdict, &st->count, sizeof(verdict), cudaMemcpyDeviceToHost, c->stream));
+    MGCG_CUDA(cudaStreamSynchronize(c->stream));
+    if (verdict[1] != 0 || verdict[0] > kCodeMax || verdict[0] <= 0) return MGCG_OK;     // too many distances: stay with CSR
+    k_code_sort<<<1, kCodeSlots, 0, c->stream>>>(st);
+    MGCG_CUDA(cudaMemsetAsync(c->code_buf + (need - 32), 0, 32, c->stream));              // the slack past the last entry
+    k_code_encode<<<grid, kCodeThreads, 0, c->stream>>>(*A, st, c->code_buf);
+    MGCG_LAUNCH_CHECK();
+    A->code = c->code_buf;
+    A->dict = st->dict;
+    c->code_ndict = verdict[0];
+    return MGCG_OK;
+}
+
+void spmv_code_free(mgcg_ctx *c)
+{
+    if (c->code_buf) pool_release(c->code_buf);
+    if (c->code_state) pool_release(c->code_state);
+    c->code_buf = nullptr; c->code_state = nullptr; c->code_cap = 0; c->code_ndict = 0;
+}
+
+}  // namespace mgcg

@@ -306,6 +306,23 @@ class Mgcg:
     def mg_apply(self, r, z):
         check(self.L.mgcg_mg_apply(self.ctx, _p(r), _p(z)), "mgcg_mg_apply")
 
+    def matrix_codes(self):
+        """Coded columns of the set-up matrix (csrc/spmv_code.cu): (dict, codes) with col[k] == row(k) + dict[codes[k]], or None when
+        the matrix is not coded."""
+        nd = C.c_int(0)
+        check(self.L.mgcg_matrix_codes(self.ctx, C.byref(nd), None, None), "mgcg_matrix_codes")
+        if nd.value == 0:
+            return None
+        d, codes = np.zeros(256, dtype=np.int32), np.empty(self.nnz, dtype=np.uint8)
+        check(self.L.mgcg_matrix_codes(self.ctx, C.byref(nd), _p(d), _p(codes)), "mgcg_matrix_codes")
+        return d[:nd.value].copy(), codes
+
+    def spmv(self, x, y, alpha=1.0, beta=0.0):
+        """y = alpha A x + beta y with the set-up matrix (runs on its coded columns when it has them)."""
+        val, rowptr, col = self._keep
+        check(self.L.mgcg_spmv(self.ctx, self.n, self.n, self.nnz, _p(val), _p(rowptr), _p(col), _p(x), _p(y), alpha, beta,
+                               self.options.spmv_kernel), "mgcg_spmv")
+
     def close(self):
         if self.ctx:
             self.L.mgcg_destroy(self.ctx)

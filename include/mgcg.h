@@ -48,6 +48,11 @@ enum { MGCG_SMOOTHER_JACOBI = 0, MGCG_SMOOTHER_RBGS = 1, MGCG_SMOOTHER_CHEBYSHEV
  * has one scalar exchange per iteration instead of two.  Same iterates in exact arithmetic; opt-in, outside the parity contract */
 enum { MGCG_CG_CLASSIC = 0, MGCG_CG_SINGLE_REDUCE = 1 };
 enum { MGCG_SPMV_AUTO = 0, MGCG_SPMV_STREAM = 1, MGCG_SPMV_VECTOR = 2, MGCG_SPMV_ROWS = 3 };
+/* internal layout of the fine operator's column indices.  OFF (default) = the caller's int32 columns.  ON = one byte per entry (the
+ * rank of col - row among the matrix's distinct distances) when there are at most 256 of them, the matrix has >= 32768 rows and its
+ * SpMV kernel reads codes (the TMA-staged stream kernel); other matrices silently stay on int32 columns.  Same entries, same order,
+ * same operands: the results are bit-identical either way.  Opt-in: measured no faster inside a solve */
+enum { MGCG_CODING_OFF = 0, MGCG_CODING_ON = 1 };
 enum { MGCG_TRANSPORT_AUTO = 0, MGCG_TRANSPORT_NCCL = 1, MGCG_TRANSPORT_PEER = 2 };
 /* aggregation of the multigrid hierarchy: AUTO = geometric blocks when nx,ny,nz are given, else strength-of-connection filter +
  * MIS-2 aggregates (caller-supplied CSR without a grid, e.g. particle matrices); BLOCKS = 8 consecutive rows when there is no
@@ -96,7 +101,8 @@ typedef struct mgcg_options {
     double mg_strength_theta;        /* MIS-2: a_ij is a strong connection when |a_ij| >= theta * min(max_k|a_ik|, max_k|a_jk|); default 0.5 */
     double mg_cheby_ratio;           /* MGCG_SMOOTHER_CHEBYSHEV: lmax / lmin of the damped window (default 6) */
     int    cg_variant;               /* MGCG_CG_* */
-    int    reserved[3];
+    int    spmv_coding;              /* MGCG_CODING_*: coded columns of the fine operator (csrc/spmv_code.cu) */
+    int    reserved[2];
 } mgcg_options;
 
 typedef struct mgcg_result {
@@ -148,6 +154,11 @@ int mgcg_spmv(mgcg_ctx *c, int rows, int cols, int elements_count,
 int mgcg_spmv_dot(mgcg_ctx *c, int rows, int cols, int elements_count,
                   const double *d_elements, const int *d_row_offsets, const int *d_column_indeces,
                   const double *d_x, double *d_y, const double *d_w, double *d_dot, int kernel);
+/* Coded columns of the matrix the context was set up with (an internal layout behind the CSR interface, csrc/spmv_code.cu): when the
+ * matrix is coded, *ndict = the number of distinct distances col - row, dict[0..256) = the sorted distances (zero-padded),
+ * codes[k] = rank of entry k's distance; otherwise *ndict = 0 and nothing else is written.
+ * mgcg_spmv / mgcg_spmv_dot called with the set-up matrix's own arrays run on the coded columns as the solver does. */
+int mgcg_matrix_codes(mgcg_ctx *c, int *ndict, int *dict /* [256] or NULL */, unsigned char *codes /* [elements_count] or NULL */);
 /* deterministic fixed-order dot / max|.| ; result to a device scalar and (if host_out != NULL) to the host */
 int mgcg_dot(mgcg_ctx *c, int n, const double *d_a, const double *d_b, double *d_out, double *host_out);
 int mgcg_max_abs(mgcg_ctx *c, int n, const double *d_a, double *d_out, double *host_out);

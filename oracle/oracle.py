@@ -74,6 +74,18 @@ def dot(a, b):
     return lib().ref_dot(len(a), a, b)
 
 
+def coded_columns(rowptr, col, max_codes=256):
+    """Checker for the library's coded-column layout (csrc/spmv_code.cu; the reference has only int32 CSR columns, Mgcg.cu:10-19):
+    the sorted distinct distances col - row and each entry's rank among them, or None when there are more than `max_codes`."""
+    rowptr = np.asarray(rowptr, dtype=np.int64)
+    row_of = np.repeat(np.arange(len(rowptr) - 1, dtype=np.int64), np.diff(rowptr))
+    d = np.asarray(col, dtype=np.int64) - row_of
+    dist = np.unique(d)
+    if len(dist) > max_codes:
+        return None
+    return dist.astype(np.int32), np.searchsorted(dist, d).astype(np.uint8)
+
+
 def cg_solve(val, rowptr, col, b, x0=None, tol=1e-8, min_iteration=0, max_iteration=None,
              norm=NORM_ABS_L2, min_strict=False):
     """ConjugateGradientCpu.Solve restatement. Returns (x, iteration_index, residual, status)."""

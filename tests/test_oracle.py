@@ -127,3 +127,21 @@ def test_threaded_port_matches_sequential(oracle, gen):
     # bounded sample: max_iteration stops the loop like the C# throw
     _, it, _, st = oracle.cg_solve_mt(v, rp, c, b, tol=0.0, max_iteration=8, threads=2)
     assert st == oracle.MAX_ITERATION_EXCEEDED and it == 9
+
+
+def test_coded_columns_restates_the_columns():
+    """the checker of the coded-column layout (csrc/spmv_code.cu): stencil matrices have a handful of distances col - row, a shard's
+    local rows shift them by a constant, an irregular matrix has too many"""
+    from conjugategradient_b200 import generators as gen
+    from oracle import oracle as O
+    v, rp, c = gen.poisson3d7(9, 7, 5)
+    d, code = O.coded_columns(rp, c)
+    assert list(d) == [-63, -9, -1, 0, 1, 9, 63] and code.dtype == np.uint8
+    row_of = np.repeat(np.arange(len(rp) - 1), np.diff(rp))
+    assert np.array_equal(row_of + d[code], c)
+    v, rp, c = gen.poisson3d7(9, 7, 6, zrange=(2, 4))           # rows of a z-slab shard, global columns
+    d2, code2 = O.coded_columns(rp, c)
+    assert list(d2) == [x + 2 * 63 for x in d]
+    rng = np.random.default_rng(0)
+    rp = np.arange(0, 4 * 1000 + 1, 4, dtype=np.int32)
+    assert O.coded_columns(rp, rng.integers(0, 1000, 4000).astype(np.int32)) is None
