@@ -93,6 +93,7 @@ struct Csr {
     // coded columns (spmv_code.cu), optional: col[k] == row + dict[code[k]]; kernels that cannot read them use `col`
     const unsigned char *code = nullptr;
     const int *dict = nullptr;       // 256 ints
+    int ndict = 0;                   // distinct distances
 };
 
 // SpMV plan: kernel choice and launch geometry for one matrix
@@ -144,6 +145,7 @@ struct GhostWait {
 struct SpmvArgs {
     Csr A;
     const double *x = nullptr;
+    int x_lo = 0, x_hi = -1;       // index range in which x may be read (x_hi < 0: [0, A.cols)); a shifted view of a shard's vector narrows it
     const double *xrow = nullptr;  // JACOBI: x indexed by ROW (nullptr: same as x; differs when x is a shifted global-index view)
     double *y = nullptr;
     const double *b = nullptr;     // RESID / JACOBI

@@ -682,6 +682,11 @@ static int dist_reduce(mgcg_ctx *c, int mode, int k, bool gated)
 }
 
 static inline const double *shifted(const double *ext, int off, int lo) { return ext - ((ptrdiff_t)off - lo); }
+// x of a product = the extended vector [lo ghosts | own rows | hi ghosts] seen through global column indices; its readable range
+static inline void set_shifted_x(SpmvArgs &a, const double *ext, int off, int lo, int own, int hi)
+{
+    a.x = shifted(ext, off, lo); a.x_lo = off - lo; a.x_hi = off + own + hi;
+}
 
 // ---- fused halo exchange (halo.cuh): with the level vectors in the peer arena, the kernel that WRITES a [lo|own|hi] vector stores
 // its boundary rows into the neighbours' ghost rows and publishes the exchange, and the kernel that READS ghost rows waits for
@@ -750,7 +755,7 @@ static int dist_cheby_smooth(mgcg_ctx *c, DistLevel &L, bool skip_first, double 
         const bool last = dot_out && k == L.cheb - 1;
         MGCG_CHECK(halo_unless_fused(c, L.xcur, L.own, L.lo, L.hi, L.halo));
         SpmvArgs a;
-        a.A = L.A; a.x = shifted(L.xcur, L.off, L.lo); a.xrow = L.xcur + L.lo; a.y = other + L.lo; a.b = L.b; a.dinv = L.dinv;
+        a.A = L.A; set_shifted_x(a, L.xcur, L.off, L.lo, L.own, L.hi); a.xrow = L.xcur + L.lo; a.y = other + L.lo; a.b = L.b; a.dinv = L.dinv;
         wait_for_ghosts(c, a);
         if (ghosts_needed || k + 1 < L.cheb) a.mir = mirror_for(c, other);
         a.alpha = c1; a.omega = c2; a.d_in = (skip_first && k == 1) ? L.xcur + L.lo : L.d; a.d_out = L.d;
@@ -766,7 +771,7 @@ static int dist_jacobi_sweep(mgcg_ctx *c, DistLevel &L, double omega, double *do
     double *other = (L.xcur == L.xa) ? L.xb : L.xa;
     MGCG_CHECK(halo_unless_fused(c, L.xcur, L.own, L.lo, L.hi, L.halo));
     SpmvArgs a;
-    a.A = L.A; a.x = shifted(L.xcur, L.off, L.lo); a.xrow = L.xcur + L.lo; a.y = other + L.lo; a.b = L.b; a.dinv = L.dinv;
+    a.A = L.A; set_shifted_x(a, L.xcur, L.off, L.lo, L.own, L.hi); a.xrow = L.xcur + L.lo; a.y = other + L.lo; a.b = L.b; a.dinv = L.dinv;
     wait_for_ghosts(c, a);
     if (ghosts_needed) a.mir = mirror_for(c, other);
     a.omega = omega; a.gated = true; a.fin = FIN_STORE; a.out = dot_out;
@@ -812,7 +817,7 @@ static int dist_vcycle(mgcg_ctx *c, double *r_ext, double **z_own, bool fuse_fir
         MGCG_CHECK(halo_unless_fused(c, L.xcur, L.own, L.lo, L.hi, L.halo));
         dist_trace(c, l == 0 ? "L0 halo(z)" : "L1+ halo(z)");
         SpmvArgs a;
-        a.A = L.A; a.x = shifted(L.xcur, L.off, L.lo); a.y = L.r + L.lo; a.b = L.b; a.gated = true;
+        a.A = L.A; set_shifted_x(a, L.xcur, L.off, L.lo, L.own, L.hi); a.y = L.r + L.lo; a.b = L.b; a.gated = true;
         wait_for_ghosts(c, a); a.mir = mirror_for(c, L.r);
         MGCG_CHECK(spmv_launch(c, L.planA, EPI_RESID, a));
         dist_trace(c, l == 0 ? "L0 residual" : "L1+ residual");
@@ -875,7 +880,7 @@ static int dist_enqueue_iteration(mgcg_ctx *c, double *x)
     MGCG_CHECK(halo_unless_fused(c, D->p, n, L0.lo, L0.hi, L0.halo));    // fused: pushed by the update of p (by dist_solve before the first iteration)
     dist_trace(c, "halo(p)");
     SpmvArgs a;
-    a.A = c->A; a.x = shifted(D->p, L0.off, L0.lo); a.y = D->Ap; a.w = p_own; a.fin = FIN_STORE; a.out = D->partial_send; a.gated = true;
+    a.A = c->A; set_shifted_x(a, D->p, L0.off, L0.lo, L0.own, L0.hi); a.y = D->Ap; a.w = p_own; a.fin = FIN_STORE; a.out = D->partial_send; a.gated = true;
     wait_for_ghosts(c, a);
     MGCG_CHECK(spmv_launch(c, c->planA, EPI_DOT, a));
     dist_trace(c, "A p + p.Ap");
@@ -934,7 +939,8 @@ static int dist_enqueue_iteration_cgcg(mgcg_ctx *c, double *x)
     SpmvArgs a;
     a.A = c->A; a.y = D->Ap; a.w = u_ext + L0.lo; a.fin = FIN_STORE; a.out = D->partial_send; a.gated = true;
     if (!(pre && D->first_replicated == 0)) wait_for_ghosts(c, a);
-    a.x = (pre && D->first_replicated == 0) ? (u_ext + L0.lo) - L0.off : shifted(u_ext, L0.off, L0.lo);
+    if (pre && D->first_replicated == 0) { a.x = (u_ext + L0.lo) - L0.off; a.x_lo = L0.off; a.x_hi = L0.off + L0.own; }
+    else set_shifted_x(a, u_ext, L0.off, L0.lo, L0.own, L0.hi);
     MGCG_CHECK(spmv_launch(c, c->planA, EPI_DOT, a));
     dist_trace(c, "A u + u.Au");
     MGCG_CHECK(dist_reduce(c, pre ? DF_CGCG : DF_CGCG_PLAIN, 3, true));
@@ -1004,7 +1010,7 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     MGCG_CHECK(dist_halo_exchange(c, D->p, n, L0.lo, L0.hi, L0.halo));
     {
         SpmvArgs a;
-        a.A = c->A; a.x = shifted(D->p, L0.off, L0.lo); a.y = D->Ap;
+        a.A = c->A; set_shifted_x(a, D->p, L0.off, L0.lo, L0.own, L0.hi); a.y = D->Ap;
         MGCG_CHECK(spmv_launch(c, c->planA, EPI_PLAIN, a));
     }
     const bool cgcg = c->opt.cg_variant == MGCG_CG_SINGLE_REDUCE;
@@ -1028,7 +1034,8 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
         if (!repl) MGCG_CHECK(dist_halo_exchange(c, u_ext, n, L0.lo, L0.hi, L0.halo));
         SpmvArgs a;
         a.A = c->A; a.y = D->Ap; a.w = u_ext + L0.lo; a.fin = FIN_STORE; a.out = D->partial_send;
-        a.x = repl ? (u_ext + L0.lo) - L0.off : shifted(u_ext, L0.off, L0.lo);
+        if (repl) { a.x = (u_ext + L0.lo) - L0.off; a.x_lo = L0.off; a.x_hi = L0.off + L0.own; }
+        else set_shifted_x(a, u_ext, L0.off, L0.lo, L0.own, L0.hi);
         MGCG_CHECK(spmv_launch(c, c->planA, EPI_DOT, a));
         MGCG_CHECK(dist_reduce(c, DF_CGCG_INIT, 1, false));
         MGCG_CUDA(cudaMemsetAsync(p_own, 0, sizeof(double) * (size_t)n, st));

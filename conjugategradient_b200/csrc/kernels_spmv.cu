@@ -352,6 +352,136 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// STENCIL (coded columns with at most kSegMax distinct distances: the 7-point and 5-point operators).  The ncu capture of the coded
+// stream kernel showed it latency-bound, not bandwidth-bound: 40 % of the stall samples on the x gathers, 22 % on the wait for the
+// next stage — the ring cannot run far enough ahead while its stages are held by threads waiting for gathers.  Here a tile's x
+// operands are staged too: for every distance d of the dictionary the rows r0 .. r0+255 of the tile read the CONTIGUOUS run
+// x[r0+d .. r0+d+255], so the producer thread requests one bulk copy per distance next to the tile's values and codes.  No thread
+// issues a dependent global load any more: rowptr -> (value, code) -> x all arrive through the TMA ring, a row is summed from shared
+// memory in storage order with explicit mul/add roundings (the same bits as every other STREAM kernel), and the ring's stages are in
+// flight for almost their whole life.  Runs that would leave the valid index range of x (tiles at the ends of the matrix; their rows
+// have no entry at that distance, or only some) are not staged: those entries fall back to a gather.
+constexpr int kSegMax = 8;                    // distances staged per tile
+constexpr int kSegLen = kTmaRows + 2;         // doubles per run: the run starts at an even index (16-byte aligned source)
+
+template <int EPI, int kStages>
+__global__ void __launch_bounds__(kTmaRows) k_spmv_stencil(SpmvArgs a, int num_tiles, int nseg, ReduceWs ws, Scalars *sc)
+{
+    constexpr int cap = kTmaCap;
+    extern __shared__ __align__(16) unsigned char st_dyn[];
+    const size_t stage_bytes = (size_t)(cap + 2) * 8 + (cap + 16) + (size_t)nseg * kSegLen * 8;     // values | codes | x runs
+    __shared__ __align__(8) unsigned long long s_full[kStages], s_empty[kStages];
+    __shared__ TmaMeta s_meta[kStages];       // .pad = bit c set: the run of distance c is staged
+    __shared__ int s_dict[kSegMax];
+    const int t = threadIdx.x;
+    const double *__restrict__ val = a.A.val;
+    const unsigned char *__restrict__ code = a.A.code;
+    const int *__restrict__ rowptr = a.A.rowptr;
+    const double *__restrict__ x = a.x;
+    const int rows = a.A.rows;
+    const long long nnz_end = (long long)a.A.nnz;
+    const int x_lo = a.x_lo, x_hi = a.x_hi >= 0 ? a.x_hi : a.A.cols;      // valid index range of x
+    double dsum = 0.0;
+
+    pdl_wait(); pdl_launch_dependents();
+    if (a.gated && sc->done) return;
+    if (t == 0) {
+        for (int s = 0; s < kStages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], kTmaRows); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (t < kSegMax) s_dict[t] = t < nseg ? a.A.dict[t] : 0;
+    bool wrote = false;
+    halo_wait(a.gw, sc);             // the x runs are requested below: ghost rows must have landed ...
+    if (a.gw.ctl && t == 0) asm volatile("fence.proxy.async;" ::: "memory");     // ... and be visible to the bulk copies
+    const int my_tiles = (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    __syncthreads();
+
+    auto issue = [&](int j) {
+        const int s = j % kStages;
+        const int tile = blockIdx.x + j * gridDim.x;
+        const int r0 = tile * kTmaRows;
+        const int nr = min(kTmaRows, rows - r0);
+        const int k0 = rowptr[r0], k1 = rowptr[r0 + nr];
+        const int ka = k0 & ~1, kc = k0 & ~15;
+        const unsigned vb = (unsigned)(((k1 - ka) * 8 + 15) & ~15), cb = (unsigned)(((k1 - kc) + 15) & ~15);
+        const bool fits = (k1 - ka) <= cap && (k1 - kc) <= cap && k1 > k0 && ((long long)ka * 8 + vb <= nnz_end * 8);
+        unsigned char *base = st_dyn + (size_t)s * stage_bytes;
+        int mask = 0;
+        if (fits)
+            for (int c = 0; c < nseg; ++c) {
+                const int s0 = (r0 + s_dict[c]) & ~1;
+                if (s0 >= x_lo && s0 + kSegLen <= x_hi) mask |= 1 << c;
+            }
+        s_meta[s].k0 = k0; s_meta[s].k1 = k1; s_meta[s].direct = fits ? 0 : 1; s_meta[s].pad = mask;
+        if (fits) {
+            mbar_arrive_expect_tx(&s_full[s], vb + cb + (unsigned)__popc(mask) * (unsigned)(kSegLen * 8));
+            tma_load_1d(base, val + ka, vb, &s_full[s]);
+            tma_load_1d(base + (size_t)(cap + 2) * 8, code + kc, cb, &s_full[s]);
+            double *sx = reinterpret_cast<double *>(base + (size_t)(cap + 2) * 8 + (cap + 16));
+            for (int c = 0; c < nseg; ++c)
+                if (mask >> c & 1) tma_load_1d(sx + c * kSegLen, x + ((r0 + s_dict[c]) & ~1), kSegLen * 8, &s_full[s]);
+        } else {
+            mbar_arrive(&s_full[s]);
+        }
+    };
+    if (t == 0)
+        for (int j = 0; j < kStages && j < my_tiles; ++j) issue(j);
+
+    int rs_n = 0, re_n = 0;
+    {
+        const int r = blockIdx.x * kTmaRows + t;
+        if (my_tiles > 0 && r < rows) { rs_n = rowptr[r]; re_n = rowptr[r + 1]; }
+    }
+    for (int j = 0; j < my_tiles; ++j) {
+        const int s = j % kStages;
+        const unsigned parity = (unsigned)((j / kStages) & 1);
+        const int tile = blockIdx.x + j * gridDim.x;
+        const int row = tile * kTmaRows + t;
+        const int rs = rs_n, re = re_n;
+        rs_n = re_n = 0;
+        if (j + 1 < my_tiles) {
+            const int rn = (tile + gridDim.x) * kTmaRows + t;
+            if (rn < rows) { rs_n = rowptr[rn]; re_n = rowptr[rn + 1]; }
+        }
+        EpiPre pre;
+        if (row < rows) epi_prefetch<EPI>(row, a, pre);
+        const bool active = row < rows;
+        mbar_wait(&s_full[s], parity);
+        double acc = 0.0;
+        if (active) {
+            if (!s_meta[s].direct) {
+                const int k0 = s_meta[s].k0, mask = s_meta[s].pad;
+                const unsigned char *base = st_dyn + (size_t)s * stage_bytes;
+                const double *sv = reinterpret_cast<const double *>(base) - (k0 & ~1);
+                const unsigned char *scd = base + (size_t)(cap + 2) * 8 - (k0 & ~15);
+                const double *sx = reinterpret_cast<const double *>(base + (size_t)(cap + 2) * 8 + (cap + 16)) + t;
+                for (int k = rs; k < re; ++k) {
+                    const int c = scd[k];
+                    const int d = s_dict[c];
+                    // the run of distance d starts at the even index (r0 + d) & ~1 and r0 is even: this row's operand is at t + (d & 1)
+                    const double xv = (mask >> c & 1) ? sx[c * kSegLen + (d & 1)] : x[row + d];
+                    acc = __dadd_rn(acc, __dmul_rn(sv[k], xv));
+                }
+            } else {
+                for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(__ldcs(val + k), x[row + s_dict[__ldcs(code + k)]]));
+            }
+        }
+        mbar_arrive(&s_empty[s]);
+        if (t == 0 && j + kStages < my_tiles) {
+            mbar_wait(&s_empty[s], parity);
+            issue(j + kStages);
+        }
+        if (active) epilogue_pre<EPI>(row, acc, a, dsum, pre, wrote);
+    }
+    if (EpiTraits<EPI>::reduces) {
+        double m = 0.0;
+        block_reduce<false>(dsum, m);
+        grid_reduce_finish<false>(dsum, m, ws, a.fin, sc, a.out);
+    }
+    halo_signal(a.mir, wrote);
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // ROWS-TMA (medium and long rows: 8 .. ~300 entries — the reference's own 160-per-row band, particle matrices, restriction
 // operators, coarse Galerkin stencils; cf. the reference's ELL kernel with a local-memory window,
 // Mgcg/HandmadeCL/MgcgCL/Mgcg.cl:171-216).  A tile is 256/L consecutive rows, L lanes per row.  The tile's contiguous val/col
@@ -673,6 +803,35 @@ static int launch_coded_one(mgcg_ctx *c, const SpmvArgs &a, int tiles, int ctas)
     launch_k(a.gated, k_spmv_tma<EPI, 0, STAGES, true>, grid, kTmaRows, (size_t)smem, c->stream, a, tiles, kTmaCap, c->ws, c->d_scalars);
     return MGCG_OK;
 }
+// STENCIL kernel: stages x resident blocks from what fits (tuning knobs MGCG_STENCIL_STAGES 2..4, MGCG_STENCIL_CTAS)
+template <int EPI, int STAGES>
+static int launch_stencil_one(mgcg_ctx *c, const SpmvArgs &a, int tiles, int nseg, int ctas_env)
+{
+    static int set_bytes[64] = {0};
+    const int smem = STAGES * ((kTmaCap + 2) * 8 + (kTmaCap + 16) + nseg * kSegLen * 8);
+    const int d = c->device & 63;
+    if (smem > set_bytes[d]) {
+        MGCG_CUDA(cudaFuncSetAttribute(k_spmv_stencil<EPI, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        set_bytes[d] = smem;
+    }
+    int ctas = (224 * 1024) / (smem + 2 * 1024);
+    if (ctas_env > 0) ctas = ctas_env;
+    if (ctas < 1) ctas = 1;
+    int grid = c->sm_count * ctas;
+    if (grid > tiles) grid = tiles;
+    launch_k(a.gated, k_spmv_stencil<EPI, STAGES>, grid, kTmaRows, (size_t)smem, c->stream, a, tiles, nseg, c->ws, c->d_scalars);
+    return MGCG_OK;
+}
+template <int EPI>
+static int launch_stencil(mgcg_ctx *c, const SpmvArgs &a, int tiles, int nseg)
+{
+    static const int stages = [] { const char *e = getenv("MGCG_STENCIL_STAGES"); const int v = e ? atoi(e) : 0; return (v >= 2 && v <= 4) ? v : 3; }();
+    static const int ctas_env = [] { const char *e = getenv("MGCG_STENCIL_CTAS"); const int v = e ? atoi(e) : 0; return (v >= 1 && v <= 8) ? v : 0; }();
+    if (stages == 2) return launch_stencil_one<EPI, 2>(c, a, tiles, nseg, ctas_env);
+    if (stages == 3) return launch_stencil_one<EPI, 3>(c, a, tiles, nseg, ctas_env);
+    return launch_stencil_one<EPI, 4>(c, a, tiles, nseg, ctas_env);
+}
+
 template <int EPI>
 static int launch_coded(mgcg_ctx *c, const SpmvArgs &a, int tiles)
 {
@@ -698,6 +857,12 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
     if (plan.kernel == MGCG_SPMV_STREAM && plan.tma && aligned) {
         const int tiles = div_up(a.A.rows, kTmaRows);
         if (a.A.code && a.A.dict && spmv_plan_reads_code(plan)) {
+            // x staged as well when the dictionary is short, x is 16-byte aligned and not rewritten by this launch
+            static const bool no_stencil = getenv("MGCG_NO_STENCIL") != nullptr;
+            const bool in_place = (const double *)a.y == a.x || a.color >= 0;
+            if (!no_stencil && a.A.ndict > 0 && a.A.ndict <= kSegMax && (((uintptr_t)a.x) & 15u) == 0 && !in_place)
+                MGCG_CHECK(launch_stencil<EPI>(c, a, tiles, a.A.ndict));
+            else
             MGCG_CHECK(launch_coded<EPI>(c, a, tiles));
             c->launches++;
             MGCG_LAUNCH_CHECK();

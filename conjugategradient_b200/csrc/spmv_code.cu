@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(kCodeThreads) k_code_encode(Csr A, const CodeS
 // otherwise they stay null and the plain CSR kernels run.  One host synchronisation (the verdict of the collect pass).
 int spmv_code_build(mgcg_ctx *c, Csr *A, const SpmvPlan &plan)
 {
-    A->code = nullptr; A->dict = nullptr;
+    A->code = nullptr; A->dict = nullptr; A->ndict = 0;
     c->code_ndict = 0;
     const int min_rows = 1 << 15;          // below this the SpMV is launch-bound and the build would not pay
     static const bool env_on = [] { const char *e = getenv("MGCG_SPMV_CODED"); return e && e[0] == '1'; }();
@@ -160,6 +160,7 @@ int spmv_code_build(mgcg_ctx *c, Csr *A, const SpmvPlan &plan)
     MGCG_LAUNCH_CHECK();
     A->code = c->code_buf;
     A->dict = st->dict;
+    A->ndict = verdict[0];
     c->code_ndict = verdict[0];
     return MGCG_OK;
 }

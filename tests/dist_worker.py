@@ -60,6 +60,17 @@ def main():
         res2 = m.solve(tb, tx.zero_())
         assert res2.iterations_done == res.iterations_done and torch.equal(tx, x_first), "repeated sharded solve differs"
     torch.cuda.synchronize()
+    import ctypes as C
+    nd = C.c_int(0)
+    m.L.mgcg_matrix_codes(m.ctx, C.byref(nd), None, None)
+    if kw.get("spmv_coding", 0) == 1:
+        # coded columns restate the shard's columns exactly: the solve on int32 columns gives the same bits
+        x_coded = tx.clone()
+        kw0 = dict(kw); kw0["spmv_coding"] = 0
+        m.setup(N, r0, tv, tr, tc, S.default_options(norm=2, tolerance=cfg.get("tolerance", 1e-8), max_iteration=2000, **kw0))
+        res0 = m.solve(tb, tx.zero_())
+        assert res0.iterations_done == res.iterations_done and torch.equal(tx, x_coded), "sharded solve on coded columns differs from int32 columns"
+        torch.cuda.synchronize()
     # the same system on this GPU alone
     ms = S.Mgcg(lr)
     fv, fr, fc, fb = (torch.as_tensor(a).to(dev) for a in (v, rp, c, b))
@@ -85,7 +96,7 @@ def main():
     out = {"rank": rank, "it_dist": res.iterations_done, "it_single": rs.iterations_done, "err": err, "residual": res.residual,
            "levels": res.levels, "first_replicated": res.reserved[2], "halo_exchanges": res.reserved[0], "allgathers": res.reserved[1],
            "solve_ms": res.solve_ms, "setup_ms": res.setup_ms, "single_ms": rs.solve_ms, "launches": res.kernel_launches,
-           "transport": res.reserved[3], "graph": res.reserved[4], **tight}
+           "transport": res.reserved[3], "graph": res.reserved[4], "coded": nd.value, **tight}
     allo = [None] * world
     dist.all_gather_object(allo, out)
     if rank == 0:

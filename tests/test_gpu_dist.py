@@ -47,6 +47,11 @@ CASES = [
     ("mg_single_reduce_peer", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "cg_variant": 1}, "transport": 2,
                                "solves": 2}),
     ("mg_single_reduce_replicated_nccl", {"n": 32, "options": {"precond": 1, "dist_transport": 1, "cg_variant": 1}}),
+    # coded columns of the shard's fine operator (opt-in): x runs staged by TMA from the shifted view incl. ghost rows pushed by the
+    # neighbours' kernels; the worker also checks the result bit for bit against the same sharded solve on int32 columns
+    ("mg_coded_columns_peer", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "spmv_coding": 1}, "transport": 2,
+                               "solves": 2, "coded": 7}),
+    ("plain_cg_coded_columns_nccl", {"n": 48, "options": {"precond": 0, "dist_transport": 1, "spmv_coding": 1}, "coded": 7}),
     ("mg_chebyshev_single_reduce_w4", {"n": 48, "world": 4, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "mg_smoother": 2,
                                                                         "cg_variant": 1}, "transport": 2}),
 ]
@@ -76,4 +81,6 @@ def test_sharded_matches_single_gpu(name, cfg):
         assert r["residual"] < cfg.get("tolerance", 1e-8)
     if "transport" in cfg:
         assert all(r["transport"] == cfg["transport"] for r in res), res
+    if "coded" in cfg:
+        assert all(r["coded"] == cfg["coded"] for r in res), res
     assert len({r["it_dist"] for r in res}) == 1 and len({r["residual"] for r in res}) == 1   # identical scalars on all ranks
