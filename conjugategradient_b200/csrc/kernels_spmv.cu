@@ -364,8 +364,14 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
 constexpr int kSegMax = 8;                    // distances staged per tile
 constexpr int kSegLen = kTmaRows + 2;         // doubles per run: the run starts at an even index (16-byte aligned source)
 
+constexpr int kStencilThreads = kTmaRows + 32;      // 8 consumer warps (one thread per row of the tile) + 1 producer warp
+
+// The producer is a warp of its own: with nine bulk copies per tile behind two row-pointer loads, one consumer thread doing the
+// requests between its own rows made the request path the block's critical path (2.1 us per tile whatever the ring depth).  Its
+// lanes share the work — lane 0 the values and the barrier's byte count, lane 1 the codes, lane 2 + c the run of distance c — and the
+// next tile's row pointers are loaded before the wait for the stage to drain.
 template <int EPI, int kStages>
-__global__ void __launch_bounds__(kTmaRows) k_spmv_stencil(SpmvArgs a, int num_tiles, int nseg, ReduceWs ws, Scalars *sc)
+__global__ void __launch_bounds__(kStencilThreads) k_spmv_stencil(SpmvArgs a, int num_tiles, int nseg, ReduceWs ws, Scalars *sc)
 {
     constexpr int cap = kTmaCap;
     extern __shared__ __align__(16) unsigned char st_dyn[];
@@ -392,86 +398,101 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_stencil(SpmvArgs a, int num_t
     if (t < kSegMax) s_dict[t] = t < nseg ? a.A.dict[t] : 0;
     bool wrote = false;
     halo_wait(a.gw, sc);             // the x runs are requested below: ghost rows must have landed ...
-    if (a.gw.ctl && t == 0) asm volatile("fence.proxy.async;" ::: "memory");     // ... and be visible to the bulk copies
+    if (a.gw.ctl && (t & 31) == 0) asm volatile("fence.proxy.async;" ::: "memory");     // ... and be visible to the bulk copies
     const int my_tiles = (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
     __syncthreads();
 
-    auto issue = [&](int j) {
-        const int s = j % kStages;
-        const int tile = blockIdx.x + j * gridDim.x;
-        const int r0 = tile * kTmaRows;
-        const int nr = min(kTmaRows, rows - r0);
-        const int k0 = rowptr[r0], k1 = rowptr[r0 + nr];
-        const int ka = k0 & ~1, kc = k0 & ~15;
-        const unsigned vb = (unsigned)(((k1 - ka) * 8 + 15) & ~15), cb = (unsigned)(((k1 - kc) + 15) & ~15);
-        const bool fits = (k1 - ka) <= cap && (k1 - kc) <= cap && k1 > k0 && ((long long)ka * 8 + vb <= nnz_end * 8);
-        unsigned char *base = st_dyn + (size_t)s * stage_bytes;
-        int mask = 0;
-        if (fits)
-            for (int c = 0; c < nseg; ++c) {
-                const int s0 = (r0 + s_dict[c]) & ~1;
-                if (s0 >= x_lo && s0 + kSegLen <= x_hi) mask |= 1 << c;
+    if (t >= kTmaRows) {
+        // ---- producer warp
+        const int lane = t - kTmaRows;
+        int k0 = 0, k1 = 0;
+        if (my_tiles > 0) {
+            const int r0 = blockIdx.x * kTmaRows;
+            k0 = rowptr[r0]; k1 = rowptr[r0 + min(kTmaRows, rows - r0)];
+        }
+        for (int j = 0; j < my_tiles; ++j) {
+            const int s = j % kStages;
+            const int tile = blockIdx.x + j * gridDim.x;
+            const int r0 = tile * kTmaRows;
+            int k0n = 0, k1n = 0;
+            if (j + 1 < my_tiles) {
+                const int rn = (tile + gridDim.x) * kTmaRows;
+                k0n = rowptr[rn]; k1n = rowptr[rn + min(kTmaRows, rows - rn)];
             }
-        s_meta[s].k0 = k0; s_meta[s].k1 = k1; s_meta[s].direct = fits ? 0 : 1; s_meta[s].pad = mask;
-        if (fits) {
-            mbar_arrive_expect_tx(&s_full[s], vb + cb + (unsigned)__popc(mask) * (unsigned)(kSegLen * 8));
-            tma_load_1d(base, val + ka, vb, &s_full[s]);
-            tma_load_1d(base + (size_t)(cap + 2) * 8, code + kc, cb, &s_full[s]);
-            double *sx = reinterpret_cast<double *>(base + (size_t)(cap + 2) * 8 + (cap + 16));
-            for (int c = 0; c < nseg; ++c)
-                if (mask >> c & 1) tma_load_1d(sx + c * kSegLen, x + ((r0 + s_dict[c]) & ~1), kSegLen * 8, &s_full[s]);
-        } else {
-            mbar_arrive(&s_full[s]);
-        }
-    };
-    if (t == 0)
-        for (int j = 0; j < kStages && j < my_tiles; ++j) issue(j);
-
-    int rs_n = 0, re_n = 0;
-    {
-        const int r = blockIdx.x * kTmaRows + t;
-        if (my_tiles > 0 && r < rows) { rs_n = rowptr[r]; re_n = rowptr[r + 1]; }
-    }
-    for (int j = 0; j < my_tiles; ++j) {
-        const int s = j % kStages;
-        const unsigned parity = (unsigned)((j / kStages) & 1);
-        const int tile = blockIdx.x + j * gridDim.x;
-        const int row = tile * kTmaRows + t;
-        const int rs = rs_n, re = re_n;
-        rs_n = re_n = 0;
-        if (j + 1 < my_tiles) {
-            const int rn = (tile + gridDim.x) * kTmaRows + t;
-            if (rn < rows) { rs_n = rowptr[rn]; re_n = rowptr[rn + 1]; }
-        }
-        EpiPre pre;
-        if (row < rows) epi_prefetch<EPI>(row, a, pre);
-        const bool active = row < rows;
-        mbar_wait(&s_full[s], parity);
-        double acc = 0.0;
-        if (active) {
-            if (!s_meta[s].direct) {
-                const int k0 = s_meta[s].k0, mask = s_meta[s].pad;
-                const unsigned char *base = st_dyn + (size_t)s * stage_bytes;
-                const double *sv = reinterpret_cast<const double *>(base) - (k0 & ~1);
-                const unsigned char *scd = base + (size_t)(cap + 2) * 8 - (k0 & ~15);
-                const double *sx = reinterpret_cast<const double *>(base + (size_t)(cap + 2) * 8 + (cap + 16)) + t;
-                for (int k = rs; k < re; ++k) {
-                    const int c = scd[k];
-                    const int d = s_dict[c];
-                    // the run of distance d starts at the even index (r0 + d) & ~1 and r0 is even: this row's operand is at t + (d & 1)
-                    const double xv = (mask >> c & 1) ? sx[c * kSegLen + (d & 1)] : x[row + d];
-                    acc = __dadd_rn(acc, __dmul_rn(sv[k], xv));
+            if (j >= kStages) mbar_wait(&s_empty[s], (unsigned)(((j / kStages) - 1) & 1));     // the stage's previous tile is consumed
+            const int ka = k0 & ~1, kc = k0 & ~15;
+            const unsigned vb = (unsigned)(((k1 - ka) * 8 + 15) & ~15), cb = (unsigned)(((k1 - kc) + 15) & ~15);
+            // (the code array is allocated in whole 16-byte pieces with one to spare: its slices never run out of it)
+            const bool fits = (k1 - ka) <= cap && (k1 - kc) <= cap && k1 > k0 && ((long long)ka * 8 + vb <= nnz_end * 8);
+            unsigned char *base = st_dyn + (size_t)s * stage_bytes;
+            const int c = lane - 2;
+            int s0 = 0;
+            bool ok = false;
+            if (fits && c >= 0 && c < nseg) {
+                s0 = (r0 + s_dict[c]) & ~1;
+                ok = s0 >= x_lo && s0 + kSegLen <= x_hi;
+            }
+            const unsigned mask = __ballot_sync(0xffffffffu, ok) >> 2;
+            if (lane == 0) {
+                s_meta[s].k0 = k0; s_meta[s].k1 = k1; s_meta[s].direct = fits ? 0 : 1; s_meta[s].pad = (int)mask;
+                if (fits) {
+                    mbar_arrive_expect_tx(&s_full[s], vb + cb + (unsigned)__popc(mask) * (unsigned)(kSegLen * 8));
+                    tma_load_1d(base, val + ka, vb, &s_full[s]);
+                } else {
+                    mbar_arrive(&s_full[s]);
                 }
-            } else {
-                for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(__ldcs(val + k), x[row + s_dict[__ldcs(code + k)]]));
+            } else if (lane == 1) {
+                if (fits) tma_load_1d(base + (size_t)(cap + 2) * 8, code + kc, cb, &s_full[s]);
+            } else if (ok) {
+                double *sx = reinterpret_cast<double *>(base + (size_t)(cap + 2) * 8 + (cap + 16));
+                tma_load_1d(sx + c * kSegLen, x + s0, kSegLen * 8, &s_full[s]);
             }
+            k0 = k0n; k1 = k1n;
         }
-        mbar_arrive(&s_empty[s]);
-        if (t == 0 && j + kStages < my_tiles) {
-            mbar_wait(&s_empty[s], parity);
-            issue(j + kStages);
+    } else {
+        // ---- consumers: one thread per row of the tile
+        int rs_n = 0, re_n = 0;
+        {
+            const int r = blockIdx.x * kTmaRows + t;
+            if (my_tiles > 0 && r < rows) { rs_n = rowptr[r]; re_n = rowptr[r + 1]; }
         }
-        if (active) epilogue_pre<EPI>(row, acc, a, dsum, pre, wrote);
+        for (int j = 0; j < my_tiles; ++j) {
+            const int s = j % kStages;
+            const unsigned parity = (unsigned)((j / kStages) & 1);
+            const int tile = blockIdx.x + j * gridDim.x;
+            const int row = tile * kTmaRows + t;
+            const int rs = rs_n, re = re_n;
+            rs_n = re_n = 0;
+            if (j + 1 < my_tiles) {
+                const int rn = (tile + gridDim.x) * kTmaRows + t;
+                if (rn < rows) { rs_n = rowptr[rn]; re_n = rowptr[rn + 1]; }
+            }
+            EpiPre pre;
+            if (row < rows) epi_prefetch<EPI>(row, a, pre);
+            const bool active = row < rows;
+            mbar_wait(&s_full[s], parity);
+            double acc = 0.0;
+            if (active) {
+                if (!s_meta[s].direct) {
+                    const int k0 = s_meta[s].k0, mask = s_meta[s].pad;
+                    const unsigned char *base = st_dyn + (size_t)s * stage_bytes;
+                    const double *sv = reinterpret_cast<const double *>(base) - (k0 & ~1);
+                    const unsigned char *scd = base + (size_t)(cap + 2) * 8 - (k0 & ~15);
+                    const double *sx = reinterpret_cast<const double *>(base + (size_t)(cap + 2) * 8 + (cap + 16)) + t;
+                    for (int k = rs; k < re; ++k) {
+                        const int c = scd[k];
+                        const int d = s_dict[c];
+                        // the run of distance d starts at the even index (r0 + d) & ~1 and r0 is even: this row's operand is at t + (d & 1)
+                        const double xv = (mask >> c & 1) ? sx[c * kSegLen + (d & 1)] : x[row + d];
+                        acc = __dadd_rn(acc, __dmul_rn(sv[k], xv));
+                    }
+                } else {
+                    for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(__ldcs(val + k), x[row + s_dict[__ldcs(code + k)]]));
+                }
+            }
+            mbar_arrive(&s_empty[s]);
+            if (active) epilogue_pre<EPI>(row, acc, a, dsum, pre, wrote);
+        }
     }
     if (EpiTraits<EPI>::reduces) {
         double m = 0.0;
@@ -819,7 +840,7 @@ static int launch_stencil_one(mgcg_ctx *c, const SpmvArgs &a, int tiles, int nse
     if (ctas < 1) ctas = 1;
     int grid = c->sm_count * ctas;
     if (grid > tiles) grid = tiles;
-    launch_k(a.gated, k_spmv_stencil<EPI, STAGES>, grid, kTmaRows, (size_t)smem, c->stream, a, tiles, nseg, c->ws, c->d_scalars);
+    launch_k(a.gated, k_spmv_stencil<EPI, STAGES>, grid, kStencilThreads, (size_t)smem, c->stream, a, tiles, nseg, c->ws, c->d_scalars);
     return MGCG_OK;
 }
 template <int EPI>
