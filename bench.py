@@ -42,6 +42,7 @@ import numpy as np  # noqa: E402
 
 TOL = 1e-8
 NCU_FULL = os.path.join("profiles", "r02_ncu_full_kernels_256.csv")       # refreshed capture of the shipped kernels
+NCU_FULL_STENCIL = os.path.join("profiles", "r02_ncu_full_stencil_256.csv")  # capture of the coded-column (STENCIL) kernels
 NCU_FULL_OLD = os.path.join("profiles", "r01_ncu_full_spmv_tma_256.csv")
 
 
@@ -99,13 +100,13 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic(kernel_substr, args):
+def ncu_traffic(kernel_substr, args, files=None):
     """DRAM bytes (read + write) of one launch of the dominant kernel from the committed `ncu --set full` capture of the c4
     workload; None for other workloads or if no capture is committed."""
     import csv
     if args.config != "c4" or args.size != 256:
         return None, None
-    for rel in (NCU_FULL, NCU_FULL_OLD):
+    for rel in (files or (NCU_FULL, NCU_FULL_OLD)):
         p = os.path.join(ROOT, rel)
         if not os.path.exists(p):
             continue
@@ -479,18 +480,18 @@ def run_ours_single(args):
     torch.cuda.synchronize()
     spmv_iso_ms = s0.elapsed_time(s1) / reps
     kname = pres.reserved[5]
-    coded = (kname == 4)        # coded columns (csrc/spmv_code.cu, --opt spmv_coding=1): 8 + 1 instead of 8 + 4 bytes per entry
+    coded = (kname == 4)        # coded columns (csrc/spmv_code.cu; --opt spmv_coding=1 switches them off): 8 + 1 instead of 8 + 4 bytes per entry
     csr_bytes = 12.0 * nnz + 20.0 * n
     spmv_bytes = (9.0 if coded else 12.0) * nnz + 20.0 * n
     peak, peak_how = measured_peak()
     achieved = spmv_bytes / (spmv_ms * 1e-3) / 1e9
     kernel_text = {1: "k_spmv_tma<EPI_DOT> (fine-level A*p with fused p.Ap, TMA-staged stream kernel)",
-                   4: "k_spmv_tma<EPI_DOT, coded> (fine-level A*p with fused p.Ap, TMA-staged stream kernel on coded columns: "
-                      "9 B per entry instead of CSR's 12)",
+                   4: "k_spmv_stencil<EPI_DOT> (fine-level A*p with fused p.Ap on coded columns: values, 1-byte codes and the x runs of "
+                      "every distance staged by TMA, 9 B per entry instead of CSR's 12)",
                    2: "k_spmv_vector<EPI_DOT> (fine-level A*p with fused p.Ap, lanes-per-row kernel)",
                    3: "k_spmv_rowblock<EPI_DOT> (fine-level A*p with fused p.Ap, TMA-staged long-row kernel)",
                    0: "k_spmv_stream<EPI_DOT>"}.get(kname, "fine-level SpMV + p.Ap")
-    traffic, traffic_src = (None, None) if coded else ncu_traffic("k_spmv_tma<2", args)
+    traffic, traffic_src = ncu_traffic("k_spmv_stencil<2", args, (NCU_FULL_STENCIL,)) if coded else ncu_traffic("k_spmv_tma<2", args)
     roofline = {"bound": "hbm", "kernel": kernel_text, "achieved": achieved,
                 "layout": "coded columns (1 B) + fp64 values" if coded else "CSR (int32 columns + fp64 values)",
                 "bytes_rule": ("9 nnz + 20 N (the layout the kernel reads)" if coded else "12 nnz + 20 N (SURVEY 8d)"),

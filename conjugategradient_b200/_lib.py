@@ -18,7 +18,7 @@ TRANSPORT_AUTO, TRANSPORT_NCCL, TRANSPORT_PEER = 0, 1, 2
 AGG_AUTO, AGG_BLOCKS, AGG_MIS2 = 0, 1, 2
 SMOOTHER_JACOBI, SMOOTHER_RBGS, SMOOTHER_CHEBYSHEV = 0, 1, 2
 CG_CLASSIC, CG_SINGLE_REDUCE = 0, 1
-CODING_OFF, CODING_ON = 0, 1
+CODING_AUTO, CODING_OFF = 0, 1
 
 
 class Options(C.Structure):

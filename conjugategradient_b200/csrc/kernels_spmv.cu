@@ -846,7 +846,7 @@ static int launch_stencil_one(mgcg_ctx *c, const SpmvArgs &a, int tiles, int nse
 template <int EPI>
 static int launch_stencil(mgcg_ctx *c, const SpmvArgs &a, int tiles, int nseg)
 {
-    static const int stages = [] { const char *e = getenv("MGCG_STENCIL_STAGES"); const int v = e ? atoi(e) : 0; return (v >= 2 && v <= 4) ? v : 3; }();
+    static const int stages = [] { const char *e = getenv("MGCG_STENCIL_STAGES"); const int v = e ? atoi(e) : 0; return (v >= 2 && v <= 4) ? v : 2; }();
     static const int ctas_env = [] { const char *e = getenv("MGCG_STENCIL_CTAS"); const int v = e ? atoi(e) : 0; return (v >= 1 && v <= 8) ? v : 0; }();
     if (stages == 2) return launch_stencil_one<EPI, 2>(c, a, tiles, nseg, ctas_env);
     if (stages == 3) return launch_stencil_one<EPI, 3>(c, a, tiles, nseg, ctas_env);

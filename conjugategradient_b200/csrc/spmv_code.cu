@@ -1,6 +1,6 @@
 // spmv_code.cu — coded column indices: an internal layout behind the unchanged CSR interface (north_star subsystem 1: "an
 // optional ... internal layout behind the unchanged CSR API"; the reference hands cusparseDcsrmv plain int32 column indices,
-// Mgcg.cu:10-19).  Opt-in (mgcg_options.spmv_coding = MGCG_CODING_ON).
+// Mgcg.cu:10-19).  On by default (mgcg_options.spmv_coding = MGCG_CODING_AUTO; MGCG_CODING_OFF keeps int32 columns).
 //
 // On a stencil matrix the DISTANCE col - row of an entry takes only a handful of values (7 for the 7-point operator, 27 for the
 // 27-point one, whatever the grid size; a row-block shard adds a constant).  When a matrix has at most 256 distinct distances,
@@ -135,8 +135,8 @@ int spmv_code_build(mgcg_ctx *c, Csr *A, const SpmvPlan &plan)
     A->code = nullptr; A->dict = nullptr; A->ndict = 0;
     c->code_ndict = 0;
     const int min_rows = 1 << 15;          // below this the SpMV is launch-bound and the build would not pay
-    static const bool env_on = [] { const char *e = getenv("MGCG_SPMV_CODED"); return e && e[0] == '1'; }();
-    if (!(c->opt.spmv_coding == MGCG_CODING_ON || env_on) || !spmv_plan_reads_code(plan) || A->rows < min_rows || A->nnz <= 0) return MGCG_OK;
+    static const bool env_off = [] { const char *e = getenv("MGCG_SPMV_CODED"); return e && e[0] == '0'; }();
+    if (c->opt.spmv_coding == MGCG_CODING_OFF || env_off || !spmv_plan_reads_code(plan) || A->rows < min_rows || A->nnz <= 0) return MGCG_OK;
     if (!c->code_state) MGCG_CUDA(pool_alloc(&c->code_state, sizeof(CodeState), c->stream));
     const size_t need = (((size_t)A->nnz + 15) & ~(size_t)15) + 16;     // whole 16-byte pieces: the TMA slices may run past the end
     if (c->code_cap < need) {

@@ -48,11 +48,12 @@ enum { MGCG_SMOOTHER_JACOBI = 0, MGCG_SMOOTHER_RBGS = 1, MGCG_SMOOTHER_CHEBYSHEV
  * has one scalar exchange per iteration instead of two.  Same iterates in exact arithmetic; opt-in, outside the parity contract */
 enum { MGCG_CG_CLASSIC = 0, MGCG_CG_SINGLE_REDUCE = 1 };
 enum { MGCG_SPMV_AUTO = 0, MGCG_SPMV_STREAM = 1, MGCG_SPMV_VECTOR = 2, MGCG_SPMV_ROWS = 3 };
-/* internal layout of the fine operator's column indices.  OFF (default) = the caller's int32 columns.  ON = one byte per entry (the
- * rank of col - row among the matrix's distinct distances) when there are at most 256 of them, the matrix has >= 32768 rows and its
- * SpMV kernel reads codes (the TMA-staged stream kernel); other matrices silently stay on int32 columns.  Same entries, same order,
- * same operands: the results are bit-identical either way.  Opt-in: measured no faster inside a solve */
-enum { MGCG_CODING_OFF = 0, MGCG_CODING_ON = 1 };
+/* internal layout of the fine operator's column indices (csrc/spmv_code.cu).  AUTO (default) = one byte per entry (the rank of
+ * col - row among the matrix's distinct distances) when there are at most 256 of them, the matrix has >= 32768 rows and its SpMV
+ * kernel reads codes (the TMA-staged stream kernels; with at most 8 distances the x operands are staged by TMA as well); other
+ * matrices silently stay on int32 columns.  OFF = the caller's int32 columns.  Same entries, same order, same operands: every row
+ * sum is bit-identical either way (a fused dot follows the launch grid of the kernel that computes it) */
+enum { MGCG_CODING_AUTO = 0, MGCG_CODING_OFF = 1 };
 enum { MGCG_TRANSPORT_AUTO = 0, MGCG_TRANSPORT_NCCL = 1, MGCG_TRANSPORT_PEER = 2 };
 /* aggregation of the multigrid hierarchy: AUTO = geometric blocks when nx,ny,nz are given, else strength-of-connection filter +
  * MIS-2 aggregates (caller-supplied CSR without a grid, e.g. particle matrices); BLOCKS = 8 consecutive rows when there is no

@@ -63,10 +63,10 @@ def main():
     import ctypes as C
     nd = C.c_int(0)
     m.L.mgcg_matrix_codes(m.ctx, C.byref(nd), None, None)
-    if kw.get("spmv_coding", 0) == 1:
+    if cfg.get("coded"):
         # coded columns restate the shard's columns exactly: the solve on int32 columns gives the same bits
         x_coded = tx.clone()
-        kw0 = dict(kw); kw0["spmv_coding"] = 0
+        kw0 = dict(kw); kw0["spmv_coding"] = 1      # MGCG_CODING_OFF
         m.setup(N, r0, tv, tr, tc, S.default_options(norm=2, tolerance=cfg.get("tolerance", 1e-8), max_iteration=2000, **kw0))
         res0 = m.solve(tb, tx.zero_())
         assert res0.iterations_done == res.iterations_done and torch.equal(tx, x_coded), "sharded solve on coded columns differs from int32 columns"

@@ -1,4 +1,4 @@
-"""Coded columns of the fine operator (csrc/spmv_code.cu, opt-in): the codes against the oracle's restatement, the SpMV on them bit for
+"""Coded columns of the fine operator (csrc/spmv_code.cu): the codes against the oracle's restatement, the SpMV on them bit for
 bit against the oracle's storage-order sums and against the int32-column kernel, and whole solves with the layout on and off."""
 import numpy as np
 import pytest
@@ -21,7 +21,7 @@ def _dev(torch, a):
 def _setup(env, v, rp, c, **opt):
     torch, _lib, gen, S, O = env
     m = S.Mgcg(0)
-    opt.setdefault("spmv_coding", 1)
+    opt.setdefault("spmv_coding", 0)
     m.setup(_dev(torch, v), _dev(torch, rp), _dev(torch, c), S.default_options(**opt))
     return m
 
@@ -55,7 +55,7 @@ def test_codes_match_oracle_7pt(env):
     row_of = np.repeat(np.arange(len(rp) - 1), np.diff(rp))
     assert np.array_equal(row_of + got[0][got[1]], c)                      # the layout restates the columns exactly
     m.close()
-    m = _setup(env, v, rp, c, spmv_coding=0)                               # the default: int32 columns
+    m = _setup(env, v, rp, c, spmv_coding=1)                               # MGCG_CODING_OFF: int32 columns
     assert m.matrix_codes() is None
     m.close()
 
@@ -78,7 +78,7 @@ def test_coded_spmv_bitwise(env, case):
     m.spmv(tx, ty)
     y = ty.cpu().numpy()
     assert np.array_equal(y, O.spmv(v, rp, c, x))                          # storage-order sums, bit for bit
-    plain = _setup(env, v, rp, c, spmv_coding=0)
+    plain = _setup(env, v, rp, c, spmv_coding=1)
     assert plain.matrix_codes() is None
     ty2 = _dev(torch, np.zeros(n))
     plain.spmv(tx, ty2)
@@ -127,12 +127,12 @@ def test_solve_identical_with_and_without_codes(env, precond):
     n = nx ** 3
     b = np.random.default_rng(2).standard_normal(n)
     out = []
-    for coding in (1, 0):
+    for coding in (0, 1):                                # MGCG_CODING_AUTO, MGCG_CODING_OFF
         m = _setup(env, v, rp, c, precond=precond, nx=nx, ny=nx, nz=nx, tolerance=1e-10, norm=_lib.NORM_REL_L2, spmv_coding=coding)
-        assert (m.matrix_codes() is not None) == (coding == 1)
+        assert (m.matrix_codes() is not None) == (coding == 0)
         tx = _dev(torch, np.zeros(n))
         res = m.solve(_dev(torch, b), tx)
-        assert res.reserved[5] == (4 if coding == 1 else 1)      # TMA stream kernel on coded / on int32 columns
+        assert res.reserved[5] == (4 if coding == 0 else 1)      # TMA stream kernel on coded / on int32 columns
         out.append((res.iteration, tx.cpu().numpy()))
         m.close()
     assert out[0][0] == out[1][0]
@@ -146,7 +146,7 @@ def test_resetup_with_other_matrix(env):
     rng = np.random.default_rng(9)
     for dims in [(40, 33, 32), (50, 41, 33)]:
         v, rp, c = gen.poisson3d7(*dims)
-        m.setup(_dev(torch, v), _dev(torch, rp), _dev(torch, c), S.default_options(spmv_coding=1))
+        m.setup(_dev(torch, v), _dev(torch, rp), _dev(torch, c), S.default_options())
         want = O.coded_columns(rp, c)
         got = m.matrix_codes()
         assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
@@ -155,6 +155,6 @@ def test_resetup_with_other_matrix(env):
         m.spmv(tx, ty)
         assert np.array_equal(ty.cpu().numpy(), O.spmv(v, rp, c, x))
     v, rp, c = _few_distances(50000, 5, 300)
-    m.setup(_dev(torch, v), _dev(torch, rp), _dev(torch, c), S.default_options(spmv_coding=1))
+    m.setup(_dev(torch, v), _dev(torch, rp), _dev(torch, c), S.default_options())
     assert m.matrix_codes() is None
     m.close()

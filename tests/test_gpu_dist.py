@@ -47,11 +47,11 @@ CASES = [
     ("mg_single_reduce_peer", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "cg_variant": 1}, "transport": 2,
                                "solves": 2}),
     ("mg_single_reduce_replicated_nccl", {"n": 32, "options": {"precond": 1, "dist_transport": 1, "cg_variant": 1}}),
-    # coded columns of the shard's fine operator (opt-in): x runs staged by TMA from the shifted view incl. ghost rows pushed by the
+    # coded columns of the shard's fine operator (the default for 7-point shards of >= 32768 rows): x runs staged by TMA from the shifted view incl. ghost rows pushed by the
     # neighbours' kernels; the worker also checks the result bit for bit against the same sharded solve on int32 columns
-    ("mg_coded_columns_peer", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "spmv_coding": 1}, "transport": 2,
+    ("mg_coded_columns_peer", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2}, "transport": 2,
                                "solves": 2, "coded": 7}),
-    ("plain_cg_coded_columns_nccl", {"n": 48, "options": {"precond": 0, "dist_transport": 1, "spmv_coding": 1}, "coded": 7}),
+    ("plain_cg_coded_columns_nccl", {"n": 48, "options": {"precond": 0, "dist_transport": 1}, "coded": 7}),
     ("mg_chebyshev_single_reduce_w4", {"n": 48, "world": 4, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "mg_smoother": 2,
                                                                         "cg_variant": 1}, "transport": 2}),
 ]
