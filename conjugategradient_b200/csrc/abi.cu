@@ -151,7 +151,7 @@ void mgcg_destroy(mgcg_ctx *c)
     if (c->stream) cudaStreamSynchronize(c->stream);
     dist_free(c);
     mg_free(c);
-    spmv_code_free(c);
+    spmv_code_free(&c->code0);
     if (!c->child) pool_trim_stream(c->device, c->stream);
     if (c->graph_exec) cudaGraphExecDestroy(c->graph_exec);
     if (c->graph) cudaGraphDestroy(c->graph);
@@ -210,7 +210,7 @@ int mgcg_setup(mgcg_ctx *c, int count, int elements_count,
         cudaEvent_t e0, e1;
         MGCG_CUDA(cudaEventCreate(&e0)); MGCG_CUDA(cudaEventCreate(&e1));
         MGCG_CUDA(cudaEventRecord(e0, c->stream));
-        int s = spmv_code_build(c, &c->A, c->planA);       // coded columns of the fine operator (opt-in; timed with the set-up)
+        int s = spmv_code_build(c, &c->code0, &c->A, &c->planA);       // coded columns of the fine operator (timed with the set-up)
         if (s == MGCG_OK) s = mg_build(c);
         if (s != MGCG_OK) { mg_free(c); cudaEventDestroy(e0); cudaEventDestroy(e1); return s; }
         MGCG_CUDA(cudaEventRecord(e1, c->stream));
@@ -219,7 +219,7 @@ int mgcg_setup(mgcg_ctx *c, int count, int elements_count,
         cudaEventDestroy(e0); cudaEventDestroy(e1);
     } else {
         mg_free(c);
-        MGCG_CHECK(spmv_code_build(c, &c->A, c->planA));
+        MGCG_CHECK(spmv_code_build(c, &c->code0, &c->A, &c->planA));
     }
     c->is_setup = true;
     return MGCG_OK;
@@ -315,7 +315,7 @@ int mgcg_matrix_codes(mgcg_ctx *c, int *ndict, int *dict, unsigned char *codes)
     if (!c || !c->is_setup) { set_error("mgcg_matrix_codes: context not set up"); return MGCG_ERR_INVALID; }
     MGCG_CUDA(cudaSetDevice(c->device));
     const bool coded = c->A.code && c->A.dict;
-    if (ndict) *ndict = coded ? c->code_ndict : 0;
+    if (ndict) *ndict = coded ? c->A.ndict : 0;
     if (!coded) return MGCG_OK;
     MGCG_CUDA(cudaStreamSynchronize(c->stream));
     if (dict) MGCG_CUDA(cudaMemcpy(dict, c->A.dict, sizeof(int) * 256, cudaMemcpyDeviceToHost));

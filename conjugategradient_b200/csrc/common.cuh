@@ -94,7 +94,22 @@ struct Csr {
     const unsigned char *code = nullptr;
     const int *dict = nullptr;       // 256 ints
     int ndict = 0;                   // distinct distances
+    // ... grouped into RUNS of x: distances at most kRunSpan apart share one contiguous run per tile of rows (STENCIL kernel).
+    // seg_min[g] = smallest distance of run g; seg_off[c] = where code c's operand sits: g * (tile rows + kRunPad) + offset in the run
+    const int *seg_min = nullptr;    // kSegMax ints
+    const int *seg_off = nullptr;    // 256 ints, in units of "g * 1024 + offset" (the kernel rescales by its run length)
+    int nseg = 0;                    // runs (0: too many for the STENCIL kernel)
 };
+
+// device memory behind one matrix's coded columns (spmv_code.cu): kept across set-ups, grown on demand
+struct CodeStore {
+    unsigned char *buf = nullptr;
+    void *state = nullptr;
+    size_t cap = 0;
+};
+constexpr int kSegMax = 12;          // x runs the STENCIL kernel stages per tile (7-point: 5, 27-point: 9)
+constexpr int kRunSpan = 6;          // distances of one run lie within this span
+constexpr int kRunPad = 8;           // run length = tile rows + kRunPad (span + alignment slack, even)
 
 // SpMV plan: kernel choice and launch geometry for one matrix
 struct SpmvPlan {
@@ -110,6 +125,7 @@ struct SpmvPlan {
     int rows_unroll = 4;            // ROWS: entries a lane takes per chunk (4 or 8)
     int rows_smem = 0;              // ROWS: dynamic shared memory of the launch
     int rows_carveout = 0;          // ROWS: shared-memory share (percent) asked of the unified L1 / shared array
+    int stencil_rows = 0;           // > 0: the matrix is coded with few runs — STENCIL kernel on tiles of this many rows (256 or 64)
     int grid = 0;
 };
 
@@ -212,11 +228,7 @@ struct mgcg_ctx {
     void *host_path = nullptr;
     void *ell_path = nullptr;        // device system owned by mgcg_solve_host_ell (formats.cu)
     void *host_path_dist = nullptr;  // device copies owned by mgcg_solve_host_dist (dist.cu)
-    // coded columns of the fine-level operator (spmv_code.cu)
-    unsigned char *code_buf = nullptr;
-    void *code_state = nullptr;
-    size_t code_cap = 0;
-    int code_ndict = 0;
+    mgcg::CodeStore code0;           // coded columns of the fine-level operator (spmv_code.cu)
 };
 
 namespace mgcg {
@@ -250,10 +262,11 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel);
 int spmv_launch(mgcg_ctx *c, const SpmvPlan &plan, int epi, const SpmvArgs &a);
 int spmv_kernel_id(const SpmvPlan &plan, const Csr &A);
 bool spmv_plan_reads_code(const SpmvPlan &plan);   // the kernel this plan selects understands coded columns
+int spmv_plan_stencil_rows(const SpmvPlan &plan, int rows, int nnz);   // tile rows of the STENCIL kernel for this matrix shape (0: none)
 
 // ---- spmv_code.cu
-int spmv_code_build(mgcg_ctx *c, Csr *A, const SpmvPlan &plan);
-void spmv_code_free(mgcg_ctx *c);
+int spmv_code_build(mgcg_ctx *c, CodeStore *store, Csr *A, SpmvPlan *plan);
+void spmv_code_free(CodeStore *store);
 
 // ---- mg_setup.cu / mg_cycle.cu
 int mg_build(mgcg_ctx *c);

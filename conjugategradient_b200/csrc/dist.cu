@@ -560,7 +560,7 @@ static int dist_setup(mgcg_ctx *c, int global_count, int row_offset, int local_c
     c->A.rows = local_count; c->A.cols = global_count; c->A.nnz = local_nnz;
     c->A.val = val; c->A.rowptr = rowptr; c->A.col = col;
     c->planA = spmv_make_plan(c, local_count, local_nnz, o.spmv_kernel);
-    MGCG_CHECK(spmv_code_build(c, &c->A, c->planA));     // coded columns (opt-in): the distance col - (local row) is as regular on a shard
+    MGCG_CHECK(spmv_code_build(c, &c->code0, &c->A, &c->planA));     // coded columns: the distance col - (local row) is as regular on a shard
 
     int nx = 0, ny = 0;
     if (o.nx > 0 && o.ny > 0 && o.nz > 0 && (long long)o.nx * o.ny * o.nz == global_count) { nx = o.nx; ny = o.ny; }

@@ -352,33 +352,33 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// STENCIL (coded columns with at most kSegMax distinct distances: the 7-point and 5-point operators).  The ncu capture of the coded
-// stream kernel showed it latency-bound, not bandwidth-bound: 40 % of the stall samples on the x gathers, 22 % on the wait for the
-// next stage — the ring cannot run far enough ahead while its stages are held by threads waiting for gathers.  Here a tile's x
-// operands are staged too: for every distance d of the dictionary the rows r0 .. r0+255 of the tile read the CONTIGUOUS run
-// x[r0+d .. r0+d+255], so the producer thread requests one bulk copy per distance next to the tile's values and codes.  No thread
-// issues a dependent global load any more: rowptr -> (value, code) -> x all arrive through the TMA ring, a row is summed from shared
-// memory in storage order with explicit mul/add roundings (the same bits as every other STREAM kernel), and the ring's stages are in
-// flight for almost their whole life.  Runs that would leave the valid index range of x (tiles at the ends of the matrix; their rows
-// have no entry at that distance, or only some) are not staged: those entries fall back to a gather.
-constexpr int kSegMax = 8;                    // distances staged per tile
-constexpr int kSegLen = kTmaRows + 2;         // doubles per run: the run starts at an even index (16-byte aligned source)
-
-constexpr int kStencilThreads = kTmaRows + 32;      // 8 consumer warps (one thread per row of the tile) + 1 producer warp
-
-// The producer is a warp of its own: with nine bulk copies per tile behind two row-pointer loads, one consumer thread doing the
-// requests between its own rows made the request path the block's critical path (2.1 us per tile whatever the ring depth).  Its
-// lanes share the work — lane 0 the values and the barrier's byte count, lane 1 the codes, lane 2 + c the run of distance c — and the
-// next tile's row pointers are loaded before the wait for the stage to drain.
-template <int EPI, int kStages>
-__global__ void __launch_bounds__(kStencilThreads) k_spmv_stencil(SpmvArgs a, int num_tiles, int nseg, ReduceWs ws, Scalars *sc)
+// STENCIL (coded columns whose distances fall into at most kSegMax runs: the 5-, 7- and 27-point operators).  The ncu capture of the
+// coded stream kernel showed it latency-bound, not bandwidth-bound: 40 % of the stall samples on the x gathers, 22 % on the wait for
+// the next stage — the ring cannot run far enough ahead while its stages are held by threads waiting for gathers.  Here a tile's x
+// operands are staged too: the rows r0 .. r0+R-1 of a tile read, for every distance d of the dictionary, the CONTIGUOUS run
+// x[r0+d .. r0+d+R-1]; distances within kRunSpan of each other share one run (the 27-point operator: 9 runs of 3 distances), so the
+// producer requests one bulk copy per run next to the tile's values and codes.  No thread issues a dependent global load any more:
+// rowptr -> (value, code) -> x all arrive through the TMA ring, a row is summed from shared memory in storage order with explicit
+// mul/add roundings (the same bits as every other STREAM kernel), and the ring's stages are in flight for almost their whole life.
+// Runs that would leave the valid index range of x (tiles at the ends of the matrix, whose rows have no entry at that distance, or
+// only some) are not staged: on such a tile the entries of that run fall back to a gather.
+// The producer is a warp of its own: with up to fourteen bulk copies per tile behind two row-pointer loads, one consumer thread doing
+// the requests between its own rows made the request path the block's critical path (2.1 us per tile whatever the ring depth).  Its
+// lanes share the work — lane 0 the values and the barrier's byte count, lane 1 the codes, lane 2 + g run g — and the next tile's row
+// pointers are loaded before the wait for the stage to drain.
+// R = rows per tile = consumer threads: 256 for rows of up to ~7 entries, 64 up to ~29 (a stage holds kTmaCap entries either way).
+template <int EPI, int kStages, int R>
+__global__ void __launch_bounds__(R + 32) k_spmv_stencil(SpmvArgs a, int num_tiles, ReduceWs ws, Scalars *sc)
 {
     constexpr int cap = kTmaCap;
+    constexpr int kRunLen = R + kRunPad;
     extern __shared__ __align__(16) unsigned char st_dyn[];
-    const size_t stage_bytes = (size_t)(cap + 2) * 8 + (cap + 16) + (size_t)nseg * kSegLen * 8;     // values | codes | x runs
+    const int nseg = a.A.nseg;
+    const size_t stage_bytes = (size_t)(cap + 2) * 8 + (cap + 16) + (size_t)nseg * kRunLen * 8;     // values | codes | x runs
     __shared__ __align__(8) unsigned long long s_full[kStages], s_empty[kStages];
-    __shared__ TmaMeta s_meta[kStages];       // .pad = bit c set: the run of distance c is staged
-    __shared__ int s_dict[kSegMax];
+    __shared__ TmaMeta s_meta[kStages];       // .pad = bit g set: run g is staged
+    __shared__ int s_idx[256];                // code -> position of its operand in the stage's runs (for the tile's row 0)
+    __shared__ int s_min[kSegMax];
     const int t = threadIdx.x;
     const double *__restrict__ val = a.A.val;
     const unsigned char *__restrict__ code = a.A.code;
@@ -392,32 +392,34 @@ __global__ void __launch_bounds__(kStencilThreads) k_spmv_stencil(SpmvArgs a, in
     pdl_wait(); pdl_launch_dependents();
     if (a.gated && sc->done) return;
     if (t == 0) {
-        for (int s = 0; s < kStages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], kTmaRows); }
+        for (int s = 0; s < kStages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], R); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (t < kSegMax) s_dict[t] = t < nseg ? a.A.dict[t] : 0;
+    for (int i = t; i < 256; i += R + 32) { const int o = a.A.seg_off[i]; s_idx[i] = (o >> 10) * kRunLen + (o & 1023); }
+    if (t < kSegMax) s_min[t] = t < nseg ? a.A.seg_min[t] : 0;
     bool wrote = false;
     halo_wait(a.gw, sc);             // the x runs are requested below: ghost rows must have landed ...
     if (a.gw.ctl && (t & 31) == 0) asm volatile("fence.proxy.async;" ::: "memory");     // ... and be visible to the bulk copies
     const int my_tiles = (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int full_mask = (1 << nseg) - 1;
     __syncthreads();
 
-    if (t >= kTmaRows) {
+    if (t >= R) {
         // ---- producer warp
-        const int lane = t - kTmaRows;
+        const int lane = t - R;
         int k0 = 0, k1 = 0;
         if (my_tiles > 0) {
-            const int r0 = blockIdx.x * kTmaRows;
-            k0 = rowptr[r0]; k1 = rowptr[r0 + min(kTmaRows, rows - r0)];
+            const int r0 = blockIdx.x * R;
+            k0 = rowptr[r0]; k1 = rowptr[r0 + min(R, rows - r0)];
         }
         for (int j = 0; j < my_tiles; ++j) {
             const int s = j % kStages;
             const int tile = blockIdx.x + j * gridDim.x;
-            const int r0 = tile * kTmaRows;
+            const int r0 = tile * R;
             int k0n = 0, k1n = 0;
             if (j + 1 < my_tiles) {
-                const int rn = (tile + gridDim.x) * kTmaRows;
-                k0n = rowptr[rn]; k1n = rowptr[rn + min(kTmaRows, rows - rn)];
+                const int rn = (tile + gridDim.x) * R;
+                k0n = rowptr[rn]; k1n = rowptr[rn + min(R, rows - rn)];
             }
             if (j >= kStages) mbar_wait(&s_empty[s], (unsigned)(((j / kStages) - 1) & 1));     // the stage's previous tile is consumed
             const int ka = k0 & ~1, kc = k0 & ~15;
@@ -425,18 +427,18 @@ __global__ void __launch_bounds__(kStencilThreads) k_spmv_stencil(SpmvArgs a, in
             // (the code array is allocated in whole 16-byte pieces with one to spare: its slices never run out of it)
             const bool fits = (k1 - ka) <= cap && (k1 - kc) <= cap && k1 > k0 && ((long long)ka * 8 + vb <= nnz_end * 8);
             unsigned char *base = st_dyn + (size_t)s * stage_bytes;
-            const int c = lane - 2;
+            const int g = lane - 2;
             int s0 = 0;
             bool ok = false;
-            if (fits && c >= 0 && c < nseg) {
-                s0 = (r0 + s_dict[c]) & ~1;
-                ok = s0 >= x_lo && s0 + kSegLen <= x_hi;
+            if (fits && g >= 0 && g < nseg) {
+                s0 = (r0 + s_min[g]) & ~1;
+                ok = s0 >= x_lo && s0 + kRunLen <= x_hi;
             }
             const unsigned mask = __ballot_sync(0xffffffffu, ok) >> 2;
             if (lane == 0) {
                 s_meta[s].k0 = k0; s_meta[s].k1 = k1; s_meta[s].direct = fits ? 0 : 1; s_meta[s].pad = (int)mask;
                 if (fits) {
-                    mbar_arrive_expect_tx(&s_full[s], vb + cb + (unsigned)__popc(mask) * (unsigned)(kSegLen * 8));
+                    mbar_arrive_expect_tx(&s_full[s], vb + cb + (unsigned)__popc(mask) * (unsigned)(kRunLen * 8));
                     tma_load_1d(base, val + ka, vb, &s_full[s]);
                 } else {
                     mbar_arrive(&s_full[s]);
@@ -445,7 +447,7 @@ __global__ void __launch_bounds__(kStencilThreads) k_spmv_stencil(SpmvArgs a, in
                 if (fits) tma_load_1d(base + (size_t)(cap + 2) * 8, code + kc, cb, &s_full[s]);
             } else if (ok) {
                 double *sx = reinterpret_cast<double *>(base + (size_t)(cap + 2) * 8 + (cap + 16));
-                tma_load_1d(sx + c * kSegLen, x + s0, kSegLen * 8, &s_full[s]);
+                tma_load_1d(sx + g * kRunLen, x + s0, kRunLen * 8, &s_full[s]);
             }
             k0 = k0n; k1 = k1n;
         }
@@ -453,18 +455,18 @@ __global__ void __launch_bounds__(kStencilThreads) k_spmv_stencil(SpmvArgs a, in
         // ---- consumers: one thread per row of the tile
         int rs_n = 0, re_n = 0;
         {
-            const int r = blockIdx.x * kTmaRows + t;
+            const int r = blockIdx.x * R + t;
             if (my_tiles > 0 && r < rows) { rs_n = rowptr[r]; re_n = rowptr[r + 1]; }
         }
         for (int j = 0; j < my_tiles; ++j) {
             const int s = j % kStages;
             const unsigned parity = (unsigned)((j / kStages) & 1);
             const int tile = blockIdx.x + j * gridDim.x;
-            const int row = tile * kTmaRows + t;
+            const int row = tile * R + t;
             const int rs = rs_n, re = re_n;
             rs_n = re_n = 0;
             if (j + 1 < my_tiles) {
-                const int rn = (tile + gridDim.x) * kTmaRows + t;
+                const int rn = (tile + gridDim.x) * R + t;
                 if (rn < rows) { rs_n = rowptr[rn]; re_n = rowptr[rn + 1]; }
             }
             EpiPre pre;
@@ -479,15 +481,18 @@ __global__ void __launch_bounds__(kStencilThreads) k_spmv_stencil(SpmvArgs a, in
                     const double *sv = reinterpret_cast<const double *>(base) - (k0 & ~1);
                     const unsigned char *scd = base + (size_t)(cap + 2) * 8 - (k0 & ~15);
                     const double *sx = reinterpret_cast<const double *>(base + (size_t)(cap + 2) * 8 + (cap + 16)) + t;
-                    for (int k = rs; k < re; ++k) {
-                        const int c = scd[k];
-                        const int d = s_dict[c];
-                        // the run of distance d starts at the even index (r0 + d) & ~1 and r0 is even: this row's operand is at t + (d & 1)
-                        const double xv = (mask >> c & 1) ? sx[c * kSegLen + (d & 1)] : x[row + d];
-                        acc = __dadd_rn(acc, __dmul_rn(sv[k], xv));
+                    if (mask == full_mask) {
+#pragma unroll 4
+                        for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(sv[k], sx[s_idx[scd[k]]]));
+                    } else {
+                        for (int k = rs; k < re; ++k) {      // a tile at an end of the matrix: runs that were not staged are gathered
+                            const int c = scd[k];
+                            const double xv = (mask >> (a.A.seg_off[c] >> 10) & 1) ? sx[s_idx[c]] : x[row + a.A.dict[c]];
+                            acc = __dadd_rn(acc, __dmul_rn(sv[k], xv));
+                        }
                     }
                 } else {
-                    for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(__ldcs(val + k), x[row + s_dict[__ldcs(code + k)]]));
+                    for (int k = rs; k < re; ++k) acc = __dadd_rn(acc, __dmul_rn(__ldcs(val + k), x[row + a.A.dict[__ldcs(code + k)]]));
                 }
             }
             mbar_arrive(&s_empty[s]);
@@ -825,32 +830,39 @@ static int launch_coded_one(mgcg_ctx *c, const SpmvArgs &a, int tiles, int ctas)
     return MGCG_OK;
 }
 // STENCIL kernel: stages x resident blocks from what fits (tuning knobs MGCG_STENCIL_STAGES 2..4, MGCG_STENCIL_CTAS)
-template <int EPI, int STAGES>
-static int launch_stencil_one(mgcg_ctx *c, const SpmvArgs &a, int tiles, int nseg, int ctas_env)
+template <int EPI, int STAGES, int R>
+static int launch_stencil_one(mgcg_ctx *c, const SpmvArgs &a, int ctas_env)
 {
     static int set_bytes[64] = {0};
-    const int smem = STAGES * ((kTmaCap + 2) * 8 + (kTmaCap + 16) + nseg * kSegLen * 8);
+    const int smem = STAGES * ((kTmaCap + 2) * 8 + (kTmaCap + 16) + a.A.nseg * (R + kRunPad) * 8);
     const int d = c->device & 63;
     if (smem > set_bytes[d]) {
-        MGCG_CUDA(cudaFuncSetAttribute(k_spmv_stencil<EPI, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        MGCG_CUDA(cudaFuncSetAttribute(k_spmv_stencil<EPI, STAGES, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         set_bytes[d] = smem;
     }
-    int ctas = (224 * 1024) / (smem + 2 * 1024);
+    int ctas = (224 * 1024) / (smem + 3 * 1024);
+    if (ctas > 2048 / (R + 32)) ctas = 2048 / (R + 32);
     if (ctas_env > 0) ctas = ctas_env;
     if (ctas < 1) ctas = 1;
+    const int tiles = div_up(a.A.rows, R);
     int grid = c->sm_count * ctas;
     if (grid > tiles) grid = tiles;
-    launch_k(a.gated, k_spmv_stencil<EPI, STAGES>, grid, kStencilThreads, (size_t)smem, c->stream, a, tiles, nseg, c->ws, c->d_scalars);
+    launch_k(a.gated, k_spmv_stencil<EPI, STAGES, R>, grid, R + 32, (size_t)smem, c->stream, a, tiles, c->ws, c->d_scalars);
     return MGCG_OK;
 }
 template <int EPI>
-static int launch_stencil(mgcg_ctx *c, const SpmvArgs &a, int tiles, int nseg)
+static int launch_stencil(mgcg_ctx *c, const SpmvArgs &a, int tile_rows)
 {
     static const int stages = [] { const char *e = getenv("MGCG_STENCIL_STAGES"); const int v = e ? atoi(e) : 0; return (v >= 2 && v <= 4) ? v : 2; }();
-    static const int ctas_env = [] { const char *e = getenv("MGCG_STENCIL_CTAS"); const int v = e ? atoi(e) : 0; return (v >= 1 && v <= 8) ? v : 0; }();
-    if (stages == 2) return launch_stencil_one<EPI, 2>(c, a, tiles, nseg, ctas_env);
-    if (stages == 3) return launch_stencil_one<EPI, 3>(c, a, tiles, nseg, ctas_env);
-    return launch_stencil_one<EPI, 4>(c, a, tiles, nseg, ctas_env);
+    static const int ctas_env = [] { const char *e = getenv("MGCG_STENCIL_CTAS"); const int v = e ? atoi(e) : 0; return (v >= 1 && v <= 16) ? v : 0; }();
+    if (tile_rows == 64) {
+        if (stages == 2) return launch_stencil_one<EPI, 2, 64>(c, a, ctas_env);
+        if (stages == 3) return launch_stencil_one<EPI, 3, 64>(c, a, ctas_env);
+        return launch_stencil_one<EPI, 4, 64>(c, a, ctas_env);
+    }
+    if (stages == 2) return launch_stencil_one<EPI, 2, 256>(c, a, ctas_env);
+    if (stages == 3) return launch_stencil_one<EPI, 3, 256>(c, a, ctas_env);
+    return launch_stencil_one<EPI, 4, 256>(c, a, ctas_env);
 }
 
 template <int EPI>
@@ -875,15 +887,17 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
         return MGCG_ERR_INVALID;
     }
     const bool aligned = ((((uintptr_t)a.A.val) | ((uintptr_t)a.A.col)) & 15u) == 0;
+    // coded columns in few runs: values, codes AND the x runs staged by TMA — unless x is misaligned or rewritten by this launch
+    if (plan.stencil_rows > 0 && a.A.code && a.A.nseg > 0 && aligned && (((uintptr_t)a.x) & 15u) == 0 &&
+        (const double *)a.y != a.x && a.color < 0) {
+        MGCG_CHECK(launch_stencil<EPI>(c, a, plan.stencil_rows));
+        c->launches++;
+        MGCG_LAUNCH_CHECK();
+        return MGCG_OK;
+    }
     if (plan.kernel == MGCG_SPMV_STREAM && plan.tma && aligned) {
         const int tiles = div_up(a.A.rows, kTmaRows);
-        if (a.A.code && a.A.dict && spmv_plan_reads_code(plan)) {
-            // x staged as well when the dictionary is short, x is 16-byte aligned and not rewritten by this launch
-            static const bool no_stencil = getenv("MGCG_NO_STENCIL") != nullptr;
-            const bool in_place = (const double *)a.y == a.x || a.color >= 0;
-            if (!no_stencil && a.A.ndict > 0 && a.A.ndict <= kSegMax && (((uintptr_t)a.x) & 15u) == 0 && !in_place)
-                MGCG_CHECK(launch_stencil<EPI>(c, a, tiles, a.A.ndict));
-            else
+        if (a.A.code && a.A.dict && spmv_plan_reads_code(plan)) {       // coded, but not eligible for the STENCIL kernel: gathers
             MGCG_CHECK(launch_coded<EPI>(c, a, tiles));
             c->launches++;
             MGCG_LAUNCH_CHECK();
@@ -944,12 +958,21 @@ bool spmv_plan_reads_code(const SpmvPlan &plan)
     return plan.kernel == MGCG_SPMV_STREAM && plan.tma && !plan.tma_short && plan.tma_wide_cap == 0;
 }
 
+// tile rows of the STENCIL kernel for a matrix of this shape: a stage holds kTmaCap entries
+int spmv_plan_stencil_rows(const SpmvPlan &plan, int rows, int nnz)
+{
+    const double avg = rows > 0 ? (double)nnz / rows : 0.0;
+    if (spmv_plan_reads_code(plan)) return 256;
+    if (plan.kernel == MGCG_SPMV_ROWS && avg * 64 <= kTmaCap - 64) return 64;
+    return 0;
+}
+
 // which kernel family spmv_launch picks for this plan / matrix: 0 stream, 1 TMA-staged stream, 2 lanes-per-row vector, 3 TMA-staged rows,
 // 4 TMA-staged stream on coded columns
 int spmv_kernel_id(const SpmvPlan &plan, const Csr &A)
 {
     const bool aligned = ((((uintptr_t)A.val) | ((uintptr_t)A.col)) & 15u) == 0;
-    if (aligned && A.code && A.dict && spmv_plan_reads_code(plan)) return 4;
+    if (aligned && A.code && A.dict && (plan.stencil_rows > 0 || spmv_plan_reads_code(plan))) return 4;
     if (plan.kernel == MGCG_SPMV_STREAM) return (plan.tma && aligned) ? 1 : 0;
     if (plan.kernel == MGCG_SPMV_ROWS && aligned) return 3;
     return 2;

@@ -26,9 +26,11 @@ constexpr int kCodeThreads = 256;
 
 struct CodeState {
     int keys[kCodeSlots];
-    int count, overflow;
+    int count, overflow, nseg, pad0;      // (read back by the host in one copy)
     int dict[kCodeMax];
     int ndict, pad;
+    int seg_min[kSegMax];
+    int seg_off[kCodeMax];
 };
 
 __device__ __forceinline__ unsigned code_hash(int d) { return ((unsigned)d * 2654435761u) >> 22; }   // 10 bits
@@ -57,7 +59,7 @@ __global__ void __launch_bounds__(kCodeThreads) k_code_clear(CodeState *st)
 {
     for (int i = threadIdx.x; i < kCodeSlots; i += kCodeThreads) st->keys[i] = kCodeEmpty;
     if (threadIdx.x < kCodeMax) st->dict[threadIdx.x] = 0;
-    if (threadIdx.x == 0) { st->count = 0; st->overflow = 0; st->ndict = 0; }
+    if (threadIdx.x == 0) { st->count = 0; st->overflow = 0; st->ndict = 0; st->nseg = 0; }
 }
 
 __global__ void __launch_bounds__(kCodeThreads) k_code_collect(Csr A, CodeState *st)
@@ -104,6 +106,25 @@ __global__ void __launch_bounds__(kCodeSlots) k_code_sort(CodeState *st)
     if (t == 0) st->ndict = n;
 }
 
+// Group the sorted distances into runs: a run takes distances while they stay within kRunSpan of its first one.  One thread.
+__global__ void k_code_runs(CodeState *st)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const int n = st->ndict;
+    int g = -1, first = 0;
+    bool ok = n > 0 && st->overflow == 0;
+    for (int i = 0; i < n && ok; ++i) {
+        const int d = st->dict[i];
+        if (g < 0 || (long long)d - first > kRunSpan) {
+            if (++g >= kSegMax) { ok = false; break; }
+            first = d;
+            st->seg_min[g] = d;
+        }
+        st->seg_off[i] = g * 1024 + (d - first) + (first & 1);      // the run starts at the even index (r0 + first) & ~1, r0 even
+    }
+    st->nseg = ok ? g + 1 : 0;
+}
+
 __global__ void __launch_bounds__(kCodeThreads) k_code_encode(Csr A, const CodeState *st, unsigned char *code)
 {
     __shared__ int s_dict[kCodeMax];
@@ -127,49 +148,56 @@ __global__ void __launch_bounds__(kCodeThreads) k_code_encode(Csr A, const CodeS
     }
 }
 
-// Restate A's columns as codes when the option asks for it, the kernel `plan` selects can read them and the matrix has few enough
-// distinct distances.  On success A->code / A->dict point into the context's code store (kept across set-ups, grown on demand);
-// otherwise they stay null and the plain CSR kernels run.  One host synchronisation (the verdict of the collect pass).
-int spmv_code_build(mgcg_ctx *c, Csr *A, const SpmvPlan &plan)
+// Restate A's columns as codes unless the option forbids it, when a kernel that reads them fits the matrix shape and the matrix has
+// few enough distinct distances.  On success A->code / A->dict (and the run tables) point into `store` (kept across set-ups, grown on
+// demand) and plan->stencil_rows is set when the STENCIL kernel applies; otherwise they stay null and the plain CSR kernels run.
+// One host synchronisation (the verdict of the collect pass).
+int spmv_code_build(mgcg_ctx *c, CodeStore *store, Csr *A, SpmvPlan *plan)
 {
-    A->code = nullptr; A->dict = nullptr; A->ndict = 0;
-    c->code_ndict = 0;
+    A->code = nullptr; A->dict = nullptr; A->ndict = 0; A->seg_min = nullptr; A->seg_off = nullptr; A->nseg = 0;
+    plan->stencil_rows = 0;
     const int min_rows = 1 << 15;          // below this the SpMV is launch-bound and the build would not pay
     static const bool env_off = [] { const char *e = getenv("MGCG_SPMV_CODED"); return e && e[0] == '0'; }();
-    if (c->opt.spmv_coding == MGCG_CODING_OFF || env_off || !spmv_plan_reads_code(plan) || A->rows < min_rows || A->nnz <= 0) return MGCG_OK;
-    if (!c->code_state) MGCG_CUDA(pool_alloc(&c->code_state, sizeof(CodeState), c->stream));
+    static const bool no_stencil = getenv("MGCG_NO_STENCIL") != nullptr;
+    const int tile_rows = no_stencil ? 0 : spmv_plan_stencil_rows(*plan, A->rows, A->nnz);
+    if (c->opt.spmv_coding == MGCG_CODING_OFF || env_off || A->rows < min_rows || A->nnz <= 0) return MGCG_OK;
+    if (!spmv_plan_reads_code(*plan) && tile_rows == 0) return MGCG_OK;
+    if (!store->state) MGCG_CUDA(pool_alloc(&store->state, sizeof(CodeState), c->stream));
     const size_t need = (((size_t)A->nnz + 15) & ~(size_t)15) + 16;     // whole 16-byte pieces: the TMA slices may run past the end
-    if (c->code_cap < need) {
-        if (c->code_buf) { pool_free(c->code_buf, c->stream); c->code_buf = nullptr; c->code_cap = 0; }
-        MGCG_CUDA(pool_alloc((void **)&c->code_buf, need, c->stream));
-        c->code_cap = need;
+    if (store->cap < need) {
+        if (store->buf) { pool_free(store->buf, c->stream); store->buf = nullptr; store->cap = 0; }
+        MGCG_CUDA(pool_alloc((void **)&store->buf, need, c->stream));
+        store->cap = need;
     }
-    CodeState *st = (CodeState *)c->code_state;
+    CodeState *st = (CodeState *)store->state;
     int grid = div_up(A->rows, kCodeThreads);
     if (grid > c->sm_count * 8) grid = c->sm_count * 8;
     k_code_clear<<<1, kCodeThreads, 0, c->stream>>>(st);
     k_code_collect<<<grid, kCodeThreads, 0, c->stream>>>(*A, st);
+    k_code_sort<<<1, kCodeSlots, 0, c->stream>>>(st);
+    k_code_runs<<<1, 32, 0, c->stream>>>(st);
     MGCG_LAUNCH_CHECK();
-    int verdict[2] = {0, 1};
+    int verdict[3] = {0, 1, 0};
     MGCG_CUDA(cudaMemcpyAsync(verdict, &st->count, sizeof(verdict), cudaMemcpyDeviceToHost, c->stream));
     MGCG_CUDA(cudaStreamSynchronize(c->stream));
     if (verdict[1] != 0 || verdict[0] > kCodeMax || verdict[0] <= 0) return MGCG_OK;     // too many distances: stay with CSR
-    k_code_sort<<<1, kCodeSlots, 0, c->stream>>>(st);
-    MGCG_CUDA(cudaMemsetAsync(c->code_buf + (need - 32), 0, 32, c->stream));              // the slack past the last entry
-    k_code_encode<<<grid, kCodeThreads, 0, c->stream>>>(*A, st, c->code_buf);
+    const bool stencil = tile_rows > 0 && verdict[2] > 0;
+    if (!stencil && !spmv_plan_reads_code(*plan)) return MGCG_OK;                        // (a ROWS-shaped matrix with too many runs)
+    MGCG_CUDA(cudaMemsetAsync(store->buf + (need - 32), 0, 32, c->stream));              // the slack past the last entry
+    k_code_encode<<<grid, kCodeThreads, 0, c->stream>>>(*A, st, store->buf);
     MGCG_LAUNCH_CHECK();
-    A->code = c->code_buf;
+    A->code = store->buf;
     A->dict = st->dict;
     A->ndict = verdict[0];
-    c->code_ndict = verdict[0];
+    if (stencil) { A->seg_min = st->seg_min; A->seg_off = st->seg_off; A->nseg = verdict[2]; plan->stencil_rows = tile_rows; }
     return MGCG_OK;
 }
 
-void spmv_code_free(mgcg_ctx *c)
+void spmv_code_free(CodeStore *store)
 {
-    if (c->code_buf) pool_release(c->code_buf);
-    if (c->code_state) pool_release(c->code_state);
-    c->code_buf = nullptr; c->code_state = nullptr; c->code_cap = 0; c->code_ndict = 0;
+    if (store->buf) pool_release(store->buf);
+    if (store->state) pool_release(store->state);
+    store->buf = nullptr; store->state = nullptr; store->cap = 0;
 }
 
 }  // namespace mgcg

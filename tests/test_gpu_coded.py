@@ -158,3 +158,32 @@ def test_resetup_with_other_matrix(env):
     m.setup(_dev(torch, v), _dev(torch, rp), _dev(torch, c), S.default_options())
     assert m.matrix_codes() is None
     m.close()
+
+
+def test_27pt_operator_runs_on_the_stencil_kernel(env):
+    """27 distances in 9 runs of 3: tiles of 64 rows, the x runs staged by TMA; storage-order sums like the oracle's"""
+    torch, _lib, gen, S, O = env
+    n = 34
+    v, rp, c = gen.poisson3d27_varcoef(n)              # 39 304 rows, up to 27 per row, coefficients over six decades
+    rows = len(rp) - 1
+    m = _setup(env, v, rp, c, precond=1, nx=n, ny=n, nz=n, tolerance=1e-9, norm=_lib.NORM_REL_L2)
+    got, want = m.matrix_codes(), O.coded_columns(rp, c)
+    assert got is not None and len(want[0]) == 27
+    assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+    rng = np.random.default_rng(4)
+    x = rng.standard_normal(rows)
+    tx, ty = _dev(torch, x), _dev(torch, np.zeros(rows))
+    m.spmv(tx, ty)
+    assert np.array_equal(ty.cpu().numpy(), O.spmv(v, rp, c, x))
+    b = rng.standard_normal(rows)
+    sol = _dev(torch, np.zeros(rows))
+    res = m.solve(_dev(torch, b), sol)
+    assert res.reserved[5] == 4
+    plain = _setup(env, v, rp, c, precond=1, nx=n, ny=n, nz=n, tolerance=1e-9, norm=_lib.NORM_REL_L2, spmv_coding=1)
+    sol2 = _dev(torch, np.zeros(rows))
+    res2 = plain.solve(_dev(torch, b), sol2)
+    assert res2.reserved[5] == 3                       # ROWS kernel on int32 columns
+    assert abs(res.iteration - res2.iteration) <= 1
+    err = float((sol - sol2).abs().max() / sol2.abs().max())
+    assert err < 1e-6, err                             # two solves stopped at 1e-9 of an ill-conditioned system
+    m.close(); plain.close()

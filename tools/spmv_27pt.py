@@ -32,6 +32,23 @@ for name, kernel in (("auto (wide TMA stream)", _lib.SPMV_AUTO), ("rows", _lib.S
     ms = e0.elapsed_time(e1) / reps
     ys[name] = (y, float(d.item()))
     print(f"  {name:26s} {ms:8.3f} ms  {byt / ms / 1e6:8.0f} GB/s  {byt / ms / 1e6 / peak:5.3f} of peak")
+# the set-up matrix: coded columns, STENCIL kernel on 64-row tiles (values, codes and the x runs staged by TMA)
+m.setup(tv, tr, tc, S.default_options())
+nd = __import__("ctypes").c_int(0)
+m.L.mgcg_matrix_codes(m.ctx, __import__("ctypes").byref(nd), None, None)
+if nd.value > 0:
+    byt9 = 9.0 * nnz + 20.0 * rows
+    y = torch.empty_like(x)
+    for _ in range(3):
+        S.check(m.L.mgcg_spmv_dot(m.ctx, rows, rows, nnz, S._p(tv), S._p(tr), S._p(tc), S._p(x), S._p(y), S._p(x), S._p(d), 0), "spmv")
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        m.L.mgcg_spmv_dot(m.ctx, rows, rows, nnz, S._p(tv), S._p(tr), S._p(tc), S._p(x), S._p(y), S._p(x), S._p(d), 0)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 10
+    ys["stencil (coded, %d distances)" % nd.value] = (y, float(d.item()))
+    print(f"  {'stencil (coded columns)':26s} {ms:8.3f} ms  {byt9 / ms / 1e6:8.0f} GB/s of its 9 B/entry layout = {byt9 / ms / 1e6 / peak:5.3f} of peak; CSR-equivalent {byt / ms / 1e6:8.0f} GB/s")
 ref = ys["vector"][0]
 for k, (y, dot) in ys.items():
     print(f"  {k:26s} max|y - y_vector| / max|y| = {float((y - ref).abs().max() / ref.abs().max()):.2e}  dot {dot:.15e}")
