@@ -25,6 +25,7 @@ struct MgLevel {
     double *xa = nullptr, *xb = nullptr, *b = nullptr, *r = nullptr;   // level vectors (level 0: b is the CG residual)
     double *xcur = nullptr;
     SpmvPlan planA, planP, planR;
+    CodeStore code;        // coded columns of A on levels >= 1 (level 0: the context's store)
     int dims[3] = {0, 0, 0};
     bool rb = false;       // smoothed by red-black Gauss-Seidel: grid known and every off-diagonal entry joins cells of opposite parity
     int cheb = 0;          // smoothed by a Chebyshev polynomial of this degree in D^-1 A (0: no)

@@ -708,6 +708,7 @@ void mg_free(mgcg_ctx *c)
     for (size_t l = 0; l < H->L.size(); ++l) {
         MgLevel &L = H->L[l];
         L.Aown.free_all(); L.P.free_all(); L.R.free_all();
+        spmv_code_free(&L.code);
         pool_release(L.agg);
         pool_release(L.dinv);
         pool_release(L.xa);
@@ -832,6 +833,7 @@ int mg_build(mgcg_ctx *c)
         N.Aown = Ac;
         N.A = Ac.view();
         N.planA = spmv_make_plan(c, Ac.rows, Ac.nnz, MGCG_SPMV_AUTO);
+        MGCG_CHECK(spmv_code_build(c, &N.code, &N.A, &N.planA));     // a Galerkin operator on a grid is a stencil too (27-point on level 1)
         N.dims[0] = cd[0]; N.dims[1] = cd[1]; N.dims[2] = cd[2];
         nnz_sum += (double)Ac.nnz;
         H->L.push_back(N);   // invalidates L

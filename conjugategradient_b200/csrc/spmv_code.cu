@@ -62,20 +62,44 @@ __global__ void __launch_bounds__(kCodeThreads) k_code_clear(CodeState *st)
     if (threadIdx.x == 0) { st->count = 0; st->overflow = 0; st->ndict = 0; st->nseg = 0; }
 }
 
+// Walk the entries of a tile of kCodeThreads consecutive rows with coalesced loads: entry k of the tile's contiguous slice belongs to
+// the last row whose pointer is <= k (bisection in the tile's row pointers held in shared memory).  One thread per ROW reading its own
+// 7..27 columns measured 5 ms per pass on the 27-point operator at 256^3 (every sector fetched once per 4-byte word it holds).
+template <typename F>
+__device__ __forceinline__ void walk_tile(const Csr &A, int tile, int *s_rp, F f)
+{
+    const int t = threadIdx.x;
+    const int r0 = tile * kCodeThreads;
+    const int nr = min(kCodeThreads, A.rows - r0);
+    __syncthreads();
+    if (t < nr) s_rp[t] = A.rowptr[r0 + t];
+    if (t == 0) s_rp[nr] = A.rowptr[r0 + nr];
+    __syncthreads();
+    const int k0 = s_rp[0], k1 = s_rp[nr];
+    for (int k = k0 + t; k < k1; k += kCodeThreads) {
+        int lo = 0, hi = nr - 1;
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (s_rp[mid] <= k) lo = mid; else hi = mid - 1;
+        }
+        f(k, r0 + lo);
+    }
+}
+
 __global__ void __launch_bounds__(kCodeThreads) k_code_collect(Csr A, CodeState *st)
 {
     __shared__ int s_keys[kCodeSlots];
+    __shared__ int s_rp[kCodeThreads + 1];
     __shared__ int s_count, s_over;
     const int t = threadIdx.x;
     for (int i = t; i < kCodeSlots; i += kCodeThreads) s_keys[i] = kCodeEmpty;
     if (t == 0) { s_count = 0; s_over = *(volatile int *)&st->overflow; }
     __syncthreads();
-    const int *__restrict__ rowptr = A.rowptr;
     const int *__restrict__ col = A.col;
-    for (int row = blockIdx.x * kCodeThreads + t; row < A.rows; row += gridDim.x * kCodeThreads) {
-        if (*(volatile int *)&s_over) break;
-        const int ks = rowptr[row], ke = rowptr[row + 1];
-        for (int k = ks; k < ke; ++k) code_insert(s_keys, &s_count, &s_over, __ldcs(col + k) - row);
+    const int tiles = (A.rows + kCodeThreads - 1) / kCodeThreads;
+    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        if (__syncthreads_or(*(volatile int *)&s_over)) break;        // block-uniform: walk_tile has barriers
+        walk_tile(A, tile, s_rp, [&](int k, int row) { code_insert(s_keys, &s_count, &s_over, __ldcs(col + k) - row); });
     }
     __syncthreads();
     if (s_over) { if (t == 0) st->overflow = 1; return; }
@@ -128,15 +152,14 @@ __global__ void k_code_runs(CodeState *st)
 __global__ void __launch_bounds__(kCodeThreads) k_code_encode(Csr A, const CodeState *st, unsigned char *code)
 {
     __shared__ int s_dict[kCodeMax];
+    __shared__ int s_rp[kCodeThreads + 1];
     const int t = threadIdx.x;
     s_dict[t] = st->dict[t];
     const int n = st->ndict;
-    __syncthreads();
-    const int *__restrict__ rowptr = A.rowptr;
     const int *__restrict__ col = A.col;
-    for (int row = blockIdx.x * kCodeThreads + t; row < A.rows; row += gridDim.x * kCodeThreads) {
-        const int ks = rowptr[row], ke = rowptr[row + 1];
-        for (int k = ks; k < ke; ++k) {
+    const int tiles = (A.rows + kCodeThreads - 1) / kCodeThreads;
+    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x)
+        walk_tile(A, tile, s_rp, [&](int k, int row) {
             const int d = __ldcs(col + k) - row;
             int lo = 0, hi = n - 1;            // d is in the list: plain bisection
             while (lo < hi) {
@@ -144,8 +167,7 @@ __global__ void __launch_bounds__(kCodeThreads) k_code_encode(Csr A, const CodeS
                 if (s_dict[mid] < d) lo = mid + 1; else hi = mid;
             }
             code[k] = (unsigned char)lo;
-        }
-    }
+        });
 }
 
 // Restate A's columns as codes unless the option forbids it, when a kernel that reads them fits the matrix shape and the matrix has

@@ -51,6 +51,8 @@ CASES = [
     # neighbours' kernels; the worker also checks the result bit for bit against the same sharded solve on int32 columns
     ("mg_coded_columns_peer", {"n": 48, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2}, "transport": 2,
                                "solves": 2, "coded": 7}),
+    ("mg_27pt_coded_columns_peer", {"n": 48, "matrix": "p27", "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2},
+                                    "transport": 2, "tight": 1e-12, "coded": 27}),
     ("plain_cg_coded_columns_nccl", {"n": 48, "options": {"precond": 0, "dist_transport": 1}, "coded": 7}),
     ("mg_chebyshev_single_reduce_w4", {"n": 48, "world": 4, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "mg_smoother": 2,
                                                                         "cg_variant": 1}, "transport": 2}),
