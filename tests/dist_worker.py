@@ -69,7 +69,12 @@ def main():
         kw0 = dict(kw); kw0["spmv_coding"] = 1      # MGCG_CODING_OFF
         m.setup(N, r0, tv, tr, tc, S.default_options(norm=2, tolerance=cfg.get("tolerance", 1e-8), max_iteration=2000, **kw0))
         res0 = m.solve(tb, tx.zero_())
-        assert res0.iterations_done == res.iterations_done and torch.equal(tx, x_coded), "sharded solve on coded columns differs from int32 columns"
+        if cfg.get("matrix", "p3d7") == "p3d7":     # same kernel family, storage-order sums on both sides: the same bits
+            assert res0.iterations_done == res.iterations_done and torch.equal(tx, x_coded), "sharded solve on coded columns differs from int32 columns"
+        else:                                        # 27-point: int32 columns run on the lanes-per-row kernel (other summation order)
+            assert abs(res0.iterations_done - res.iterations_done) <= 1
+            assert float((tx - x_coded).abs().max() / x_coded.abs().max()) < 1e-6, "sharded solve on coded columns differs from int32 columns"
+        tx.copy_(x_coded)
         torch.cuda.synchronize()
     # the same system on this GPU alone
     ms = S.Mgcg(lr)
