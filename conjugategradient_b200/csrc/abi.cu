@@ -333,7 +333,7 @@ int mgcg_spmv(mgcg_ctx *c, int rows, int cols, int elements_count,
     a.A.rows = rows; a.A.cols = cols; a.A.nnz = elements_count; a.A.val = d_elements; a.A.rowptr = d_row_offsets; a.A.col = d_column_indeces;
     a.x = d_x; a.y = d_y; a.alpha = alpha; a.beta = beta;
     SpmvPlan p = spmv_make_plan(c, rows, elements_count, kernel);
-    if (same_as_setup(c, a.A) && kernel == c->opt.spmv_kernel) { a.A = c->A; p = c->planA; }   // the set-up matrix: its coded columns
+    if (same_as_setup(c, a.A) && kernel == c->opt.spmv_kernel) { a.A = c->A; p = c->planA; dist_x_range(c, &a.x_lo, &a.x_hi); }   // the set-up matrix: its coded columns
     const bool plain = (alpha == 1.0 && beta == 0.0);
     return spmv_launch(c, p, plain ? EPI_PLAIN : EPI_AXPBY, a);
 }
@@ -348,7 +348,7 @@ int mgcg_spmv_dot(mgcg_ctx *c, int rows, int cols, int elements_count,
     a.A.rows = rows; a.A.cols = cols; a.A.nnz = elements_count; a.A.val = d_elements; a.A.rowptr = d_row_offsets; a.A.col = d_column_indeces;
     a.x = d_x; a.y = d_y; a.w = d_w; a.fin = FIN_STORE; a.out = d_dot;
     SpmvPlan p = spmv_make_plan(c, rows, elements_count, kernel);
-    if (same_as_setup(c, a.A) && kernel == c->opt.spmv_kernel) { a.A = c->A; p = c->planA; }
+    if (same_as_setup(c, a.A) && kernel == c->opt.spmv_kernel) { a.A = c->A; p = c->planA; dist_x_range(c, &a.x_lo, &a.x_hi); }
     return spmv_launch(c, p, EPI_DOT, a);
 }
 

@@ -280,6 +280,7 @@ const double *mg_level0_dinv(mgcg_ctx *c);
 // ---- dist.cu
 void dist_free(mgcg_ctx *c);
 void dist_host_path_free(mgcg_ctx *c);
+bool dist_x_range(const mgcg_ctx *c, int *x_lo, int *x_hi);   // sharded context: global indices [own rows +- ghost rows] a product's x may be read at
 
 // ---- cg.cu
 int cg_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res);

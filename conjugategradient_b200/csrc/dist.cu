@@ -1261,6 +1261,15 @@ __global__ void k_rebase_rowptr(int n, int *rp, int base)
 {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) rp[i] -= base;
 }
+bool dist_x_range(const mgcg_ctx *c, int *x_lo, int *x_hi)
+{
+    const DistState *D = c->dist;
+    if (!D || D->L.empty()) return false;
+    const DistLevel &L0 = D->L[0];
+    *x_lo = L0.off - L0.lo; *x_hi = L0.off + L0.own + L0.hi;
+    return true;
+}
+
 void dist_host_path_free(mgcg_ctx *c)
 {
     if (!c->host_path_dist) return;
