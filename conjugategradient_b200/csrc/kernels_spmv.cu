@@ -360,6 +360,7 @@ __global__ void __launch_bounds__(kTmaRows) k_spmv_tma(SpmvArgs a, int num_tiles
 // producer requests one bulk copy per run next to the tile's values and codes.  No thread issues a dependent global load any more:
 // rowptr -> (value, code) -> x all arrive through the TMA ring, a row is summed from shared memory in storage order with explicit
 // mul/add roundings (the same bits as every other STREAM kernel), and the ring's stages are in flight for almost their whole life.
+// A run starts at an index of the same parity as x's own 8-byte misalignment, so that its source is 16-byte aligned.
 // Runs that would leave the valid index range of x (tiles at the ends of the matrix, whose rows have no entry at that distance, or
 // only some) are not staged: on such a tile the entries of that run fall back to a gather.
 // The producer is a warp of its own: with up to fourteen bulk copies per tile behind two row-pointer loads, one consumer thread doing
@@ -395,7 +396,17 @@ __global__ void __launch_bounds__(R + 32) k_spmv_stencil(SpmvArgs a, int num_til
         for (int s = 0; s < kStages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], R); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int i = t; i < 256; i += R + 32) { const int o = a.A.seg_off[i]; s_idx[i] = (o >> 10) * kRunLen + (o & 1023); }
+    // x is 8-byte aligned; a run must start 16-byte aligned: its first index has the parity xpar of x's own misalignment (a shard's
+    // shifted view with an odd ghost width), and the position of an operand inside its run moves with it
+    const int xpar = (int)((reinterpret_cast<uintptr_t>(x) >> 3) & 1u);
+    for (int i = t; i < 256; i += R + 32) {
+        int idx = 0;
+        if (i < a.A.ndict) {
+            const int o = a.A.seg_off[i], g = o >> 10, first = a.A.seg_min[g];
+            idx = g * kRunLen + (o & 1023) - (first & 1) + ((first - xpar) & 1);
+        }
+        s_idx[i] = idx;
+    }
     if (t < kSegMax) s_min[t] = t < nseg ? a.A.seg_min[t] : 0;
     bool wrote = false;
     halo_wait(a.gw, sc);             // the x runs are requested below: ghost rows must have landed ...
@@ -431,7 +442,7 @@ __global__ void __launch_bounds__(R + 32) k_spmv_stencil(SpmvArgs a, int num_til
             int s0 = 0;
             bool ok = false;
             if (fits && g >= 0 && g < nseg) {
-                s0 = (r0 + s_min[g]) & ~1;
+                s0 = ((r0 + s_min[g] - xpar) & ~1) + xpar;
                 ok = s0 >= x_lo && s0 + kRunLen <= x_hi;
             }
             const unsigned mask = __ballot_sync(0xffffffffu, ok) >> 2;
@@ -887,8 +898,8 @@ static int launch_epi(mgcg_ctx *c, const SpmvPlan &plan, const SpmvArgs &a)
         return MGCG_ERR_INVALID;
     }
     const bool aligned = ((((uintptr_t)a.A.val) | ((uintptr_t)a.A.col)) & 15u) == 0;
-    // coded columns in few runs: values, codes AND the x runs staged by TMA — unless x is misaligned or rewritten by this launch
-    if (plan.stencil_rows > 0 && a.A.code && a.A.nseg > 0 && aligned && (((uintptr_t)a.x) & 15u) == 0 &&
+    // coded columns in few runs: values, codes AND the x runs staged by TMA — unless x is rewritten by this launch
+    if (plan.stencil_rows > 0 && a.A.code && a.A.nseg > 0 && aligned && (((uintptr_t)a.x) & 7u) == 0 &&
         (const double *)a.y != a.x && a.color < 0) {
         MGCG_CHECK(launch_stencil<EPI>(c, a, plan.stencil_rows));
         c->launches++;

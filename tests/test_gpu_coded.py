@@ -187,3 +187,21 @@ def test_27pt_operator_runs_on_the_stencil_kernel(env):
     err = float((sol - sol2).abs().max() / sol2.abs().max())
     assert err < 1e-6, err                             # two solves stopped at 1e-9 of an ill-conditioned system
     m.close(); plain.close()
+
+
+@pytest.mark.parametrize("kind", ["p3d7", "p27"])
+def test_stencil_kernel_on_an_x_that_is_only_8_byte_aligned(env, kind):
+    """a shard's shifted x view with an odd ghost width is 8-byte but not 16-byte aligned: the runs then start at odd indices"""
+    torch, _lib, gen, S, O = env
+    v, rp, c = gen.poisson3d7(40, 33, 32) if kind == "p3d7" else gen.poisson3d27_varcoef(34)
+    n = len(rp) - 1
+    m = _setup(env, v, rp, c)
+    assert m.matrix_codes() is not None
+    x = np.random.default_rng(8).standard_normal(n)
+    big = _dev(torch, np.concatenate([[0.0], x, [0.0, 0.0, 0.0]]))
+    tx = big[1:n + 1]
+    assert tx.data_ptr() % 16 == 8
+    ty = _dev(torch, np.zeros(n))
+    m.spmv(tx, ty)
+    assert np.array_equal(ty.cpu().numpy(), O.spmv(v, rp, c, x))
+    m.close()
