@@ -1,13 +1,17 @@
-// kernels_spmv.cu — fp64 CSR SpMV family for sm_100a with fused epilogues (p.Ap dot, residual, Jacobi sweep).
+// kernels_spmv.cu — fp64 CSR SpMV family for sm_100a with fused epilogues (p.Ap dot, residual, Jacobi / Chebyshev sweep).
 // Replaces cusparseDcsrmv (Mgcg.cu:17, SimpleConjugateGradient.cu:75,96) and, for the p.Ap epilogue, the
-// host-synchronous cublasDdot that follows it (Mgcg.cu:245).  HBM-bound: 12 B per non-zero + 20 B per row.
+// host-synchronous cublasDdot that follows it (Mgcg.cu:245).  HBM-bound: 12 B per non-zero + 20 B per row on the caller's CSR,
+// 9 B per non-zero where the set-up restated the columns as one-byte codes (spmv_code.cu).
 //
-//  * STREAM  (short rows, stencils): a tile of consecutive rows is a CONTIGUOUS slice of val/col, so the block
-//    streams that slice with perfectly coalesced loads, stages the products a_k*x[col_k] in shared memory, and one
-//    thread per row then adds its segment in STORAGE order — the same order as SparseMatrix.Multiply
-//    (SparseMatrix.cs:78-85), products rounded before the add (no FMA across the staging) => bit-identical row sums.
-//  * VECTOR  (long rows, e.g. the reference's 160/row band): L lanes per row, coalesced strided loads, shuffle tree.
-// Both run as persistent grids (static tile->block map, so the fused reduction is deterministic).
+//  * STREAM  (short rows, stencils): a tile of consecutive rows is a CONTIGUOUS slice of val/col; one thread per row adds its
+//    segment in STORAGE order — the same order as SparseMatrix.Multiply (SparseMatrix.cs:78-85), products rounded before the add
+//    => bit-identical row sums.  k_spmv_stream: the slice is streamed with coalesced loads and staged as products;
+//    k_spmv_tma: val/col (or val/code) slices arrive in a ring of shared-memory stages by 1-D TMA bulk copies on mbarriers.
+//  * STENCIL (coded columns in few runs of distances: 5-, 7-, 27-point operators): as k_spmv_tma, and the tile's x operands are
+//    staged by TMA too (one contiguous run of x per run of distances), requested by a producer warp: no dependent global load left.
+//  * ROWS    (8 .. ~300 per row): TMA-staged slices, L lanes per row, shuffle tree.
+//  * VECTOR  (longer rows, unaligned arrays): L lanes per row straight from global memory, shuffle tree.
+// All run as persistent grids with a static tile->block map, so the fused reduction is deterministic for a given kernel and grid.
 #include "common.cuh"
 #include "reduce.cuh"
 #include "halo.cuh"
