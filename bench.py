@@ -7,14 +7,17 @@
                          is quoted on.  c2: the same at 128^3, one GPU.  c3: particle (MPS) pressure matrix, 160^3 = 4 096 000
                          particles, neighbour radius --re (2.1 or 3.1 lattice spacings), assembled on the device, no grid given to
                          the solver (strength filter + MIS-2 aggregation), one GPU.  c5: 27-point variable-coefficient 512^3,
-                         sharded (needs N >= 2: the global matrix has 3.6e9 non-zeros), assembled per shard on the device.
+                         sharded (needs N >= 2: the global matrix has 3.6e9 non-zeros), assembled per shard on the device
+                         (--size 256 or less runs the same operator on one GPU).
 A "step" is ONE complete solve of the system to 1e-8 relative residual (x0 = 0).  One JSON line is printed by rank 0:
   value / ms_per_step : solve time with the matrix, the hierarchy and b resident in HBM (CUDA events, max over ranks)
   e2e                 : the same solve through ONE host-pointer C-ABI call (mgcg_solve_host / mgcg_solve_host_dist): pinned host
                         CSR + b in, x out; upload + hierarchy build + solve + download inside the timed region.  e2e_cold is the
                         first such call of the process (allocations, peer mappings, graph instantiation included).
-  roofline            : the fine-level SpMV(+p.Ap) kernel, algorithmic bytes 12*nnz + 20*N per launch, timed live with CUDA
-                        events inside a solve, against MEASURED_PEAKS.json's HBM copy bandwidth
+  roofline            : the fine-level SpMV(+p.Ap) kernel timed live with CUDA events inside a solve, against MEASURED_PEAKS.json's HBM
+                        copy bandwidth.  Bytes per launch = what the kernel's layout must move: 9*nnz + 20*N on the library's coded
+                        columns (fp64 value + 1-byte code per entry; the default for stencil operators), 12*nnz + 20*N on the
+                        caller's int32 columns (--opt spmv_coding=1); the CSR figure is reported beside it (csr_equivalent_gbs)
   parity              : x of the timed solve against a 1e-12 solve of the same system on the same device (the CPU twin at 256^3
                         takes minutes: it is compared at 128^3 in tests/test_gpu_parity_c2.py and once at 256^3 by
                         tools/parity_c4.py -> profiles/); the plain-CG iteration count measured on the GPU; N > 1: the sharded
