@@ -86,6 +86,19 @@ def coded_columns(rowptr, col, max_codes=256):
     return dist.astype(np.int32), np.searchsorted(dist, d).astype(np.uint8)
 
 
+def coded_runs(dist, span=6, max_runs=12):
+    """Checker for the run grouping of the coded distances (csrc/spmv_code.cu k_code_runs): a run takes sorted distances while they
+    stay within `span` of its first one.  -> (first distance of every run, run index of every distance) or None beyond `max_runs`."""
+    firsts, run_of = [], []
+    for d in (int(v) for v in dist):
+        if not firsts or d - firsts[-1] > span:
+            firsts.append(d)
+        run_of.append(len(firsts) - 1)
+    if len(firsts) > max_runs:
+        return None
+    return np.array(firsts, dtype=np.int64), np.array(run_of, dtype=np.int64)
+
+
 def cg_solve(val, rowptr, col, b, x0=None, tol=1e-8, min_iteration=0, max_iteration=None,
              norm=NORM_ABS_L2, min_strict=False):
     """ConjugateGradientCpu.Solve restatement. Returns (x, iteration_index, residual, status)."""

@@ -145,3 +145,27 @@ def test_coded_columns_restates_the_columns():
     rng = np.random.default_rng(0)
     rp = np.arange(0, 4 * 1000 + 1, 4, dtype=np.int32)
     assert O.coded_columns(rp, rng.integers(0, 1000, 4000).astype(np.int32)) is None
+
+
+def test_stencil_run_addressing_model():
+    """The index algebra of the STENCIL kernel (csrc/kernels_spmv.cu k_spmv_stencil), restated in numpy: for a tile of R rows starting
+    at the even row r0, run g of the distances is staged from the index s0 = ((r0 + first_g - xpar) & ~1) + xpar (16-byte aligned
+    source when x itself is misaligned by xpar doubles), and row r0 + t finds the operand of an entry of distance d at
+    s0 + t + (d - first_g) + ((first_g - xpar) & 1) — which must be its column, within a run of R + 8 doubles."""
+    from conjugategradient_b200 import generators as gen
+    from oracle import oracle as O
+    for (v, rp, c), nruns in ((gen.poisson3d7(12, 10, 9), 5), (gen.poisson3d27_varcoef(10), 9)):
+        dist, code = O.coded_columns(rp, c)
+        firsts, run_of = O.coded_runs(dist)
+        assert len(firsts) == nruns
+        row_of = np.repeat(np.arange(len(rp) - 1), np.diff(rp))
+        for R in (256, 64):
+            for xpar in (0, 1):
+                r0 = (row_of // R) * R
+                t = row_of - r0
+                first = firsts[run_of[code]]
+                s0 = ((r0 + first - xpar) & ~1) + xpar
+                pos = t + (dist[code].astype(np.int64) - first) + ((first - xpar) & 1)
+                assert np.array_equal(s0 + pos, c)
+                assert pos.min() >= 0 and pos.max() < R + 8
+                assert np.all((s0 + xpar) % 2 == 0)            # (x address / 8 + s0) even: the bulk copy's source is 16-byte aligned
