@@ -828,7 +828,7 @@ static int rows_prepare(mgcg_ctx *c, const SpmvPlan &plan)
 // Coded columns: the ring lives in dynamic shared memory so that it can be deeper than the int32 kernel's.  A stage is 9 instead of
 // 12 bytes per entry; with the int32 kernel's two stages and four resident blocks per SM too few bytes were in flight per SM to
 // cover the HBM latency (0.303 ms per fine-level product inside a 256^3 solve against 0.273 ms on int32 columns); three stages x four
-// blocks: 0.281 ms.  Stages and resident blocks are tuning knobs (MGCG_CODED_STAGES 2..4, MGCG_CODED_CTAS).
+// blocks: 0.281 ms.  Stages and resident blocks are tuning knobs (MGCG_CODED_STAGES 2|3, MGCG_CODED_CTAS).
 template <int EPI, int STAGES>
 static int launch_coded_one(mgcg_ctx *c, const SpmvArgs &a, int tiles, int ctas)
 {
@@ -844,7 +844,7 @@ static int launch_coded_one(mgcg_ctx *c, const SpmvArgs &a, int tiles, int ctas)
     launch_k(a.gated, k_spmv_tma<EPI, 0, STAGES, true>, grid, kTmaRows, (size_t)smem, c->stream, a, tiles, kTmaCap, c->ws, c->d_scalars);
     return MGCG_OK;
 }
-// STENCIL kernel: stages x resident blocks from what fits (tuning knobs MGCG_STENCIL_STAGES 2..4, MGCG_STENCIL_CTAS)
+// STENCIL kernel: stages x resident blocks from what fits (tuning knobs MGCG_STENCIL_STAGES 2|3, MGCG_STENCIL_CTAS)
 template <int EPI, int STAGES, int R>
 static int launch_stencil_one(mgcg_ctx *c, const SpmvArgs &a, int ctas_env)
 {
@@ -868,29 +868,27 @@ static int launch_stencil_one(mgcg_ctx *c, const SpmvArgs &a, int ctas_env)
 template <int EPI>
 static int launch_stencil(mgcg_ctx *c, const SpmvArgs &a, int tile_rows)
 {
-    static const int stages = [] { const char *e = getenv("MGCG_STENCIL_STAGES"); const int v = e ? atoi(e) : 0; return (v >= 2 && v <= 4) ? v : 2; }();
+    // (4 stages measured slower than 2 and 3 on both tile shapes and is not instantiated)
+    static const int stages = [] { const char *e = getenv("MGCG_STENCIL_STAGES"); const int v = e ? atoi(e) : 0; return v == 3 ? 3 : 2; }();
     static const int ctas_env = [] { const char *e = getenv("MGCG_STENCIL_CTAS"); const int v = e ? atoi(e) : 0; return (v >= 1 && v <= 16) ? v : 0; }();
     if (tile_rows == 64) {
         if (stages == 2) return launch_stencil_one<EPI, 2, 64>(c, a, ctas_env);
-        if (stages == 3) return launch_stencil_one<EPI, 3, 64>(c, a, ctas_env);
-        return launch_stencil_one<EPI, 4, 64>(c, a, ctas_env);
+        return launch_stencil_one<EPI, 3, 64>(c, a, ctas_env);
     }
     if (stages == 2) return launch_stencil_one<EPI, 2, 256>(c, a, ctas_env);
-    if (stages == 3) return launch_stencil_one<EPI, 3, 256>(c, a, ctas_env);
-    return launch_stencil_one<EPI, 4, 256>(c, a, ctas_env);
+    return launch_stencil_one<EPI, 3, 256>(c, a, ctas_env);
 }
 
 template <int EPI>
 static int launch_coded(mgcg_ctx *c, const SpmvArgs &a, int tiles)
 {
-    static const int stages = [] { const char *e = getenv("MGCG_CODED_STAGES"); const int v = e ? atoi(e) : 0; return (v >= 2 && v <= 4) ? v : 3; }();
+    static const int stages = [] { const char *e = getenv("MGCG_CODED_STAGES"); const int v = e ? atoi(e) : 0; return v == 2 ? 2 : 3; }();
     static const int ctas_env = [] { const char *e = getenv("MGCG_CODED_CTAS"); const int v = e ? atoi(e) : 0; return (v >= 1 && v <= 8) ? v : 0; }();
     const int fit = (224 * 1024) / (stages * ((kTmaCap + 2) * 8 + (kTmaCap + 16)) + 3 * 1024);
     int ctas = ctas_env > 0 ? ctas_env : fit;
     if (ctas > 6) ctas = 6;
     if (stages == 2) return launch_coded_one<EPI, 2>(c, a, tiles, ctas);
-    if (stages == 3) return launch_coded_one<EPI, 3>(c, a, tiles, ctas);
-    return launch_coded_one<EPI, 4>(c, a, tiles, ctas);
+    return launch_coded_one<EPI, 3>(c, a, tiles, ctas);
 }
 
 template <int EPI>
