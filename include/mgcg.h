@@ -166,6 +166,20 @@ int mgcg_max_abs(mgcg_ctx *c, int n, const double *d_a, double *d_out, double *h
 int mgcg_axpy(mgcg_ctx *c, int n, double alpha, const double *d_x, double *d_y);  /* y += alpha x */
 int mgcg_scal(mgcg_ctx *c, int n, double alpha, double *d_x);
 int mgcg_copy(mgcg_ctx *c, int n, const double *d_x, double *d_y);
+/* The dot product of mgcg_dot for callers that must not allocate device memory: no context, no cudaMalloc / cudaFree and no
+ * allocating library routine on any call, the first included.  NO COUNTERPART IN THE REFERENCE (its dot is cublasDdot on a handle
+ * that owns a workspace, Mgcg.cu:28-37); added for hosts that hand all GPU memory to their own arena at start-up, for time-step
+ * loops that cannot absorb the device-wide synchronisation of cudaMalloc, and for plug-ins whose embedding application forbids
+ * runtime allocation.  The reduction workspace is a 33 024-byte __device__ array inside libMgcgGpu.so (csrc/noalloc.cu); every GPU
+ * that loads the library holds it until the process exits.
+ *   - n <= MGCG_DOT_STATIC_MAX_N, else MGCG_ERR_INVALID with a message in mgcg_last_error (the array has room for 4096 block sums).
+ *   - *d_out = sum_i d_a[i]*d_b[i], written in stream order on cuda_stream (a cudaStream_t, NULL = the default stream); the call
+ *     does not synchronise.  Same summation order as mgcg_dot: same bits for the same n on the same GPU.
+ *   - the first call on a device looks up the array's address there (cudaGetSymbolAddress): make it before any stream capture.
+ *   - ALL calls on a GPU share the one array: calls that can overlap on the GPU (two streams, two threads) race and return
+ *     garbage — order them on one stream or with events.  Each call clears the counter it needs itself. */
+#define MGCG_DOT_STATIC_MAX_N (1 << 28)
+int mgcg_dot_static(int device, int n, const double *d_a, const double *d_b, double *d_out, void *cuda_stream);
 /* fused CG updates (replace Solve2 / Solve3 bodies, Mgcg.cu:181-183,197) */
 int mgcg_update_xr(mgcg_ctx *c, int n, double alpha, const double *d_p, const double *d_Ap,
                    double *d_x, double *d_r, double *d_rr, double *host_rr);
