@@ -52,7 +52,7 @@ NATIVE_SYMBOLS = [
     "mgcg_mg_level_get", "mgcg_mg_level_aggregates", "mgcg_mg_apply", "mgcg_partition_offsets",
     "mgcg_comm_unique_id", "mgcg_comm_init", "mgcg_setup_dist", "mgcg_solve_dist", "mgcg_solve_host_dist", "mgcg_comm_finalize", "mgcg_dist_microbench",
     "mgcg_generate_poisson3d7_nnz", "mgcg_generate_poisson3d7", "mgcg_generate_poisson3d27_nnz", "mgcg_generate_poisson3d27",
-    "mgcg_mps_order", "mgcg_mps_count", "mgcg_mps_fill", "mgcg_test_scan_counts", "mgcg_matrix_codes", "mgcg_dot_static",
+    "mgcg_mps_order", "mgcg_mps_count", "mgcg_mps_fill", "mgcg_test_scan_counts", "mgcg_matrix_codes", "mgcg_dot_static", "mgcg_test_pool_stats",
 ]
 # every symbol include/mgcg_formats.h declares (ELL input, Write/Solve/Read/Iteration object)
 FORMAT_SYMBOLS = [
@@ -106,6 +106,7 @@ def lib():
     L.mgcg_dot.argtypes = [vp, ci, vp, vp, vp, dp]
     L.mgcg_max_abs.argtypes = [vp, ci, vp, vp, dp]
     L.mgcg_dot_static.argtypes = [ci, ci, vp, vp, vp, vp]
+    L.mgcg_test_pool_stats.argtypes = [ci, ci, vp]
     L.mgcg_axpy.argtypes = [vp, ci, cd, vp, vp]
     L.mgcg_scal.argtypes = [vp, ci, cd, vp]
     L.mgcg_copy.argtypes = [vp, ci, vp, vp]

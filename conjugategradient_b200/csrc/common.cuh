@@ -322,6 +322,7 @@ void pool_reserve(size_t bytes);     // size of the next slab the block cache ca
 void pool_trim_stream(int device, cudaStream_t st);
 void pool_trim(int device);          // give the cached blocks of a device (-1: all) back to the driver
 size_t pool_cached_bytes();
+void pool_stats(int device, long long out[5]);
 int ctx_ensure_work(mgcg_ctx *c, int n);
 inline int div_up(int a, int b) { return (a + b - 1) / b; }
 

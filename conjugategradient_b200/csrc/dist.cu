@@ -981,6 +981,11 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
 {
     DistState *D = c->dist;
     if (!D || D->L.empty()) { set_error("mgcg_solve_dist: mgcg_setup_dist has not been called"); return MGCG_ERR_INVALID; }
+    if (!c->is_setup) {
+        set_error("mgcg_solve_dist: no valid set-up (the last mgcg_setup_dist failed, or a solve ended in MGCG_ERR_COMM and left the "
+                  "exchange counters of the ranks out of step): call mgcg_setup_dist again on every rank");
+        return MGCG_ERR_INVALID;
+    }
     DistLevel &L0 = D->L[0];
     const int n = L0.own;
     const bool pre = (c->opt.precond == MGCG_PRECOND_MG);
@@ -1133,7 +1138,9 @@ static int dist_solve(mgcg_ctx *c, const double *b, double *x, mgcg_result *res)
     if (D->trace) dist_trace_dump(c, fin.iteration + 1, ms);
     if (!fin.done) { set_error("mgcg_solve_dist: iteration cap reached without the device flag"); return MGCG_ERR_NOT_CONVERGED; }
     if (fin.status != MGCG_OK)
-        set_error(fin.status == MGCG_ERR_NOT_CONVERGED ? "mgcg_solve_dist: Iteration > MaxIteration" : "mgcg_solve_dist: breakdown (p.Ap <= 0 or NaN)");
+        set_error(fin.status == MGCG_ERR_NOT_CONVERGED ? "mgcg_solve_dist: Iteration > MaxIteration"
+                  : fin.status == MGCG_ERR_COMM ? "mgcg_solve_dist: a peer-memory exchange timed out inside the loop (a rank fell behind or died); the set-up is void"
+                  : "mgcg_solve_dist: breakdown (p.Ap <= 0 or NaN)");
     return fin.status;
 }
 
@@ -1239,6 +1246,10 @@ extern "C" int mgcg_solve_dist(mgcg_ctx *c, const double *d_b_local, double *d_x
     if (!c || !d_b_local || !d_x_local) { set_error("mgcg_solve_dist: null argument"); return MGCG_ERR_INVALID; }
     MGCG_CUDA(cudaSetDevice(c->device));
     int s = dist_solve(c, d_b_local, d_x_local, res);
+    // A wait that timed out inside the loop (halo.cuh halo_wait) ends the solve with blocks that never reached halo_signal: the
+    // ticket of the exchange and this rank's sequence number no longer agree with the peers'.  Only peer_open resets them, so the
+    // set-up is void until mgcg_setup_dist runs again — the next solve must not read ghost rows through stale counters.
+    if (s == MGCG_ERR_COMM) c->is_setup = false;
     if (res) res->status = s;
     return s;
 }

@@ -27,7 +27,7 @@ enum {
     MGCG_ERR_CUDA = 2,           /* CUDA runtime failure (see mgcg_last_error) */
     MGCG_ERR_NOT_CONVERGED = 3,  /* iteration index exceeded max_iteration (== the C# ApplicationException) */
     MGCG_ERR_BREAKDOWN = 4,      /* p.Ap <= 0 or NaN: matrix not SPD / preconditioner not SPD */
-    MGCG_ERR_COMM = 5,           /* NCCL failure */
+    MGCG_ERR_COMM = 5,           /* NCCL failure, or a peer-memory exchange timed out; after it from mgcg_solve_dist the set-up is void: call mgcg_setup_dist again on every rank */
     MGCG_ERR_UNSUPPORTED = 6
 };
 
@@ -195,6 +195,10 @@ int mgcg_mg_level_aggregates(mgcg_ctx *c, int level, int *agg);
 /* test hook: the 64-bit-checked scan that sizes every level operator, on `rows` rows of `per_row` entries (no product is built);
  * MGCG_ERR_UNSUPPORTED when the total does not fit the int32 index range of a level */
 int mgcg_test_scan_counts(mgcg_ctx *c, int rows, int per_row, long long *nnz_out);
+/* test hook: the block cache under the hierarchy build (csrc/alloc.cu) on `device`.  out5 = {bytes cached in the free lists,
+ * slabs, their total bytes, bytes below their bump pointers, bytes of holes given back inside them}; trim != 0 first drops every
+ * cached block of the device (what an out-of-memory retry does).  No counterpart in the reference (it allocates per call). */
+int mgcg_test_pool_stats(int device, int trim, long long *out5);
 /* z = M r : one V-cycle applied to a device vector */
 int mgcg_mg_apply(mgcg_ctx *c, const double *d_r, double *d_z);
 
