@@ -532,7 +532,7 @@ __global__ void __launch_bounds__(R + 32) k_spmv_stencil(SpmvArgs a, int num_til
 // the STREAM kernels).  The plain VECTOR kernel reads val/col through the same dependent chain rowptr -> (val,col) -> x[col]
 // and measured 0.69 of the HBM peak on the 79-per-row restriction operator.
 // Stage capacity, stage count and resident blocks per SM are launch parameters (spmv_make_plan): the sweep over them on the
-// particle matrices (profiles/r02_spmv_rows_sweep.txt) showed the kernel short of independent x gathers in flight rather than of
+// particle matrices (round 2, tools/spmv_sweep.py; the table itself was not kept) showed the kernel short of independent x gathers in flight rather than of
 // staged bytes — 2 -> 5 resident blocks per SM took the 35-per-row matrix from 0.42 to 0.81 of the HBM peak with the same ring.
 constexpr int kRowsTotalMax = 16384;      // non-zeros the ring may hold: (8 + 4) B x 16384 = 192 KB
 constexpr int kRowsMaxStages = 8;
@@ -728,7 +728,7 @@ SpmvPlan spmv_make_plan(const mgcg_ctx *c, int rows, int nnz, int kernel)
     }
     p.kernel = kernel;
     if (kernel == MGCG_SPMV_ROWS) {
-        // Shape chosen from the sweep in profiles/r02_spmv_rows_sweep.txt (tools/spmv_sweep.py): what the kernel is short of is
+        // Shape chosen from a round-2 sweep with tools/spmv_sweep.py (table not kept; the chosen shape is what profiles/r02_bench_c3_* measure): what the kernel is short of is
         // independent gathers in flight, not staged bytes — so as many resident blocks as fit (up to 5 per SM), a small ring of 2
         // stages, and L = the smallest power of two that leaves a lane at most ~8 entries of its row.
         // Tuning knobs: MGCG_ROWS_LANES, MGCG_ROWS_STAGES, MGCG_ROWS_CAPF (stage capacity / average tile), MGCG_ROWS_CTAS.

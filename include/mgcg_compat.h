@@ -82,7 +82,8 @@ void Solve(MgcgBlas *cublas, MgcgSparse *cusparse, MgcgMatDescr *matDescr,
            int *iteration, double *residual);
 
 /* ---- SimpleConjugateGradient.cu:12-126 SolveGpu on raw device pointers (the C++ overload taking
- *      thrust::device_vector lives in mgcg.hpp): x0 forced to 0 (:53), strict min-iteration (:107). */
+ *      thrust::device_vector is the header-only include/mgcg.hpp, tests/test_solvegpu_overload.py): x0 forced to 0 (:53),
+ *      strict min-iteration (:107). */
 void SolveGpu_c(const double *elements, const int *rowOffsets, const int *columnIndeces,
                 double *x, const double *b, int elementsCount, int count,
                 double allowableResidual, int minIteration, int maxIteration, int *iteration, double *residual);
