@@ -571,6 +571,57 @@ def main():
     return run_ours_single(args)
 
 
+def dist_vs_twin(S, m, dist, dev, rank, world, extra):
+    """Oracle leg of the sharded path (not timed; one of the places that execute oracle/): two small systems — 48^3 7-point and
+    24^3 27-point variable-coefficient — solved sharded over ALL the ranks of this run and, on rank 0's host cores, by the CPU twin
+    oracle/mg_ref.c (MgRef.pcg, the restatement the single-GPU path is pinned to).  Iteration index at 1e-8 on both sides, and the
+    solutions of both taken to 1e-12 compared as max|dx| / max|x|.  The reference compares its multi-device solve with its CPU solve
+    the same way (Mgcg/cuBlas/Mgcg/MgcgMain.cs:151-162)."""
+    import torch
+    from conjugategradient_b200 import generators as g
+    out = {}
+    for name, ns, make in (("poisson3d7_48", 48, g.poisson3d7), ("poisson3d27_varcoef_24", 24, g.poisson3d27_varcoef)):
+        try:
+            v, rp, c = make(ns)
+            N = ns ** 3
+            b = g.rhs_uniform(N, 0)
+            planes = [ns // world] * world
+            planes[-1] += ns - sum(planes)
+            zo = np.concatenate([[0], np.cumsum(planes)]) * ns * ns
+            r0, r1 = int(zo[rank]), int(zo[rank + 1])
+            k0, k1 = int(rp[r0]), int(rp[r1])
+            tv, tc = torch.as_tensor(v[k0:k1]).to(dev), torch.as_tensor(c[k0:k1]).to(dev)
+            tr = torch.as_tensor((rp[r0:r1 + 1] - rp[r0]).astype(np.int32)).to(dev)
+            tb = torch.as_tensor(b[r0:r1]).to(dev)
+            tx = torch.zeros(r1 - r0, dtype=torch.float64, device=dev)
+            rec = {}
+            xs = {}
+            for tol in (1e-8, 1e-12):
+                m.setup(N, r0, tv, tr, tc, S.default_options(precond=1, nx=ns, ny=ns, nz=ns, norm=2, tolerance=tol, max_iteration=2000, **extra))
+                res = m.solve(tb, tx.zero_())
+                torch.cuda.synchronize()
+                parts = [None] * world
+                dist.all_gather_object(parts, tx.cpu().numpy())
+                xs[tol] = np.concatenate(parts)
+                rec[tol] = (res.iteration, res.residual)
+            if rank == 0:
+                from oracle import oracle as o
+                H = o.MgRef(v, rp, c, ns, ns, ns)
+                _, it8, res8, st8 = H.pcg(b, tol=1e-8, norm=o.NORM_REL_L2, max_iteration=2000)
+                xt, it12, res12, st12 = H.pcg(b, tol=1e-12, norm=o.NORM_REL_L2, max_iteration=2000)
+                H.close()
+                err = float(np.abs(xs[1e-12] - xt).max() / np.abs(xt).max())
+                out[name] = {"it_dist": rec[1e-8][0], "it_twin": it8, "residual_dist": rec[1e-8][1], "residual_twin": res8,
+                             "it_dist_1e-12": rec[1e-12][0], "it_twin_1e-12": it12, "x_rel_err": err, "twin_status": [st8, st12],
+                             "pass": bool(abs(rec[1e-8][0] - it8) <= 1 and err <= 1e-10)}
+        except Exception as e:      # a failed check is reported in the line, it does not take the measurement down
+            out[name] = {"error": repr(e)[:300], "pass": False}
+    if rank == 0:
+        out["what"] = (f"sharded over {world} ranks vs the CPU twin oracle/mg_ref.c on rank 0's host: 0-based iteration index at 1e-8 (bar +-1), "
+                       "max|dx|/max|x| of the two 1e-12 solves (bar 1e-10)")
+    return out
+
+
 def run_ours_dist(args):
     """N > 1 (torchrun, one rank per GPU): the SAME system row-block sharded over the ranks (strong scaling): z-slab shards,
     halo exchange of p and of the multigrid level vectors plus rank-ordered scalar reductions over NVLink."""
@@ -726,6 +777,13 @@ def run_ours_dist(args):
                       "norm": "max|dx| / max|x|; single-GPU solves of the same device-assembled system on rank 0's GPU, outside the timed region"}
             ms1.close()
             del xd, xdt, fx, ft, fv, fr, fc, fb
+        dist.barrier()
+    if not args.no_parity:
+        twin = dist_vs_twin(S, m, dist, dev, rank, world, extra)
+        if rank == 0:
+            parity = dict(parity or {})
+            parity["dist_vs_twin"] = twin
+        m.setup(n, r0, tv, tr, tc, opts)
         dist.barrier()
 
     # e2e: ONE C-ABI call per rank on pinned host shards (mgcg_solve_host_dist): upload + hierarchy + solve + download timed

@@ -100,7 +100,33 @@ def main():
         tight = {"tight_residual": rt.residual, "tight_it": rt.iterations_done,
                  "err_tight_dist": float((tx - xt[r0:r1]).abs().max() / sc), "err_tight_single": float((fx - xt).abs().max() / sc),
                  "err_tight_single_local": float((fx[r0:r1] - xt[r0:r1]).abs().max() / sc)}
-    out = {"rank": rank, "it_dist": res.iterations_done, "it_single": rs.iterations_done, "err": err, "residual": res.residual,
+    # oracle leg: the same system on rank 0's host cores by the CPU restatements (oracle/cg_ref.c for plain CG, the twin oracle/mg_ref.c
+    # for MGCG with a grid hint) — the reference's own check of its multi-device solver is against its CPU solver too
+    # (Mgcg/cuBlas/Mgcg/MgcgMain.cs:151-162).  Without a grid hint the sharded levels aggregate per shard; that variant has no twin.
+    twin = {}
+    pre = kw.get("precond", 0)
+    if pre == 0 or cfg.get("hint", True):
+        xt = np.empty(N)
+        if rank == 0:
+            from oracle import oracle as orc
+            tol = cfg.get("tolerance", 1e-8)
+            if pre == 0:
+                xt, itt, _, stt = orc.cg_solve(v, rp, c, b, tol=tol, norm=orc.NORM_REL_L2, max_iteration=2000)
+            else:
+                H = orc.MgRef(v, rp, c, n, n, n)
+                if kw.get("mg_smoother", 0) == 2:
+                    H.set_chebyshev(2, 6.0)                      # the library defaults (mgcg_options_default)
+                xt, itt, _, stt = H.pcg(b, tol=tol, norm=orc.NORM_REL_L2, max_iteration=2000)
+                H.close()
+            twin = {"it_twin": itt + 1, "twin_status": stt}      # iterations done = 0-based index + 1
+        bx = torch.from_numpy(np.ascontiguousarray(xt))
+        dist.broadcast(bx, src=0)
+        xt = bx.numpy()
+        tw = [twin]
+        dist.broadcast_object_list(tw, src=0)
+        twin = dict(tw[0])
+        twin["err_twin"] = float(np.abs(tx.cpu().numpy() - xt[r0:r1]).max() / np.abs(xt).max())
+    out = {"rank": rank, **twin, "it_dist": res.iterations_done, "it_single": rs.iterations_done, "err": err, "residual": res.residual,
            "levels": res.levels, "first_replicated": res.reserved[2], "halo_exchanges": res.reserved[0], "allgathers": res.reserved[1],
            "solve_ms": res.solve_ms, "setup_ms": res.setup_ms, "single_ms": rs.solve_ms, "launches": res.kernel_launches,
            "transport": res.reserved[3], "graph": res.reserved[4], "coded": nd.value, **tight}

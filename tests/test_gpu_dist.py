@@ -1,4 +1,5 @@
-"""Sharded solve (mgcg_setup_dist / mgcg_solve_dist) against the single-GPU solve of the same system; needs >= 2 GPUs.
+"""Sharded solve (mgcg_setup_dist / mgcg_solve_dist) against the single-GPU solve of the same system AND against the CPU oracle
+(oracle/cg_ref.c, the twin oracle/mg_ref.c) on rank 0's host; needs >= 2 GPUs.
 One process per GPU under torchrun (tests/dist_worker.py)."""
 import json
 import os
@@ -54,6 +55,11 @@ CASES = [
     ("mg_27pt_coded_columns_peer", {"n": 48, "matrix": "p27", "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2},
                                     "transport": 2, "tight": 1e-12, "coded": 27}),
     ("plain_cg_coded_columns_nccl", {"n": 48, "options": {"precond": 0, "dist_transport": 1}, "coded": 7}),
+    # eight ranks (6 fine planes and 2 level-1 planes per rank at 48^3; 4 planes per rank at 32^3)
+    ("plain_cg_peer_w8", {"n": 32, "world": 8, "options": {"precond": 0, "dist_transport": 2}, "transport": 2}),
+    ("mg_two_sharded_levels_peer_w8", {"n": 48, "world": 8, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2}, "transport": 2,
+                                       "solves": 2}),
+    ("mg_replicated_nccl_w8", {"n": 48, "world": 8, "options": {"precond": 1, "dist_transport": 1}}),
     ("mg_chebyshev_single_reduce_w4", {"n": 48, "world": 4, "options": {"precond": 1, "dist_replicate_below": 1000, "dist_transport": 2, "mg_smoother": 2,
                                                                         "cg_variant": 1}, "transport": 2}),
 ]
@@ -81,6 +87,13 @@ def test_sharded_matches_single_gpu(name, cfg):
         else:
             assert r["err"] <= 1e-10 if r["it_dist"] == r["it_single"] else r["err"] <= 1e-6, r
         assert r["residual"] < cfg.get("tolerance", 1e-8)
+        if "it_twin" in r:
+            # ... and against the CPU oracle / twin on the same inputs: iteration count +-1; x to 1e-10 of max|x| when both stopped at the
+            # same iteration of the same recurrence on a well-conditioned system (else two 1e-8 solves differ at the 1e-8 level times
+            # the conditioning: the 27-point contrast-1e6 cases and the single-reduce recurrence get the looser bound)
+            assert r["twin_status"] == 0 and abs(r["it_dist"] - r["it_twin"]) <= 1, r
+            exact = r["it_dist"] == r["it_twin"] and "tight" not in cfg and cfg["options"].get("cg_variant", 0) == 0
+            assert r["err_twin"] <= (1e-10 if exact else 1e-5), r
     if "transport" in cfg:
         assert all(r["transport"] == cfg["transport"] for r in res), res
     if "coded" in cfg:
