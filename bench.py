@@ -62,6 +62,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=30.0, help="budget of the CPU baseline leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extra-512", action="store_true", help="default config only: skip the extra_512 object (the 7-point 512^3 solve on the same GPUs)")
     ap.add_argument("--no-parity", action="store_true", help="skip the parity block (tight solve, plain-CG count, sharded-vs-single)")
     ap.add_argument("--device-gen", action="store_true", help="assemble the matrix on the device; implied for c3, c5 and --size > 256")
     ap.add_argument("--graph", type=int, default=-1, help="use_graph option: 0 eager, 1 one iteration per graph launch, 2 device-side while loop "
@@ -543,6 +544,12 @@ def run_ours_single(args):
 
     label = f"{args.config} {n_side}^3"
     cpu = None if (args.no_cpu or problem is None) else cpu_baseline_leg(problem, label, args.cpu_seconds, plain_it)
+    x512 = None
+    if args.config == "c4" and n_side == 256 and not args.no_extra_512:
+        try:
+            x512 = extra_512_single(args, S, dev)
+        except Exception as e:      # the extra leg never takes the headline line down
+            x512 = {"error": repr(e)[:300]}
     out = {"metric": metric_name(args.config), "value": ms, "unit": "ms", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
            "data": "synthetic",
@@ -555,7 +562,7 @@ def run_ours_single(args):
            "true_relative_residual": true_rel, "true_residual_kernel": "VECTOR on int32 columns (not the solve's coded kernel)", "setup_ms": setup_ms, "setup_cold_ms": setup_cold_ms, "first_solve_ms": solve_cold_ms,
            "levels": res.levels, "operator_complexity": res.operator_complexity, "spmv_gbs": achieved,
            "assembly_ms": device_problem.assembly_ms,
-           "gpu_launches": launches, "clocks": clk, "roofline": roofline, "parity": parity, "cpu_baseline": cpu, "e2e": e2e}
+           "gpu_launches": launches, "clocks": clk, "roofline": roofline, "parity": parity, "cpu_baseline": cpu, "e2e": e2e, "extra_512": x512}
     print(json.dumps(out), flush=True)
     m.close()
     return 0
@@ -619,6 +626,113 @@ def dist_vs_twin(S, m, dist, dev, rank, world, extra):
     if rank == 0:
         out["what"] = (f"sharded over {world} ranks vs the CPU twin oracle/mg_ref.c on rank 0's host: 0-based iteration index at 1e-8 (bar +-1), "
                        "max|dx|/max|x| of the two 1e-12 solves (bar 1e-10)")
+    return out
+
+
+def _args_512(args):
+    a2 = argparse.Namespace(**vars(args))
+    a2.config, a2.size = "c4", 512
+    return a2
+
+
+def extra_512_single(args, S, dev):
+    """north_star's scaling target (7-point 512^3, T1 / T8 >= 5) under the same clock as the headline: the 512^3 system assembled on the
+    device, set up and solved to 1e-8 on ONE GPU; device-timed like `value` (CUDA events, 2 warm-up + 3 timed solves).  Not part of
+    `value`; reported as `extra_512` in the same JSON line."""
+    import torch
+    a2 = _args_512(args)
+    n = a2.size ** 3
+    m = S.Mgcg(0, use_torch_stream=True)
+    try:
+        tv, tr, tc, tb = device_problem(a2, m, dev)
+        nnz = tv.numel()
+        tx = torch.zeros(n, dtype=torch.float64, device=dev)
+        opts = solver_options(a2, S)
+        m.setup(tv, tr, tc, opts)
+        for _ in range(2):
+            res = m.solve(tb, tx.zero_())
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(3):
+            tx.zero_()
+            res = m.solve(tb, tx)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 3
+        m.setup(tv, tr, tc, opts)
+        setup_ms = m.solve(tb, tx.zero_()).setup_ms
+        ty = torch.empty_like(tx)
+        S.check(m.L.mgcg_spmv(m.ctx, n, n, nnz, S._p(tv), S._p(tr), S._p(tc), S._p(tx), S._p(ty), 1.0, 0.0, 2), "mgcg_spmv")   # int32 columns, VECTOR kernel
+        torch.cuda.synchronize()
+        true_rel = float(torch.linalg.vector_norm(tb - ty) / torch.linalg.vector_norm(tb))
+        return {"workload": workload_text(a2), "rows": n, "nnz": nnz, "n_gpus": 1, "value": ms, "unit": "ms", "steps": 3, "warmup": 2,
+                "iterations": res.iterations_done, "final_relative_residual": res.residual, "true_relative_residual": true_rel,
+                "setup_ms": setup_ms, "levels": res.levels}
+    finally:
+        m.close()
+
+
+def extra_512_dist(args, S, m, dist, dev, rank, world, lr, extra):
+    """The same 512^3 system row-block sharded over the ranks of this run (see extra_512_single): max over ranks of the device time of
+    3 solves after 2 warm-ups; x against the single-GPU solve of the same system on rank 0's GPU, both taken to 1e-12."""
+    import torch
+    a2 = _args_512(args)
+    ns = a2.size
+    n = ns ** 3
+    planes = [ns // world] * world
+    planes[-1] += ns - sum(planes)
+    zo = np.concatenate([[0], np.cumsum(planes)])
+    z0, z1 = int(zo[rank]), int(zo[rank + 1])
+    r0, r1 = z0 * ns * ns, z1 * ns * ns
+    tv, tr, tc, tb = device_problem(a2, m, dev, zrange=(z0, z1))
+    tx = torch.zeros(r1 - r0, dtype=torch.float64, device=dev)
+    opts = solver_options(a2, S, **extra)
+    m.setup(n, r0, tv, tr, tc, opts)
+    for _ in range(2):
+        res = m.solve(tb, tx.zero_())
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(3):
+        tx.zero_()
+        res = m.solve(tb, tx)
+    e1.record()
+    torch.cuda.synchronize(); dist.barrier()
+    m.setup(n, r0, tv, tr, tc, opts)
+    setup_ms = m.solve(tb, tx.zero_()).setup_ms
+    t = torch.tensor([e0.elapsed_time(e1) / 3, setup_ms], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, setup_ms = (float(v) for v in t.tolist())
+    m.setup(n, r0, tv, tr, tc, solver_options(a2, S, tolerance=1e-12, **extra))
+    rt = m.solve(tb, tx.zero_())
+    torch.cuda.synchronize()
+    if rank == 0:
+        parts = [tx] + [torch.empty(int(zo[q + 1] - zo[q]) * ns * ns, dtype=torch.float64, device=dev) for q in range(1, world)]
+        for r_ in [dist.irecv(parts[q], src=q) for q in range(1, world)]:
+            r_.wait()
+        xd = torch.cat(parts)
+        del parts
+    else:
+        dist.send(tx, dst=0)
+    out = None
+    if rank == 0:
+        err = None
+        ms1 = S.Mgcg(lr, use_torch_stream=True)
+        try:
+            fv, fr, fc, fb = device_problem(a2, ms1, dev)
+            ft = torch.zeros(n, dtype=torch.float64, device=dev)
+            ms1.setup(fv, fr, fc, solver_options(a2, S, tolerance=1e-12))
+            r1g = ms1.solve(fb, ft)
+            err = float((xd - ft).abs().max() / ft.abs().max())
+            it1 = r1g.iterations_done
+        finally:
+            ms1.close()
+        out = {"workload": workload_text(a2), "rows": n, "n_gpus": world, "value": ms, "unit": "ms", "steps": 3, "warmup": 2,
+               "iterations": res.iterations_done, "final_relative_residual": res.residual, "setup_ms": setup_ms, "levels": res.levels,
+               "distributed_levels": res.reserved[2], "dist_x_rel_err": err,
+               "dist_x_rel_err_note": f"sharded vs single-GPU solution on rank 0's GPU, both solved to 1e-12 relative residual ({rt.iterations_done} / {it1} iterations); max|dx| / max|x|"}
+    dist.barrier()
     return out
 
 
@@ -810,6 +924,12 @@ def run_ours_dist(args):
                "e2e_cold_ms": comm_init_ms + setup_cold_ms + solve_cold_ms,
                "e2e_cold_note": "communicator init + first sharded setup (peer arena, IPC mappings) + first solve (graph capture), wall clock, max over ranks",
                "api": "mgcg_solve_host_dist (include/mgcg.h): one call per rank on its pinned host row block; bytes are per rank"}
+    x512 = None
+    if args.config == "c4" and n_side == 256 and not args.no_extra_512:
+        try:
+            x512 = extra_512_dist(args, S, m, dist, dev, rank, world, lr, extra)
+        except Exception as e:      # (an exception on one rank only would leave the others in a collective: the legs above ran the same calls)
+            x512 = {"error": repr(e)[:300]}
     if rank == 0:
         out = {"metric": metric_name(args.config), "value": ms, "unit": "ms", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                "ms_per_step": ms, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -831,7 +951,7 @@ def run_ours_dist(args):
                             "bytes_rule": "9 nnz + 20 N" if coded_used else "12 nnz + 20 N", "achieved": achieved,
                             "peak": peak, "unit": "GB/s", "frac": achieved / peak, "frac_of_8TBs_nominal": achieved / 8000.0, "traffic": None,
                             "peak_source": peak_how, "bytes_per_launch": spmv_bytes, "ms_per_launch": spmv_ms},
-               "parity": parity, "cpu_baseline": None, "e2e": e2e}
+               "parity": parity, "cpu_baseline": None, "e2e": e2e, "extra_512": x512}
         print(json.dumps(out), flush=True)
     m.close()
     dist.barrier()
