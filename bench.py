@@ -68,6 +68,8 @@ def parse():
     ap.add_argument("--graph", type=int, default=-1, help="use_graph option: 0 eager, 1 one iteration per graph launch, 2 device-side while loop "
                     "(library default); profilers want 0")
     ap.add_argument("--transport", type=int, default=0, help="sharded arm: 0 auto (peer memory on one node), 1 NCCL, 2 peer memory")
+    ap.add_argument("--align-planes", type=int, default=0, help="sharded arm: shard cuts on multiples of this many z-planes (0 = the reference's floor "
+                    "rule); 6 keeps the 3- and 2-plane aggregates of two multigrid levels whole")
     ap.add_argument("--replicate-below", type=int, default=0, help="sharded arm: replicate multigrid levels smaller than this (0 = library default)")
     ap.add_argument("--smoother", type=int, default=-1, help="multigrid smoother (-1 = library default)")
     ap.add_argument("--opt", action="append", default=[], help="extra mgcg_options field, name=value (repeatable)")
@@ -736,6 +738,21 @@ def extra_512_dist(args, S, m, dist, dev, rank, world, lr, extra):
     return out
 
 
+def shard_planes(n_side, world, align=0):
+    """z-planes per rank.  align <= 1: the reference's rule, offsets[i] = offsets[i-1] + floor(Count / D), remainder to the last device
+    (ConjugateGradientParallelGpu.cs:271-277; the same thing in planes when world divides n_side).  align = K > 1: every cut falls on
+    a multiple of K planes, so that geometric aggregates (3 planes on level 0, 2 on the levels below: K = 6 keeps two levels whole,
+    K = 12 three) are not clipped by a shard boundary; the K-plane units are dealt out as evenly as they go, the remainder planes
+    go to the last rank."""
+    if align <= 1 or n_side // align < world:
+        planes = [n_side // world] * world
+    else:
+        units = n_side // align
+        planes = [(units // world + (1 if q < units % world else 0)) * align for q in range(world)]
+    planes[-1] += n_side - sum(planes)
+    return planes
+
+
 def run_ours_dist(args):
     """N > 1 (torchrun, one rank per GPU): the SAME system row-block sharded over the ranks (strong scaling): z-slab shards,
     halo exchange of p and of the multigrid level vectors plus rank-ordered scalar reductions over NVLink."""
@@ -753,8 +770,7 @@ def run_ours_dist(args):
     torch.cuda.set_stream(torch.cuda.Stream(dev))
     n_side = args.size
     n = n_side ** 3
-    planes = [n_side // world] * world          # == offsets[i] = offsets[i-1] + floor(Count/D) (cs:271-277) when world | n
-    planes[-1] += n_side - sum(planes)
+    planes = shard_planes(n_side, world, args.align_planes)
     zo = np.concatenate([[0], np.cumsum(planes)])
     z0, z1 = int(zo[rank]), int(zo[rank + 1])
     r0, r1 = z0 * n_side * n_side, z1 * n_side * n_side
@@ -937,6 +953,7 @@ def run_ours_dist(args):
                           "rows": n, "nnz": nnz_global,
                           "preconditioner": precond_text(args) + "; coarse levels replicated",
                           "l2": "per-rank shard (matrix + vectors) larger than the 126 MB L2 at 256^3 up to 8 ranks; no flush",
+                          "planes_per_rank": planes,
                           "parallelism": f"row-block (z-slab) shards over {world} GPUs; halo exchange, coarse all-gather and rank-ordered "
                                          "scalar reductions by " + ("the library's own kernels over NVLink peer memory, iteration replayed as a CUDA graph"
                                                                     if res.reserved[3] == 2 else "NCCL send/recv + all-gather")},
