@@ -84,3 +84,28 @@ def test_two_rank_shard_layout_and_reductions():
         assert p.exitcode == 0
     got = sorted(q.get(timeout=5) for _ in range(world))
     assert got[0][1] == got[1][1]          # identical on every rank (same data, same order)
+
+
+def test_bench_shard_planes_rules():
+    """bench.py's z-plane split: the default is the reference's floor rule (ConjugateGradientParallelGpu.cs:271-277) in planes;
+    --align-planes K puts every cut on a multiple of K planes without losing or duplicating a plane."""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "bench.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    from conjugategradient_b200 import sharding
+    for n, w in ((256, 8), (512, 8), (48, 4), (50, 4), (24, 8)):
+        p = b.shard_planes(n, w, 0)
+        assert sum(p) == n and len(p) == w
+        offs = sharding.partition_offsets(n * n * n, w)          # the reference's rule on rows
+        if n % w == 0:
+            assert [int(o) for o in offs] == [sum(p[:q]) * n * n for q in range(w + 1)]
+        for k in (6, 12):
+            pk = b.shard_planes(n, w, k)
+            assert sum(pk) == n and len(pk) == w and min(pk) > 0
+            if n // k >= w:
+                assert all(sum(pk[:q]) % k == 0 for q in range(1, w))     # every interior cut on a multiple of k
+            else:
+                assert pk == p                                            # too few units: falls back to the floor rule
+    assert b.shard_planes(512, 8, 6) == [66, 66, 66, 66, 66, 60, 60, 62]
